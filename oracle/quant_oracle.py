@@ -1,0 +1,320 @@
+"""CPU oracle for the group-quantized dequantize+matmul path  (TEST INFRASTRUCTURE ONLY).
+
+This file is the checker, never the product: only ``tests/``, ``__graft_entry__.smoke()``
+and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs may import it.  The shipped
+path (``mlc_llm_b200``) never imports anything from ``oracle/``.
+
+It is a numpy restatement of the reference's TVM tensor-expression formulas.  Every
+function cites the reference lines (relative to /root/reference) it follows.
+
+Parity pin: ``oracle/gen_golden.py`` executes the reference's *own* ``encoding_func`` /
+``decoding_func`` / ``fused_decode*_matmul*`` PrimFuncs (TVM C backend, this container) and
+stores their outputs under ``tests/golden/``; ``tests/test_oracle_golden.py`` checks this
+restatement bit-for-bit against those vectors.  The reference itself ships no golden vectors
+(SURVEY.md section 4), so those fixtures are the pin.
+"""
+from __future__ import annotations
+
+import dataclasses
+import math
+
+import numpy as np
+
+# --------------------------------------------------------------------------------------
+# format description  (reference flags: build.py:19-25,114; utils.py:31-36)
+# --------------------------------------------------------------------------------------
+
+
+@dataclasses.dataclass(frozen=True)
+class Fmt:
+    """One symmetric ("_0") group-quantization scheme.
+
+    name          BASELINE name
+    nbit          bits per value                       (quantization.py:313  nbit = int(mode[-1]))
+    group         values sharing one scale             (build.py:114  40 if int3 else 32)
+    storage_nbit  bits of the storage word             (build.py:22-25)
+    dtype         model dtype = scale / activation / accumulate dtype (utils.py:31-36)
+    """
+
+    name: str
+    nbit: int
+    group: int
+    dtype: str
+    storage_nbit: int = 32
+
+    @property
+    def npu(self) -> int:  # values per storage word  (quantization.py:144)
+        return self.storage_nbit // self.nbit
+
+    @property
+    def maxint(self) -> int:  # quantization.py:145
+        return (1 << (self.nbit - 1)) - 1
+
+    @property
+    def np_dtype(self):
+        return np.float16 if self.dtype == "float16" else np.float32
+
+    def n_groups(self, K: int) -> int:  # quantization.py:143
+        return -(-K // self.group)
+
+    def n_words(self, K: int) -> int:  # quantization.py:170  n_i32
+        return -(-self.group // self.npu) * self.n_groups(K)
+
+
+FORMATS = {
+    "q4f16_0": Fmt("q4f16_0", 4, 32, "float16"),
+    "q3f16_0": Fmt("q3f16_0", 3, 40, "float16"),
+    "q4f32_0": Fmt("q4f32_0", 4, 32, "float32"),
+    "q8f16_0": Fmt("q8f16_0", 8, 32, "float16"),
+}
+
+# epilogue ids shared with include/b200q.h
+EP_NONE, EP_ADD, EP_MULTIPLY, EP_SILU, EP_CAST_F32, EP_BIAS, EP_BIAS_GELU, EP_BIAS_ADD2 = range(8)
+EPILOGUES = {
+    "none": EP_NONE,
+    "add": EP_ADD,
+    "multiply": EP_MULTIPLY,
+    "silu": EP_SILU,
+    "cast_f32": EP_CAST_F32,
+    "bias": EP_BIAS,
+    "bias_gelu": EP_BIAS_GELU,
+    "bias_add2": EP_BIAS_ADD2,
+}
+
+
+def _round_half_away(x: np.ndarray) -> np.ndarray:
+    """tir.round -> C roundf: halves away from zero (harness lowering; LLVM llvm.round)."""
+    x64 = x.astype(np.float64)
+    return np.copysign(np.floor(np.abs(x64) + 0.5), x64)
+
+
+# --------------------------------------------------------------------------------------
+# a1: encode   (transform/quantization.py:142-177  te_encode_sym, transpose=True)
+# --------------------------------------------------------------------------------------
+
+
+def encode_sym(W: np.ndarray, fmt: Fmt):
+    """W[N, K] (fmt dtype) -> packed uint32[n_words, N], scale dtype[n_groups, N].
+
+    Every arithmetic op is rounded to ``fmt.dtype`` exactly as the TE expression is typed.
+    """
+    dt = fmt.np_dtype
+    assert W.dtype == dt and W.ndim == 2
+    N, K = W.shape
+    g, npu, maxint = fmt.group, fmt.npu, fmt.maxint
+    G, R = fmt.n_groups(K), fmt.n_words(K)
+    assert g % npu == 0  # quantization.py:146
+
+    # max_abs over in-range k; out-of-range contributes tir.min_value(dtype)   (:150)
+    Wp = np.full((N, G * g), np.finfo(dt).min, dtype=dt)
+    Wp[:, :K] = np.abs(W)
+    max_abs = Wp.reshape(N, G, g).max(axis=2)
+    # scale = max(max_abs, 1e-4) / maxint, all in dtype                          (:152-156)
+    scale = (np.maximum(max_abs, dt(1e-4)) / dt(maxint)).astype(dt)
+
+    # q = clamp(round(W / scale + maxint), 0, 2*maxint)                          (:159-164)
+    s_full = np.repeat(scale, g, axis=1)[:, :K]
+    t = (W / s_full).astype(dt)
+    t = (t + dt(maxint)).astype(dt)
+    q = _round_half_away(t)
+    q = np.minimum(np.maximum(q, 0.0), float(2 * maxint)).astype(np.uint32)
+
+    # pack npu values per word, zero beyond K; word j of row n holds k = j*npu + t (:169-176)
+    qp = np.zeros((N, R * npu), dtype=np.uint32)
+    qp[:, :K] = q
+    qp = qp.reshape(N, R, npu)
+    packed = np.zeros((N, R), dtype=np.uint32)
+    for tpos in range(npu):
+        packed |= qp[:, :, tpos] << np.uint32(tpos * fmt.nbit)
+    return np.ascontiguousarray(packed.T), np.ascontiguousarray(scale.T)
+
+
+# --------------------------------------------------------------------------------------
+# a2: decode   (quantization.py:213-230 te_decode_sym; :40-48 _tir_packed_uint_to_uint_to_float)
+# --------------------------------------------------------------------------------------
+
+
+def decode_sym(packed: np.ndarray, scale: np.ndarray, K: int, fmt: Fmt, transpose_output: bool = False):
+    """packed uint32[R, N], scale dtype[G, N] -> w dtype[K, N]  (or [N, K] if transpose_output)."""
+    dt = fmt.np_dtype
+    assert packed.dtype == np.uint32 and scale.dtype == dt
+    k = np.arange(K)
+    word = packed[k // fmt.npu, :]
+    shift = ((k % fmt.npu) * fmt.nbit).astype(np.uint32)[:, None]
+    q = (word >> shift) & np.uint32((1 << fmt.nbit) - 1)
+    w = (q.astype(dt) - dt(fmt.maxint)).astype(dt)  # exact in f16 and f32
+    w = (w * scale[k // fmt.group, :]).astype(dt)  # the single rounding
+    return np.ascontiguousarray(w.T) if transpose_output else w
+
+
+# --------------------------------------------------------------------------------------
+# quantized embedding gather  (quantization.py:235-270 te_take_decode_sym; transpose=False layout)
+# --------------------------------------------------------------------------------------
+
+
+def encode_sym_rowmajor(W: np.ndarray, fmt: Fmt):
+    """Embedding layout: packed uint32[V, n_words], scale dtype[V, n_groups] (quantization.py:175-176)."""
+    p, s = encode_sym(W, fmt)
+    return np.ascontiguousarray(p.T), np.ascontiguousarray(s.T)
+
+
+def take_decode_sym(packed_rm: np.ndarray, scale_rm: np.ndarray, ids: np.ndarray, K: int, fmt: Fmt):
+    dt = fmt.np_dtype
+    j = np.arange(K)
+    word = packed_rm[ids][:, j // fmt.npu]
+    shift = ((j % fmt.npu) * fmt.nbit).astype(np.uint32)[None, :]
+    q = (word >> shift) & np.uint32((1 << fmt.nbit) - 1)
+    w = (q.astype(dt) - dt(fmt.maxint)).astype(dt)
+    return (w * scale_rm[ids][:, j // fmt.group]).astype(dt)
+
+
+# --------------------------------------------------------------------------------------
+# epilogues, op-for-op in dtype like the fused PrimFuncs
+# --------------------------------------------------------------------------------------
+
+
+def _erf(x: np.ndarray) -> np.ndarray:
+    return np.vectorize(math.erf, otypes=[np.float64])(x.astype(np.float64))
+
+
+def apply_epilogue(y: np.ndarray, epilogue: int, ep0=None, ep1=None, ep2=None):
+    """y: matmul result already rounded to dtype.  Follows
+    add       dispatch_tir_operator_adreno.py:86-91   out = r + y
+    multiply  :150-152                                out = other * y
+    silu      :216-228                                out = y * sigmoid(y)
+    cast_f32  :364-369                                out = f32(y)
+    bias      gpt_neox/dolly_v2_3b_mod.py:41-46       out = y + bias[n]
+    bias_gelu :204-251   v=y+b; t=v*f16(0.7071..); e=f16(erf(f32(t))); out=v*(f16(.5)+e*f16(.5))
+    bias_add2 :88-110    out = ((y + bias) + r1) + r2   (fused_NT_matmul1_add3_add5_add5)
+    """
+    dt = y.dtype.type
+    if epilogue == EP_NONE:
+        return y
+    if epilogue == EP_ADD:
+        return (ep0.astype(dt) + y).astype(dt)
+    if epilogue == EP_MULTIPLY:
+        return (ep0.astype(dt) * y).astype(dt)
+    if epilogue == EP_SILU:
+        # TVM legalises sigmoid(y) to 1/(1+exp(-y)) with every op typed in dtype (exp via expf)
+        e = np.exp((-y).astype(np.float32)).astype(dt)
+        sig = (dt(1) / (dt(1) + e).astype(dt)).astype(dt)
+        return (y * sig).astype(dt)
+    if epilogue == EP_CAST_F32:
+        return y.astype(np.float32)
+    if epilogue == EP_BIAS:
+        return (y + ep0.astype(dt)).astype(dt)
+    if epilogue == EP_BIAS_GELU:
+        v = (y + ep0.astype(dt)).astype(dt)
+        t = (v * dt(0.70710678118654757)).astype(dt)
+        e = _erf(t.astype(np.float32)).astype(np.float32).astype(dt)
+        h = (dt(0.5) + (e * dt(0.5)).astype(dt)).astype(dt)
+        return (v * h).astype(dt)
+    if epilogue == EP_BIAS_ADD2:
+        v = (y + ep0.astype(dt)).astype(dt)
+        v = (v + ep1.astype(dt)).astype(dt)
+        return (v + ep2.astype(dt)).astype(dt)
+    raise ValueError(epilogue)
+
+
+# --------------------------------------------------------------------------------------
+# a5: fused decode GEMV, reference semantics  (dispatch_tir_operator_adreno.py:5-23 et al.)
+# --------------------------------------------------------------------------------------
+
+
+def gemv_ref(packed, scale, x, fmt: Fmt, epilogue=EP_NONE, ep0=None, K=None, reassociate=False):
+    """y[n] = sum_k x[k]*w[k,n], accumulated IN dtype, init 0, k ascending (the reference's chain).
+
+    reassociate=True mirrors the int3 "after" kernels ((x*(q-3))*s, dispatch/llama/main.py:5547).
+    Vectorised over n; sequential over k (so O(K) numpy steps: keep K*N modest).
+    """
+    dt = fmt.np_dtype
+    K = x.size if K is None else K
+    x = x.reshape(-1).astype(dt)
+    N = packed.shape[1]
+    acc = np.zeros(N, dtype=dt)
+    mask = np.uint32((1 << fmt.nbit) - 1)
+    for k in range(K):
+        q = (packed[k // fmt.npu] >> np.uint32((k % fmt.npu) * fmt.nbit)) & mask
+        qf = (q.astype(dt) - dt(fmt.maxint)).astype(dt)
+        s = scale[k // fmt.group]
+        if reassociate:
+            term = ((x[k] * qf).astype(dt) * s).astype(dt)
+        else:
+            term = (x[k] * (qf * s).astype(dt)).astype(dt)
+        acc = (acc + term).astype(dt)
+    return apply_epilogue(acc, epilogue, ep0)
+
+
+def gemv_f64(packed, scale, x, fmt: Fmt, K=None):
+    """f64 evaluation of the same dequantised weights (the 'truth' tolerances are stated against)
+    plus sum_k |x_k w_kn| for the error bound."""
+    K = x.size if K is None else K
+    w = decode_sym(packed, scale, K, fmt).astype(np.float64)
+    xv = x.reshape(-1).astype(np.float64)[:K]
+    return xv @ w, np.abs(xv) @ np.abs(w)
+
+
+# --------------------------------------------------------------------------------------
+# a7: prefill dense NT GEMM  (transform/transpose_matmul.py:34-101; main.py:3884-3898)
+# --------------------------------------------------------------------------------------
+
+
+def nt_matmul_ref(X, T, dtype=np.float16):
+    """Y[m,n] = sum_k X[m,k]*T[n,k] accumulated in dtype, k ascending (reference semantics)."""
+    M, K = X.shape
+    acc = np.zeros((M, T.shape[0]), dtype=dtype)
+    Tt = T.T
+    for k in range(K):
+        acc = (acc + (X[:, k : k + 1] * Tt[k : k + 1, :]).astype(dtype)).astype(dtype)
+    return acc
+
+
+def gemm_f64(packed, scale, X, fmt: Fmt):
+    K = X.shape[-1]
+    w = decode_sym(packed, scale, K, fmt).astype(np.float64)
+    X64 = X.astype(np.float64)
+    return X64 @ w, np.abs(X64) @ np.abs(w)
+
+
+# --------------------------------------------------------------------------------------
+# tolerances  
+# --------------------------------------------------------------------------------------
+
+
+def tolerance(y64: np.ndarray, abs_sum: np.ndarray, out_f32: bool) -> np.ndarray:
+    """|y - y64| <= rel*|y64| + 2^-14 * sum|x w| + 2^-24 ; rel = 2^-10 (f16 out) or 2^-22 (f32 out)."""
+    rel = 2.0**-22 if out_f32 else 2.0**-10
+    return rel * np.abs(y64) + 2.0**-14 * abs_sum + 2.0**-24
+
+
+# --------------------------------------------------------------------------------------
+# algorithmic bytes  
+# --------------------------------------------------------------------------------------
+
+
+def gemv_bytes(K: int, N: int, fmt: Fmt, epilogue=EP_NONE) -> int:
+    sb = 2 if fmt.dtype == "float16" else 4
+    ob = 4 if (epilogue == EP_CAST_F32 or fmt.dtype == "float32") else 2
+    b = 4 * fmt.n_words(K) * N + sb * fmt.n_groups(K) * N + sb * K + ob * N
+    if epilogue in (EP_ADD, EP_MULTIPLY):
+        b += ob * N
+    if epilogue in (EP_BIAS, EP_BIAS_GELU):
+        b += sb * N
+    return b
+
+
+# --------------------------------------------------------------------------------------
+# synthetic data  (seed 0xB200, W ~ N(0, 0.02^2), x ~ N(0,1))
+# --------------------------------------------------------------------------------------
+
+SEED = 0xB200
+
+
+def synth_weight(N: int, K: int, fmt: Fmt, seed: int = SEED):
+    rng = np.random.default_rng(seed)
+    return (rng.standard_normal((N, K), dtype=np.float32) * 0.02).astype(fmt.np_dtype)
+
+
+def synth_act(shape, fmt: Fmt, seed: int = SEED + 1, std: float = 1.0):
+    rng = np.random.default_rng(seed)
+    return (rng.standard_normal(shape, dtype=np.float32) * std).astype(fmt.np_dtype)
