@@ -1,0 +1,177 @@
+/*
+ * b200q.h — C-ABI of the B200-native (sm_100a) group-quantized dequantize+matmul path.
+ *
+ * This is the drop-in boundary for ONE hot path of mlc-llm (reference mounted at /root/reference;
+ * all file:line citations below are relative to it): the kernels TVM generates for
+ *
+ *   fused_decode*_matmul*        decode-step dequant-GEMV      (one PrimFunc per Linear)
+ *   decode*                      prefill dequantize-to-dense   (a6)
+ *   NT_matmul* / fused_NT_matmul*  prefill dense GEMM           (a7)
+ *   fused_decode*_NT_matmul*     prefill dequant fused into the GEMM (a8)
+ *   take_decode                  quantized embedding gather
+ *
+ * Tensor layouts are the reference's, unchanged (mlc_llm/transform/quantization.py:142-177):
+ *   packed  uint32 [n_words(K), N]   row-major, N contiguous; value k of column n lives in word
+ *                                    k / npu, bits [(k % npu) * nbit, +nbit);  npu = 32 / nbit
+ *   scale   dtype  [n_groups(K), N]  one scale per `group` consecutive k of a column
+ *   n_groups = ceil(K / group),  n_words = ceil(group / npu) * n_groups
+ *   w[k, n] = (dtype(q) - (2^(nbit-1) - 1)) * scale[k / group, n]          (quantization.py:213-230)
+ *
+ * Conventions (mirroring the PrimFunc destination-passing signature,
+ * mlc_llm/dispatch/dispatch_tir_operator_adreno.py:6,128):
+ *   - argument order (packed, scale, x[, epilogue operands], out); outputs never alias inputs
+ *   - every pointer is a DEVICE pointer unless the function name ends in _host
+ *   - the callee allocates nothing, never synchronizes, launches only on `stream`
+ *     (a cudaStream_t passed as void*), and is CUDA-graph capturable
+ *   - return 0 on success, a negative b200q_status otherwise; b200q_last_error() returns the
+ *     calling thread's last message (TVM's "non-zero return + TVMGetLastError" convention)
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef B200Q_H_
+#define B200Q_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200Q_VERSION 100 /* major*100 + minor */
+
+#if defined(__GNUC__)
+#define B200Q_API __attribute__((visibility("default")))
+#else
+#define B200Q_API
+#endif
+
+/* Quantization formats ("_0" = symmetric, scale only, transposed (K/.., N) layout, uint32 storage).
+ * Reference flags: build.py:19-25,114; utils.py:31-36 (see SURVEY.md section 0 for the name mapping). */
+typedef enum {
+  B200Q_Q4F16_0 = 0, /* int4, group 32, f16 scale/activation/output            (offset 7)   */
+  B200Q_Q3F16_0 = 1, /* int3, group 40, 10 values per word (2 dead bits), f16  (offset 3)   */
+  B200Q_Q4F32_0 = 2, /* int4, group 32, f32 scale/activation/output            (offset 7)   */
+  B200Q_Q8F16_0 = 3, /* int8, group 32, 4 values per word, f16                 (offset 127) */
+  B200Q_NUM_FMT = 4
+} b200q_fmt;
+
+/* Epilogues fused by FuseDecodeMatmulEwise (mlc_llm/transform/decode_matmul_ewise.py:49-75) and by
+ * the default Relax FuseOps pipeline for the prefill GEMMs.  `y` is the matmul result rounded to
+ * the model dtype; each epilogue op is evaluated in the model dtype, op for op like the PrimFunc. */
+typedef enum {
+  B200Q_EP_NONE = 0,      /* out = y                                   adreno.py:5-23        */
+  B200Q_EP_ADD = 1,       /* out = ep0[n] + y        (residual)        adreno.py:86-91       */
+  B200Q_EP_MULTIPLY = 2,  /* out = ep0[n] * y        (SwiGLU up*act)   adreno.py:150-152     */
+  B200Q_EP_SILU = 3,      /* out = y * (1 / (1 + exp(-y)))             adreno.py:216-228     */
+  B200Q_EP_CAST_F32 = 4,  /* out(f32) = y, kept at f32 accumulate precision  adreno.py:364-369 */
+  B200Q_EP_BIAS = 5,      /* out = y + ep0[n]        (ep0 = bias[N])   gpt_neox/dolly_v2_3b_mod.py:41-46 */
+  B200Q_EP_BIAS_GELU = 6, /* v=y+b; out = v*(0.5 + erf(v*0.70710678)*0.5)   dolly_v2_3b_mod.py:204-251 */
+  B200Q_EP_BIAS_ADD2 = 7, /* out = ((y + bias) + ep1) + ep2  (GEMM only)    dolly_v2_3b_mod.py:88-110 */
+  B200Q_NUM_EP = 8
+} b200q_epilogue;
+
+typedef enum {
+  B200Q_OK = 0,
+  B200Q_ERR_BAD_SHAPE = -1,   /* K/N not supported by the layout rules below              */
+  B200Q_ERR_BAD_ALIGN = -2,   /* a pointer is not 16-byte aligned                          */
+  B200Q_ERR_UNSUPPORTED = -3, /* unknown fmt / epilogue / combination                      */
+  B200Q_ERR_CUDA = -4,        /* a CUDA runtime call failed (message has cudaGetErrorString) */
+  B200Q_ERR_NULL = -5         /* a required pointer is NULL                                 */
+} b200q_status;
+
+/* flags for the launch */
+#define B200Q_FLAG_PDL 1u /* launch with programmatic dependent launch: the kernel prefetches its
+                             (constant) packed weights before waiting on the previous kernel in the
+                             stream.  Only legal when no earlier kernel in flight WRITES packed/scale. */
+
+/* ---- introspection ------------------------------------------------------------------------- */
+B200Q_API int b200q_version(void);
+B200Q_API const char* b200q_last_error(void);
+/* number of CUDA kernels this library has launched from the calling process (for bench.py's
+ * gpu_launches claim) */
+B200Q_API unsigned long long b200q_launch_count(void);
+/* layout helpers; return <0 on a bad format */
+B200Q_API int b200q_n_groups(int fmt, int K);
+B200Q_API int b200q_n_words(int fmt, int K);
+/* algorithmic HBM bytes of one GEMV: packed + scale + x + out (+ epilogue operands) */
+B200Q_API long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue);
+
+/* ---- a5: decode-step fused dequant-GEMV ------------------------------------------------------
+ * Replaces fused_decode*_matmul* (dispatch_tir_operator_adreno.py:5-411, dispatch/llama/main.py:
+ * 4235-6363, tuning.py:39-108).
+ *   y[n] = sum_{k<K} x[k] * w[k, n],  w bit-identical to the reference decode, products exact,
+ *   accumulation in f32 (the reference accumulates in dtype), then the epilogue.
+ *   x   dtype[K]         out  dtype[N]  (float[N] for B200Q_EP_CAST_F32 and for q4f32_0)
+ *   ep0 dtype[N] or NULL (ADD / MULTIPLY / BIAS / BIAS_GELU)
+ * Requirements: N % 8 == 0; packed, scale 16-byte aligned; x, ep0, out aligned to their element. */
+B200Q_API int b200q_gemv(const void* packed, const void* scale, const void* x, const void* ep0, void* out,
+               int K, int N, int fmt, int epilogue, unsigned flags, void* stream);
+
+/* Several GEMVs that read the SAME activation vector in ONE launch (q|k|v, gate|up: the reference
+ * launches them back to back on the same x, relax_model/llama.py:233-236,147-152).  Tensors stay
+ * the reference's separate per-Linear arrays. */
+typedef struct {
+  const void* packed;
+  const void* scale;
+  const void* ep0;
+  void* out;
+  int N;
+  int epilogue;
+} b200q_gemv_op;
+B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt,
+                     unsigned flags, void* stream);
+
+/* Tuning override for experiments (0 = heuristic).  wn: warps across N per CTA (1,2,4,8);
+ * ksplit: CTAs of one cluster splitting K (1,2,4,8). Thread-local. */
+B200Q_API void b200q_gemv_tune(int wn, int ksplit);
+
+/* Same GEMV with HOST activation / output buffers (weights stay resident in HBM as in the
+ * reference, cpp/llm_chat.cc:858-861): copies x host->device, runs, copies out device->host and
+ * synchronizes `stream`.  x_dev / out_dev are caller-provided device scratch of K / N elements. */
+B200Q_API int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,
+                    void* out_host, void* x_dev, void* out_dev, int K, int N, int fmt, int epilogue,
+                    void* stream);
+
+/* ---- a2 / a6: dequantize ---------------------------------------------------------------------
+ * Replaces decode* (dispatch/llama/main.py:3984-4232, tuning.py:111-147, quantization.py:213-230).
+ *   transposed == 0: out dtype[K, N]      (decode-step shape)
+ *   transposed != 0: out dtype[N, K]      (prefill shape, feeds NT_matmul)
+ * Bit-exact against the reference decode. */
+B200Q_API int b200q_dequant(const void* packed, const void* scale, void* out, int K, int N, int fmt,
+                  int transposed, void* stream);
+
+/* Quantized embedding gather, row-major (V, n_words) layout (quantization.py:235-270,397-420).
+ *   packed_rm uint32[V, n_words(K)], scale_rm dtype[V, n_groups(K)], ids int32[n_ids]
+ *   out dtype[n_ids, K] */
+B200Q_API int b200q_take_decode(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out,
+                      int n_ids, int V, int K, int fmt, void* stream);
+
+/* ---- a1: encode ------------------------------------------------------------------------------
+ * Group-quantize W dtype[N, K] (te_encode_sym, quantization.py:142-177; the reference runs it once
+ * on the host through LLVM, utils.py:98-110).  Bit-exact against the reference encoder.
+ *   transpose != 0: packed uint32[n_words(K), N], scale dtype[n_groups(K), N]   (matmul weights)
+ *   transpose == 0: packed uint32[N, n_words(K)], scale dtype[N, n_groups(K)]   (embedding table) */
+B200Q_API int b200q_encode(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
+                 void* stream);
+
+/* ---- a7 / a8: prefill GEMM -------------------------------------------------------------------
+ * Y[m, n] = sum_k X[m, k] * w[k, n]  (+ epilogue), X dtype[M, K] row-major, Y dtype[M, N].
+ * b200q_gemm dequantizes inside the GEMM (replaces fused_decode*_NT_matmul*,
+ * dispatch_tir_operator_adreno.py:414-1021, and the decode* + NT_matmul* pair on CUDA):
+ * packed tiles are unpacked to f16 in registers, staged through shared memory in the tcgen05
+ * canonical layout and multiplied on the 5th-gen tensor cores with f32 accumulators in TMEM.
+ * f16 formats only.  ep0/ep1/ep2 as in b200q_epilogue (bias is [N]; residuals are [M, N]).
+ * Requirements: K % 64 == 0 for q4/q8 (K % 40 == 0 or zero-padded x for q3), N % 8 == 0. */
+B200Q_API int b200q_gemm(const void* packed, const void* scale, const void* X, const void* ep0,
+               const void* ep1, const void* ep2, void* Y, int M, int K, int N, int fmt,
+               int epilogue, unsigned flags, void* stream);
+
+/* Dense NT GEMM on an already dequantized weight  T dtype[N, K]  (replaces NT_matmul*,
+ * transform/transpose_matmul.py:34-101, dispatch/llama/main.py:3884-3981). f16 only. */
+B200Q_API int b200q_nt_matmul(const void* X, const void* T, const void* ep0, const void* ep1,
+                    const void* ep2, void* Y, int M, int K, int N, int epilogue, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200Q_H_ */

@@ -1,0 +1,99 @@
+"""ctypes binding of libb200q.so (the C-ABI declared in include/b200q.h).
+
+The library is built in-tree by ``make -C mlc_llm_b200/csrc`` (or ``__graft_entry__.build()``).
+There is no fallback of any kind: if the shared object is missing or a call fails, an exception
+is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200q.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+c_void_p, c_int, c_uint, c_ll, c_ull = (
+    ctypes.c_void_p,
+    ctypes.c_int,
+    ctypes.c_uint,
+    ctypes.c_longlong,
+    ctypes.c_ulonglong,
+)
+
+
+class GemvOp(ctypes.Structure):
+    """b200q_gemv_op (include/b200q.h)."""
+
+    _fields_ = [
+        ("packed", c_void_p),
+        ("scale", c_void_p),
+        ("ep0", c_void_p),
+        ("out", c_void_p),
+        ("N", c_int),
+        ("epilogue", c_int),
+    ]
+
+
+# name -> (restype, argtypes); must list every symbol include/b200q.h declares
+PROTOTYPES = {
+    "b200q_version": (c_int, []),
+    "b200q_last_error": (ctypes.c_char_p, []),
+    "b200q_launch_count": (c_ull, []),
+    "b200q_n_groups": (c_int, [c_int, c_int]),
+    "b200q_n_words": (c_int, [c_int, c_int]),
+    "b200q_gemv_bytes": (c_ll, [c_int, c_int, c_int, c_int]),
+    "b200q_gemv": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_uint, c_void_p]),
+    "b200q_gemv_multi": (c_int, [ctypes.POINTER(GemvOp), c_int, c_void_p, c_int, c_int, c_uint, c_void_p]),
+    "b200q_gemv_tune": (None, [c_int, c_int]),
+    "b200q_gemv_host": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
+    "b200q_dequant": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
+    "b200q_take_decode": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
+    "b200q_encode": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
+    "b200q_gemm": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_uint, c_void_p]),
+    "b200q_nt_matmul": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
+}
+
+_lib = None
+
+
+class B200QError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"b200q error {code}: {msg}")
+        self.code = code
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    """Compile the CUDA sources for sm_100a into mlc_llm_b200/libb200q.so (nvcc cross-compiles
+    without a GPU)."""
+    cmd = ["make", "-C", CSRC, "-j8"] + (["-B"] if force else [])
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout[-4000:])
+        print(r.stderr[-4000:])
+    if r.returncode != 0:
+        raise RuntimeError("building libb200q.so failed")
+    return LIB_PATH
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `make -C mlc_llm_b200/csrc` "
+                "(there is no CPU / PyTorch fallback for this path)"
+            )
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(L, name)  # AttributeError if the header and the library drift apart
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        raise B200QError(code, lib().b200q_last_error().decode())

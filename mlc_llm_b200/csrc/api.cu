@@ -1,0 +1,191 @@
+// C-ABI entry points declared in include/b200q.h: argument validation, error plumbing, dispatch to
+// the kernels.  No torch types, no allocation, no synchronization (except the *_host helpers).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "common.cuh"
+
+namespace b200q {
+
+static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return B200Q_OK;
+  return set_error(B200Q_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+// kernels (gemv.cu, gemv_f32.cu, dequant.cu, gemm.cu)
+int gemv_f16_launch(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt, unsigned flags,
+                    cudaStream_t stream);
+int gemv_f32_launch(const b200q_gemv_op* ops, int n_ops, const void* x, int K, unsigned flags,
+                    cudaStream_t stream);
+void gemv_tune(int wn, int ksplit);
+int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
+                   cudaStream_t stream);
+int take_decode_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
+                       int V, int K, int fmt, cudaStream_t stream);
+int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
+                  cudaStream_t stream);
+int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
+                const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
+                cudaStream_t stream);
+int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,
+                     int M, int K, int N, int epilogue, cudaStream_t stream);
+
+static bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+static int check_fmt(int fmt, const char* who) {
+  if (fmt < 0 || fmt >= B200Q_NUM_FMT) return set_error(B200Q_ERR_UNSUPPORTED, "%s: unknown fmt %d", who, fmt);
+  return B200Q_OK;
+}
+
+static int check_gemv_op(const b200q_gemv_op& op, int fmt, const char* who) {
+  if (!op.packed || !op.scale || !op.out) return set_error(B200Q_ERR_NULL, "%s: NULL packed/scale/out", who);
+  if (op.N <= 0 || op.N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "%s: N=%d must be a positive multiple of 8", who, op.N);
+  if (!aligned(op.packed, 16) || !aligned(op.scale, 16))
+    return set_error(B200Q_ERR_BAD_ALIGN, "%s: packed/scale must be 16-byte aligned", who);
+  const int ep = op.epilogue;
+  if (ep < 0 || ep >= B200Q_NUM_EP || ep == B200Q_EP_BIAS_ADD2)
+    return set_error(B200Q_ERR_UNSUPPORTED, "%s: epilogue %d not available for the GEMV", who, ep);
+  const bool needs_ep0 = ep == B200Q_EP_ADD || ep == B200Q_EP_MULTIPLY || ep == B200Q_EP_BIAS || ep == B200Q_EP_BIAS_GELU;
+  if (needs_ep0 && !op.ep0) return set_error(B200Q_ERR_NULL, "%s: epilogue %d needs ep0", who, ep);
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  if (!aligned(op.out, (ep == B200Q_EP_CAST_F32) ? 4 : el) || (needs_ep0 && !aligned(op.ep0, el)))
+    return set_error(B200Q_ERR_BAD_ALIGN, "%s: out/ep0 misaligned", who);
+  return B200Q_OK;
+}
+
+}  // namespace b200q
+
+using namespace b200q;
+
+extern "C" {
+
+int b200q_version(void) { return B200Q_VERSION; }
+const char* b200q_last_error(void) { return g_err; }
+unsigned long long b200q_launch_count(void) { return g_launches.load(); }
+
+int b200q_n_groups(int fmt, int K) {
+  if (check_fmt(fmt, "b200q_n_groups")) return B200Q_ERR_UNSUPPORTED;
+  return n_groups(fmt, K);
+}
+int b200q_n_words(int fmt, int K) {
+  if (check_fmt(fmt, "b200q_n_words")) return B200Q_ERR_UNSUPPORTED;
+  return n_words(fmt, K);
+}
+long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue) {
+  if (check_fmt(fmt, "b200q_gemv_bytes")) return B200Q_ERR_UNSUPPORTED;
+  const long long sb = fmt_is_f32(fmt) ? 4 : 2;
+  const long long ob = (epilogue == B200Q_EP_CAST_F32 || fmt_is_f32(fmt)) ? 4 : 2;
+  long long b = 4LL * n_words(fmt, K) * N + sb * n_groups(fmt, K) * N + sb * K + ob * N;
+  if (epilogue == B200Q_EP_ADD || epilogue == B200Q_EP_MULTIPLY) b += ob * N;
+  if (epilogue == B200Q_EP_BIAS || epilogue == B200Q_EP_BIAS_GELU) b += sb * N;
+  return b;
+}
+
+void b200q_gemv_tune(int wn, int ksplit) { gemv_tune(wn, ksplit); }
+
+int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt, unsigned flags,
+                     void* stream) {
+  if (int e = check_fmt(fmt, "b200q_gemv")) return e;
+  if (!ops || !x) return set_error(B200Q_ERR_NULL, "b200q_gemv: NULL ops/x");
+  if (n_ops < 1 || n_ops > 4) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_multi: n_ops=%d not in [1,4]", n_ops);
+  if (K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv: K=%d", K);
+  if (!aligned(x, fmt_is_f32(fmt) ? 4 : 2)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv: x misaligned");
+  for (int i = 0; i < n_ops; ++i)
+    if (int e = check_gemv_op(ops[i], fmt, "b200q_gemv")) return e;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (fmt_is_f32(fmt)) {
+    for (int i = 0; i < n_ops; ++i)
+      if (ops[i].epilogue == B200Q_EP_CAST_F32) {
+        // f32 model: the cast is the identity
+      }
+    return gemv_f32_launch(ops, n_ops, x, K, flags, s);
+  }
+  return gemv_f16_launch(ops, n_ops, x, K, fmt, flags, s);
+}
+
+int b200q_gemv(const void* packed, const void* scale, const void* x, const void* ep0, void* out, int K,
+               int N, int fmt, int epilogue, unsigned flags, void* stream) {
+  b200q_gemv_op op{packed, scale, ep0, out, N, epilogue};
+  return b200q_gemv_multi(&op, 1, x, K, fmt, flags, stream);
+}
+
+int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,
+                    void* out_host, void* x_dev, void* out_dev, int K, int N, int fmt, int epilogue,
+                    void* stream) {
+  if (int e = check_fmt(fmt, "b200q_gemv_host")) return e;
+  if (!x_host || !out_host || !x_dev || !out_dev) return set_error(B200Q_ERR_NULL, "b200q_gemv_host: NULL buffer");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  const size_t oel = (epilogue == B200Q_EP_CAST_F32) ? 4 : el;
+  if (int e = check_cuda(cudaMemcpyAsync(x_dev, x_host, el * K, cudaMemcpyHostToDevice, s), "H2D x")) return e;
+  if (int e = b200q_gemv(packed, scale, x_dev, ep0, out_dev, K, N, fmt, epilogue, 0, stream)) return e;
+  if (int e = check_cuda(cudaMemcpyAsync(out_host, out_dev, oel * N, cudaMemcpyDeviceToHost, s), "D2H out")) return e;
+  return check_cuda(cudaStreamSynchronize(s), "cudaStreamSynchronize");
+}
+
+int b200q_dequant(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
+                  void* stream) {
+  if (int e = check_fmt(fmt, "b200q_dequant")) return e;
+  if (!packed || !scale || !out) return set_error(B200Q_ERR_NULL, "b200q_dequant: NULL pointer");
+  if (K <= 0 || N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_dequant: K=%d N=%d (N %% 8 == 0 required)", K, N);
+  if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(out, 16))
+    return set_error(B200Q_ERR_BAD_ALIGN, "b200q_dequant: pointers must be 16-byte aligned");
+  return dequant_launch(packed, scale, out, K, N, fmt, transposed, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_take_decode(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
+                      int V, int K, int fmt, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_take_decode")) return e;
+  if (!packed_rm || !scale_rm || !ids || !out) return set_error(B200Q_ERR_NULL, "b200q_take_decode: NULL pointer");
+  if (K <= 0 || V <= 0 || n_ids < 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode: K=%d V=%d n_ids=%d", K, V, n_ids);
+  if (n_ids == 0) return B200Q_OK;
+  if (n_ids > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode: n_ids=%d > 65535", n_ids);
+  return take_decode_launch(packed_rm, scale_rm, ids, out, n_ids, V, K, fmt, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_encode(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_encode")) return e;
+  if (!W || !packed || !scale) return set_error(B200Q_ERR_NULL, "b200q_encode: NULL pointer");
+  if (N <= 0 || K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_encode: N=%d K=%d", N, K);
+  return encode_launch(W, packed, scale, N, K, fmt, transpose, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_gemm(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
+               const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
+               void* stream) {
+  if (int e = check_fmt(fmt, "b200q_gemm")) return e;
+  if (fmt_is_f32(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: f16 formats only (q4f32_0 prefill: dequant + f32 GEMM is out of scope)");
+  if (!packed || !scale || !X || !Y) return set_error(B200Q_ERR_NULL, "b200q_gemm: NULL pointer");
+  if (M < 0 || K <= 0 || N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm: M=%d K=%d N=%d", M, K, N);
+  if (M == 0) return B200Q_OK;
+  if (epilogue < 0 || epilogue >= B200Q_NUM_EP) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: epilogue %d", epilogue);
+  if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(X, 16) || !aligned(Y, 16))
+    return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm: pointers must be 16-byte aligned");
+  return gemm_launch(packed, scale, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags,
+                     reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_nt_matmul(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,
+                    int M, int K, int N, int epilogue, void* stream) {
+  if (!X || !T || !Y) return set_error(B200Q_ERR_NULL, "b200q_nt_matmul: NULL pointer");
+  if (M < 0 || K <= 0 || N <= 0 || N % 8 != 0 || K % 8 != 0)
+    return set_error(B200Q_ERR_BAD_SHAPE, "b200q_nt_matmul: M=%d K=%d N=%d", M, K, N);
+  if (M == 0) return B200Q_OK;
+  if (!aligned(X, 16) || !aligned(T, 16) || !aligned(Y, 16))
+    return set_error(B200Q_ERR_BAD_ALIGN, "b200q_nt_matmul: pointers must be 16-byte aligned");
+  return nt_matmul_launch(X, T, ep0, ep1, ep2, Y, M, K, N, epilogue, reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

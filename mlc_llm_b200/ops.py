@@ -1,0 +1,226 @@
+"""PyTorch-tensor wrappers over the C-ABI (device memory and streams come from torch; every
+computation is a kernel of libb200q.so, launched on torch's current stream).
+
+Argument order follows the reference PrimFuncs: (packed, scale, x[, epilogue operands]) -> out
+(mlc_llm/dispatch/dispatch_tir_operator_adreno.py:6,128).  Outputs may be passed in (destination
+passing, like R.call_tir) or are allocated here.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from .quant_spec import EPILOGUES, FLAG_PDL, SPECS, QuantSpec
+
+
+def _spec(spec) -> QuantSpec:
+    return SPECS[spec] if isinstance(spec, str) else spec
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("b200q ops take CUDA tensors only (there is no CPU path)")
+        if t is not None and not t.is_contiguous():
+            raise ValueError("b200q ops take contiguous tensors (compact row-major, as the reference's buffers)")
+
+
+def _ep_id(epilogue) -> int:
+    return EPILOGUES[epilogue] if isinstance(epilogue, str) else int(epilogue)
+
+
+def _check_weight(spec: QuantSpec, packed: torch.Tensor, scale: torch.Tensor, K: int):
+    if packed.dtype not in (torch.int32, torch.uint32) or packed.dim() != 2:
+        raise ValueError("packed must be a 2-D uint32/int32 tensor [n_words, N]")
+    N = packed.shape[1]
+    if packed.shape[0] != spec.n_words(K):
+        raise ValueError(f"packed has {packed.shape[0]} word rows, {spec.name} with K={K} needs {spec.n_words(K)}")
+    if scale.dtype != spec.torch_dtype or tuple(scale.shape) != (spec.n_groups(K), N):
+        raise ValueError(f"scale must be {spec.dtype}[{spec.n_groups(K)}, {N}]")
+    return N
+
+
+def gemv(
+    packed: torch.Tensor,
+    scale: torch.Tensor,
+    x: torch.Tensor,
+    spec,
+    epilogue="none",
+    ep0: Optional[torch.Tensor] = None,
+    out: Optional[torch.Tensor] = None,
+    pdl: bool = False,
+) -> torch.Tensor:
+    """fused_decode*_matmul*: y[..., n] = sum_k x[..., k] * decode(packed, scale)[k, n] (+ epilogue).
+
+    x: dtype[..., K] with every leading dim == 1 (the reference fuses only for the constant 1,
+    transform/decode_matmul_ewise.py:8-11).  Returns dtype[1, 1, N] (float32 for cast_f32)."""
+    spec = _spec(spec)
+    ep = _ep_id(epilogue)
+    _need_cuda(packed, scale, x, ep0, out)
+    K = x.shape[-1]
+    if x.numel() != K:
+        raise ValueError("gemv is the batch-1 decode path: x must have exactly K elements")
+    if x.dtype != spec.torch_dtype:
+        raise ValueError(f"x must be {spec.dtype}")
+    N = _check_weight(spec, packed, scale, K)
+    odt = torch.float32 if (ep == EPILOGUES["cast_f32"] or spec.dtype == "float32") else torch.float16
+    if out is None:
+        out = torch.empty((1, 1, N), dtype=odt, device=x.device)
+    elif out.numel() != N or out.dtype != odt:
+        raise ValueError(f"out must be {odt}[{N}]")
+    if ep0 is not None and (ep0.numel() != N or ep0.dtype != spec.torch_dtype):
+        raise ValueError(f"ep0 must be {spec.dtype}[{N}]")
+    L = _lib.lib()
+    _lib.check(
+        L.b200q_gemv(
+            packed.data_ptr(), scale.data_ptr(), x.data_ptr(), _ptr(ep0), out.data_ptr(),
+            K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, _stream(),
+        )
+    )
+    return out
+
+
+def gemv_multi(
+    weights: Sequence[tuple],
+    x: torch.Tensor,
+    spec,
+    epilogues: Optional[Sequence] = None,
+    ep0s: Optional[Sequence[Optional[torch.Tensor]]] = None,
+    outs: Optional[Sequence[torch.Tensor]] = None,
+    pdl: bool = False,
+):
+    """Up to four GEMVs that share x (q|k|v, gate|up) in one launch.  weights: [(packed, scale), ...]."""
+    spec = _spec(spec)
+    n = len(weights)
+    epilogues = list(epilogues) if epilogues is not None else ["none"] * n
+    ep0s = list(ep0s) if ep0s is not None else [None] * n
+    K = x.shape[-1]
+    _need_cuda(x)
+    if x.numel() != K or x.dtype != spec.torch_dtype:
+        raise ValueError("x must be dtype[K]")
+    ops = (_lib.GemvOp * n)()
+    results = []
+    for i, (packed, scale) in enumerate(weights):
+        _need_cuda(packed, scale, ep0s[i])
+        N = _check_weight(spec, packed, scale, K)
+        ep = _ep_id(epilogues[i])
+        odt = torch.float32 if (ep == EPILOGUES["cast_f32"] or spec.dtype == "float32") else torch.float16
+        o = outs[i] if outs is not None else torch.empty((1, 1, N), dtype=odt, device=x.device)
+        if o.numel() != N or o.dtype != odt:
+            raise ValueError(f"out[{i}] must be {odt}[{N}]")
+        ops[i] = _lib.GemvOp(packed.data_ptr(), scale.data_ptr(), _ptr(ep0s[i]), o.data_ptr(), N, ep)
+        results.append(o)
+    L = _lib.lib()
+    _lib.check(L.b200q_gemv_multi(ops, n, x.data_ptr(), K, spec.fmt_id, FLAG_PDL if pdl else 0, _stream()))
+    return results
+
+
+def gemv_tune(wn: int = 0, ksplit: int = 0) -> None:
+    _lib.lib().b200q_gemv_tune(wn, ksplit)
+
+
+def dequantize(packed, scale, K: int, spec, transpose_output: bool = False, out=None) -> torch.Tensor:
+    """decode*: packed/scale -> dtype[K, N] (or [N, K]); bit-exact against the reference decode."""
+    spec = _spec(spec)
+    _need_cuda(packed, scale, out)
+    N = _check_weight(spec, packed, scale, K)
+    shape = (N, K) if transpose_output else (K, N)
+    if out is None:
+        out = torch.empty(shape, dtype=spec.torch_dtype, device=packed.device)
+    elif tuple(out.shape) != shape or out.dtype != spec.torch_dtype:
+        raise ValueError(f"out must be {spec.dtype}{list(shape)}")
+    L = _lib.lib()
+    _lib.check(L.b200q_dequant(packed.data_ptr(), scale.data_ptr(), out.data_ptr(), K, N, spec.fmt_id,
+                               int(transpose_output), _stream()))
+    return out
+
+
+def take_decode(packed_rm, scale_rm, ids, K: int, spec, out=None) -> torch.Tensor:
+    """take_decode: quantized embedding gather from the row-major (V, n_words) layout."""
+    spec = _spec(spec)
+    _need_cuda(packed_rm, scale_rm, ids, out)
+    V = packed_rm.shape[0]
+    if packed_rm.shape[1] != spec.n_words(K) or tuple(scale_rm.shape) != (V, spec.n_groups(K)):
+        raise ValueError("packed_rm / scale_rm do not match (V, n_words) / (V, n_groups)")
+    if ids.dtype != torch.int32 or ids.dim() != 1:
+        raise ValueError("ids must be a 1-D int32 tensor")
+    n = ids.numel()
+    if out is None:
+        out = torch.empty((n, K), dtype=spec.torch_dtype, device=packed_rm.device)
+    L = _lib.lib()
+    _lib.check(L.b200q_take_decode(packed_rm.data_ptr(), scale_rm.data_ptr(), ids.data_ptr(), out.data_ptr(),
+                                   n, V, K, spec.fmt_id, _stream()))
+    return out
+
+
+def encode(W: torch.Tensor, spec, transpose: bool = True):
+    """encoding_func (te_encode_sym): W dtype[N, K] -> (packed uint32, scale dtype); bit-exact."""
+    spec = _spec(spec)
+    _need_cuda(W)
+    if W.dim() != 2 or W.dtype != spec.torch_dtype:
+        raise ValueError(f"W must be {spec.dtype}[N, K]")
+    N, K = W.shape
+    R, G = spec.n_words(K), spec.n_groups(K)
+    pshape, sshape = ((R, N), (G, N)) if transpose else ((N, R), (N, G))
+    packed = torch.empty(pshape, dtype=torch.int32, device=W.device)
+    scale = torch.empty(sshape, dtype=spec.torch_dtype, device=W.device)
+    L = _lib.lib()
+    _lib.check(L.b200q_encode(W.data_ptr(), packed.data_ptr(), scale.data_ptr(), N, K, spec.fmt_id,
+                              int(transpose), _stream()))
+    return packed, scale
+
+
+def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, pdl: bool = False):
+    """fused_decode*_NT_matmul* / decode + NT_matmul: Y[m, n] = sum_k X[m, k] * w[k, n] (+ epilogue)
+    on the tcgen05 tensor cores.  X dtype[..., M, K] -> Y dtype[..., M, N]."""
+    spec = _spec(spec)
+    ep = _ep_id(epilogue)
+    _need_cuda(packed, scale, X, ep0, ep1, ep2, out)
+    K = X.shape[-1]
+    M = X.numel() // K
+    N = _check_weight(spec, packed, scale, K)
+    if X.dtype != spec.torch_dtype:
+        raise ValueError(f"X must be {spec.dtype}")
+    odt = torch.float32 if ep == EPILOGUES["cast_f32"] else spec.torch_dtype
+    oshape = tuple(X.shape[:-1]) + (N,)
+    if out is None:
+        out = torch.empty(oshape, dtype=odt, device=X.device)
+    elif out.numel() != M * N or out.dtype != odt:
+        raise ValueError(f"out must be {odt}[{M}, {N}]")
+    L = _lib.lib()
+    _lib.check(L.b200q_gemm(packed.data_ptr(), scale.data_ptr(), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
+                            out.data_ptr(), M, K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, _stream()))
+    return out
+
+
+def nt_matmul(X, T, epilogue="none", ep0=None, ep1=None, ep2=None, out=None):
+    """NT_matmul: Y[m, n] = sum_k X[m, k] * T[n, k] (+ epilogue), f16, tcgen05."""
+    ep = _ep_id(epilogue)
+    _need_cuda(X, T, ep0, ep1, ep2, out)
+    K = X.shape[-1]
+    M = X.numel() // K
+    N = T.shape[0]
+    if T.shape[1] != K or X.dtype != torch.float16 or T.dtype != torch.float16:
+        raise ValueError("nt_matmul: X f16[..., K], T f16[N, K]")
+    odt = torch.float32 if ep == EPILOGUES["cast_f32"] else torch.float16
+    if out is None:
+        out = torch.empty(tuple(X.shape[:-1]) + (N,), dtype=odt, device=X.device)
+    L = _lib.lib()
+    _lib.check(L.b200q_nt_matmul(X.data_ptr(), T.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2), out.data_ptr(),
+                                 M, K, N, ep, _stream()))
+    return out
+
+
+def launch_count() -> int:
+    return int(_lib.lib().b200q_launch_count())

@@ -1,0 +1,94 @@
+"""Quantization scheme description: one dataclass that maps 1:1 onto the reference's four flags
+(--dtype, --quantization-mode, --quantization-sym, --quantization-storage-nbit; build.py:19-25,
+utils.py:31-36) and onto the BASELINE names q4f16_0 / q3f16_0 / q4f32_0 / q8f16_0."""
+from __future__ import annotations
+
+import dataclasses
+
+import torch
+
+# ids shared with include/b200q.h
+FMT_IDS = {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3}
+EPILOGUES = {
+    "none": 0,
+    "add": 1,
+    "multiply": 2,
+    "silu": 3,
+    "cast_f32": 4,
+    "bias": 5,
+    "bias_gelu": 6,
+    "bias_add2": 7,
+}
+FLAG_PDL = 1
+
+
+@dataclasses.dataclass(frozen=True)
+class QuantSpec:
+    name: str
+    mode: str  # "int4" | "int3" | "int8"   (--quantization-mode)
+    dtype: str  # "float16" | "float32"     (--dtype)
+    group_size: int  # build.py:114: 40 for int3 else 32
+    sym: bool = True  # --quantization-sym
+    storage_nbit: int = 32  # --quantization-storage-nbit
+
+    @property
+    def nbit(self) -> int:  # quantization.py:313
+        return int(self.mode[-1])
+
+    @property
+    def npu(self) -> int:
+        return self.storage_nbit // self.nbit
+
+    @property
+    def maxint(self) -> int:
+        return (1 << (self.nbit - 1)) - 1
+
+    @property
+    def fmt_id(self) -> int:
+        return FMT_IDS[self.name]
+
+    @property
+    def torch_dtype(self) -> torch.dtype:
+        return torch.float16 if self.dtype == "float16" else torch.float32
+
+    def n_groups(self, K: int) -> int:
+        return -(-K // self.group_size)
+
+    def n_words(self, K: int) -> int:
+        return -(-self.group_size // self.npu) * self.n_groups(K)
+
+    def gemv_bytes(self, K: int, N: int, epilogue: str = "none") -> int:
+        """Algorithmic HBM bytes of one GEMV."""
+        sb = 2 if self.dtype == "float16" else 4
+        ob = 4 if (epilogue == "cast_f32" or self.dtype == "float32") else 2
+        b = 4 * self.n_words(K) * N + sb * self.n_groups(K) * N + sb * K + ob * N
+        if epilogue in ("add", "multiply"):
+            b += ob * N
+        if epilogue in ("bias", "bias_gelu"):
+            b += sb * N
+        return b
+
+
+SPECS = {
+    "q4f16_0": QuantSpec("q4f16_0", "int4", "float16", 32),
+    "q3f16_0": QuantSpec("q3f16_0", "int3", "float16", 40),
+    "q4f32_0": QuantSpec("q4f32_0", "int4", "float32", 32),
+    "q8f16_0": QuantSpec("q8f16_0", "int8", "float16", 32),
+}
+
+
+def spec_from_flags(dtype: str, mode: str, sym: bool, storage_nbit: int, group_size: int | None = None) -> QuantSpec:
+    """The reference's CLI flags -> QuantSpec.  Raises for combinations outside the `_0` contract
+    (asymmetric, uint16/uint8 storage, fp4): those are SURVEY.md 8(f) 'next' rows."""
+    if not sym:
+        raise NotImplementedError("asymmetric group quantization is not on this path yet (SURVEY.md 8f rank 1)")
+    if storage_nbit != 32:
+        raise NotImplementedError("only uint32 storage is on this path (SURVEY.md 8f rank 4)")
+    if not mode.startswith("int"):
+        raise NotImplementedError("fp4 is not on this path (SURVEY.md 8f rank 4)")
+    for s in SPECS.values():
+        if s.mode == mode and s.dtype == dtype:
+            if group_size is not None and group_size != s.group_size:
+                raise NotImplementedError(f"group size {group_size} (the reference hard-wires {s.group_size})")
+            return s
+    raise NotImplementedError(f"{mode}/{dtype}")

@@ -1,0 +1,96 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol
+include/b200q.h declares, the ctypes prototypes cover them, and argument validation (which runs
+before any CUDA call) returns the documented error codes.  No compute happens here."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from mlc_llm_b200 import _lib
+from mlc_llm_b200.quant_spec import SPECS, spec_from_flags
+from oracle import quant_oracle as qo
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    txt = open(os.path.join(ROOT, "include", "b200q.h")).read()
+    return sorted(set(re.findall(r"B200Q_API[^;(]*?\b(b200q_\w+)\s*\(", txt)))
+
+
+def test_header_symbols_exported_and_bound():
+    names = declared_symbols()
+    assert len(names) >= 15
+    L = _lib.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/b200q.h but not exported by libb200q.so"
+        assert n in _lib.PROTOTYPES, f"{n} has no ctypes prototype"
+    assert set(_lib.PROTOTYPES) == set(names)
+
+
+def test_version_and_layout_helpers_match_oracle():
+    L = _lib.lib()
+    assert L.b200q_version() == 100
+    for name, spec in SPECS.items():
+        f = qo.FORMATS[name]
+        assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3}[name]
+        for K in (32, 40, 100, 2560, 4096, 5120, 11008, 13824, 22016):
+            assert L.b200q_n_groups(spec.fmt_id, K) == f.n_groups(K) == spec.n_groups(K)
+            assert L.b200q_n_words(spec.fmt_id, K) == f.n_words(K) == spec.n_words(K)
+        for ep_name, ep in qo.EPILOGUES.items():
+            if ep_name == "bias_add2":
+                continue
+            for K, N in ((4096, 4096), (4096, 11008), (11008, 4096), (4096, 32000)):
+                assert L.b200q_gemv_bytes(spec.fmt_id, K, N, ep) == qo.gemv_bytes(K, N, f, ep) == spec.gemv_bytes(K, N, ep_name)
+    assert L.b200q_n_groups(9, 64) < 0
+
+
+def test_epilogue_ids_match():
+    from mlc_llm_b200.quant_spec import EPILOGUES
+
+    assert EPILOGUES == qo.EPILOGUES
+
+
+def test_argument_validation_codes():
+    """Validation happens before any CUDA call, so fake (aligned) addresses are enough."""
+    L = _lib.lib()
+    a = 0x10000  # 16-byte aligned fake device address
+    st = None
+    # N not a multiple of 8
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 12, 0, 0, 0, st) == -1
+    assert b"multiple of 8" in L.b200q_last_error()
+    # unknown format / epilogue
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 7, 0, 0, st) == -3
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 42, 0, st) == -3
+    # epilogue that needs an operand
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 1, 0, st) == -5
+    # NULL / misaligned
+    assert L.b200q_gemv(None, a, a, None, a, 4096, 4096, 0, 0, 0, st) == -5
+    assert L.b200q_gemv(a + 4, a, a, None, a, 4096, 4096, 0, 0, 0, st) == -2
+    assert L.b200q_dequant(a, a, a, 4096, 4100, 0, 0, st) == -1
+    assert L.b200q_gemm(a, a, a, None, None, None, a, 16, 4096, 4096, 2, 0, 0, st) == -3  # f32 GEMM
+    assert L.b200q_take_decode(a, a, a, a, 0, 10, 64, 0, st) == 0  # empty gather is a no-op
+
+
+def test_spec_from_flags():
+    assert spec_from_flags("float16", "int4", True, 32).name == "q4f16_0"
+    assert spec_from_flags("float16", "int3", True, 32).name == "q3f16_0"
+    assert spec_from_flags("float32", "int4", True, 32).name == "q4f32_0"
+    assert spec_from_flags("float16", "int8", True, 32).name == "q8f16_0"
+    with pytest.raises(NotImplementedError):
+        spec_from_flags("float16", "int4", False, 32)
+    with pytest.raises(NotImplementedError):
+        spec_from_flags("float16", "int3", True, 16)
+
+
+def test_ops_refuse_cpu_tensors():
+    import torch
+
+    from mlc_llm_b200 import ops
+
+    p = torch.zeros((512, 64), dtype=torch.int32)
+    s = torch.zeros((128, 64), dtype=torch.float16)
+    x = torch.zeros((1, 1, 4096), dtype=torch.float16)
+    with pytest.raises(ValueError, match="no CPU path"):
+        ops.gemv(p, s, x, "q4f16_0")
