@@ -1,0 +1,294 @@
+"""Layer-sequence driver for the decode step: the quantized-Linear launches of one token, in the
+reference's order, standing in for the compiled Relax `decoding` function
+(mlc_llm/relax_model/llama.py:581-611 built from LlamaDecoderLayer :340-401; GPT-NeoX:
+mlc_llm/relax_model/gpt_neox.py:134-288; call stack SURVEY.md 3.2).
+
+Per Llama layer the reference launches 7 fused dequant-GEMVs (q, k, v, o+residual, gate+silu,
+up*gate, down+residual) and one more for lm_head (cast to f32): 225 per token for 7B.  Here
+q|k|v share one launch (they read the same activation), everything is captured in one CUDA graph
+with programmatic dependent launch, and - for tensor parallelism - q/k/v/gate/up are
+column-sharded, o/down row-sharded, with one all-reduce per sharded block.
+
+Attention, norms and rotary embedding are NOT part of this path: the
+activation that would come out of attention is taken from the q projection so that the
+dependency chain between launches is the real one.
+
+Weights are synthetic: W ~ N(0, 0.02^2) (HF initializer_range, llama.py:24) drawn on the device
+and packed by the library's own encoder (b200q_encode, bit-exact against the reference's
+te_encode_sym - tests/test_gpu_parity.py).
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import ops
+from .quant_spec import SPECS, QuantSpec
+
+
+@dataclasses.dataclass(frozen=True)
+class ModelShape:
+    name: str
+    family: str  # "llama" | "gpt_neox"
+    hidden: int
+    inter: int
+    layers: int
+    vocab: int
+
+
+# llama.py:18-22,51-54; gpt_neox.py:50-57,99-107; 13B / 65B are BASELINE.json shapes
+MODEL_SHAPES = {
+    "llama-7b": ModelShape("llama-7b", "llama", 4096, 11008, 32, 32000),
+    "llama-13b": ModelShape("llama-13b", "llama", 5120, 13824, 40, 32000),
+    "llama-65b": ModelShape("llama-65b", "llama", 8192, 22016, 80, 32000),
+    "redpajama-3b": ModelShape("redpajama-3b", "gpt_neox", 2560, 10240, 32, 50432),
+    "dolly-v2-3b": ModelShape("dolly-v2-3b", "gpt_neox", 2560, 10240, 32, 50280),
+}
+
+
+def linear_list(shape: ModelShape) -> List[Tuple[str, int, int, str]]:
+    """(name, K, N, epilogue) of every quantized Linear of ONE layer, in launch order."""
+    h, i = shape.hidden, shape.inter
+    if shape.family == "llama":
+        return [("q", h, h, "none"), ("k", h, h, "none"), ("v", h, h, "none"), ("o", h, h, "add"),
+                ("gate", h, i, "silu"), ("up", h, i, "multiply"), ("down", i, h, "add")]
+    return [("q", h, h, "bias"), ("k", h, h, "bias"), ("v", h, h, "bias"), ("dense", h, h, "bias"),
+            ("h_to_4h", h, i, "bias_gelu"), ("4h_to_h", i, h, "bias")]
+
+
+def token_bytes(shape: ModelShape, spec: QuantSpec, tp: int = 1) -> int:
+    """Algorithmic HBM bytes of one token's quantized-Linear launches on ONE rank."""
+    total = 0
+    for name, K, N, ep in linear_list(shape):
+        if name in ("o", "down", "dense", "4h_to_h"):
+            K //= tp
+        else:
+            N //= tp
+        total += spec.gemv_bytes(K, N, ep)
+    total *= shape.layers
+    total += spec.gemv_bytes(shape.hidden, shape.vocab // tp, "cast_f32")
+    return total
+
+
+def token_macs(shape: ModelShape) -> int:
+    return shape.layers * sum(K * N for _, K, N, _ in linear_list(shape)) + shape.hidden * shape.vocab
+
+
+class QuantWeight:
+    """One packed Linear weight: packed uint32[n_words(K), N] + scale dtype[n_groups(K), N]."""
+
+    def __init__(self, packed: torch.Tensor, scale: torch.Tensor, K: int, N: int):
+        self.packed, self.scale, self.K, self.N = packed, scale, K, N
+
+
+def synth_weight(spec: QuantSpec, K: int, N: int, seed: int, device, col_slice=None, row_slice=None) -> QuantWeight:
+    """Draw W[N, K] ~ N(0, 0.02^2) on the device, pack it with the library encoder, slice for TP.
+
+    col_slice=(r, tp): keep output columns [r*N/tp, (r+1)*N/tp)     (column parallel)
+    row_slice=(r, tp): keep input rows    [r*K/tp, (r+1)*K/tp)      (row parallel; K/tp % group == 0)"""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    W = torch.empty((N, K), dtype=torch.float32, device=device)
+    W.normal_(0.0, 0.02, generator=g)
+    W = W.to(spec.torch_dtype)
+    packed, scale = ops.encode(W, spec, transpose=True)
+    del W
+    if col_slice is not None:
+        r, tp = col_slice
+        n = N // tp
+        if n % 8 or N % tp:
+            raise ValueError(f"column shard {N}/{tp} is not a multiple of 8")
+        packed = packed[:, r * n:(r + 1) * n].contiguous()
+        scale = scale[:, r * n:(r + 1) * n].contiguous()
+        N = n
+    if row_slice is not None:
+        r, tp = row_slice
+        k = K // tp
+        if K % tp or k % spec.group_size:
+            raise ValueError(f"row shard {K}/{tp} is not a multiple of the group size {spec.group_size}")
+        wpg = spec.n_words(spec.group_size)
+        gk = k // spec.group_size
+        packed = packed[r * gk * wpg:(r + 1) * gk * wpg].contiguous()
+        scale = scale[r * gk:(r + 1) * gk].contiguous()
+        K = k
+    return QuantWeight(packed, scale, K, N)
+
+
+class DecodeStack:
+    """The quantized-Linear stream of one decode step, graph-captured.
+
+    decode_step(): hidden state already on the device (x_in) -> logits on the device.
+    decode_step_host(x_host, logits_host): pinned host buffers in and out (what the reference's
+    LLMChatModule::Forward does around `decoding`, cpp/llm_chat.cc:920-946: token in, logits out).
+    """
+
+    def __init__(self, shape, spec, device=None, tp_rank: int = 0, tp_size: int = 1, seed: int = 0xB200,
+                 layers: Optional[int] = None, process_group=None, fuse_qkv: bool = True, pdl: bool = True,
+                 use_graph: bool = True):
+        self.shape = MODEL_SHAPES[shape] if isinstance(shape, str) else shape
+        self.spec = SPECS[spec] if isinstance(spec, str) else spec
+        self.device = torch.device(device if device is not None else "cuda")
+        self.tp_rank, self.tp_size, self.pg = tp_rank, tp_size, process_group
+        self.n_layers = self.shape.layers if layers is None else layers
+        self.fuse_qkv, self.pdl, self.use_graph = fuse_qkv, pdl, use_graph
+        if tp_size > 1 and self.spec.dtype != "float16":
+            raise NotImplementedError("tensor parallel decode is wired for the f16 schemes")
+        self.dt = self.spec.torch_dtype
+        self._build_weights(seed)
+        self._build_buffers()
+        self.graph = None
+        self.launches_per_step = 0
+        self.collectives_per_step = 0
+
+    # ------------------------------------------------------------------ weights
+    def _build_weights(self, seed: int):
+        sh, sp, tp, r = self.shape, self.spec, self.tp_size, self.tp_rank
+        self.layers: List[Dict[str, QuantWeight]] = []
+        self.biases: List[Dict[str, torch.Tensor]] = []
+        row_parallel = ("o", "down", "dense", "4h_to_h")
+        for li in range(self.n_layers):
+            ws, bs = {}, {}
+            for j, (name, K, N, ep) in enumerate(linear_list(sh)):
+                s = seed * 1000003 + li * 16 + j
+                if tp > 1 and name in row_parallel:
+                    ws[name] = synth_weight(sp, K, N, s, self.device, row_slice=(r, tp))
+                elif tp > 1:
+                    ws[name] = synth_weight(sp, K, N, s, self.device, col_slice=(r, tp))
+                else:
+                    ws[name] = synth_weight(sp, K, N, s, self.device)
+                if ep.startswith("bias"):
+                    g = torch.Generator(device=self.device)
+                    g.manual_seed(s + 7)
+                    b = torch.empty(N, dtype=torch.float32, device=self.device).normal_(0.0, 0.02, generator=g).to(self.dt)
+                    if tp > 1 and name not in row_parallel:
+                        n = N // tp
+                        b = b[r * n:(r + 1) * n].contiguous()
+                    bs[name] = b
+            self.layers.append(ws)
+            self.biases.append(bs)
+        self.lm_head = synth_weight(sp, sh.hidden, sh.vocab, seed * 1000003 + 999983, self.device,
+                                    col_slice=(r, tp) if tp > 1 else None)
+
+    def weight_bytes(self) -> int:
+        tot = 0
+        for ws in self.layers:
+            for w in ws.values():
+                tot += w.packed.numel() * 4 + w.scale.numel() * w.scale.element_size()
+        return tot + self.lm_head.packed.numel() * 4 + self.lm_head.scale.numel() * self.lm_head.scale.element_size()
+
+    # ------------------------------------------------------------------ activations
+    def _build_buffers(self):
+        sh, tp, dev, dt = self.shape, self.tp_size, self.device, self.dt
+        h, i = sh.hidden, sh.inter
+        e = lambda n, d=dt: torch.zeros(n, dtype=d, device=dev)
+        self.x_in = e(h)
+        self.buf = []
+        for _ in range(self.n_layers):
+            self.buf.append({"q": e(h // tp), "k": e(h // tp), "v": e(h // tp), "x1": e(h), "g": e(i // tp),
+                             "a": e(i // tp), "x2": e(h)})
+        self.logits_part = e(sh.vocab // tp, torch.float32)
+        self.logits = self.logits_part if tp == 1 else e(sh.vocab, torch.float32)
+
+    # ------------------------------------------------------------------ the launch sequence
+    def _gemv(self, w: QuantWeight, x, ep, ep0, out):
+        ops.gemv(w.packed, w.scale, x, self.spec, ep, ep0, out=out, pdl=self.pdl)
+        self.launches_per_step += 1
+
+    def _all_reduce(self, t):
+        import torch.distributed as dist
+
+        dist.all_reduce(t, group=self.pg)
+        self.collectives_per_step += 1
+
+    def _row_parallel(self, w, x, residual, out, ep_single):
+        """o / down: out = residual + sum_ranks(x_r @ w_r).  Rank 0 carries the residual (or bias)
+        into the sum so the reduction result is the final value."""
+        if self.tp_size == 1:
+            self._gemv(w, x, ep_single, residual, out)
+            return
+        if self.tp_rank == 0:
+            self._gemv(w, x, ep_single, residual, out)
+        else:
+            self._gemv(w, x, "none", None, out)
+        self._all_reduce(out)
+
+    def _run_llama(self):
+        x = self.x_in
+        for li in range(self.n_layers):
+            w, b = self.layers[li], self.buf[li]
+            if self.fuse_qkv:
+                ops.gemv_multi([(w["q"].packed, w["q"].scale), (w["k"].packed, w["k"].scale), (w["v"].packed, w["v"].scale)],
+                               x, self.spec, outs=[b["q"], b["k"], b["v"]], pdl=self.pdl)
+                self.launches_per_step += 1
+            else:
+                for n in ("q", "k", "v"):
+                    self._gemv(w[n], x, "none", None, b[n])
+            attn = b["q"]  # stand-in for the attention output (same shape, same dependency)
+            self._row_parallel(w["o"], attn, x, b["x1"], "add")
+            self._gemv(w["gate"], b["x1"], "silu", None, b["g"])
+            self._gemv(w["up"], b["x1"], "multiply", b["g"], b["a"])
+            self._row_parallel(w["down"], b["a"], b["x1"], b["x2"], "add")
+            x = b["x2"]
+        return x
+
+    def _run_neox(self):
+        x = self.x_in
+        for li in range(self.n_layers):
+            w, b, bias = self.layers[li], self.buf[li], self.biases[li]
+            if self.fuse_qkv:
+                ops.gemv_multi([(w[n].packed, w[n].scale) for n in ("q", "k", "v")], x, self.spec,
+                               epilogues=["bias"] * 3, ep0s=[bias[n] for n in ("q", "k", "v")],
+                               outs=[b["q"], b["k"], b["v"]], pdl=self.pdl)
+                self.launches_per_step += 1
+            else:
+                for n in ("q", "k", "v"):
+                    self._gemv(w[n], x, "bias", bias[n], b[n])
+            self._row_parallel(w["dense"], b["q"], bias["dense"], b["x1"], "bias")
+            self._gemv(w["h_to_4h"], b["x1"], "bias_gelu", bias["h_to_4h"], b["a"])
+            self._row_parallel(w["4h_to_h"], b["a"], bias["4h_to_h"], b["x2"], "bias")
+            x = b["x2"]
+        return x
+
+    def _run(self):
+        self.launches_per_step = 0
+        self.collectives_per_step = 0
+        x = self._run_llama() if self.shape.family == "llama" else self._run_neox()
+        self._gemv(self.lm_head, x, "none" if self.spec.dtype == "float32" else "cast_f32", None, self.logits_part)
+        if self.tp_size > 1:
+            import torch.distributed as dist
+
+            dist.all_gather_into_tensor(self.logits, self.logits_part, group=self.pg)
+            self.collectives_per_step += 1
+        return self.logits
+
+    def capture(self):
+        """Warm up on a side stream and capture the step into one CUDA graph."""
+        if not self.use_graph:
+            return
+        st = torch.cuda.Stream(device=self.device)
+        st.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(st):
+            for _ in range(2):
+                self._run()
+            st.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=st):
+                self._run()
+        torch.cuda.current_stream(self.device).wait_stream(st)
+        self.graph = g
+
+    def decode_step(self) -> torch.Tensor:
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._run()
+        return self.logits
+
+    def decode_step_host(self, x_host: torch.Tensor, logits_host: torch.Tensor) -> torch.Tensor:
+        self.x_in.copy_(x_host, non_blocking=True)
+        self.decode_step()
+        logits_host.copy_(self.logits, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return logits_host

@@ -1,0 +1,79 @@
+"""Dispatch registry: the plug-in seam of the reference, restated for the CUDA path.
+
+The reference replaces a compiler-generated PrimFunc by a hand-scheduled one when the two are
+structurally equal (mlc_llm/dispatch/dispatch_tir_operator.py:22-33; lookup_func,
+mlc_llm/dispatch/llama/main.py:6452-6458).  A key there is one exact
+(quantization scheme, K, N, epilogue) tuple; a miss returns None and the caller keeps the
+unscheduled function.  ``lookup`` keeps that contract: it returns a destination-passing callable
+``f(packed, scale, x[, ep0...], out)`` - the PrimFunc argument order
+(dispatch_tir_operator_adreno.py:6,128) - or None when this library does not handle the tuple.
+There is no fallback behind a miss: callers decide, nothing silently runs on the CPU.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+from . import ops
+from .quant_spec import EPILOGUES, SPECS, QuantSpec
+
+# what the reference's FuseDecodeMatmulEwise / FuseOps produce for each path
+GEMV_EPILOGUES = ("none", "add", "multiply", "silu", "cast_f32", "bias", "bias_gelu")
+GEMM_EPILOGUES = ("none", "add", "multiply", "silu", "cast_f32", "bias", "bias_gelu", "bias_add2")
+N_OPERANDS = {"none": 0, "add": 1, "multiply": 1, "silu": 0, "cast_f32": 0, "bias": 1, "bias_gelu": 1, "bias_add2": 3}
+
+
+def reference_name(spec: QuantSpec, K: int, N: int, epilogue: str, m_is_one: bool) -> str:
+    """A readable stand-in for the reference's generated function names
+    (fused_decode4_matmul3, fused_decode5_fused_matmul6_silu1, fused_decode_NT_matmul ...)."""
+    core = "matmul" if m_is_one else "NT_matmul"
+    ep = "" if epilogue == "none" else "_" + epilogue
+    return f"fused_decode_{spec.name}_{core}_k{K}_n{N}{ep}"
+
+
+def lookup(spec, K: int, N: int, epilogue: str = "none", m_is_one: bool = True) -> Optional[Callable]:
+    """Return the CUDA operator for (scheme, K, N, epilogue) or None (the reference's miss)."""
+    if isinstance(spec, str):
+        spec = SPECS.get(spec)
+    if spec is None or epilogue not in EPILOGUES:
+        return None
+    if K <= 0 or N <= 0 or N % 8 != 0:
+        return None
+    if m_is_one:
+        if epilogue not in GEMV_EPILOGUES:
+            return None
+
+        def gemv_op(packed, scale, x, *rest):
+            *eps, out = rest
+            if len(eps) != N_OPERANDS[epilogue]:
+                raise TypeError(f"{reference_name(spec, K, N, epilogue, True)} takes {N_OPERANDS[epilogue]} epilogue operand(s)")
+            return ops.gemv(packed, scale, x, spec, epilogue, eps[0] if eps else None, out=out, pdl=False)
+
+        gemv_op.__name__ = reference_name(spec, K, N, epilogue, True)
+        return gemv_op
+    # prefill: dequantize inside the tensor-core GEMM (f16 schemes only)
+    if spec.dtype != "float16" or epilogue not in GEMM_EPILOGUES:
+        return None
+
+    def gemm_op(packed, scale, x, *rest):
+        *eps, out = rest
+        if len(eps) != N_OPERANDS[epilogue]:
+            raise TypeError(f"{reference_name(spec, K, N, epilogue, False)} takes {N_OPERANDS[epilogue]} epilogue operand(s)")
+        eps = list(eps) + [None] * (3 - len(eps))
+        return ops.gemm(packed, scale, x, spec, epilogue, eps[0], eps[1], eps[2], out=out)
+
+    gemm_op.__name__ = reference_name(spec, K, N, epilogue, False)
+    return gemm_op
+
+
+def lookup_decode(spec, K: int, N: int, transpose_output: bool) -> Optional[Callable]:
+    """decode* (dequantize-to-dense) operators: f(packed, scale, out)."""
+    if isinstance(spec, str):
+        spec = SPECS.get(spec)
+    if spec is None or N % 8 != 0:
+        return None
+
+    def decode_op(packed, scale, out):
+        return ops.dequantize(packed, scale, K, spec, transpose_output, out=out)
+
+    decode_op.__name__ = f"decode_{spec.name}_k{K}_n{N}" + ("_T" if transpose_output else "")
+    return decode_op
