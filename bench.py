@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--no-per-shape", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-fuse-qkv", action="store_true")
+    ap.add_argument("--no-fuse-gate-up", action="store_true")
+    ap.add_argument("--tune", default="", help="ctas_per_sm,stages,dbg_flags for b200q_gemv_tune (experiments)")
     return ap.parse_args()
 
 
@@ -238,7 +240,9 @@ def main():
     shape = MODEL_SHAPES[args.model]
 
     stack = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, layers=args.layers,
-                        pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv)
+                        pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up)
+    if args.tune:
+        ops.gemv_tune(*[int(v) for v in args.tune.split(",")])
     stack.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(stack.dt))
     stack.capture()
     torch.cuda.synchronize()
@@ -363,6 +367,7 @@ def bench_shapes(stack, spec, torch, iters: int = 20):
     cases[f"o {h}->{h} +residual"] = ("single", "o", "q", ("add", "x1"))
     cases[f"gate {h}->{i} silu"] = ("single", "gate", "x1", ("silu", None))
     cases[f"up {h}->{i} *gate"] = ("single", "up", "x1", ("multiply", "g"))
+    cases[f"gate|up 2x({h}->{i}) one launch"] = ("multi", ["gate", "up"], "x1", None)
     cases[f"down {i}->{h} +residual"] = ("single", "down", "a", ("add", "x1"))
     for label, (kind, names, xname, ep) in cases.items():
         def sweep():
@@ -370,10 +375,12 @@ def bench_shapes(stack, spec, torch, iters: int = 20):
                 w, b = stack.layers[li], stack.buf[li]
                 x = stack.x_in if xname == "x_in" else b[xname]
                 if kind == "multi":
-                    ops.gemv_multi([(w[n].packed, w[n].scale) for n in names], x, spec, outs=[b[n] for n in names], pdl=True)
+                    ops.gemv_multi([(w[n].packed, w[n].scale) for n in names], x, spec,
+                                   outs=[b["g"], b["u"]] if names[0] == "gate" else [b[n] for n in names], pdl=True,
+                                   ws=stack.ws)
                 else:
                     ops.gemv(w[names].packed, w[names].scale, x, spec, ep[0], b[ep[1]] if ep[1] else None,
-                             out=b["x2"] if w[names].N == stack.shape.hidden else b["a"], pdl=True)
+                             out=b["x2"] if w[names].N == stack.shape.hidden else b["a"], pdl=True, ws=stack.ws)
         st = torch.cuda.Stream()
         st.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(st):
@@ -407,7 +414,7 @@ def bench_shapes(stack, spec, torch, iters: int = 20):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        ops.gemv(stack.lm_head.packed, stack.lm_head.scale, x, spec, "cast_f32", None, out=stack.logits_part)
+        ops.gemv(stack.lm_head.packed, stack.lm_head.scale, x, spec, "cast_f32", None, out=stack.logits_part, ws=stack.ws)
         e1.record()
         torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1) * 1e3)

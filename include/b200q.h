@@ -103,13 +103,24 @@ B200Q_API long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue);
  *   accumulation in f32 (the reference accumulates in dtype), then the epilogue.
  *   x   dtype[K]         out  dtype[N]  (float[N] for B200Q_EP_CAST_F32 and for q4f32_0)
  *   ep0 dtype[N] or NULL (ADD / MULTIPLY / BIAS / BIAS_GELU)
- * Requirements: N % 8 == 0; packed, scale 16-byte aligned; x, ep0, out aligned to their element. */
+ * Requirements: N % 8 == 0; packed, scale 16-byte aligned; x, ep0, out aligned to their element.
+ *
+ * workspace: optional device scratch (b200q_gemv_workspace_bytes() bytes, 16-byte aligned) that lets
+ * the kernel split a column panel's K range over several CTAs.  The caller zero-fills it ONCE
+ * (cudaMemset) before its first use; every launch leaves it zeroed again.  It must not be shared
+ * by launches that may run concurrently (one per stream).  NULL: whole panels are dealt to CTAs
+ * (correct, slower for small N).  The callee itself never allocates (SURVEY.md 8b "Ownership"). */
+B200Q_API size_t b200q_gemv_workspace_bytes(void);
 B200Q_API int b200q_gemv(const void* packed, const void* scale, const void* x, const void* ep0, void* out,
-               int K, int N, int fmt, int epilogue, unsigned flags, void* stream);
+               int K, int N, int fmt, int epilogue, unsigned flags, void* workspace,
+               size_t workspace_bytes, void* stream);
 
 /* Several GEMVs that read the SAME activation vector in ONE launch (q|k|v, gate|up: the reference
  * launches them back to back on the same x, relax_model/llama.py:233-236,147-152).  Tensors stay
- * the reference's separate per-Linear arrays. */
+ * the reference's separate per-Linear arrays.
+ * x_mul (optional, dtype[K]): the activation is x[k] * x_mul[k], rounded to dtype - the SwiGLU
+ * product that the reference forms with fused_decode5_fused_matmul6_multiply1's epilogue
+ * (dispatch_tir_operator_adreno.py:150-152) before down_proj reads it; same single rounding. */
 typedef struct {
   const void* packed;
   const void* scale;
@@ -118,19 +129,20 @@ typedef struct {
   int N;
   int epilogue;
 } b200q_gemv_op;
-B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt,
-                     unsigned flags, void* stream);
+B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K,
+                     int fmt, unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
 
-/* Tuning override for experiments (0 = heuristic).  wn: warps across N per CTA (1,2,4,8);
- * ksplit: CTAs of one cluster splitting K (1,2,4,8). Thread-local. */
-B200Q_API void b200q_gemv_tune(int wn, int ksplit);
+/* Tuning override for experiments (0 = default).  ctas_per_sm: 1 or 2 persistent CTAs per SM;
+ * stages: cap of the shared-memory ring depth; dbg_flags bit 0: stream only, skip the math
+ * (results are garbage - for bandwidth probes). Thread-local. */
+B200Q_API void b200q_gemv_tune(int ctas_per_sm, int stages, int dbg_flags);
 
 /* Same GEMV with HOST activation / output buffers (weights stay resident in HBM as in the
  * reference, cpp/llm_chat.cc:858-861): copies x host->device, runs, copies out device->host and
  * synchronizes `stream`.  x_dev / out_dev are caller-provided device scratch of K / N elements. */
 B200Q_API int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,
                     void* out_host, void* x_dev, void* out_dev, int K, int N, int fmt, int epilogue,
-                    void* stream);
+                    void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- a2 / a6: dequantize ---------------------------------------------------------------------
  * Replaces decode* (dispatch/llama/main.py:3984-4232, tuning.py:111-147, quantization.py:213-230).

@@ -44,10 +44,12 @@ PROTOTYPES = {
     "b200q_n_groups": (c_int, [c_int, c_int]),
     "b200q_n_words": (c_int, [c_int, c_int]),
     "b200q_gemv_bytes": (c_ll, [c_int, c_int, c_int, c_int]),
-    "b200q_gemv": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_uint, c_void_p]),
-    "b200q_gemv_multi": (c_int, [ctypes.POINTER(GemvOp), c_int, c_void_p, c_int, c_int, c_uint, c_void_p]),
-    "b200q_gemv_tune": (None, [c_int, c_int]),
-    "b200q_gemv_host": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
+    "b200q_gemv_workspace_bytes": (ctypes.c_size_t, []),
+    "b200q_gemv": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
+    "b200q_gemv_multi": (c_int, [ctypes.POINTER(GemvOp), c_int, c_void_p, c_void_p, c_int, c_int, c_uint, c_void_p,
+                                 ctypes.c_size_t, c_void_p]),
+    "b200q_gemv_tune": (None, [c_int, c_int, c_int]),
+    "b200q_gemv_host": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_dequant": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
     "b200q_take_decode": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
     "b200q_encode": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),

@@ -25,11 +25,10 @@ int check_cuda(cudaError_t e, const char* what) {
 void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 // kernels (gemv.cu, gemv_f32.cu, dequant.cu, gemm.cu)
-int gemv_f16_launch(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt, unsigned flags,
-                    cudaStream_t stream);
-int gemv_f32_launch(const b200q_gemv_op* ops, int n_ops, const void* x, int K, unsigned flags,
-                    cudaStream_t stream);
-void gemv_tune(int wn, int ksplit);
+int gemv_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K, int fmt,
+                unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+void gemv_tune(int ctas_per_sm, int stages, int flags);
+size_t gemv_workspace_bytes();
 int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
                    cudaStream_t stream);
 int take_decode_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
@@ -93,44 +92,41 @@ long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue) {
   return b;
 }
 
-void b200q_gemv_tune(int wn, int ksplit) { gemv_tune(wn, ksplit); }
+void b200q_gemv_tune(int ctas_per_sm, int stages, int dbg_flags) { gemv_tune(ctas_per_sm, stages, dbg_flags); }
+size_t b200q_gemv_workspace_bytes(void) { return gemv_workspace_bytes(); }
 
-int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt, unsigned flags,
-                     void* stream) {
+int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K, int fmt,
+                     unsigned flags, void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_fmt(fmt, "b200q_gemv")) return e;
   if (!ops || !x) return set_error(B200Q_ERR_NULL, "b200q_gemv: NULL ops/x");
   if (n_ops < 1 || n_ops > 4) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_multi: n_ops=%d not in [1,4]", n_ops);
   if (K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv: K=%d", K);
-  if (!aligned(x, fmt_is_f32(fmt) ? 4 : 2)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv: x misaligned");
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  if (!aligned(x, el) || (x_mul && !aligned(x_mul, el))) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv: x misaligned");
+  if (workspace && !aligned(workspace, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv: workspace must be 16-byte aligned");
   for (int i = 0; i < n_ops; ++i)
     if (int e = check_gemv_op(ops[i], fmt, "b200q_gemv")) return e;
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (fmt_is_f32(fmt)) {
-    for (int i = 0; i < n_ops; ++i)
-      if (ops[i].epilogue == B200Q_EP_CAST_F32) {
-        // f32 model: the cast is the identity
-      }
-    return gemv_f32_launch(ops, n_ops, x, K, flags, s);
-  }
-  return gemv_f16_launch(ops, n_ops, x, K, fmt, flags, s);
+  return gemv_launch(ops, n_ops, x, x_mul, K, fmt, flags, workspace, workspace ? workspace_bytes : 0,
+                     reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200q_gemv(const void* packed, const void* scale, const void* x, const void* ep0, void* out, int K,
-               int N, int fmt, int epilogue, unsigned flags, void* stream) {
+               int N, int fmt, int epilogue, unsigned flags, void* workspace, size_t workspace_bytes,
+               void* stream) {
   b200q_gemv_op op{packed, scale, ep0, out, N, epilogue};
-  return b200q_gemv_multi(&op, 1, x, K, fmt, flags, stream);
+  return b200q_gemv_multi(&op, 1, x, nullptr, K, fmt, flags, workspace, workspace_bytes, stream);
 }
 
 int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,
                     void* out_host, void* x_dev, void* out_dev, int K, int N, int fmt, int epilogue,
-                    void* stream) {
+                    void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_fmt(fmt, "b200q_gemv_host")) return e;
   if (!x_host || !out_host || !x_dev || !out_dev) return set_error(B200Q_ERR_NULL, "b200q_gemv_host: NULL buffer");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const size_t el = fmt_is_f32(fmt) ? 4 : 2;
   const size_t oel = (epilogue == B200Q_EP_CAST_F32) ? 4 : el;
   if (int e = check_cuda(cudaMemcpyAsync(x_dev, x_host, el * K, cudaMemcpyHostToDevice, s), "H2D x")) return e;
-  if (int e = b200q_gemv(packed, scale, x_dev, ep0, out_dev, K, N, fmt, epilogue, 0, stream)) return e;
+  if (int e = b200q_gemv(packed, scale, x_dev, ep0, out_dev, K, N, fmt, epilogue, 0, workspace, workspace_bytes, stream)) return e;
   if (int e = check_cuda(cudaMemcpyAsync(out_host, out_dev, oel * N, cudaMemcpyDeviceToHost, s), "D2H out")) return e;
   return check_cuda(cudaStreamSynchronize(s), "cudaStreamSynchronize");
 }

@@ -1,63 +1,155 @@
-// Decode-step fused dequantize + GEMV for the f16 group-quantized formats (q4f16_0, q3f16_0,
-// q8f16_0), sm_100a.
+// Decode-step fused dequantize + GEMV for all four group-quantized formats, sm_100a.
 //
 // Replaces the reference's fused_decode*_matmul* PrimFuncs
 // (mlc_llm/dispatch/dispatch_tir_operator_adreno.py:5-411, mlc_llm/dispatch/llama/main.py:4235-6363;
 // schedule generator mlc_llm/tuning.py:39-108: one output column per thread, sequential K,
-// N/256 blocks).  This design instead:
+// N/256 blocks, 4-byte weight loads, no async copy).  A batch-1 GEMV of these sizes (9-75 MB) lasts
+// 1.5-11 us at HBM speed, so the design is about never letting the memory pipe drain:
 //
-//   * streams the packed words with 128-bit L1-bypassing loads, 4 consecutive columns per lane,
-//     one full 128-byte line per (word row, 32-column warp tile); a lane keeps two "units"
-//     (4 word rows x 4 columns + their 4 scales = 72 B) in flight, i.e. ~37 KB per 256-thread CTA;
-//   * unpacks in registers to the bit-exact f16 weight  half((q - maxint) * s)  (common.cuh);
-//   * contracts over K with mma.sync.m16n8k16 (f16 x f16 products exact, f32 accumulate): the
-//     packed layout puts 8 consecutive k of ONE column into a lane's register, so weights are the
-//     A operand (16 columns x 16 k per instruction) and the activation vector is replicated over
-//     the 8 B columns.  A SIMT formulation needs >= 3.5 issue slots per weight (2 cvt + 2 fma per
-//     half2 on top of the unpack) against a budget of 3.1 at HBM speed; this one needs ~1.9;
-//   * splits K across the warps of a CTA (shared-memory reduce) and, for small N, across the CTAs
-//     of a thread-block cluster (distributed-shared-memory reduce) - deterministic, no atomics,
-//     no workspace;
-//   * with B200Q_FLAG_PDL, issues the first weight loads BEFORE griddepcontrol.wait: weights are
-//     constants, so their fetch overlaps the tail of the previous kernel in the stream.
+//   * ONE persistent CTA per SM (grid = #SMs); the matrix is cut into blocks of 32 packed-word rows
+//     x 128 columns and the flattened block sequence (row blocks fastest inside a 128-column panel)
+//     is divided EVENLY over the CTAs ("stream-K"), whatever K and N are;
+//   * a producer warp streams its CTA's blocks into a multi-stage shared-memory ring with the bulk
+//     async-copy engine (cp.async.bulk ... mbarrier::complete_tx, L2 evict-first): one 512-byte row
+//     segment per copy, ~19 KB per stage, 75-95 KB in flight per SM, no registers tied up;
+//   * the weights are constants, so the producer starts BEFORE griddepcontrol.wait: with
+//     programmatic dependent launch the next GEMV of the stream fills its ring (the second CTA slot
+//     of every SM) while the current one is still computing / reducing;
+//   * eight consumer warps unpack the words in registers to the bit-exact f16 weight
+//     half((q - maxint) * s) (common.cuh) and contract over K with mma.sync.m16n8k16 (f16 x f16
+//     products are exact, f32 accumulate): the packed layout puts 8 consecutive k of ONE column in a
+//     register, so weights are the A operand (16 columns x 16 k per instruction) and the activation
+//     vector is replicated over the 8 B columns.  A SIMT formulation needs >= 3.5 issue slots per
+//     weight against a budget of ~3.1 at HBM speed; this one needs ~1.9.  (q4f32_0 has f32 weights:
+//     FFMA, same pipeline.);
+//   * panels whose K range is shared by several CTAs are finished by the LAST CTA to arrive
+//     (counter in a caller-provided workspace, partial sums added in CTA order => deterministic,
+//     no spinning, self-cleaning).  Without a workspace whole panels are dealt out instead;
+//   * epilogues (residual add, multiply, silu, bias, bias+gelu, cast) are applied op for op in the
+//     model dtype like the reference PrimFuncs; optionally the activation is formed on the fly as
+//     x * x_mul (the SwiGLU product feeding down_proj) - bit-identical to the reference's separate
+//     `multiply` epilogue.
 //
-// Layout of the activation vector in shared memory: for word row r (npu consecutive k) the lane
-// needs x in the pair order the unpack produces; rows are stored [i = r % 4][unit = r / 4] so the
-// four lanes of a quad (which own consecutive units) read consecutive addresses.
-#include <cooperative_groups.h>
-
+// Shared-memory layout of a stage: word row r of the block at  r * 512 + (r / 4) * 32  bytes, scale
+// row g at  g * (pitch + 32): the 32-byte skew per 4-row unit makes the 128-bit reads of a quarter
+// warp (2 column quads x 4 units) hit 8 distinct 16-byte bank groups.
 #include "common.cuh"
-
-namespace cg = cooperative_groups;
 
 namespace b200q {
 
-constexpr int kThreads = 256;
-constexpr int kWarps = kThreads / 32;
-constexpr int kMaxOps = 4;
+namespace {
 
-struct GemvOp {
+constexpr int kConsumerWarps = 8;
+constexpr int kConsumerThreads = kConsumerWarps * 32;
+constexpr int kThreads = kConsumerThreads + 32;  // + producer warp
+constexpr int kMaxOps = 4;
+constexpr int kPanelCols = 128;
+constexpr int kBlockRows = 32;
+constexpr int kUnitsPerBlock = kBlockRows / 4;
+constexpr int kRowPitch = kPanelCols * 4;
+constexpr int kSkew = 32;
+constexpr int kWordStageBytes = kBlockRows * kRowPitch + kUnitsPerBlock * kSkew;  // 16640
+constexpr int kMaxStages = 12;
+constexpr int kMaxPanels = 4096;
+constexpr int kCounterBytes = kMaxPanels * 4;
+constexpr int kSmemHeader = 1280;  // barriers (256) + red[2][128] f32 (1024)
+constexpr int kSmemPerSm = 227 * 1024;
+
+template <int FMT>
+struct Stream {
+  using F = Fmt<FMT>;
+  using scale_t = typename F::scale_t;
+  static constexpr bool kF32 = (FMT == B200Q_Q4F32_0);
+  static constexpr int kGroupsPerBlock = kBlockRows / F::kRowsPerGroup;
+  static constexpr int kScalePitch = kPanelCols * (int)sizeof(scale_t) + kSkew;
+  static constexpr int kScaleStageBytes = kGroupsPerBlock * kScalePitch;
+  static constexpr int kStageBytes = kWordStageBytes + kScaleStageBytes;
+  // permuted activation bytes per packed word row
+  static constexpr int kXRowBytes = kF32 ? 32 : F::kQuads * 8;
+  static_assert(kStageBytes % 128 == 0, "stage alignment");
+};
+
+struct StreamOp {
   const uint32_t* packed;
-  const __half* scale;
-  const __half* ep0;
+  const void* scale;
+  const void* ep0;
   void* out;
   int N;
   int epilogue;
-  int tile_begin;  // first column tile (of 32 * WN columns) of this op in the grid
+  int panel_begin;
 };
 
-struct GemvParams {
-  GemvOp op[kMaxOps];
+struct StreamParams {
+  StreamOp op[kMaxOps];
   int n_ops;
-  const __half* x;
+  const void* x;
+  const void* x_mul;  // optional: activation = x * x_mul (elementwise, model dtype)
   int K;
-  int n_rows;   // packed word rows = n_words(K)
-  int n_units;  // ceil(n_rows / 4)
-  int units_per_cta;  // multiple of 4
+  int n_rows;    // packed word rows
+  int RB;        // row blocks per panel
+  int n_panels;  // over all ops
+  int T;         // total blocks
+  int stages;
+  int xs_bytes;
+  int aligned;   // 1: CTAs own whole panels (no workspace)
+  int c_max;     // partial slots per panel
+  float* ws_partial;
+  unsigned* ws_counter;
+  int no_compute;  // debug: stream only
 };
 
-__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
-                                         uint32_t a3, uint32_t b0, uint32_t b1) {
+// ---- PTX helpers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar,
+                                         uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+      : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t a) {
+  uint2 r;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ float ld_cg_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
   asm volatile(
       "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
       "{%0,%1,%2,%3};"
@@ -65,59 +157,23 @@ __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// bytes of permuted x per word row
+// ---- f16 formats: one unit = 4 word rows x 4 columns + the 4 column scales ------------------------
+// acc[m][*]: MMA m covers columns (4c + 2m) [A rows 0-7] and (4c + 2m + 1) [A rows 8-15] of the
+// lane's column quad c; the four lanes of a quad own different units (different k).
 template <int FMT>
-__host__ __device__ constexpr int x_row_bytes() {
-  return Fmt<FMT>::kQuads * 8;
-}
-
-// One unit = 4 word rows x 4 columns of packed words + the 4 column scales.
-struct Unit {
-  uint4 w[4];
-  uint2 s;
-};
-
-template <int FMT>
-__device__ __forceinline__ void load_unit(Unit& u, const uint32_t* __restrict__ packed,
-                                          const __half* __restrict__ scale, int unit, int n_rows,
-                                          int col, int N, bool valid, uint64_t pol) {
-  constexpr int kUnitsPerGroup = Fmt<FMT>::kRowsPerGroup / 4;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    int row = unit * 4 + i;
-    if (valid && row < n_rows) {
-      u.w[i] = ldg_stream_v4(packed + (size_t)row * N + col, pol);
-    } else {
-      u.w[i] = make_uint4(0, 0, 0, 0);
-    }
-  }
-  if (valid) {
-    u.s = ldg_stream_v2(scale + (size_t)(unit / kUnitsPerGroup) * N + col, pol);
-  } else {
-    u.s = make_uint2(0, 0);
-  }
-}
-
-// Accumulate one unit. acc[m][*]: MMA m covers columns (4c + 2m) [rows 0-7] and (4c + 2m + 1)
-// [rows 8-15] of the lane's column quad c.
-template <int FMT>
-__device__ __forceinline__ void compute_unit(const Unit& u, const unsigned char* xs_unit,
-                                             int xs_i_stride, float (&acc)[2][4]) {
-  using F = Fmt<FMT>;
+__device__ __forceinline__ void compute_unit_f16(const uint4 (&w)[4], uint2 sc, uint32_t xs_unit,
+                                                 uint32_t xs_i_stride, float (&acc)[2][4]) {
   __half2 s2[4];
-  {
-    uint32_t s01 = u.s.x, s23 = u.s.y;
-    s2[0] = u32_as_h2(__byte_perm(s01, 0, 0x1010));
-    s2[1] = u32_as_h2(__byte_perm(s01, 0, 0x3232));
-    s2[2] = u32_as_h2(__byte_perm(s23, 0, 0x1010));
-    s2[3] = u32_as_h2(__byte_perm(s23, 0, 0x3232));
-  }
+  s2[0] = u32_as_h2(__byte_perm(sc.x, 0, 0x1010));
+  s2[1] = u32_as_h2(__byte_perm(sc.x, 0, 0x3232));
+  s2[2] = u32_as_h2(__byte_perm(sc.y, 0, 0x1010));
+  s2[3] = u32_as_h2(__byte_perm(sc.y, 0, 0x3232));
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const uint32_t wv[4] = {u.w[i].x, u.w[i].y, u.w[i].z, u.w[i].w};
-    const unsigned char* xr = xs_unit + i * xs_i_stride;
+    const uint32_t wv[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+    const uint32_t xr = xs_unit + i * xs_i_stride;
     if constexpr (FMT == B200Q_Q4F16_0) {
-      uint4 xv = *reinterpret_cast<const uint4*>(xr);  // (x0,x4)(x1,x5)(x2,x6)(x3,x7)
+      uint4 xv = lds128(xr);  // (x0,x4)(x1,x5)(x2,x6)(x3,x7)
       __half2 h[4][4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) unpack_q4(wv[j], s2[j], h[j]);
@@ -129,25 +185,21 @@ __device__ __forceinline__ void compute_unit(const Unit& u, const unsigned char*
                  h2_as_u32(h[2 * m + 1][3]), xv.z, xv.w);
       }
     } else if constexpr (FMT == B200Q_Q3F16_0) {
-      // (x0,x5)(x1,x6) | (x2,x7)(x3,x8) | (x4,x9)(0,0)
-      // rows are 24 bytes apart: only 8-byte alignment is guaranteed
-      uint2 x01 = *reinterpret_cast<const uint2*>(xr);
-      uint2 x23 = *reinterpret_cast<const uint2*>(xr + 8);
-      uint2 xb = *reinterpret_cast<const uint2*>(xr + 16);
-      uint4 xa = make_uint4(x01.x, x01.y, x23.x, x23.y);
+      // (x0,x5)(x1,x6) | (x2,x7)(x3,x8) | (x4,x9)(0,0); rows are 24 bytes apart: 8-byte alignment
+      uint2 x01 = lds64(xr), x23 = lds64(xr + 8), xb = lds64(xr + 16);
       __half2 h[4][5];
 #pragma unroll
       for (int j = 0; j < 4; ++j) unpack_q3(wv[j], s2[j], h[j]);
 #pragma unroll
       for (int m = 0; m < 2; ++m) {
         mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-                 h2_as_u32(h[2 * m + 1][1]), xa.x, xa.y);
+                 h2_as_u32(h[2 * m + 1][1]), x01.x, x01.y);
         mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
-                 h2_as_u32(h[2 * m + 1][3]), xa.z, xa.w);
+                 h2_as_u32(h[2 * m + 1][3]), x23.x, x23.y);
         mma16816(acc[m], h2_as_u32(h[2 * m][4]), h2_as_u32(h[2 * m + 1][4]), 0u, 0u, xb.x, xb.y);
       }
     } else {  // Q8: (x0,x1)(x2,x3)
-      uint2 xv = *reinterpret_cast<const uint2*>(xr);
+      uint2 xv = lds64(xr);
       __half2 h[4][2];
 #pragma unroll
       for (int j = 0; j < 4; ++j) unpack_q8(wv[j], s2[j], h[j]);
@@ -160,199 +212,354 @@ __device__ __forceinline__ void compute_unit(const Unit& u, const unsigned char*
   }
 }
 
-// Stage x[k0 .. ) for `units` units into shared memory in the permuted pair order, zero beyond K.
-template <int FMT>
-__device__ __forceinline__ void stage_x(unsigned char* xs, const __half* __restrict__ x, int K,
-                                        int unit_begin, int units) {
-  using F = Fmt<FMT>;
-  constexpr int XB = x_row_bytes<FMT>();
-  const int rows = units * 4;
-  for (int lr = threadIdx.x; lr < rows; lr += kThreads) {
-    int ul = lr >> 2, i = lr & 3;
-    int k0 = ((unit_begin + ul) * 4 + i) * F::kNpu;
-    __half v[12];
+// ---- q4f32_0: f32 weights  fl32(f32(q - 7) * s), FFMA into four column accumulators ----------------
+// (q | 0x4B000000) is the f32 2^23 + q; subtracting 2^23 + 7 gives q - 7 exactly.
+__device__ __forceinline__ float nib_to_f32(uint32_t w, int t) {
+  uint32_t q = (w >> (4 * t)) & 0xFu;
+  return __uint_as_float(q | 0x4B000000u) - 8388615.0f;
+}
+__device__ __forceinline__ void compute_unit_f32(const uint4 (&w)[4], uint4 sc, uint32_t xs_unit, float (&acc)[4]) {
+  const float s[4] = {__uint_as_float(sc.x), __uint_as_float(sc.y), __uint_as_float(sc.z), __uint_as_float(sc.w)};
 #pragma unroll
-    for (int t = 0; t < 12; ++t) v[t] = __ushort_as_half(0);
-    if constexpr (F::kNpu == 8) {
-      if (k0 + 8 <= K && ((reinterpret_cast<uintptr_t>(x + k0) & 15) == 0)) {
-        uint4 q = *reinterpret_cast<const uint4*>(x + k0);
-        *reinterpret_cast<uint4*>(v) = q;
-      } else {
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t wv[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+    uint4 xa = lds128(xs_unit + i * 32), xb = lds128(xs_unit + i * 32 + 16);
+    const float xv[8] = {__uint_as_float(xa.x), __uint_as_float(xa.y), __uint_as_float(xa.z), __uint_as_float(xa.w),
+                         __uint_as_float(xb.x), __uint_as_float(xb.y), __uint_as_float(xb.z), __uint_as_float(xb.w)};
 #pragma unroll
-        for (int t = 0; t < 8; ++t)
-          if (k0 + t < K) v[t] = x[k0 + t];
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        float wt = __fmul_rn(nib_to_f32(wv[j], t), s[j]);  // the reference's single rounding
+        acc[j] = fmaf(xv[t], wt, acc[j]);
       }
-    } else {
-#pragma unroll
-      for (int t = 0; t < F::kNpu; ++t)
-        if (k0 + t < K) v[t] = x[k0 + t];
     }
-    __half o[12];
-    if constexpr (FMT == B200Q_Q4F16_0) {
-      o[0] = v[0]; o[1] = v[4]; o[2] = v[1]; o[3] = v[5];
-      o[4] = v[2]; o[5] = v[6]; o[6] = v[3]; o[7] = v[7];
-    } else if constexpr (FMT == B200Q_Q3F16_0) {
-      o[0] = v[0]; o[1] = v[5]; o[2] = v[1]; o[3] = v[6];
-      o[4] = v[2]; o[5] = v[7]; o[6] = v[3]; o[7] = v[8];
-      o[8] = v[4]; o[9] = v[9]; o[10] = __ushort_as_half(0); o[11] = __ushort_as_half(0);
-    } else {
-      o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
-    }
-    unsigned char* dst = xs + ((size_t)i * units + ul) * XB;
-#pragma unroll
-    for (int t = 0; t < XB / 8; ++t)
-      reinterpret_cast<uint2*>(dst)[t] = reinterpret_cast<const uint2*>(o)[t];
   }
 }
 
-// WN warps across N (each 32 columns), WK = 8 / WN warps across K.  gridDim.x = column tiles,
-// gridDim.y = K splits (= cluster size along y when > 1).
-template <int FMT, int WN, bool CLUSTER>
-__global__ void __launch_bounds__(kThreads, 2) gemv_f16_kernel(const GemvParams p) {
+// ---- activation staging: the whole x (optionally x * x_mul) into shared memory ---------------------
+// f16 formats: word row r -> [i = r % 4][unit = r / 4][kXRowBytes] in the pair order the unpack produces.
+template <int FMT>
+__device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const void* xmul, int K, int units) {
+  using S = Stream<FMT>;
   using F = Fmt<FMT>;
-  constexpr int WK = kWarps / WN;
-  constexpr int XB = x_row_bytes<FMT>();
-  constexpr int kCols = 32 * WN;
-  extern __shared__ __align__(16) unsigned char smem[];
+  if constexpr (S::kF32) {
+    const float* x = reinterpret_cast<const float*>(xg);
+    const float* m = reinterpret_cast<const float*>(xmul);
+    float* dst = reinterpret_cast<float*>(xs);
+    const int n = units * 32;
+    for (int k = threadIdx.x; k < n; k += kConsumerThreads) {
+      float v = 0.f;
+      if (k < K) v = m ? __fmul_rn(x[k], m[k]) : x[k];
+      dst[k] = v;
+    }
+  } else {
+    const __half* x = reinterpret_cast<const __half*>(xg);
+    const __half* m = reinterpret_cast<const __half*>(xmul);
+    constexpr int XB = S::kXRowBytes;
+    const int rows = units * 4;
+    const bool vec_ok = (F::kNpu == 8) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                        (m == nullptr || (reinterpret_cast<uintptr_t>(m) & 15) == 0);
+    for (int lr = threadIdx.x; lr < rows; lr += kConsumerThreads) {
+      const int ul = lr >> 2, i = lr & 3;
+      const int k0 = lr * F::kNpu;
+      __align__(16) __half v[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) v[t] = __ushort_as_half(0);
+      if (vec_ok && k0 + 8 <= K) {
+        *reinterpret_cast<uint4*>(v) = *reinterpret_cast<const uint4*>(x + k0);
+        if (m) {
+          __align__(16) __half mv[8];
+          *reinterpret_cast<uint4*>(mv) = *reinterpret_cast<const uint4*>(m + k0);
+#pragma unroll
+          for (int t = 0; t < 8; ++t) v[t] = __hmul(v[t], mv[t]);
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < F::kNpu; ++t)
+          if (k0 + t < K) v[t] = m ? __hmul(x[k0 + t], m[k0 + t]) : x[k0 + t];
+      }
+      __align__(8) __half o[12];
+      if constexpr (FMT == B200Q_Q4F16_0) {
+        o[0] = v[0]; o[1] = v[4]; o[2] = v[1]; o[3] = v[5];
+        o[4] = v[2]; o[5] = v[6]; o[6] = v[3]; o[7] = v[7];
+      } else if constexpr (FMT == B200Q_Q3F16_0) {
+        o[0] = v[0]; o[1] = v[5]; o[2] = v[1]; o[3] = v[6];
+        o[4] = v[2]; o[5] = v[7]; o[6] = v[3]; o[7] = v[8];
+        o[8] = v[4]; o[9] = v[9]; o[10] = __ushort_as_half(0); o[11] = __ushort_as_half(0);
+      } else {
+        o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
+      }
+      unsigned char* d = xs + ((size_t)i * units + ul) * XB;
+#pragma unroll
+      for (int t = 0; t < XB / 8; ++t) reinterpret_cast<uint2*>(d)[t] = reinterpret_cast<const uint2*>(o)[t];
+    }
+  }
+}
 
-  pdl_launch_dependents();
-  const uint64_t pol = l2_evict_first_policy();
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wn = warp % WN, wk = warp / WN;
-  const int c = lane >> 2, tig = lane & 3;
-
-  // which op does this column tile belong to (ops are laid out back to back along gridDim.x)
+__device__ __forceinline__ int find_op(const StreamParams& p, int panel) {
   int oi = 0;
 #pragma unroll
   for (int t = 1; t < kMaxOps; ++t)
-    if (t < p.n_ops && (int)blockIdx.x >= p.op[t].tile_begin) oi = t;
-  const GemvOp& op = p.op[oi];
-  const int N = op.N;
-  const int col_tile0 = ((int)blockIdx.x - op.tile_begin) * kCols;
-  const int col = col_tile0 + wn * 32 + c * 4;
-  const bool col_ok = col < N;
+    if (t < p.n_ops && panel >= p.op[t].panel_begin) oi = t;
+  return oi;
+}
 
-  const int unit_begin = (int)blockIdx.y * p.units_per_cta;
-  const int unit_end = min(unit_begin + p.units_per_cta, p.n_units);
-  const int cta_units = p.units_per_cta;          // smem rows are allocated for all of them
-  const int n_iter = (unit_end - unit_begin + 3) >> 2;  // warp iterations (4 units each)
+// first block of CTA i
+__device__ __forceinline__ int cta_begin(const StreamParams& p, int i, int G) {
+  if (p.aligned) return (int)((long long)i * p.n_panels / G) * p.RB;
+  return (int)((long long)i * p.T / G);
+}
+// CTA that owns block t (non-aligned split)
+__device__ __forceinline__ int block_owner(const StreamParams& p, int t, int G) {
+  return (int)((((long long)t + 1) * G - 1) / p.T);
+}
 
-  unsigned char* xs = smem;                                     // [4][cta_units][XB]
-  float* red = reinterpret_cast<float*>(smem + (size_t)4 * cta_units * XB);  // [WK][kCols]
+template <int FMT>
+__global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_constant__ StreamParams p) {
+  using S = Stream<FMT>;
+  using F = Fmt<FMT>;
+  using scale_t = typename S::scale_t;
+  extern __shared__ __align__(128) unsigned char smem[];
 
-  float acc[2][4];
-#pragma unroll
-  for (int m = 0; m < 2; ++m)
-#pragma unroll
-    for (int r = 0; r < 4; ++r) acc[m][r] = 0.f;
+  pdl_launch_dependents();
 
-  // prefetch the first unit (constant weights: legal before the dependency wait)
-  Unit cur, nxt;
-  int it = wk;
-  {
-    int unit = unit_begin + it * 4 + tig;
-    load_unit<FMT>(cur, op.packed, op.scale, unit, p.n_rows, col, N,
-                   col_ok && it < n_iter && unit < unit_end, pol);
-  }
-  {
-    int itn = it + WK;
-    int unit = unit_begin + itn * 4 + tig;
-    load_unit<FMT>(nxt, op.packed, op.scale, unit, p.n_rows, col, N,
-                   col_ok && itn < n_iter && unit < unit_end, pol);
-  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = gridDim.x;
+  const int t0 = cta_begin(p, blockIdx.x, G), t1 = cta_begin(p, blockIdx.x + 1, G);
+  const int stages = p.stages;
 
-  pdl_wait();  // x (and ep0 / out) belong to the previous kernel until here
-  stage_x<FMT>(xs, p.x, p.K, unit_begin, cta_units);
-  __syncthreads();
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);  // full[kMaxStages], empty[kMaxStages]
+  int* flag = reinterpret_cast<int*>(smem + 240);
+  float* red = reinterpret_cast<float*>(smem + 256);  // [2][128]
+  unsigned char* xs = smem + kSmemHeader;
+  const uint32_t stage_base = smem_u32(smem + kSmemHeader + p.xs_bytes);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
 
-  const int xs_i_stride = cta_units * XB;
-  while (it < n_iter) {
-    compute_unit<FMT>(cur, xs + (size_t)(it * 4 + tig) * XB, xs_i_stride, acc);
-    cur = nxt;
-    it += WK;
-    int itn = it + WK;
-    int unit = unit_begin + itn * 4 + tig;
-    load_unit<FMT>(nxt, op.packed, op.scale, unit, p.n_rows, col, N,
-                   col_ok && itn < n_iter && unit < unit_end, pol);
-  }
-
-  // ---- reduce over the K-split warps of the CTA ------------------------------------------------
-  if (tig == 0) {
-    float4 v = make_float4(acc[0][0], acc[0][2], acc[1][0], acc[1][2]);  // columns 4c .. 4c+3
-    *reinterpret_cast<float4*>(red + wk * kCols + wn * 32 + c * 4) = v;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, kConsumerWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 
-  float sum = 0.f;
-  const int tc = threadIdx.x;  // column within the tile handled by this thread in the tail
-  if (tc < kCols) {
-#pragma unroll
-    for (int w = 0; w < WK; ++w) sum += red[w * kCols + tc];
+  if (warp == kConsumerWarps) {
+    // ================= producer: stream the CTA's blocks into the ring (weights are constants:
+    // legal before the dependency wait) =================================================================
+    const uint64_t pol = l2_evict_first_policy();
+    int s = 0;
+    uint32_t ph = 0;
+    int panel = t0 / p.RB, rb = t0 - panel * p.RB;
+    for (int t = t0; t < t1; ++t) {
+      const StreamOp& op = p.op[find_op(p, panel)];
+      const int col0 = (panel - op.panel_begin) * kPanelCols;
+      const int ncols = min(kPanelCols, op.N - col0);
+      const int row0 = rb * kBlockRows;
+      const int rows = min(kBlockRows, p.n_rows - row0);
+      const int groups = rows / F::kRowsPerGroup;
+      mbar_wait(empty0 + 8 * s, ph ^ 1);
+      if (lane == 0)
+        mbar_expect_tx(full0 + 8 * s, (uint32_t)(rows * ncols * 4 + groups * ncols * (int)sizeof(scale_t)));
+      __syncwarp();
+      const uint32_t sw = stage_base + s * S::kStageBytes;
+      if (lane < rows)
+        bulk_g2s(sw + lane * kRowPitch + (lane >> 2) * kSkew, op.packed + (size_t)(row0 + lane) * op.N + col0,
+                 ncols * 4, full0 + 8 * s, pol);
+      if (lane < groups)
+        bulk_g2s(sw + kWordStageBytes + lane * S::kScalePitch,
+                 reinterpret_cast<const scale_t*>(op.scale) + (size_t)(rb * S::kGroupsPerBlock + lane) * op.N + col0,
+                 ncols * (int)sizeof(scale_t), full0 + 8 * s, pol);
+      if (++s == stages) { s = 0; ph ^= 1; }
+      if (++rb == p.RB) { rb = 0; ++panel; }
+    }
+    return;
   }
 
-  if constexpr (CLUSTER) {
-    cg::cluster_group cluster = cg::this_cluster();
-    const unsigned nranks = cluster.num_blocks();
-    const unsigned rank = cluster.block_rank();
-    __syncthreads();
-    if (tc < kCols) red[tc] = sum;  // CTA partial at red[0 .. kCols)
-    cluster.sync();
-    if (rank == 0 && tc < kCols) {
-      for (unsigned r = 1; r < nranks; ++r) {
-        const float* remote = cluster.map_shared_rank(red, r);
-        sum += remote[tc];
+  // ================= consumers ===========================================================================
+  const int cq = warp & 3, rh = warp >> 2;  // column quarter (32 columns), row half (4 units)
+  const int c = lane >> 2, tig = lane & 3;
+  const int u = rh * 4 + tig;               // unit of the block owned by this lane
+  const int units_alloc = p.RB * kUnitsPerBlock;
+
+  pdl_wait();  // x / x_mul / ep0 / out belong to the previous kernel until here
+  stage_x<FMT>(xs, p.x, p.x_mul, p.K, units_alloc);
+  consumer_sync();
+
+  const uint32_t xs_base = smem_u32(xs);
+  const uint32_t lane_w_off = (u * 4) * kRowPitch + u * kSkew + (cq * 32 + c * 4) * 4;
+  const uint32_t lane_s_off = kWordStageBytes + (u * 4 / F::kRowsPerGroup) * S::kScalePitch +
+                              (cq * 32 + c * 4) * (int)sizeof(scale_t);
+
+  int s = 0;
+  uint32_t ph = 0;
+  int t = t0;
+  int panel = t0 / p.RB, rb = t0 - panel * p.RB;
+  while (t < t1) {
+    const int rb_begin = rb;
+    const int seg_end = min(t1, t + (p.RB - rb));
+    float acc[2][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int r = 0; r < 4; ++r) acc[m][r] = 0.f;
+
+    for (; t < seg_end; ++t, ++rb) {
+      mbar_wait(full0 + 8 * s, ph);
+      const uint32_t sw = stage_base + s * S::kStageBytes;
+      const bool unit_ok = (rb * kBlockRows + u * 4) < p.n_rows;
+      if (!p.no_compute) {
+        uint4 w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = unit_ok ? lds128(sw + lane_w_off + i * kRowPitch) : make_uint4(0, 0, 0, 0);
+        const int unit_g = rb * kUnitsPerBlock + u;
+        if constexpr (S::kF32) {
+          uint4 sc = unit_ok ? lds128(sw + lane_s_off) : make_uint4(0, 0, 0, 0);
+          compute_unit_f32(w, sc, xs_base + unit_g * 128, acc[0]);
+        } else {
+          uint2 sc = unit_ok ? lds64(sw + lane_s_off) : make_uint2(0, 0);
+          compute_unit_f16<FMT>(w, sc, xs_base + unit_g * S::kXRowBytes, units_alloc * S::kXRowBytes, acc);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      if (++s == stages) { s = 0; ph ^= 1; }
+    }
+
+    // ---- reduce the segment: quad lanes (f32 path), the two row halves, then other CTAs -------------
+    float4 v4;
+    if constexpr (S::kF32) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[0][j] += __shfl_xor_sync(0xffffffffu, acc[0][j], 1);
+        acc[0][j] += __shfl_xor_sync(0xffffffffu, acc[0][j], 2);
+      }
+      v4 = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+    } else {
+      v4 = make_float4(acc[0][0], acc[0][2], acc[1][0], acc[1][2]);  // columns 4c .. 4c+3
+    }
+    if (tig == 0) *reinterpret_cast<float4*>(red + rh * kPanelCols + cq * 32 + c * 4) = v4;
+    consumer_sync();
+
+    const StreamOp& op = p.op[find_op(p, panel)];
+    const int col0 = (panel - op.panel_begin) * kPanelCols;
+    const int tc = threadIdx.x;
+    const int n = col0 + tc;
+    float sum = 0.f;
+    if (tc < kPanelCols) sum = red[tc] + red[kPanelCols + tc];
+    bool do_epilogue = (tc < kPanelCols);
+    const bool complete = (rb_begin == 0) && (rb == p.RB);
+    if (!complete) {
+      // this panel's K range is shared with other CTAs: publish the partial, last arriver finishes
+      const int first = block_owner(p, panel * p.RB, G);
+      const int last = block_owner(p, panel * p.RB + p.RB - 1, G);
+      const int n_contrib = last - first + 1;
+      float* slot0 = p.ws_partial + (size_t)panel * p.c_max * kPanelCols;
+      if (tc < kPanelCols) {
+        slot0[(size_t)((int)blockIdx.x - first) * kPanelCols + tc] = sum;
+        __threadfence();
+      }
+      consumer_sync();
+      if (tc == 0) {
+        const unsigned old = atomicAdd(p.ws_counter + panel, 1u);
+        const int is_last = (old == (unsigned)(n_contrib - 1));
+        if (is_last) p.ws_counter[panel] = 0u;  // self-cleaning: nobody else touches it in this launch
+        *flag = is_last;
+      }
+      consumer_sync();
+      do_epilogue = do_epilogue && (*flag != 0);
+      if (do_epilogue) {
+        __threadfence();
+        sum = 0.f;
+        for (int o = 0; o < n_contrib; ++o) sum += ld_cg_f32(slot0 + (size_t)o * kPanelCols + tc);
       }
     }
-    cluster.sync();  // keep the other CTAs' shared memory alive until rank 0 has read it
-    if (rank != 0) return;
+    if (do_epilogue && n < op.N) {
+      if constexpr (S::kF32) {
+        reinterpret_cast<float*>(op.out)[n] = ep_f32(sum, op.epilogue, reinterpret_cast<const float*>(op.ep0), n);
+      } else {
+        if (op.epilogue == B200Q_EP_CAST_F32)
+          reinterpret_cast<float*>(op.out)[n] = sum;
+        else
+          reinterpret_cast<__half*>(op.out)[n] = ep_f16(sum, op.epilogue, reinterpret_cast<const __half*>(op.ep0), n);
+      }
+    }
+    consumer_sync();  // red / flag are reused by the next segment
+    if (rb == p.RB) { rb = 0; ++panel; }
   }
+}
 
-  const int n = col_tile0 + tc;
-  if (tc < kCols && n < N) {
-    if (op.epilogue == B200Q_EP_CAST_F32) {
-      reinterpret_cast<float*>(op.out)[n] = sum;
-    } else {
-      reinterpret_cast<__half*>(op.out)[n] = ep_f16(sum, op.epilogue, op.ep0, n);
+// ---- host side --------------------------------------------------------------------------------------
+thread_local int g_tune_ctas_per_sm = 0, g_tune_stages = 0, g_tune_flags = 0;
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+template <int FMT>
+int launch_stream(StreamParams& p, unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  using S = Stream<FMT>;
+  p.RB = ceil_div(p.n_rows, kBlockRows);
+  p.T = p.n_panels * p.RB;
+  p.xs_bytes = ((p.RB * kBlockRows * S::kXRowBytes) + 127) / 128 * 128;
+  const int per_sm = (g_tune_ctas_per_sm == 2) ? 2 : 1;
+  int G = sm_count() * per_sm;
+  if (G > p.T) G = p.T;
+
+  // stages: two CTAs must fit per SM (the second slot is the next launch's prefetching CTA)
+  const int budget = kSmemPerSm / 2 - 1024 - kSmemHeader - p.xs_bytes;
+  int stages = budget / S::kStageBytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (g_tune_stages > 0 && g_tune_stages < stages) stages = g_tune_stages;
+  if (stages < 2) {
+    // very long K: give the CTA the whole SM
+    stages = (kSmemPerSm - 1024 - kSmemHeader - p.xs_bytes) / S::kStageBytes;
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages < 2) return set_error(B200Q_ERR_BAD_SHAPE, "gemv: K=%d too large for the activation stage", p.K);
+  }
+  p.stages = stages;
+  const size_t smem = (size_t)kSmemHeader + p.xs_bytes + (size_t)stages * S::kStageBytes;
+
+  // split panels across CTAs only with a workspace big enough for the partial sums
+  p.aligned = 1;
+  p.c_max = 0;
+  p.ws_partial = nullptr;
+  p.ws_counter = nullptr;
+  if (workspace && p.n_panels <= kMaxPanels && G > 1) {
+    const int per_cta = p.T / G;  // >= 1
+    const int c_max = ceil_div(p.RB, per_cta) + 1;
+    const size_t need = (size_t)kCounterBytes + (size_t)p.n_panels * c_max * kPanelCols * sizeof(float);
+    if (need <= workspace_bytes) {
+      p.aligned = 0;
+      p.c_max = c_max;
+      p.ws_counter = reinterpret_cast<unsigned*>(workspace);
+      p.ws_partial = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + kCounterBytes);
     }
   }
-}
+  if (p.aligned && G > p.n_panels) G = p.n_panels;
+  p.no_compute = (g_tune_flags & 1);
 
-// ---- host side --------------------------------------------------------------------------------
-static thread_local int g_tune_wn = 0, g_tune_ksplit = 0;
-void gemv_tune(int wn, int ksplit) {
-  g_tune_wn = wn;
-  g_tune_ksplit = ksplit;
-}
-void gemv_get_tune(int* wn, int* ksplit) {
-  *wn = g_tune_wn;
-  *ksplit = g_tune_ksplit;
-}
-
-template <int FMT, int WN, bool CLUSTER>
-static int launch_cfg(const GemvParams& p, int tiles, int ksplit, size_t smem, unsigned flags,
-                      cudaStream_t stream) {
-  auto kern = gemv_f16_kernel<FMT, WN, CLUSTER>;
+  auto kern = gemv_stream_kernel<FMT>;
   static thread_local size_t smem_set = 0;  // per instantiation
-  if (smem > 48 * 1024 && smem > smem_set) {
+  if (smem > smem_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemv smem)");
     smem_set = smem;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(tiles, ksplit, 1);
+  cfg.gridDim = dim3(G, 1, 1);
   cfg.blockDim = dim3(kThreads, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attrs[2];
+  cudaLaunchAttribute attrs[1];
   int na = 0;
-  if (CLUSTER) {
-    attrs[na].id = cudaLaunchAttributeClusterDimension;
-    attrs[na].val.clusterDim.x = 1;
-    attrs[na].val.clusterDim.y = ksplit;
-    attrs[na].val.clusterDim.z = 1;
-    ++na;
-  }
   if (flags & B200Q_FLAG_PDL) {
     attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attrs[na].val.programmaticStreamSerializationAllowed = 1;
@@ -366,71 +573,42 @@ static int launch_cfg(const GemvParams& p, int tiles, int ksplit, size_t smem, u
   return B200Q_OK;
 }
 
-template <int FMT>
-static int launch_fmt(GemvParams& p, const int* Ns, unsigned flags, cudaStream_t stream) {
-  constexpr int XB = x_row_bytes<FMT>();
-  // ---- heuristic: fill >= 2 CTAs per SM, keep >= 1 iteration per warp ---------------------------
-  int total_n = 0;
-  for (int i = 0; i < p.n_ops; ++i) total_n += Ns[i];
-  int wn = g_tune_wn;
-  if (wn != 1 && wn != 2 && wn != 4 && wn != 8) wn = (total_n >= 16384) ? 2 : 1;
-  int tiles = 0;
-  for (int i = 0; i < p.n_ops; ++i) {
-    p.op[i].tile_begin = tiles;
-    tiles += ceil_div(Ns[i], 32 * wn);
-  }
-  const int wk = kWarps / wn;
-  const int iters = ceil_div(p.n_units, 4);  // warp iterations over all of K
-  int ksplit = g_tune_ksplit;
-  if (ksplit != 1 && ksplit != 2 && ksplit != 4 && ksplit != 8) {
-    ksplit = 1;
-    while (ksplit < 8 && tiles * ksplit < 2 * 148 && iters / (ksplit * 2) >= wk) ksplit *= 2;
-  }
-  while (ksplit > 1 && iters < ksplit) ksplit /= 2;
-  int units_per_cta = ceil_div(ceil_div(p.n_units, ksplit), 4) * 4;
-  while (ksplit > 1 && units_per_cta * (ksplit - 1) >= p.n_units) {  // no empty CTAs
-    ksplit /= 2;
-    units_per_cta = ceil_div(ceil_div(p.n_units, ksplit), 4) * 4;
-  }
-  p.units_per_cta = units_per_cta;
-  size_t smem = (size_t)4 * units_per_cta * XB + (size_t)wk * 32 * wn * sizeof(float);
-  if (smem > 200 * 1024) return set_error(B200Q_ERR_BAD_SHAPE, "gemv: K=%d too large for one CTA's x stage", p.K);
+}  // namespace
 
-#define B200Q_LAUNCH(WN_)                                                                        \
-  (ksplit > 1 ? launch_cfg<FMT, WN_, true>(p, tiles, ksplit, smem, flags, stream)                \
-              : launch_cfg<FMT, WN_, false>(p, tiles, ksplit, smem, flags, stream))
-  switch (wn) {
-    case 1: return B200Q_LAUNCH(1);
-    case 2: return B200Q_LAUNCH(2);
-    case 4: return B200Q_LAUNCH(4);
-    default: return B200Q_LAUNCH(8);
-  }
-#undef B200Q_LAUNCH
+void gemv_tune(int ctas_per_sm, int stages, int flags) {
+  g_tune_ctas_per_sm = ctas_per_sm;
+  g_tune_stages = stages;
+  g_tune_flags = flags;
 }
 
-int gemv_f16_launch(const b200q_gemv_op* ops, int n_ops, const void* x, int K, int fmt,
-                    unsigned flags, cudaStream_t stream) {
-  GemvParams p{};
-  int Ns[kMaxOps];
+size_t gemv_workspace_bytes() { return (size_t)kCounterBytes + (size_t)4 * 1024 * 1024; }
+
+int gemv_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K, int fmt,
+                unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  StreamParams p{};
   p.n_ops = n_ops;
-  p.x = reinterpret_cast<const __half*>(x);
+  p.x = x;
+  p.x_mul = x_mul;
   p.K = K;
   p.n_rows = n_words(fmt, K);
-  p.n_units = ceil_div(p.n_rows, 4);
+  int panels = 0;
   for (int i = 0; i < n_ops; ++i) {
     p.op[i].packed = reinterpret_cast<const uint32_t*>(ops[i].packed);
-    p.op[i].scale = reinterpret_cast<const __half*>(ops[i].scale);
-    p.op[i].ep0 = reinterpret_cast<const __half*>(ops[i].ep0);
+    p.op[i].scale = ops[i].scale;
+    p.op[i].ep0 = ops[i].ep0;
     p.op[i].out = ops[i].out;
     p.op[i].N = ops[i].N;
     p.op[i].epilogue = ops[i].epilogue;
-    Ns[i] = ops[i].N;
+    p.op[i].panel_begin = panels;
+    panels += ceil_div(ops[i].N, kPanelCols);
   }
+  p.n_panels = panels;
   switch (fmt) {
-    case B200Q_Q4F16_0: return launch_fmt<B200Q_Q4F16_0>(p, Ns, flags, stream);
-    case B200Q_Q3F16_0: return launch_fmt<B200Q_Q3F16_0>(p, Ns, flags, stream);
-    case B200Q_Q8F16_0: return launch_fmt<B200Q_Q8F16_0>(p, Ns, flags, stream);
-    default: return set_error(B200Q_ERR_UNSUPPORTED, "gemv_f16: fmt %d", fmt);
+    case B200Q_Q4F16_0: return launch_stream<B200Q_Q4F16_0>(p, flags, workspace, workspace_bytes, stream);
+    case B200Q_Q3F16_0: return launch_stream<B200Q_Q3F16_0>(p, flags, workspace, workspace_bytes, stream);
+    case B200Q_Q8F16_0: return launch_stream<B200Q_Q8F16_0>(p, flags, workspace, workspace_bytes, stream);
+    case B200Q_Q4F32_0: return launch_stream<B200Q_Q4F32_0>(p, flags, workspace, workspace_bytes, stream);
+    default: return set_error(B200Q_ERR_UNSUPPORTED, "gemv: fmt %d", fmt);
   }
 }
 

@@ -24,7 +24,7 @@ from typing import Dict, List, Optional, Tuple
 
 import torch
 
-from . import ops
+from . import _lib, ops
 from .quant_spec import SPECS, QuantSpec
 
 
@@ -125,14 +125,14 @@ class DecodeStack:
     """
 
     def __init__(self, shape, spec, device=None, tp_rank: int = 0, tp_size: int = 1, seed: int = 0xB200,
-                 layers: Optional[int] = None, process_group=None, fuse_qkv: bool = True, pdl: bool = True,
-                 use_graph: bool = True):
+                 layers: Optional[int] = None, process_group=None, fuse_qkv: bool = True, fuse_gate_up: bool = True,
+                 pdl: bool = True, use_graph: bool = True):
         self.shape = MODEL_SHAPES[shape] if isinstance(shape, str) else shape
         self.spec = SPECS[spec] if isinstance(spec, str) else spec
         self.device = torch.device(device if device is not None else "cuda")
         self.tp_rank, self.tp_size, self.pg = tp_rank, tp_size, process_group
         self.n_layers = self.shape.layers if layers is None else layers
-        self.fuse_qkv, self.pdl, self.use_graph = fuse_qkv, pdl, use_graph
+        self.fuse_qkv, self.fuse_gate_up, self.pdl, self.use_graph = fuse_qkv, fuse_gate_up, pdl, use_graph
         if tp_size > 1 and self.spec.dtype != "float16":
             raise NotImplementedError("tensor parallel decode is wired for the f16 schemes")
         self.dt = self.spec.torch_dtype
@@ -187,14 +187,22 @@ class DecodeStack:
         self.buf = []
         for _ in range(self.n_layers):
             self.buf.append({"q": e(h // tp), "k": e(h // tp), "v": e(h // tp), "x1": e(h), "g": e(i // tp),
-                             "a": e(i // tp), "x2": e(h)})
+                             "u": e(i // tp), "a": e(i // tp), "x2": e(h)})
+        # split-K scratch of the GEMV kernels: owned by this stack (one stream), zeroed once
+        self.ws = torch.zeros(int(_lib.lib().b200q_gemv_workspace_bytes()), dtype=torch.uint8, device=dev)
         self.logits_part = e(sh.vocab // tp, torch.float32)
         self.logits = self.logits_part if tp == 1 else e(sh.vocab, torch.float32)
 
     # ------------------------------------------------------------------ the launch sequence
-    def _gemv(self, w: QuantWeight, x, ep, ep0, out):
-        ops.gemv(w.packed, w.scale, x, self.spec, ep, ep0, out=out, pdl=self.pdl)
+    def _launch(self, items, x, x_mul=None):
+        """One kernel launch: items = [(weight, epilogue, ep0, out), ...] all reading x (* x_mul)."""
+        ops.gemv_multi([(w.packed, w.scale) for w, _, _, _ in items], x, self.spec,
+                       epilogues=[ep for _, ep, _, _ in items], ep0s=[e0 for _, _, e0, _ in items],
+                       outs=[o for _, _, _, o in items], pdl=self.pdl, x_mul=x_mul, ws=self.ws)
         self.launches_per_step += 1
+
+    def _gemv(self, w: QuantWeight, x, ep, ep0, out):
+        self._launch([(w, ep, ep0, out)], x)
 
     def _all_reduce(self, t):
         import torch.distributed as dist
@@ -202,34 +210,36 @@ class DecodeStack:
         dist.all_reduce(t, group=self.pg)
         self.collectives_per_step += 1
 
-    def _row_parallel(self, w, x, residual, out, ep_single):
+    def _row_parallel(self, w, x, residual, out, ep_single, x_mul=None):
         """o / down: out = residual + sum_ranks(x_r @ w_r).  Rank 0 carries the residual (or bias)
         into the sum so the reduction result is the final value."""
-        if self.tp_size == 1:
-            self._gemv(w, x, ep_single, residual, out)
-            return
-        if self.tp_rank == 0:
-            self._gemv(w, x, ep_single, residual, out)
+        if self.tp_size == 1 or self.tp_rank == 0:
+            self._launch([(w, ep_single, residual, out)], x, x_mul)
         else:
-            self._gemv(w, x, "none", None, out)
-        self._all_reduce(out)
+            self._launch([(w, "none", None, out)], x, x_mul)
+        if self.tp_size > 1:
+            self._all_reduce(out)
 
     def _run_llama(self):
         x = self.x_in
         for li in range(self.n_layers):
             w, b = self.layers[li], self.buf[li]
             if self.fuse_qkv:
-                ops.gemv_multi([(w["q"].packed, w["q"].scale), (w["k"].packed, w["k"].scale), (w["v"].packed, w["v"].scale)],
-                               x, self.spec, outs=[b["q"], b["k"], b["v"]], pdl=self.pdl)
-                self.launches_per_step += 1
+                self._launch([(w[n], "none", None, b[n]) for n in ("q", "k", "v")], x)
             else:
                 for n in ("q", "k", "v"):
                     self._gemv(w[n], x, "none", None, b[n])
             attn = b["q"]  # stand-in for the attention output (same shape, same dependency)
             self._row_parallel(w["o"], attn, x, b["x1"], "add")
-            self._gemv(w["gate"], b["x1"], "silu", None, b["g"])
-            self._gemv(w["up"], b["x1"], "multiply", b["g"], b["a"])
-            self._row_parallel(w["down"], b["a"], b["x1"], b["x2"], "add")
+            if self.fuse_gate_up:
+                # gate|up in one launch; the SwiGLU product silu(gate) * up is formed while down_proj
+                # stages its activation (bit-identical to the reference's `multiply` epilogue)
+                self._launch([(w["gate"], "silu", None, b["g"]), (w["up"], "none", None, b["u"])], b["x1"])
+                self._row_parallel(w["down"], b["g"], b["x1"], b["x2"], "add", x_mul=b["u"])
+            else:
+                self._gemv(w["gate"], b["x1"], "silu", None, b["g"])
+                self._gemv(w["up"], b["x1"], "multiply", b["g"], b["a"])
+                self._row_parallel(w["down"], b["a"], b["x1"], b["x2"], "add")
             x = b["x2"]
         return x
 
@@ -238,10 +248,7 @@ class DecodeStack:
         for li in range(self.n_layers):
             w, b, bias = self.layers[li], self.buf[li], self.biases[li]
             if self.fuse_qkv:
-                ops.gemv_multi([(w[n].packed, w[n].scale) for n in ("q", "k", "v")], x, self.spec,
-                               epilogues=["bias"] * 3, ep0s=[bias[n] for n in ("q", "k", "v")],
-                               outs=[b["q"], b["k"], b["v"]], pdl=self.pdl)
-                self.launches_per_step += 1
+                self._launch([(w[n], "bias", bias[n], b[n]) for n in ("q", "k", "v")], x)
             else:
                 for n in ("q", "k", "v"):
                     self._gemv(w[n], x, "bias", bias[n], b[n])

@@ -36,6 +36,33 @@ def _need_cuda(*ts):
             raise ValueError("b200q ops take contiguous tensors (compact row-major, as the reference's buffers)")
 
 
+_WORKSPACES: dict = {}
+
+
+def workspace(device=None) -> torch.Tensor:
+    """The GEMV split-K scratch of (device, current stream): allocated and zero-filled once, kept
+    clean by the kernels (include/b200q.h).  One per stream because concurrent launches must not
+    share it."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), _stream())
+    ws = _WORKSPACES.get(key)
+    if ws is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("allocate the b200q workspace before graph capture: call ops.workspace() or run the op once on this stream")
+        ws = torch.zeros(int(_lib.lib().b200q_gemv_workspace_bytes()), dtype=torch.uint8, device=dev)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+def _ws_args(ws):
+    """(pointer, bytes) of a workspace tensor; False = run without one."""
+    if ws is False:
+        return None, 0
+    if ws is None:
+        ws = workspace()
+    return ws.data_ptr(), ws.numel() * ws.element_size()
+
+
 def _ep_id(epilogue) -> int:
     return EPILOGUES[epilogue] if isinstance(epilogue, str) else int(epilogue)
 
@@ -60,6 +87,7 @@ def gemv(
     ep0: Optional[torch.Tensor] = None,
     out: Optional[torch.Tensor] = None,
     pdl: bool = False,
+    ws=None,
 ) -> torch.Tensor:
     """fused_decode*_matmul*: y[..., n] = sum_k x[..., k] * decode(packed, scale)[k, n] (+ epilogue).
 
@@ -82,10 +110,11 @@ def gemv(
     if ep0 is not None and (ep0.numel() != N or ep0.dtype != spec.torch_dtype):
         raise ValueError(f"ep0 must be {spec.dtype}[{N}]")
     L = _lib.lib()
+    wp, wb = _ws_args(ws)
     _lib.check(
         L.b200q_gemv(
             packed.data_ptr(), scale.data_ptr(), x.data_ptr(), _ptr(ep0), out.data_ptr(),
-            K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, _stream(),
+            K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, wp, wb, _stream(),
         )
     )
     return out
@@ -99,16 +128,21 @@ def gemv_multi(
     ep0s: Optional[Sequence[Optional[torch.Tensor]]] = None,
     outs: Optional[Sequence[torch.Tensor]] = None,
     pdl: bool = False,
+    x_mul: Optional[torch.Tensor] = None,
+    ws=None,
 ):
-    """Up to four GEMVs that share x (q|k|v, gate|up) in one launch.  weights: [(packed, scale), ...]."""
+    """Up to four GEMVs that share x (q|k|v, gate|up) in one launch.  weights: [(packed, scale), ...].
+    x_mul: the activation is x * x_mul (the SwiGLU product read by down_proj)."""
     spec = _spec(spec)
     n = len(weights)
     epilogues = list(epilogues) if epilogues is not None else ["none"] * n
     ep0s = list(ep0s) if ep0s is not None else [None] * n
     K = x.shape[-1]
-    _need_cuda(x)
+    _need_cuda(x, x_mul)
     if x.numel() != K or x.dtype != spec.torch_dtype:
         raise ValueError("x must be dtype[K]")
+    if x_mul is not None and (x_mul.numel() != K or x_mul.dtype != spec.torch_dtype):
+        raise ValueError("x_mul must be dtype[K]")
     ops = (_lib.GemvOp * n)()
     results = []
     for i, (packed, scale) in enumerate(weights):
@@ -122,12 +156,14 @@ def gemv_multi(
         ops[i] = _lib.GemvOp(packed.data_ptr(), scale.data_ptr(), _ptr(ep0s[i]), o.data_ptr(), N, ep)
         results.append(o)
     L = _lib.lib()
-    _lib.check(L.b200q_gemv_multi(ops, n, x.data_ptr(), K, spec.fmt_id, FLAG_PDL if pdl else 0, _stream()))
+    wp, wb = _ws_args(ws)
+    _lib.check(L.b200q_gemv_multi(ops, n, x.data_ptr(), _ptr(x_mul), K, spec.fmt_id, FLAG_PDL if pdl else 0, wp, wb,
+                                  _stream()))
     return results
 
 
-def gemv_tune(wn: int = 0, ksplit: int = 0) -> None:
-    _lib.lib().b200q_gemv_tune(wn, ksplit)
+def gemv_tune(ctas_per_sm: int = 0, stages: int = 0, dbg_flags: int = 0) -> None:
+    _lib.lib().b200q_gemv_tune(ctas_per_sm, stages, dbg_flags)
 
 
 def dequantize(packed, scale, K: int, spec, transpose_output: bool = False, out=None) -> torch.Tensor:

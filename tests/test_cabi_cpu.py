@@ -58,16 +58,18 @@ def test_argument_validation_codes():
     a = 0x10000  # 16-byte aligned fake device address
     st = None
     # N not a multiple of 8
-    assert L.b200q_gemv(a, a, a, None, a, 4096, 12, 0, 0, 0, st) == -1
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 12, 0, 0, 0, None, 0, st) == -1
     assert b"multiple of 8" in L.b200q_last_error()
     # unknown format / epilogue
-    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 7, 0, 0, st) == -3
-    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 42, 0, st) == -3
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 7, 0, 0, None, 0, st) == -3
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 42, 0, None, 0, st) == -3
     # epilogue that needs an operand
-    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 1, 0, st) == -5
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 1, 0, None, 0, st) == -5
     # NULL / misaligned
-    assert L.b200q_gemv(None, a, a, None, a, 4096, 4096, 0, 0, 0, st) == -5
-    assert L.b200q_gemv(a + 4, a, a, None, a, 4096, 4096, 0, 0, 0, st) == -2
+    assert L.b200q_gemv(None, a, a, None, a, 4096, 4096, 0, 0, 0, None, 0, st) == -5
+    assert L.b200q_gemv(a + 4, a, a, None, a, 4096, 4096, 0, 0, 0, None, 0, st) == -2
+    assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 0, 0, a + 8, 1 << 20, st) == -2  # workspace
+    assert L.b200q_gemv_workspace_bytes() >= 1 << 20
     assert L.b200q_dequant(a, a, a, 4096, 4100, 0, 0, st) == -1
     assert L.b200q_gemm(a, a, a, None, None, None, a, 16, 4096, 4096, 2, 0, 0, st) == -3  # f32 GEMM
     assert L.b200q_take_decode(a, a, a, a, 0, 10, 64, 0, st) == 0  # empty gather is a no-op

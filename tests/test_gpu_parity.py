@@ -232,23 +232,54 @@ def test_gemv_f32_epilogues():
 
 @pytest.mark.parametrize("name", list(qo.FORMATS))
 def test_gemv_every_launch_config_agrees(name):
-    """All (warps-across-N, cluster K-split) configurations and the PDL launch give the same result
-    up to f32 summation order."""
+    """1 or 2 persistent CTAs per SM, every ring depth, with and without the split-K workspace, with
+    and without PDL: the same result up to f32 summation order."""
     fmt = qo.FORMATS[name]
-    K, N = 4096, 1280
-    packed, scale = rand_weight(fmt, K, N, seed=31)
-    x = qo.synth_act(K, fmt, seed=32)
-    p, s, xd = dev(packed), dev(scale), dev(x)
+    p = s = xd = None
     try:
-        for wn in (1, 2, 4, 8):
-            for ks in (1, 2, 4, 8):
-                ops.gemv_tune(wn, ks)
-                for pdl in (False, True):
-                    y = host(ops.gemv(p, s, xd, name, pdl=pdl)).reshape(-1)
-                    check_gemv_tolerance(y, packed, scale, x, fmt, out_f32=(fmt.dtype == "float32"),
-                                         what=f"{name} wn={wn} ks={ks} pdl={pdl}")
+        for K, N in ((4096, 1280), (11008 if fmt.nbit != 3 else 4000, 136)):
+            packed, scale = rand_weight(fmt, K, N, seed=31)
+            x = qo.synth_act(K, fmt, seed=32)
+            p, s, xd = dev(packed), dev(scale), dev(x)
+            for per_sm in (1, 2):
+                for stages in (0, 2, 3):
+                    ops.gemv_tune(per_sm, stages)
+                    for pdl in (False, True):
+                        for ws in (None, False):
+                            y = host(ops.gemv(p, s, xd, name, pdl=pdl, ws=ws)).reshape(-1)
+                            check_gemv_tolerance(y, packed, scale, x, fmt, out_f32=(fmt.dtype == "float32"),
+                                                 what=f"{name} {K}x{N} per_sm={per_sm} stages={stages} pdl={pdl} ws={ws}")
+        torch.cuda.synchronize()
+        assert not ops.workspace().any(), "the split-K workspace must be left zeroed"
     finally:
         ops.gemv_tune(0, 0)
+
+
+def test_gemv_deterministic():
+    """Split-K partial sums are added in CTA order: repeated launches are bit-identical."""
+    name = "q4f16_0"
+    fmt = qo.FORMATS[name]
+    K, N = 11008, 4096
+    packed, scale = rand_weight(fmt, K, N, seed=33)
+    p, s, xd = dev(packed), dev(scale), dev(qo.synth_act(K, fmt, seed=34))
+    y0 = ops.gemv(p, s, xd, name).clone()
+    for _ in range(20):
+        assert torch.equal(ops.gemv(p, s, xd, name), y0)
+
+
+@pytest.mark.parametrize("name", ["q4f16_0", "q4f32_0"])
+def test_gemv_x_mul_equals_multiply_epilogue_chain(name):
+    """x * x_mul formed on the fly == feeding the separately multiplied activation, bit for bit."""
+    fmt = qo.FORMATS[name]
+    K, N = 11008, 512
+    packed, scale = rand_weight(fmt, K, N, seed=35)
+    a = qo.synth_act(K, fmt, seed=36)
+    b = qo.synth_act(K, fmt, seed=37)
+    p, s = dev(packed), dev(scale)
+    prod = (a * b).astype(fmt.np_dtype)
+    y_ref = ops.gemv(p, s, dev(prod), name)
+    (y,) = ops.gemv_multi([(p, s)], dev(a), name, x_mul=dev(b))
+    assert torch.equal(y, y_ref)
 
 
 @pytest.mark.parametrize("name", ["q4f16_0", "q8f16_0", "q4f32_0"])
@@ -336,8 +367,10 @@ def test_gemv_host_entry_point():
     xd = torch.empty(K, dtype=torch.float16, device="cuda")
     od = torch.empty(N, dtype=torch.float16, device="cuda")
     L = _lib.lib()
+    ws = ops.workspace()
     _lib.check(L.b200q_gemv_host(p.data_ptr(), s.data_ptr(), xh.data_ptr(), None, oh.data_ptr(), xd.data_ptr(),
-                                 od.data_ptr(), K, N, 0, 0, torch.cuda.current_stream().cuda_stream))
+                                 od.data_ptr(), K, N, 0, 0, ws.data_ptr(), ws.numel(),
+                                 torch.cuda.current_stream().cuda_stream))
     check_gemv_tolerance(oh.numpy(), packed, scale, x, fmt, out_f32=False, what="host entry")
 
 
