@@ -107,7 +107,7 @@ B200Q_API long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue);
  *
  * workspace: optional device scratch (b200q_gemv_workspace_bytes() bytes, 16-byte aligned) that lets
  * the kernel split a column panel's K range over several CTAs.  The caller zero-fills it ONCE
- * (cudaMemset) before its first use; every launch leaves it zeroed again.  It must not be shared
+ * (cudaMemset) before its first use; every launch leaves its counter area zeroed again.  It must not be shared
  * by launches that may run concurrently (one per stream).  NULL: whole panels are dealt to CTAs
  * (correct, slower for small N).  The callee itself never allocates (SURVEY.md 8b "Ownership"). */
 B200Q_API size_t b200q_gemv_workspace_bytes(void);

@@ -9,9 +9,11 @@
 //   * ONE persistent CTA per SM (grid = #SMs); the matrix is cut into blocks of 32 packed-word rows
 //     x 128 columns and the flattened block sequence (row blocks fastest inside a 128-column panel)
 //     is divided EVENLY over the CTAs ("stream-K"), whatever K and N are;
-//   * a producer warp streams its CTA's blocks into a multi-stage shared-memory ring with the bulk
-//     async-copy engine (cp.async.bulk ... mbarrier::complete_tx, L2 evict-first): one 512-byte row
-//     segment per copy, ~19 KB per stage, 75-95 KB in flight per SM, no registers tied up;
+//   * a producer thread streams its CTA's blocks into a multi-stage shared-memory ring with TMA
+//     (cp.async.bulk.tensor.2d ... mbarrier::complete_tx, L2 evict-first): four 32x32-word boxes
+//     (128B-swizzled, so the 128-bit reads below are bank-conflict free) + one scale box per stage,
+//     ~18 KB per stage, 75-95 KB in flight per SM, no registers tied up, out-of-range rows/columns
+//     zero-filled by the hardware;
 //   * the weights are constants, so the producer starts BEFORE griddepcontrol.wait: with
 //     programmatic dependent launch the next GEMV of the stream fills its ring (the second CTA slot
 //     of every SM) while the current one is still computing / reducing;
@@ -30,9 +32,12 @@
 //     x * x_mul (the SwiGLU product feeding down_proj) - bit-identical to the reference's separate
 //     `multiply` epilogue.
 //
-// Shared-memory layout of a stage: word row r of the block at  r * 512 + (r / 4) * 32  bytes, scale
-// row g at  g * (pitch + 32): the 32-byte skew per 4-row unit makes the 128-bit reads of a quarter
-// warp (2 column quads x 4 units) hit 8 distinct 16-byte bank groups.
+// Lane mapping inside a stage: warp (cq, rh) owns columns [32 cq, +32) x rows [16 rh, +16) of the
+// block; lane (c = lane / 4, tig = lane % 4) owns columns 4c..4c+3 of rows {2 tig, 2 tig + 1,
+// 8 + 2 tig, 9 + 2 tig} of that half: with the 128-byte swizzle (16-byte chunk index XOR row & 7)
+// the eight lanes of a quarter warp hit eight distinct bank groups.
+#include <cuda.h>
+
 #include "common.cuh"
 
 namespace b200q {
@@ -45,10 +50,9 @@ constexpr int kThreads = kConsumerThreads + 32;  // + producer warp
 constexpr int kMaxOps = 4;
 constexpr int kPanelCols = 128;
 constexpr int kBlockRows = 32;
-constexpr int kUnitsPerBlock = kBlockRows / 4;
-constexpr int kRowPitch = kPanelCols * 4;
-constexpr int kSkew = 32;
-constexpr int kWordStageBytes = kBlockRows * kRowPitch + kUnitsPerBlock * kSkew;  // 16640
+constexpr int kBoxCols = 32;                                   // one TMA box: 32 rows x 32 words, 128B rows
+constexpr int kBoxBytes = kBlockRows * kBoxCols * 4;           // 4096
+constexpr int kWordStageBytes = kBlockRows * kPanelCols * 4;   // 16384
 constexpr int kMaxStages = 12;
 constexpr int kMaxPanels = 4096;
 constexpr int kCounterBytes = kMaxPanels * 4;
@@ -61,12 +65,12 @@ struct Stream {
   using scale_t = typename F::scale_t;
   static constexpr bool kF32 = (FMT == B200Q_Q4F32_0);
   static constexpr int kGroupsPerBlock = kBlockRows / F::kRowsPerGroup;
-  static constexpr int kScalePitch = kPanelCols * (int)sizeof(scale_t) + kSkew;
+  static constexpr int kScalePitch = kPanelCols * (int)sizeof(scale_t);
   static constexpr int kScaleStageBytes = kGroupsPerBlock * kScalePitch;
-  static constexpr int kStageBytes = kWordStageBytes + kScaleStageBytes;
+  static constexpr int kStageTx = kWordStageBytes + kScaleStageBytes;       // bytes TMA delivers per stage
+  static constexpr int kStageBytes = (kStageTx + 1023) / 1024 * 1024;       // swizzled boxes need 1024B alignment
   // permuted activation bytes per packed word row
   static constexpr int kXRowBytes = kF32 ? 32 : F::kQuads * 8;
-  static_assert(kStageBytes % 128 == 0, "stage alignment");
 };
 
 struct StreamOp {
@@ -80,6 +84,8 @@ struct StreamOp {
 };
 
 struct StreamParams {
+  CUtensorMap tm_w[kMaxOps];  // packed  uint32[n_rows, N], box 32 x 32, 128B swizzle
+  CUtensorMap tm_s[kMaxOps];  // scale   dtype[n_groups, N], box kGroupsPerBlock x 128
   StreamOp op[kMaxOps];
   int n_ops;
   const void* x;
@@ -124,12 +130,16 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar,
-                                         uint64_t pol) {
+__device__ __forceinline__ void tma_2d(uint32_t dst, const CUtensorMap* tm, int c_inner, int c_outer, uint32_t bar,
+                                       uint64_t pol) {
   asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%2, %3}], [%4], %5;"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c_inner), "r"(c_outer), "r"(bar), "l"(pol)
       : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
 __device__ __forceinline__ uint4 lds128(uint32_t a) {
@@ -157,57 +167,53 @@ __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// ---- f16 formats: one unit = 4 word rows x 4 columns + the 4 column scales ------------------------
+// ---- f16 formats: one packed row = 4 words (columns 4c..4c+3) of one lane -------------------------
 // acc[m][*]: MMA m covers columns (4c + 2m) [A rows 0-7] and (4c + 2m + 1) [A rows 8-15] of the
-// lane's column quad c; the four lanes of a quad own different units (different k).
-template <int FMT>
-__device__ __forceinline__ void compute_unit_f16(const uint4 (&w)[4], uint2 sc, uint32_t xs_unit,
-                                                 uint32_t xs_i_stride, float (&acc)[2][4]) {
-  __half2 s2[4];
+// lane's column quad c; the four lanes of a quad own different rows (different k).
+__device__ __forceinline__ void split_scales(uint2 sc, __half2 (&s2)[4]) {
   s2[0] = u32_as_h2(__byte_perm(sc.x, 0, 0x1010));
   s2[1] = u32_as_h2(__byte_perm(sc.x, 0, 0x3232));
   s2[2] = u32_as_h2(__byte_perm(sc.y, 0, 0x1010));
   s2[3] = u32_as_h2(__byte_perm(sc.y, 0, 0x3232));
+}
+template <int FMT>
+__device__ __forceinline__ void compute_row_f16(uint4 w, const __half2 (&s2)[4], uint32_t xr, float (&acc)[2][4]) {
+  const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
+  if constexpr (FMT == B200Q_Q4F16_0) {
+    uint4 xv = lds128(xr);  // (x0,x4)(x1,x5)(x2,x6)(x3,x7)
+    __half2 h[4][4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const uint32_t wv[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
-    const uint32_t xr = xs_unit + i * xs_i_stride;
-    if constexpr (FMT == B200Q_Q4F16_0) {
-      uint4 xv = lds128(xr);  // (x0,x4)(x1,x5)(x2,x6)(x3,x7)
-      __half2 h[4][4];
+    for (int j = 0; j < 4; ++j) unpack_q4(wv[j], s2[j], h[j]);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) unpack_q4(wv[j], s2[j], h[j]);
+    for (int m = 0; m < 2; ++m) {
+      mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
+               h2_as_u32(h[2 * m + 1][1]), xv.x, xv.y);
+      mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
+               h2_as_u32(h[2 * m + 1][3]), xv.z, xv.w);
+    }
+  } else if constexpr (FMT == B200Q_Q3F16_0) {
+    // (x0,x5)(x1,x6) | (x2,x7)(x3,x8) | (x4,x9)(0,0); rows are 24 bytes apart: 8-byte alignment
+    uint2 x01 = lds64(xr), x23 = lds64(xr + 8), xb = lds64(xr + 16);
+    __half2 h[4][5];
 #pragma unroll
-      for (int m = 0; m < 2; ++m) {
-        mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-                 h2_as_u32(h[2 * m + 1][1]), xv.x, xv.y);
-        mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
-                 h2_as_u32(h[2 * m + 1][3]), xv.z, xv.w);
-      }
-    } else if constexpr (FMT == B200Q_Q3F16_0) {
-      // (x0,x5)(x1,x6) | (x2,x7)(x3,x8) | (x4,x9)(0,0); rows are 24 bytes apart: 8-byte alignment
-      uint2 x01 = lds64(xr), x23 = lds64(xr + 8), xb = lds64(xr + 16);
-      __half2 h[4][5];
+    for (int j = 0; j < 4; ++j) unpack_q3(wv[j], s2[j], h[j]);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) unpack_q3(wv[j], s2[j], h[j]);
+    for (int m = 0; m < 2; ++m) {
+      mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
+               h2_as_u32(h[2 * m + 1][1]), x01.x, x01.y);
+      mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
+               h2_as_u32(h[2 * m + 1][3]), x23.x, x23.y);
+      mma16816(acc[m], h2_as_u32(h[2 * m][4]), h2_as_u32(h[2 * m + 1][4]), 0u, 0u, xb.x, xb.y);
+    }
+  } else {  // Q8: (x0,x1)(x2,x3)
+    uint2 xv = lds64(xr);
+    __half2 h[4][2];
 #pragma unroll
-      for (int m = 0; m < 2; ++m) {
-        mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-                 h2_as_u32(h[2 * m + 1][1]), x01.x, x01.y);
-        mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
-                 h2_as_u32(h[2 * m + 1][3]), x23.x, x23.y);
-        mma16816(acc[m], h2_as_u32(h[2 * m][4]), h2_as_u32(h[2 * m + 1][4]), 0u, 0u, xb.x, xb.y);
-      }
-    } else {  // Q8: (x0,x1)(x2,x3)
-      uint2 xv = lds64(xr);
-      __half2 h[4][2];
+    for (int j = 0; j < 4; ++j) unpack_q8(wv[j], s2[j], h[j]);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) unpack_q8(wv[j], s2[j], h[j]);
-#pragma unroll
-      for (int m = 0; m < 2; ++m) {
-        mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-                 h2_as_u32(h[2 * m + 1][1]), xv.x, xv.y);
-      }
+    for (int m = 0; m < 2; ++m) {
+      mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
+               h2_as_u32(h[2 * m + 1][1]), xv.x, xv.y);
     }
   }
 }
@@ -218,36 +224,33 @@ __device__ __forceinline__ float nib_to_f32(uint32_t w, int t) {
   uint32_t q = (w >> (4 * t)) & 0xFu;
   return __uint_as_float(q | 0x4B000000u) - 8388615.0f;
 }
-__device__ __forceinline__ void compute_unit_f32(const uint4 (&w)[4], uint4 sc, uint32_t xs_unit, float (&acc)[4]) {
+__device__ __forceinline__ void compute_row_f32(uint4 w, uint4 sc, uint32_t xr, float (&acc)[4]) {
   const float s[4] = {__uint_as_float(sc.x), __uint_as_float(sc.y), __uint_as_float(sc.z), __uint_as_float(sc.w)};
+  const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
+  uint4 xa = lds128(xr), xb = lds128(xr + 16);
+  const float xv[8] = {__uint_as_float(xa.x), __uint_as_float(xa.y), __uint_as_float(xa.z), __uint_as_float(xa.w),
+                       __uint_as_float(xb.x), __uint_as_float(xb.y), __uint_as_float(xb.z), __uint_as_float(xb.w)};
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const uint32_t wv[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
-    uint4 xa = lds128(xs_unit + i * 32), xb = lds128(xs_unit + i * 32 + 16);
-    const float xv[8] = {__uint_as_float(xa.x), __uint_as_float(xa.y), __uint_as_float(xa.z), __uint_as_float(xa.w),
-                         __uint_as_float(xb.x), __uint_as_float(xb.y), __uint_as_float(xb.z), __uint_as_float(xb.w)};
+  for (int j = 0; j < 4; ++j) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        float wt = __fmul_rn(nib_to_f32(wv[j], t), s[j]);  // the reference's single rounding
-        acc[j] = fmaf(xv[t], wt, acc[j]);
-      }
+    for (int t = 0; t < 8; ++t) {
+      float wt = __fmul_rn(nib_to_f32(wv[j], t), s[j]);  // the reference's single rounding
+      acc[j] = fmaf(xv[t], wt, acc[j]);
     }
   }
 }
 
 // ---- activation staging: the whole x (optionally x * x_mul) into shared memory ---------------------
-// f16 formats: word row r -> [i = r % 4][unit = r / 4][kXRowBytes] in the pair order the unpack produces.
+// f16 formats: word row r -> xs[r][kXRowBytes] in the pair order the unpack produces.
 template <int FMT>
-__device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const void* xmul, int K, int units) {
+__device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const void* xmul, int K, int rows) {
   using S = Stream<FMT>;
   using F = Fmt<FMT>;
   if constexpr (S::kF32) {
     const float* x = reinterpret_cast<const float*>(xg);
     const float* m = reinterpret_cast<const float*>(xmul);
     float* dst = reinterpret_cast<float*>(xs);
-    const int n = units * 32;
+    const int n = rows * 8;
     for (int k = threadIdx.x; k < n; k += kConsumerThreads) {
       float v = 0.f;
       if (k < K) v = m ? __fmul_rn(x[k], m[k]) : x[k];
@@ -257,11 +260,9 @@ __device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const
     const __half* x = reinterpret_cast<const __half*>(xg);
     const __half* m = reinterpret_cast<const __half*>(xmul);
     constexpr int XB = S::kXRowBytes;
-    const int rows = units * 4;
     const bool vec_ok = (F::kNpu == 8) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
                         (m == nullptr || (reinterpret_cast<uintptr_t>(m) & 15) == 0);
     for (int lr = threadIdx.x; lr < rows; lr += kConsumerThreads) {
-      const int ul = lr >> 2, i = lr & 3;
       const int k0 = lr * F::kNpu;
       __align__(16) __half v[12];
 #pragma unroll
@@ -290,7 +291,7 @@ __device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const
       } else {
         o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
       }
-      unsigned char* d = xs + ((size_t)i * units + ul) * XB;
+      unsigned char* d = xs + (size_t)lr * XB;
 #pragma unroll
       for (int t = 0; t < XB / 8; ++t) reinterpret_cast<uint2*>(d)[t] = reinterpret_cast<const uint2*>(o)[t];
     }
@@ -333,7 +334,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
   int* flag = reinterpret_cast<int*>(smem + 240);
   float* red = reinterpret_cast<float*>(smem + 256);  // [2][128]
   unsigned char* xs = smem + kSmemHeader;
-  const uint32_t stage_base = smem_u32(smem + kSmemHeader + p.xs_bytes);
+  const uint32_t stage_base = (smem_u32(smem + kSmemHeader + p.xs_bytes) + 1023u) & ~1023u;
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
 
   if (threadIdx.x == 0) {
@@ -348,49 +349,51 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
   if (warp == kConsumerWarps) {
     // ================= producer: stream the CTA's blocks into the ring (weights are constants:
     // legal before the dependency wait) =================================================================
-    const uint64_t pol = l2_evict_first_policy();
-    int s = 0;
-    uint32_t ph = 0;
-    int panel = t0 / p.RB, rb = t0 - panel * p.RB;
-    for (int t = t0; t < t1; ++t) {
-      const StreamOp& op = p.op[find_op(p, panel)];
-      const int col0 = (panel - op.panel_begin) * kPanelCols;
-      const int ncols = min(kPanelCols, op.N - col0);
-      const int row0 = rb * kBlockRows;
-      const int rows = min(kBlockRows, p.n_rows - row0);
-      const int groups = rows / F::kRowsPerGroup;
-      mbar_wait(empty0 + 8 * s, ph ^ 1);
-      if (lane == 0)
-        mbar_expect_tx(full0 + 8 * s, (uint32_t)(rows * ncols * 4 + groups * ncols * (int)sizeof(scale_t)));
-      __syncwarp();
-      const uint32_t sw = stage_base + s * S::kStageBytes;
-      if (lane < rows)
-        bulk_g2s(sw + lane * kRowPitch + (lane >> 2) * kSkew, op.packed + (size_t)(row0 + lane) * op.N + col0,
-                 ncols * 4, full0 + 8 * s, pol);
-      if (lane < groups)
-        bulk_g2s(sw + kWordStageBytes + lane * S::kScalePitch,
-                 reinterpret_cast<const scale_t*>(op.scale) + (size_t)(rb * S::kGroupsPerBlock + lane) * op.N + col0,
-                 ncols * (int)sizeof(scale_t), full0 + 8 * s, pol);
-      if (++s == stages) { s = 0; ph ^= 1; }
-      if (++rb == p.RB) { rb = 0; ++panel; }
+    if (lane == 0) {
+      const uint64_t pol = l2_evict_first_policy();
+      for (int i = 0; i < p.n_ops; ++i) {
+        prefetch_tmap(&p.tm_w[i]);
+        prefetch_tmap(&p.tm_s[i]);
+      }
+      int s = 0;
+      uint32_t ph = 0;
+      int panel = t0 / p.RB, rb = t0 - panel * p.RB;
+      for (int t = t0; t < t1; ++t) {
+        const int oi = find_op(p, panel);
+        const int col0 = (panel - p.op[oi].panel_begin) * kPanelCols;
+        const uint32_t bar = full0 + 8 * s;
+        mbar_wait(empty0 + 8 * s, ph ^ 1);
+        mbar_expect_tx(bar, (uint32_t)S::kStageTx);
+        const uint32_t sw = stage_base + s * S::kStageBytes;
+#pragma unroll
+        for (int q = 0; q < kPanelCols / kBoxCols; ++q)
+          tma_2d(sw + q * kBoxBytes, &p.tm_w[oi], col0 + q * kBoxCols, rb * kBlockRows, bar, pol);
+        tma_2d(sw + kWordStageBytes, &p.tm_s[oi], col0, rb * S::kGroupsPerBlock, bar, pol);
+        if (++s == stages) { s = 0; ph ^= 1; }
+        if (++rb == p.RB) { rb = 0; ++panel; }
+      }
     }
     return;
   }
 
   // ================= consumers ===========================================================================
-  const int cq = warp & 3, rh = warp >> 2;  // column quarter (32 columns), row half (4 units)
+  const int cq = warp & 3, rh = warp >> 2;  // column quarter (one 32-column box), row half (16 rows)
   const int c = lane >> 2, tig = lane & 3;
-  const int u = rh * 4 + tig;               // unit of the block owned by this lane
-  const int units_alloc = p.RB * kUnitsPerBlock;
+  const int rows_alloc = p.RB * kBlockRows;
 
   pdl_wait();  // x / x_mul / ep0 / out belong to the previous kernel until here
-  stage_x<FMT>(xs, p.x, p.x_mul, p.K, units_alloc);
+  stage_x<FMT>(xs, p.x, p.x_mul, p.K, rows_alloc);
   consumer_sync();
 
-  const uint32_t xs_base = smem_u32(xs);
-  const uint32_t lane_w_off = (u * 4) * kRowPitch + u * kSkew + (cq * 32 + c * 4) * 4;
-  const uint32_t lane_s_off = kWordStageBytes + (u * 4 / F::kRowsPerGroup) * S::kScalePitch +
-                              (cq * 32 + c * 4) * (int)sizeof(scale_t);
+  // lane rows of the 16-row half: 2 tig + j + 8 m  (j, m in {0,1}); swizzled chunk = c ^ (row & 7)
+  const uint32_t xs_base = smem_u32(xs) + (rh * 16 + 2 * tig) * S::kXRowBytes;
+  const uint32_t w_off0 = cq * kBoxBytes + (rh * 16 + 2 * tig) * 128 + ((c ^ (2 * tig)) << 4);
+  const uint32_t w_off1 = cq * kBoxBytes + (rh * 16 + 2 * tig + 1) * 128 + ((c ^ (2 * tig + 1)) << 4);
+  // scale group of rows (16 rh + 8 m + 2 tig): rows-per-group 4 -> 4 rh + 2 m + tig / 2; 8 -> 2 rh + m
+  const int g0 = (rh * 16 + 2 * tig) / F::kRowsPerGroup, g1 = (rh * 16 + 8 + 2 * tig) / F::kRowsPerGroup;
+  const uint32_t s_col = (cq * 32 + c * 4) * (int)sizeof(scale_t);
+  const uint32_t s_off0 = kWordStageBytes + g0 * S::kScalePitch + s_col;
+  const uint32_t s_off1 = kWordStageBytes + g1 * S::kScalePitch + s_col;
 
   int s = 0;
   uint32_t ph = 0;
@@ -408,18 +411,24 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
     for (; t < seg_end; ++t, ++rb) {
       mbar_wait(full0 + 8 * s, ph);
       const uint32_t sw = stage_base + s * S::kStageBytes;
-      const bool unit_ok = (rb * kBlockRows + u * 4) < p.n_rows;
       if (!p.no_compute) {
-        uint4 w[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) w[i] = unit_ok ? lds128(sw + lane_w_off + i * kRowPitch) : make_uint4(0, 0, 0, 0);
-        const int unit_g = rb * kUnitsPerBlock + u;
+        const uint4 w00 = lds128(sw + w_off0), w01 = lds128(sw + w_off1);
+        const uint4 w10 = lds128(sw + w_off0 + 8 * 128), w11 = lds128(sw + w_off1 + 8 * 128);
+        const uint32_t xr = xs_base + rb * kBlockRows * S::kXRowBytes;
         if constexpr (S::kF32) {
-          uint4 sc = unit_ok ? lds128(sw + lane_s_off) : make_uint4(0, 0, 0, 0);
-          compute_unit_f32(w, sc, xs_base + unit_g * 128, acc[0]);
+          const uint4 sc0 = lds128(sw + s_off0), sc1 = lds128(sw + s_off1);
+          compute_row_f32(w00, sc0, xr, acc[0]);
+          compute_row_f32(w01, sc0, xr + S::kXRowBytes, acc[0]);
+          compute_row_f32(w10, sc1, xr + 8 * S::kXRowBytes, acc[0]);
+          compute_row_f32(w11, sc1, xr + 9 * S::kXRowBytes, acc[0]);
         } else {
-          uint2 sc = unit_ok ? lds64(sw + lane_s_off) : make_uint2(0, 0);
-          compute_unit_f16<FMT>(w, sc, xs_base + unit_g * S::kXRowBytes, units_alloc * S::kXRowBytes, acc);
+          __half2 s2[4];
+          split_scales(lds64(sw + s_off0), s2);
+          compute_row_f16<FMT>(w00, s2, xr, acc);
+          compute_row_f16<FMT>(w01, s2, xr + S::kXRowBytes, acc);
+          split_scales(lds64(sw + s_off1), s2);
+          compute_row_f16<FMT>(w10, s2, xr + 8 * S::kXRowBytes, acc);
+          compute_row_f16<FMT>(w11, s2, xr + 9 * S::kXRowBytes, acc);
         }
       }
       __syncwarp();
@@ -503,29 +512,74 @@ int sm_count() {
   return n;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency:
+// the library must load on a machine without a driver for the CPU-side checks).
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+    tried = true;
+  }
+  return fn;
+}
+
+// 2-D row-major tensor [outer, inner] of `elem_bytes` elements, box [box_outer, box_inner].
+int make_tmap(CUtensorMap* tm, CUtensorMapDataType dt, int elem_bytes, const void* ptr, int inner, int outer,
+              int box_inner, int box_outer, CUtensorMapSwizzle sw) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return set_error(B200Q_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)inner * elem_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(B200Q_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for [%d, %d]", (int)r, outer, inner);
+  return B200Q_OK;
+}
+
 template <int FMT>
 int launch_stream(StreamParams& p, unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   using S = Stream<FMT>;
+  using F = Fmt<FMT>;
   p.RB = ceil_div(p.n_rows, kBlockRows);
   p.T = p.n_panels * p.RB;
   p.xs_bytes = ((p.RB * kBlockRows * S::kXRowBytes) + 127) / 128 * 128;
+  const int n_grp = p.n_rows / F::kRowsPerGroup;
+  for (int i = 0; i < p.n_ops; ++i) {
+    if (int e = make_tmap(&p.tm_w[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, p.op[i].packed, p.op[i].N, p.n_rows, kBoxCols,
+                          kBlockRows, CU_TENSOR_MAP_SWIZZLE_128B))
+      return e;
+    if (int e = make_tmap(&p.tm_s[i], S::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                          (int)sizeof(typename S::scale_t), p.op[i].scale, p.op[i].N, n_grp, kPanelCols,
+                          S::kGroupsPerBlock, CU_TENSOR_MAP_SWIZZLE_NONE))
+      return e;
+  }
   const int per_sm = (g_tune_ctas_per_sm == 2) ? 2 : 1;
   int G = sm_count() * per_sm;
   if (G > p.T) G = p.T;
 
   // stages: two CTAs must fit per SM (the second slot is the next launch's prefetching CTA)
-  const int budget = kSmemPerSm / 2 - 1024 - kSmemHeader - p.xs_bytes;
+  const int budget = kSmemPerSm / 2 - 1024 - kSmemHeader - p.xs_bytes - 1024;
   int stages = budget / S::kStageBytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (g_tune_stages > 0 && g_tune_stages < stages) stages = g_tune_stages;
   if (stages < 2) {
     // very long K: give the CTA the whole SM
-    stages = (kSmemPerSm - 1024 - kSmemHeader - p.xs_bytes) / S::kStageBytes;
+    stages = (kSmemPerSm - 1024 - kSmemHeader - p.xs_bytes - 1024) / S::kStageBytes;
     if (stages > kMaxStages) stages = kMaxStages;
     if (stages < 2) return set_error(B200Q_ERR_BAD_SHAPE, "gemv: K=%d too large for the activation stage", p.K);
   }
   p.stages = stages;
-  const size_t smem = (size_t)kSmemHeader + p.xs_bytes + (size_t)stages * S::kStageBytes;
+  const size_t smem = (size_t)kSmemHeader + p.xs_bytes + 1024 + (size_t)stages * S::kStageBytes;
 
   // split panels across CTAs only with a workspace big enough for the partial sums
   p.aligned = 1;

@@ -250,7 +250,7 @@ def test_gemv_every_launch_config_agrees(name):
                             check_gemv_tolerance(y, packed, scale, x, fmt, out_f32=(fmt.dtype == "float32"),
                                                  what=f"{name} {K}x{N} per_sm={per_sm} stages={stages} pdl={pdl} ws={ws}")
         torch.cuda.synchronize()
-        assert not ops.workspace().any(), "the split-K workspace must be left zeroed"
+        assert not ops.workspace()[:16384].any(), "the split-K counters must be left zeroed"
     finally:
         ops.gemv_tune(0, 0)
 
