@@ -1,12 +1,501 @@
-// placeholder until the tcgen05 GEMM lands (next commit): fail loudly, never fall back.
+// Prefill GEMM on the 5th-generation tensor cores (tcgen05 / TMEM), sm_100a.
+//
+//   Y[m, n] = sum_k X[m, k] * w[k, n]  (+ epilogue)
+//
+// Replaces three reference operators at once:
+//   decode* + NT_matmul*           (mlc_llm/dispatch/llama/main.py:3984-4232 + 3884-3981; the reference
+//                                   re-materialises the whole f16 weight in HBM on every call and then
+//                                   runs a SIMT f16-accumulating GEMM on it)
+//   fused_decode*_NT_matmul*       (dispatch_tir_operator_adreno.py:414-1021: dequant in registers, SIMT)
+//   NT_matmul* on a dense weight   (transform/transpose_matmul.py:34-101)   -> b200q_nt_matmul
+//
+// Design (one persistent CTA per SM, 128 x 256 output tiles, m fastest so CTAs that run together
+// share one column panel of weights in L2):
+//   warp 0      TMA producer: X tiles [128 rows x 64 k] f16, K-major, 128-byte swizzle (and, for the
+//               dense-weight variant, T tiles [256 rows x 64 k] the same way)
+//   warp 1      allocates TMEM (2 accumulators x 256 columns = all 512) and issues tcgen05.mma
+//               (M=128, N=256, K=16 per instruction; one elected thread)
+//   warps 2-5   epilogue: tcgen05.ld the f32 accumulator (each warp its 32-lane quarter), round to
+//               f16, apply the reference's epilogue op for op, 16-byte global stores; runs on tile i
+//               while the MMA warp already accumulates tile i+1 in the other TMEM half
+//   warps 6-13  dequantizers: read packed words + scales from global (L2-resident: a panel is
+//               shared by all m tiles), unpack to the bit-exact f16 weight half((q - maxint) * s)
+//               with the same magic-number arithmetic as the GEMV, and store them into shared memory
+//               DIRECTLY in the tcgen05 canonical MN-major 128B-swizzled layout (the packed layout
+//               has N contiguous, so eight neighbouring columns of one k are one 16-byte chunk:
+//               no transpose, conflict-free 16-byte stores)
+// The A ring (64-k stages) and the B ring (64-k stages; 80-k for int3 whose groups are 40 wide) are
+// independent: the MMA thread walks 16-k steps and waits / releases each ring at its own stage
+// boundaries, so the int3 word geometry never has to line up with the 128-byte swizzle atom of X.
+#include <cuda.h>
+
 #include "common.cuh"
+#include "ptx.cuh"
+
 namespace b200q {
-int gemm_launch(const void*, const void*, const void*, const void*, const void*, const void*, void*, int, int,
-                int, int, int, unsigned, cudaStream_t) {
-  return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: not built yet");
+namespace {
+
+using namespace ptx;
+
+constexpr int kBM = 128;                 // tile rows (UMMA M)
+constexpr int kBN = 256;                 // tile columns (UMMA N)
+constexpr int kAK = 64;                  // k per A stage (one 128-byte swizzle row of f16)
+constexpr int kAStageBytes = kBM * kAK * 2;  // 16 KB
+constexpr int kAStages = 4;
+constexpr int kNAtoms = kBN / 64;        // MN-major swizzle atoms along N per B stage
+constexpr int kKAtomBytes = kNAtoms * 1024;  // one 8-k slab of a B stage: [n atom][8 k rows][128 B]
+constexpr int kDqWarps = 8;
+constexpr int kEpWarps = 4;
+constexpr int kFirstEpWarp = 2;
+constexpr int kFirstDqWarp = kFirstEpWarp + kEpWarps;
+constexpr int kGemmThreads = (kFirstDqWarp + kDqWarps) * 32;  // 448
+constexpr int kTmemCols = 512;
+constexpr int kDense = -1;               // B operand mode: dense f16 T[N, K] through TMA
+
+template <int FMT>
+struct BCfg {  // quantized B: stage geometry per format
+  using F = Fmt<FMT>;
+  static constexpr int kBK = (FMT == B200Q_Q3F16_0) ? 80 : 64;   // k per B stage (whole groups, multiple of 16)
+  static constexpr int kRows = kBK / F::kNpu;                    // packed word rows per stage: 8 / 8 / 16
+  static constexpr int kItems = kRows / kDqWarps;                // word rows per dequant warp per stage
+  static constexpr int kStages = (FMT == B200Q_Q3F16_0) ? 3 : 4;
+  static constexpr int kStageBytes = kBN * kBK * 2;              // 32 KB (40 KB int3)
+  static constexpr int kKSteps = kBK / 16;
+};
+template <>
+struct BCfg<kDense> {
+  static constexpr int kBK = 64, kStages = 4, kStageBytes = kBN * kAK * 2, kKSteps = 4;
+};
+
+struct GemmParams {
+  CUtensorMap tm_a;  // X f16 [M, K], box 128 x 64, 128B swizzle
+  CUtensorMap tm_b;  // dense mode: T f16 [N, K], box 256 x 64, 128B swizzle
+  const uint32_t* packed;
+  const __half* scale;
+  const __half* ep0;
+  const __half* ep1;
+  const __half* ep2;
+  void* Y;
+  int M, K, N;
+  int n_rows;    // packed word rows
+  int epilogue;
+  int tiles_m, tiles_n;
+};
+
+// ---- dequantize one 8-column chunk of one packed word row into the B stage ---------------------------
+// w[8]: the words of columns n0..n0+7 of word row r; s[4]: their scales as half2 pairs (n, n+1).
+// Writes kNpu k-rows; k row `kl` (stage-local) of chunk `chunk` (8 columns) lives at
+//   (kl / 8) * kKAtomBytes + (chunk / 8) * 1024 + (kl % 8) * 128 + ((chunk % 8) ^ (kl % 8)) * 16
+__device__ __forceinline__ uint32_t b_chunk_addr(uint32_t stage, int kl, int chunk) {
+  return stage + (kl >> 3) * kKAtomBytes + (chunk >> 3) * 1024 + (kl & 7) * 128 + ((((chunk & 7) ^ (kl & 7))) << 4);
 }
-int nt_matmul_launch(const void*, const void*, const void*, const void*, const void*, void*, int, int, int, int,
-                     cudaStream_t) {
-  return set_error(B200Q_ERR_UNSUPPORTED, "b200q_nt_matmul: not built yet");
+__device__ __forceinline__ void sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
+
+template <int FMT>
+__device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint32_t (&s)[4], uint32_t stage, int kl0,
+                                              int chunk) {
+  const uint32_t kMagic = 0x64006400u;
+  if constexpr (FMT == B200Q_Q4F16_0) {
+    const __half2 kSubLo = u32_as_h2(0xE407E407u);  // -(1024 + 7)
+    const __half2 kMul16 = u32_as_h2(0x2C002C00u);  // 1/16
+    const __half2 kSubHi = u32_as_h2(0xD470D470u);  // -(64 + 7)
+    uint32_t o[8][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2 s2 = u32_as_h2(s[j]);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {  // nibbles 0-3 / 4-7 of columns (2j, 2j+1)
+        const uint32_t p = __byte_perm(w[2 * j], w[2 * j + 1], h ? 0x7632 : 0x5410);
+        const uint32_t p8 = p >> 8;
+        o[4 * h + 0][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(lop3_and_or(p, 0x000F000Fu, kMagic)), kSubLo), s2));
+        o[4 * h + 1][j] = h2_as_u32(__hmul2(__hfma2(u32_as_h2(lop3_and_or(p, 0x00F000F0u, kMagic)), kMul16, kSubHi), s2));
+        o[4 * h + 2][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(lop3_and_or(p8, 0x000F000Fu, kMagic)), kSubLo), s2));
+        o[4 * h + 3][j] = h2_as_u32(__hmul2(__hfma2(u32_as_h2(lop3_and_or(p8, 0x00F000F0u, kMagic)), kMul16, kSubHi), s2));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sts128(b_chunk_addr(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+  } else if constexpr (FMT == B200Q_Q3F16_0) {
+    const __half2 kSub1 = u32_as_h2(0xE403E403u);   // -(1024 + 3)
+    const __half2 kMul8 = u32_as_h2(0x30003000u);   // 1/8
+    const __half2 kSub8 = u32_as_h2(0xD818D818u);   // -(128 + 3)
+    const __half2 kMul64 = u32_as_h2(0x24002400u);  // 1/64
+    const __half2 kSub64 = u32_as_h2(0xCCC0CCC0u);  // -(16 + 3)
+    uint32_t o[10][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2 s2 = u32_as_h2(s[j]);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {  // values 0-4 / 5-9 of columns (2j, 2j+1)
+        const uint32_t p = h ? __byte_perm(w[2 * j] >> 15, w[2 * j + 1] >> 15, 0x5410)
+                             : __byte_perm(w[2 * j], w[2 * j + 1], 0x5410);
+        const uint32_t q = p >> 9;
+        o[5 * h + 0][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(lop3_and_or(p, 0x00070007u, kMagic)), kSub1), s2));
+        o[5 * h + 1][j] = h2_as_u32(__hmul2(__hfma2(u32_as_h2(lop3_and_or(p, 0x00380038u, kMagic)), kMul8, kSub8), s2));
+        o[5 * h + 2][j] = h2_as_u32(__hmul2(__hfma2(u32_as_h2(lop3_and_or(p, 0x01C001C0u, kMagic)), kMul64, kSub64), s2));
+        o[5 * h + 3][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(lop3_and_or(q, 0x00070007u, kMagic)), kSub1), s2));
+        o[5 * h + 4][j] = h2_as_u32(__hmul2(__hfma2(u32_as_h2(lop3_and_or(q, 0x00380038u, kMagic)), kMul8, kSub8), s2));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 10; ++i) sts128(b_chunk_addr(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+  } else {  // Q8: 4 values per word
+    const __half2 kSub = u32_as_h2(0xE47FE47Fu);  // -(1024 + 127)
+    uint32_t o[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2 s2 = u32_as_h2(s[j]);
+      // bytes (b_i of column 2j, b_i of column 2j+1) -> low bytes of the two halves, 0x64 above them
+      const uint32_t p02 = __byte_perm(w[2 * j], w[2 * j + 1], 0x6240);  // b0 b0' at bytes 0,1 ; b2 b2' at 2,3
+      const uint32_t p13 = __byte_perm(w[2 * j], w[2 * j + 1], 0x7351);
+      const uint32_t v0 = __byte_perm(p02, 0x64646464u, 0x4140);  // b0, 0x64, b0', 0x64
+      const uint32_t v2 = __byte_perm(p02, 0x64646464u, 0x4342);
+      const uint32_t v1 = __byte_perm(p13, 0x64646464u, 0x4140);
+      const uint32_t v3 = __byte_perm(p13, 0x64646464u, 0x4342);
+      o[0][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(v0), kSub), s2));
+      o[1][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(v1), kSub), s2));
+      o[2][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(v2), kSub), s2));
+      o[3][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(v3), kSub), s2));
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) sts128(b_chunk_addr(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+  }
+}
+
+// ---- epilogue: 32 consecutive columns of one output row ------------------------------------------------
+// y = f16(acc) first (the reference's matmul result is an f16 tensor), then every epilogue op in f16,
+// op for op (ep_f16 in common.cuh).  bias operands are [N]; residual / multiply operands are [M, N].
+__device__ __forceinline__ void epilogue_row(const GemmParams& p, const uint32_t (&acc)[32], int m, int n0) {
+  const int ep = p.epilogue;
+  const size_t row = (size_t)m * p.N;
+  if (ep == B200Q_EP_CAST_F32) {
+    float* y = reinterpret_cast<float*>(p.Y) + row + n0;
+#pragma unroll
+    for (int c = 0; c < 32; c += 4) {
+      if (n0 + c < p.N)
+        *reinterpret_cast<float4*>(y + c) = make_float4(__uint_as_float(acc[c]), __uint_as_float(acc[c + 1]),
+                                                        __uint_as_float(acc[c + 2]), __uint_as_float(acc[c + 3]));
+    }
+    return;
+  }
+  __half* y = reinterpret_cast<__half*>(p.Y) + row + n0;
+  const bool bias_like = (ep == B200Q_EP_BIAS || ep == B200Q_EP_BIAS_GELU || ep == B200Q_EP_BIAS_ADD2);
+  const __half* e0 = p.ep0 ? (bias_like ? p.ep0 + n0 : p.ep0 + row + n0) : nullptr;
+#pragma unroll
+  for (int c = 0; c < 32; c += 8) {
+    if (n0 + c >= p.N) break;  // N % 8 == 0: a chunk of 8 is all in or all out
+    __align__(16) __half o[8];
+    __align__(16) __half a0[8], a1[8], a2[8];
+    if (e0) *reinterpret_cast<uint4*>(a0) = *reinterpret_cast<const uint4*>(e0 + c);
+    if (ep == B200Q_EP_BIAS_ADD2) {
+      *reinterpret_cast<uint4*>(a1) = *reinterpret_cast<const uint4*>(p.ep1 + row + n0 + c);
+      *reinterpret_cast<uint4*>(a2) = *reinterpret_cast<const uint4*>(p.ep2 + row + n0 + c);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float v = __uint_as_float(acc[c + i]);
+      if (ep == B200Q_EP_BIAS_ADD2) {
+        o[i] = __hadd(__hadd(__hadd(__float2half_rn(v), a0[i]), a1[i]), a2[i]);
+      } else {
+        o[i] = ep_f16(v, ep, a0, i);
+      }
+    }
+    *reinterpret_cast<uint4*>(y + c) = *reinterpret_cast<const uint4*>(o);
+  }
+}
+
+// smem map (dynamic, 1024-aligned): [A ring][B ring][barriers]
+template <int MODE>
+struct Smem {
+  using B = BCfg<MODE>;
+  static constexpr int kAOff = 0;
+  static constexpr int kBOff = kAStages * kAStageBytes;
+  static constexpr int kBarOff = kBOff + B::kStages * B::kStageBytes;
+  // barriers: a_full, a_empty [kAStages]; b_full, b_empty [B::kStages]; tmem_full, tmem_empty [2]; tmem ptr
+  static constexpr int kNumBars = 2 * kAStages + 2 * B::kStages + 4;
+  static constexpr int kBytes = kBarOff + kNumBars * 8 + 16;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams p) {
+  using B = BCfg<MODE>;
+  using S = Smem<MODE>;
+  constexpr bool kDenseB = (MODE == kDense);
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  // the runtime only guarantees 16-byte alignment of dynamic smem: align by hand (host adds 1024 slack)
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t a_ring = base + S::kAOff, b_ring = base + S::kBOff;
+  const uint32_t bars = base + S::kBarOff;
+  const uint32_t a_full = bars, a_empty = a_full + 8 * kAStages;
+  const uint32_t b_full = a_empty + 8 * kAStages, b_empty = b_full + 8 * B::kStages;
+  const uint32_t t_full = b_empty + 8 * B::kStages, t_empty = t_full + 16;
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(base_ptr + S::kBarOff + S::kNumBars * 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = p.tiles_m * p.tiles_n;
+  const int n_ksteps = (p.K + 15) >> 4;
+  const int n_a_stages = (n_ksteps + 3) >> 2;
+  const int n_b_stages = (n_ksteps + B::kKSteps - 1) / B::kKSteps;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tm_a);
+    if constexpr (kDenseB) prefetch_tmap(&p.tm_b);
+    for (int s = 0; s < kAStages; ++s) {
+      mbar_init(a_full + 8 * s, 1);
+      mbar_init(a_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < B::kStages; ++s) {
+      mbar_init(b_full + 8 * s, kDenseB ? 1 : kDqWarps);
+      mbar_init(b_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(t_full + 8 * s, 1);
+      mbar_init(t_empty + 8 * s, kEpWarps);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_ptr_smem)), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ================= TMA producer =====================================================================
+    if (lane == 0) {
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int m0 = (tile % p.tiles_m) * kBM, n0 = (tile / p.tiles_m) * kBN;
+        for (int i = 0; i < n_a_stages; ++i) {
+          mbar_wait(a_empty + 8 * sa, pa ^ 1);
+          mbar_expect_tx(a_full + 8 * sa, kAStageBytes);
+          tma_load_2d(a_ring + sa * kAStageBytes, &p.tm_a, i * kAK, m0, a_full + 8 * sa);
+          if (++sa == kAStages) { sa = 0; pa ^= 1; }
+          if constexpr (kDenseB) {  // same stage cadence for the dense B operand
+            mbar_wait(b_empty + 8 * sb, pb ^ 1);
+            mbar_expect_tx(b_full + 8 * sb, B::kStageBytes);
+            tma_load_2d(b_ring + sb * B::kStageBytes, &p.tm_b, i * kAK, n0, b_full + 8 * sb);
+            if (++sb == B::kStages) { sb = 0; pb ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer ========================================================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(kBM, kBN, 0, kDenseB ? 0 : 1);
+      int sa = 0, sb = 0, it = 0;
+      uint32_t pa = 0, pb = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + acc * kBN;
+        int ka = 0, kb = 0;  // k-step inside the current A / B stage
+        for (int ks = 0; ks < n_ksteps; ++ks) {
+          if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
+          if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
+          tc_fence_after();
+          // A: K-major SW128, 8-row groups 1024 B apart; +32 B per 16-k step inside the swizzle row
+          const uint64_t da = make_smem_desc_sw128(a_ring + sa * kAStageBytes + ka * 32, 16, 1024);
+          uint64_t db;
+          if constexpr (kDenseB) {
+            db = make_smem_desc_sw128(b_ring + sb * B::kStageBytes + kb * 32, 16, 1024);
+          } else {
+            // B: MN-major SW128: 64-column atoms 1024 B apart (LBO), 8-k slabs kKAtomBytes apart (SBO)
+            db = make_smem_desc_sw128(b_ring + sb * B::kStageBytes + kb * 2 * kKAtomBytes, 1024, kKAtomBytes);
+          }
+          umma_f16(d, da, db, idesc, ks > 0 ? 1u : 0u);
+          const bool last = (ks == n_ksteps - 1);
+          if (++ka == 4 || last) {
+            umma_commit(a_empty + 8 * sa);
+            ka = 0;
+            if (++sa == kAStages) { sa = 0; pa ^= 1; }
+          }
+          if (++kb == B::kKSteps || last) {
+            umma_commit(b_empty + 8 * sb);
+            kb = 0;
+            if (++sb == B::kStages) { sb = 0; pb ^= 1; }
+          }
+        }
+        umma_commit(t_full + 8 * acc);
+      }
+    }
+  } else if (warp < kFirstDqWarp) {
+    // ================= epilogue ============================================================================
+    const int quarter = warp & 3;  // TMEM lanes [32 * quarter, +32) are the ones this warp may read
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const int m0 = (tile % p.tiles_m) * kBM, n0 = (tile / p.tiles_m) * kBN;
+      mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
+      tc_fence_after();
+      const int m = m0 + quarter * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < kBN; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * kBN + c, v);
+        tmem_ld_wait();
+        if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(t_empty + 8 * acc);
+    }
+  } else {
+    // ================= dequantizers =========================================================================
+    if constexpr (!kDenseB) {
+      using F = Fmt<MODE>;
+      const int dw = warp - kFirstDqWarp;
+      const int chunk = lane;  // 8 columns each: 32 chunks = 256 columns
+      int sb = 0;
+      uint32_t pb = 0;
+      uint32_t w[B::kItems][8], s[B::kItems][4];
+      auto load_stage = [&](int n0, int i) {
+#pragma unroll
+        for (int t = 0; t < B::kItems; ++t) {
+          const int r = i * B::kRows + dw + t * kDqWarps;  // global packed word row
+          const int n = n0 + chunk * 8;
+          if (r < p.n_rows && n < p.N) {
+            const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)r * p.N + n);
+            const uint4 lo = __ldg(src), hi = __ldg(src + 1);
+            w[t][0] = lo.x; w[t][1] = lo.y; w[t][2] = lo.z; w[t][3] = lo.w;
+            w[t][4] = hi.x; w[t][5] = hi.y; w[t][6] = hi.z; w[t][7] = hi.w;
+            const uint4 sv = __ldg(reinterpret_cast<const uint4*>(p.scale + (size_t)(r / F::kRowsPerGroup) * p.N + n));
+            s[t][0] = sv.x; s[t][1] = sv.y; s[t][2] = sv.z; s[t][3] = sv.w;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[t][j] = 0u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s[t][j] = 0u;
+          }
+        }
+      };
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int n0 = (tile / p.tiles_m) * kBN;
+        load_stage(n0, 0);
+        for (int i = 0; i < n_b_stages; ++i) {
+          uint32_t wc[B::kItems][8], sc[B::kItems][4];
+#pragma unroll
+          for (int t = 0; t < B::kItems; ++t) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) wc[t][j] = w[t][j];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) sc[t][j] = s[t][j];
+          }
+          if (i + 1 < n_b_stages) load_stage(n0, i + 1);  // in flight while this stage is unpacked
+          mbar_wait(b_empty + 8 * sb, pb ^ 1);
+          const uint32_t stage = b_ring + sb * B::kStageBytes;
+#pragma unroll
+          for (int t = 0; t < B::kItems; ++t)
+            dequant_chunk<MODE>(wc[t], sc[t], stage, (dw + t * kDqWarps) * F::kNpu, chunk);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(b_full + 8 * sb);
+          if (++sb == B::kStages) { sb = 0; pb ^= 1; }
+        }
+      }
+    }
+  }
+
+  // ---- teardown ---------------------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace
+
+// gemv.cu
+int make_tmap_2d(CUtensorMap* tm, CUtensorMapDataType dt, int elem_bytes, const void* ptr, int inner, int outer,
+                 int box_inner, int box_outer, CUtensorMapSwizzle sw);
+int device_sm_count();
+
+namespace {
+
+template <int MODE>
+int launch_gemm(GemmParams& p, cudaStream_t stream) {
+  using S = Smem<MODE>;
+  p.tiles_m = ceil_div(p.M, kBM);
+  p.tiles_n = ceil_div(p.N, kBN);
+  const int n_tiles = p.tiles_m * p.tiles_n;
+  int grid = device_sm_count();
+  if (grid > n_tiles) grid = n_tiles;
+  const size_t smem = (size_t)S::kBytes + 1024;  // + alignment slack
+  auto kern = gemm_tc_kernel<MODE>;
+  static thread_local bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemm smem)");
+    attr_set = true;
+  }
+  kern<<<grid, kGemmThreads, smem, stream>>>(p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return check_cuda(e, "gemm launch");
+  count_launch();
+  return B200Q_OK;
+}
+
+int check_epilogue_operands(int epilogue, const void* ep0, const void* ep1, const void* ep2, const char* who) {
+  const bool needs0 = epilogue == B200Q_EP_ADD || epilogue == B200Q_EP_MULTIPLY || epilogue == B200Q_EP_BIAS ||
+                      epilogue == B200Q_EP_BIAS_GELU || epilogue == B200Q_EP_BIAS_ADD2;
+  if (needs0 && !ep0) return set_error(B200Q_ERR_NULL, "%s: epilogue %d needs ep0", who, epilogue);
+  if (epilogue == B200Q_EP_BIAS_ADD2 && (!ep1 || !ep2)) return set_error(B200Q_ERR_NULL, "%s: bias_add2 needs ep1 and ep2", who);
+  auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15) != 0; };
+  if (mis(ep0) || mis(ep1) || mis(ep2)) return set_error(B200Q_ERR_BAD_ALIGN, "%s: epilogue operands must be 16-byte aligned", who);
+  return B200Q_OK;
+}
+
+}  // namespace
+
+int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
+                const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned /*flags*/,
+                cudaStream_t stream) {
+  if (K % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm: K=%d must be a multiple of 8 (16-byte rows of X)", K);
+  if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_gemm")) return e;
+  GemmParams p{};
+  p.packed = reinterpret_cast<const uint32_t*>(packed);
+  p.scale = reinterpret_cast<const __half*>(scale);
+  p.ep0 = reinterpret_cast<const __half*>(ep0);
+  p.ep1 = reinterpret_cast<const __half*>(ep1);
+  p.ep2 = reinterpret_cast<const __half*>(ep2);
+  p.Y = Y;
+  p.M = M; p.K = K; p.N = N;
+  p.n_rows = n_words(fmt, K);
+  p.epilogue = epilogue;
+  if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
+  switch (fmt) {
+    case B200Q_Q4F16_0: return launch_gemm<B200Q_Q4F16_0>(p, stream);
+    case B200Q_Q3F16_0: return launch_gemm<B200Q_Q3F16_0>(p, stream);
+    case B200Q_Q8F16_0: return launch_gemm<B200Q_Q8F16_0>(p, stream);
+    default: return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: fmt %d", fmt);
+  }
+}
+
+int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y, int M,
+                     int K, int N, int epilogue, cudaStream_t stream) {
+  if (epilogue < 0 || epilogue >= B200Q_NUM_EP) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_nt_matmul: epilogue %d", epilogue);
+  if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_nt_matmul")) return e;
+  GemmParams p{};
+  p.ep0 = reinterpret_cast<const __half*>(ep0);
+  p.ep1 = reinterpret_cast<const __half*>(ep1);
+  p.ep2 = reinterpret_cast<const __half*>(ep2);
+  p.Y = Y;
+  p.M = M; p.K = K; p.N = N;
+  p.epilogue = epilogue;
+  if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
+  if (int e = make_tmap_2d(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, T, K, N, kAK, kBN, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
+  return launch_gemm<kDense>(p, stream);
+}
+
 }  // namespace b200q

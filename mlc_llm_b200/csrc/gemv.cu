@@ -629,6 +629,13 @@ int launch_stream(StreamParams& p, unsigned flags, void* workspace, size_t works
 
 }  // namespace
 
+// shared with gemm.cu
+int make_tmap_2d(CUtensorMap* tm, CUtensorMapDataType dt, int elem_bytes, const void* ptr, int inner, int outer,
+                 int box_inner, int box_outer, CUtensorMapSwizzle sw) {
+  return make_tmap(tm, dt, elem_bytes, ptr, inner, outer, box_inner, box_outer, sw);
+}
+int device_sm_count() { return sm_count(); }
+
 void gemv_tune(int ctas_per_sm, int stages, int flags) {
   g_tune_ctas_per_sm = ctas_per_sm;
   g_tune_stages = stages;

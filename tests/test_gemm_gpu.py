@@ -1,0 +1,161 @@
+"""GPU parity tests of the prefill path: the tcgen05 dequant-GEMM (b200q_gemm) and the dense NT GEMM
+(b200q_nt_matmul) against the oracle (checker only).
+
+Bar: the dequantized weights fed to the tensor cores are the bit-exact reference
+weights (checked here through X = identity: Y == decode(W) bit for bit, the f16 x f16 products and the
+f32 sums being exact), and Y is within  2^-10 |y64| + 2^-14 sum|x w| + 2^-24  of the f64 evaluation
+on the same dequantized weights.  The reference's own f16-accumulating NT_matmul is compared too.
+"""
+import numpy as np
+import pytest
+import torch
+
+from mlc_llm_b200 import dispatch, ops
+from oracle import c_oracle as co
+from oracle import quant_oracle as qo
+from util import beq, dev, host, rand_weight
+
+pytestmark = pytest.mark.gpu
+
+F16 = ["q4f16_0", "q3f16_0", "q8f16_0"]
+
+
+def _check(Y, packed, scale, X, fmt, what, out_f32=False):
+    y64, ab = qo.gemm_f64(packed, scale, X, fmt)
+    tol = qo.tolerance(y64, ab, out_f32)
+    err = np.abs(Y.astype(np.float64) - y64)
+    worst = float((err / tol).max())
+    assert worst <= 1.0, f"{what}: error/tolerance = {worst:.3f} (max abs err {err.max():.3e})"
+
+
+@pytest.mark.parametrize("name", F16)
+def test_gemm_identity_reproduces_decode_bit_exact(name):
+    """X = I (K x K): Y[k, n] must be the dequantized weight itself - every k row, every code."""
+    fmt = qo.FORMATS[name]
+    K, N = 320, 512  # 320 = lcm-friendly for all three: 10 groups of 32, 8 groups of 40
+    packed, scale = rand_weight(fmt, K, N, seed=77)
+    X = np.eye(K, dtype=np.float16)
+    Y = host(ops.gemm(dev(packed), dev(scale), dev(X), name))
+    assert beq(Y, co.decode(packed, scale, K, fmt))
+
+
+@pytest.mark.parametrize("name", F16)
+@pytest.mark.parametrize("M,K,N", [(128, 256, 256), (256, 2560, 512), (2048, 2560, 2560), (300, 640, 1000),
+                                   (1, 4096, 4096), (77, 1280, 264), (512, 10240, 256)])
+def test_gemm_tolerance_shapes(name, M, K, N):
+    fmt = qo.FORMATS[name]
+    packed, scale = rand_weight(fmt, K, N, seed=M + K + N)
+    X = qo.synth_act((M, K), fmt, seed=M)
+    Y = host(ops.gemm(dev(packed), dev(scale), dev(X), name))
+    assert Y.shape == (M, N) and Y.dtype == np.float16
+    if M * K * N > 2**31:  # keep the f64 check in seconds: sample rows
+        rows = np.random.default_rng(0).choice(M, 64, replace=False)
+        _check(Y[rows], packed, scale, X[rows], fmt, f"{name} {M}x{K}x{N}")
+    else:
+        _check(Y, packed, scale, X, fmt, f"{name} {M}x{K}x{N}")
+
+
+@pytest.mark.parametrize("name", F16)
+def test_gemm_encoded_weights_ragged_k(name):
+    """Encoder-produced weights with K not a multiple of the group / of the stage depth."""
+    fmt = qo.FORMATS[name]
+    for K in (200, 1000, 4096):
+        N, M = 264, 130
+        W = qo.synth_weight(N, K, fmt, seed=K)
+        packed, scale = qo.encode_sym(W, fmt)
+        X = qo.synth_act((M, K), fmt, seed=3)
+        Y = host(ops.gemm(dev(packed), dev(scale), dev(X), name))
+        y64 = X.astype(np.float64) @ qo.decode_sym(packed, scale, K, fmt).astype(np.float64)
+        ab = np.abs(X.astype(np.float64)) @ np.abs(qo.decode_sym(packed, scale, K, fmt).astype(np.float64))
+        err = np.abs(Y.astype(np.float64) - y64)
+        assert (err <= qo.tolerance(y64, ab, False)).all(), (name, K, float((err / qo.tolerance(y64, ab, False)).max()))
+
+
+def test_gemm_row_equals_gemv():
+    """Row m of the prefill GEMM and the decode GEMV on the same activation are two f32 sums of the
+    same exact products in different orders: both inside the tolerance, hence within 2x of each other."""
+    name = "q4f16_0"
+    fmt = qo.FORMATS[name]
+    K, N, M = 4096, 1024, 64
+    packed, scale = rand_weight(fmt, K, N, seed=5)
+    X = qo.synth_act((M, K), fmt, seed=6)
+    p, s = dev(packed), dev(scale)
+    Y = host(ops.gemm(p, s, dev(X), name))
+    y64, ab = qo.gemm_f64(packed, scale, X, fmt)
+    tol = qo.tolerance(y64, ab, False)
+    for m in (0, 17, 63):
+        y = host(ops.gemv(p, s, dev(X[m]), name)).reshape(-1)
+        assert (np.abs(Y[m].astype(np.float64) - y.astype(np.float64)) <= 2 * tol[m]).all()
+        assert (np.abs(Y[m].view(np.int16).astype(np.int32) - y.view(np.int16).astype(np.int32)) <= 1).mean() > 0.99
+
+
+@pytest.mark.parametrize("name", F16)
+def test_gemm_epilogues_op_for_op(name):
+    fmt = qo.FORMATS[name]
+    M, K, N = 200, 640, 520
+    packed, scale = rand_weight(fmt, K, N, seed=31)
+    X = qo.synth_act((M, K), fmt, seed=32)
+    bias = qo.synth_act(N, fmt, seed=33)
+    r1 = qo.synth_act((M, N), fmt, seed=34)
+    r2 = qo.synth_act((M, N), fmt, seed=35)
+    p, s, xd = dev(packed), dev(scale), dev(X)
+    y0 = host(ops.gemm(p, s, xd, name))
+    for ep, e0 in (("add", r1), ("multiply", r1), ("bias", bias)):
+        y = host(ops.gemm(p, s, xd, name, ep, dev(e0)))
+        assert beq(y, qo.apply_epilogue(y0, qo.EPILOGUES[ep], e0)), ep
+    y = host(ops.gemm(p, s, xd, name, "bias_add2", dev(bias), dev(r1), dev(r2)))
+    assert beq(y, qo.apply_epilogue(y0, qo.EP_BIAS_ADD2, bias, r1, r2))
+    for ep in ("silu", "bias_gelu"):
+        y = host(ops.gemm(p, s, xd, name, ep, dev(bias) if ep == "bias_gelu" else None))
+        e = qo.apply_epilogue(y0, qo.EPILOGUES[ep], bias)
+        ulp = np.abs(y.view(np.int16).astype(np.int32) - e.view(np.int16).astype(np.int32))
+        assert ulp.max() <= 1, (ep, ulp.max())
+    y32 = host(ops.gemm(p, s, xd, name, "cast_f32"))
+    assert y32.dtype == np.float32 and beq(y32.astype(np.float16), y0)
+    _check(y32, packed, scale, X, fmt, "cast_f32", out_f32=True)
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 128, 256), (200, 2560, 520), (1024, 1024, 1024), (5, 64, 8)])
+def test_nt_matmul_dense(M, K, N):
+    """NT_matmul on a dense f16 weight T[N, K]: within tolerance of f64, and at least as close to f64
+    as the reference's f16-accumulating loop."""
+    rng = np.random.default_rng(M + N)
+    X = rng.standard_normal((M, K)).astype(np.float16)
+    T = (rng.standard_normal((N, K)) * 0.02).astype(np.float16)
+    Y = host(ops.nt_matmul(dev(X), dev(T)))
+    y64, ab = co.nt_matmul_f64_f16(X, T)
+    err = np.abs(Y.astype(np.float64) - y64)
+    assert (err <= qo.tolerance(y64, ab, False)).all()
+    if M * K * N <= 2**27:
+        yref = co.nt_matmul_ref_f16(X, T)
+        assert err.max() <= np.abs(yref.astype(np.float64) - y64).max() + 1e-12
+
+
+def test_two_kernel_prefill_equals_fused():
+    """The reference-shaped route (decode to dense [N, K], then NT_matmul) and the fused dequant-GEMM
+    see the same weights and the same k order inside a 16-k MMA step: results agree to 1 f16 ulp."""
+    name = "q4f16_0"
+    fmt = qo.FORMATS[name]
+    M, K, N = 256, 1024, 512
+    packed, scale = rand_weight(fmt, K, N, seed=8)
+    X = qo.synth_act((M, K), fmt, seed=9)
+    p, s, xd = dev(packed), dev(scale), dev(X)
+    T = ops.dequantize(p, s, K, name, transpose_output=True)
+    y2 = host(ops.nt_matmul(xd, T))
+    y1 = host(ops.gemm(p, s, xd, name))
+    assert beq(y1, y2)  # same weights, same tile shape, same k order: identical f32 sums
+
+
+def test_gemm_dispatch_lookup_and_errors():
+    fmt = qo.FORMATS["q3f16_0"]
+    M, K, N = 64, 2560, 256
+    packed, scale = rand_weight(fmt, K, N, seed=1)
+    X = qo.synth_act((1, M, K), fmt, seed=2)
+    f = dispatch.lookup("q3f16_0", K, N, "none", m_is_one=False)
+    assert f is not None and "NT_matmul" in f.__name__
+    out = torch.empty((1, M, N), dtype=torch.float16, device="cuda")
+    f(dev(packed), dev(scale), dev(X), out)
+    _check(host(out)[0], packed, scale, X[0], fmt, "dispatch q3")
+    assert dispatch.lookup("q4f32_0", K, N, "none", m_is_one=False) is None  # f32 prefill: a miss, like the reference
+    with pytest.raises(Exception):
+        ops.gemm(dev(packed), dev(scale), dev(X[0, :, :-4].copy()), "q3f16_0")  # K mismatch
