@@ -29,6 +29,8 @@
 // boundaries, so the int3 word geometry never has to line up with the 128-byte swizzle atom of X.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -80,6 +82,7 @@ struct GemmParams {
   int n_rows;    // packed word rows
   int epilogue;
   int tiles_m, tiles_n;
+  int debug;  // experiments (B200Q_GEMM_DEBUG): 1 = operands are not loaded / unpacked (protocol intact, data garbage), 2 = epilogue does not store
 };
 
 // ---- dequantize one 8-column chunk of one packed word row into the B stage ---------------------------
@@ -234,7 +237,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   const uint32_t t_full = b_empty + 8 * B::kStages, t_empty = t_full + 16;
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(base_ptr + S::kBarOff + S::kNumBars * 8);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // provably warp-uniform
   const int n_tiles = p.tiles_m * p.tiles_n;
   const int n_ksteps = (p.K + 15) >> 4;
   const int n_a_stages = (n_ksteps + 3) >> 2;
@@ -267,65 +270,76 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
-    // ================= TMA producer =====================================================================
-    if (lane == 0) {
-      int sa = 0, sb = 0;
-      uint32_t pa = 0, pb = 0;
-      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int m0 = (tile % p.tiles_m) * kBM, n0 = (tile / p.tiles_m) * kBN;
-        for (int i = 0; i < n_a_stages; ++i) {
-          mbar_wait(a_empty + 8 * sa, pa ^ 1);
-          mbar_expect_tx(a_full + 8 * sa, kAStageBytes);
-          tma_load_2d(a_ring + sa * kAStageBytes, &p.tm_a, i * kAK, m0, a_full + 8 * sa);
-          if (++sa == kAStages) { sa = 0; pa ^= 1; }
-          if constexpr (kDenseB) {  // same stage cadence for the dense B operand
-            mbar_wait(b_empty + 8 * sb, pb ^ 1);
-            mbar_expect_tx(b_full + 8 * sb, B::kStageBytes);
-            tma_load_2d(b_ring + sb * B::kStageBytes, &p.tm_b, i * kAK, n0, b_full + 8 * sb);
-            if (++sb == B::kStages) { sb = 0; pb ^= 1; }
+    // ================= TMA producer (warp-uniform loop, one elected lane issues) ==========================
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int m0 = (tile % p.tiles_m) * kBM, n0 = (tile / p.tiles_m) * kBN;
+      for (int i = 0; i < n_a_stages; ++i) {
+        mbar_wait(a_empty + 8 * sa, pa ^ 1);
+        if (elect_one()) {
+          if (p.debug & 1) {
+            mbar_arrive(a_full + 8 * sa);
+          } else {
+            mbar_expect_tx(a_full + 8 * sa, kAStageBytes);
+            tma_load_2d(a_ring + sa * kAStageBytes, &p.tm_a, i * kAK, m0, a_full + 8 * sa);
           }
+        }
+        if (++sa == kAStages) { sa = 0; pa ^= 1; }
+        if constexpr (kDenseB) {  // same stage cadence for the dense B operand
+          mbar_wait(b_empty + 8 * sb, pb ^ 1);
+          if (elect_one()) {
+            if (p.debug & 1) {
+              mbar_arrive(b_full + 8 * sb);
+            } else {
+              mbar_expect_tx(b_full + 8 * sb, B::kStageBytes);
+              tma_load_2d(b_ring + sb * B::kStageBytes, &p.tm_b, i * kAK, n0, b_full + 8 * sb);
+            }
+          }
+          if (++sb == B::kStages) { sb = 0; pb ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer ========================================================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_f16(kBM, kBN, 0, kDenseB ? 0 : 1);
-      int sa = 0, sb = 0, it = 0;
-      uint32_t pa = 0, pb = 0;
-      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t d = tmem_base + acc * kBN;
-        int ka = 0, kb = 0;  // k-step inside the current A / B stage
-        for (int ks = 0; ks < n_ksteps; ++ks) {
-          if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
-          if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
-          tc_fence_after();
-          // A: K-major SW128, 8-row groups 1024 B apart; +32 B per 16-k step inside the swizzle row
-          const uint64_t da = make_smem_desc_sw128(a_ring + sa * kAStageBytes + ka * 32, 16, 1024);
-          uint64_t db;
-          if constexpr (kDenseB) {
-            db = make_smem_desc_sw128(b_ring + sb * B::kStageBytes + kb * 32, 16, 1024);
-          } else {
-            // B: MN-major SW128: 64-column atoms 1024 B apart (LBO), 8-k slabs kKAtomBytes apart (SBO)
-            db = make_smem_desc_sw128(b_ring + sb * B::kStageBytes + kb * 2 * kKAtomBytes, 1024, kKAtomBytes);
-          }
+    // ================= MMA issuer (warp-uniform loop, one elected lane issues) ===========================
+    // experiments: bits 4-5 of debug shrink the UMMA N (garbage results)
+    const uint32_t idesc = make_idesc_f16(kBM, kBN >> ((p.debug >> 4) & 3), 0, kDenseB ? 0 : 1);
+    // descriptor high words are constants; the low word carries the start address
+    const uint64_t da_hi = make_smem_desc_sw128(0, 16, 1024) & 0xFFFFFFFF00000000ull;
+    const uint64_t db_hi = (kDenseB ? make_smem_desc_sw128(0, 16, 1024) : make_smem_desc_sw128(0, 1024, kKAtomBytes)) &
+                           0xFFFFFFFF00000000ull;
+    const uint32_t da_lo0 = (uint32_t)make_smem_desc_sw128(0, 16, 1024);
+    const uint32_t db_lo0 = (uint32_t)(kDenseB ? make_smem_desc_sw128(0, 16, 1024) : make_smem_desc_sw128(0, 1024, kKAtomBytes));
+    constexpr uint32_t kBStep = kDenseB ? 32u : 2u * kKAtomBytes;  // bytes per 16-k step inside a B stage
+    int sa = 0, sb = 0, it = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t d = tmem_base + acc * kBN;
+      int ka = 0, kb = 0;  // k-step inside the current A / B stage
+      for (int ks = 0; ks < n_ksteps; ++ks) {
+        if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
+        if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
+        if (ka == 0 || kb == 0) tc_fence_after();
+        // A: K-major SW128, 8-row groups 1024 B apart; +32 B per 16-k step inside the swizzle row
+        // B: MN-major SW128: 64-column atoms 1024 B apart (LBO), 8-k slabs kKAtomBytes apart (SBO)
+        const uint32_t a_addr = a_ring + sa * kAStageBytes + ka * 32;
+        const uint32_t b_addr = b_ring + sb * B::kStageBytes + kb * kBStep;
+        const uint64_t da = da_hi | (uint64_t)(da_lo0 | ((a_addr & 0x3FFFFu) >> 4));
+        const uint64_t db = db_hi | (uint64_t)(db_lo0 | ((b_addr & 0x3FFFFu) >> 4));
+        const bool last = (ks == n_ksteps - 1);
+        const bool rel_a = (ka == 3) || last, rel_b = (kb == B::kKSteps - 1) || last;
+        if (elect_one()) {
           umma_f16(d, da, db, idesc, ks > 0 ? 1u : 0u);
-          const bool last = (ks == n_ksteps - 1);
-          if (++ka == 4 || last) {
-            umma_commit(a_empty + 8 * sa);
-            ka = 0;
-            if (++sa == kAStages) { sa = 0; pa ^= 1; }
-          }
-          if (++kb == B::kKSteps || last) {
-            umma_commit(b_empty + 8 * sb);
-            kb = 0;
-            if (++sb == B::kStages) { sb = 0; pb ^= 1; }
-          }
+          if (rel_a) umma_commit(a_empty + 8 * sa);
+          if (rel_b) umma_commit(b_empty + 8 * sb);
+          if (last) umma_commit(t_full + 8 * acc);
         }
-        umma_commit(t_full + 8 * acc);
+        __syncwarp();
+        if (rel_a) { ka = 0; if (++sa == kAStages) { sa = 0; pa ^= 1; } } else { ++ka; }
+        if (rel_b) { kb = 0; if (++sb == B::kStages) { sb = 0; pb ^= 1; } } else { ++kb; }
       }
     }
   } else if (warp < kFirstDqWarp) {
@@ -343,7 +357,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * kBN + c, v);
         tmem_ld_wait();
-        if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+        if (m < p.M && n0 + c < p.N && !(p.debug & 2)) epilogue_row(p, v, m, n0 + c);
       }
       tc_fence_before();
       __syncwarp();
@@ -393,9 +407,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
           if (i + 1 < n_b_stages) load_stage(n0, i + 1);  // in flight while this stage is unpacked
           mbar_wait(b_empty + 8 * sb, pb ^ 1);
           const uint32_t stage = b_ring + sb * B::kStageBytes;
+          if (!(p.debug & 1)) {
 #pragma unroll
-          for (int t = 0; t < B::kItems; ++t)
-            dequant_chunk<MODE>(wc[t], sc[t], stage, (dw + t * kDqWarps) * F::kNpu, chunk);
+            for (int t = 0; t < B::kItems; ++t)
+              dequant_chunk<MODE>(wc[t], sc[t], stage, (dw + t * kDqWarps) * F::kNpu, chunk);
+          }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(b_full + 8 * sb);
@@ -429,6 +445,10 @@ int launch_gemm(GemmParams& p, cudaStream_t stream) {
   p.tiles_m = ceil_div(p.M, kBM);
   p.tiles_n = ceil_div(p.N, kBN);
   const int n_tiles = p.tiles_m * p.tiles_n;
+  {
+    static const int dbg = getenv("B200Q_GEMM_DEBUG") ? atoi(getenv("B200Q_GEMM_DEBUG")) : 0;
+    p.debug = dbg;
+  }
   int grid = device_sm_count();
   if (grid > n_tiles) grid = n_tiles;
   const size_t smem = (size_t)S::kBytes + 1024;  // + alignment slack
