@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-per-shape", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
+    ap.add_argument("--no-program", action="store_true", help="one launch per Linear (PDL chain) instead of the persistent decode program")
     ap.add_argument("--no-fuse-qkv", action="store_true")
     ap.add_argument("--no-fuse-gate-up", action="store_true")
     ap.add_argument("--tune", default="", help="ctas_per_sm,stages,dbg_flags for b200q_gemv_tune (experiments)")
@@ -240,7 +241,8 @@ def main():
     shape = MODEL_SHAPES[args.model]
 
     stack = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, layers=args.layers,
-                        pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up)
+                        pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up,
+                        use_program=not args.no_program)
     if args.tune:
         ops.gemv_tune(*[int(v) for v in args.tune.split(",")])
     stack.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(stack.dt))
@@ -317,7 +319,9 @@ def main():
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": ncu_traffic("gemv_q4f16_0_4096x11008_dram_bytes"),
-            "kernel": "b200q::gemv_f16_kernel<q4f16_0> (all of the step's launches are this kernel at N=1)",
+            "kernel": ("b200q::gemv_program_kernel (persistent: every GEMV of the step in one cooperative launch per "
+                       "collective-free segment)") if stack.use_program else "b200q::gemv_stream_kernel (one launch per fused Linear group, PDL chain)",
+            "gemv_steps_per_launch": (sum(o.n_steps for k, o in stack._plan if k == "program") / max(1, launches)) if stack.use_program else 1,
             "bytes_per_step_per_rank": step_bytes, "launches_per_step": launches,
             "avg_launch_us": ms_per_step * 1e3 / launches,
             "peak_source": peak_src + (" of measured" if "measured" in peak_src else " of fallback"),

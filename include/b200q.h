@@ -132,6 +132,37 @@ typedef struct {
 B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K,
                      int fmt, unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- the whole decode step in ONE persistent launch ----------------------------------------------
+ * The reference runs the GEMV chain of one token as one compiled Relax function (`decoding`,
+ * mlc_llm/relax_model/llama.py:581-611) whose call_tir sites are the fused_decode*_matmul* PrimFuncs.
+ * A "program" is that chain as data: a list of steps, each step = 1..4 GEMVs reading the same
+ * activation (x, optionally x * x_mul) exactly like b200q_gemv_multi.  The library derives the
+ * dependencies between steps from pointer overlap (a step waits for the steps that write its x /
+ * x_mul / ep0, or whose inputs / outputs it overwrites) and runs everything in one cooperative,
+ * persistent kernel: weights of later steps stream into shared memory while earlier steps finish.
+ * Results are identical to running the steps one by one through b200q_gemv_multi with a workspace
+ * (same kernels' arithmetic, same deterministic split-K order for a given SM count).
+ *
+ *   1. b200q_gemv_program_build fills a HOST blob of b200q_gemv_program_bytes(n_steps) bytes
+ *      (tensor-map descriptors + step table; needs a CUDA context but launches nothing);
+ *   2. the caller copies the blob to a 64-byte aligned DEVICE buffer and zero-fills a 256-byte aligned
+ *      device workspace of b200q_gemv_program_workspace_bytes(host_blob) bytes ONCE;
+ *   3. b200q_gemv_program_run launches it (CUDA-graph capturable; leaves the workspace clean).
+ * All buffers named by the steps must stay alive and in place while the program is in use. */
+typedef struct {
+  b200q_gemv_op ops[4];
+  int n_ops;
+  const void* x;
+  const void* x_mul; /* optional */
+  int K;
+} b200q_gemv_step;
+B200Q_API size_t b200q_gemv_program_bytes(int n_steps);
+B200Q_API int b200q_gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob,
+                             size_t blob_bytes);
+B200Q_API size_t b200q_gemv_program_workspace_bytes(const void* host_blob);
+B200Q_API int b200q_gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
 /* Tuning override for experiments (0 = default).  ctas_per_sm: 1 or 2 persistent CTAs per SM;
  * stages: cap of the shared-memory ring depth; dbg_flags bit 0: stream only, skip the math
  * (results are garbage - for bandwidth probes). Thread-local. */

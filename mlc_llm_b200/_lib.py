@@ -36,6 +36,12 @@ class GemvOp(ctypes.Structure):
     ]
 
 
+class GemvStep(ctypes.Structure):
+    """b200q_gemv_step (include/b200q.h)."""
+
+    _fields_ = [("ops", GemvOp * 4), ("n_ops", c_int), ("x", c_void_p), ("x_mul", c_void_p), ("K", c_int)]
+
+
 # name -> (restype, argtypes); must list every symbol include/b200q.h declares
 PROTOTYPES = {
     "b200q_version": (c_int, []),
@@ -48,6 +54,10 @@ PROTOTYPES = {
     "b200q_gemv": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_gemv_multi": (c_int, [ctypes.POINTER(GemvOp), c_int, c_void_p, c_void_p, c_int, c_int, c_uint, c_void_p,
                                  ctypes.c_size_t, c_void_p]),
+    "b200q_gemv_program_bytes": (ctypes.c_size_t, [c_int]),
+    "b200q_gemv_program_build": (c_int, [ctypes.POINTER(GemvStep), c_int, c_int, c_void_p, ctypes.c_size_t]),
+    "b200q_gemv_program_workspace_bytes": (ctypes.c_size_t, [c_void_p]),
+    "b200q_gemv_program_run": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_gemv_tune": (None, [c_int, c_int, c_int]),
     "b200q_gemv_host": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_dequant": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),

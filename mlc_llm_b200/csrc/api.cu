@@ -29,6 +29,11 @@ int gemv_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* 
                 unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 void gemv_tune(int ctas_per_sm, int stages, int flags);
 size_t gemv_workspace_bytes();
+size_t gemv_program_bytes(int n_steps);
+int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes);
+size_t gemv_program_workspace_bytes(const void* host_blob);
+int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
+                     cudaStream_t stream);
 int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
                    cudaStream_t stream);
 int take_decode_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
@@ -115,6 +120,34 @@ int b200q_gemv(const void* packed, const void* scale, const void* x, const void*
                void* stream) {
   b200q_gemv_op op{packed, scale, ep0, out, N, epilogue};
   return b200q_gemv_multi(&op, 1, x, nullptr, K, fmt, flags, workspace, workspace_bytes, stream);
+}
+
+size_t b200q_gemv_program_bytes(int n_steps) { return n_steps > 0 ? gemv_program_bytes(n_steps) : 0; }
+
+int b200q_gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes) {
+  if (int e = check_fmt(fmt, "b200q_gemv_program_build")) return e;
+  if (!steps || !host_blob) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_build: NULL steps/blob");
+  if (n_steps < 1 || n_steps > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_program_build: n_steps=%d", n_steps);
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  for (int j = 0; j < n_steps; ++j) {
+    const b200q_gemv_step& st = steps[j];
+    if (st.n_ops < 1 || st.n_ops > 4) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_program_build: step %d has %d ops", j, st.n_ops);
+    if (!st.x || st.K <= 0) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_build: step %d: NULL x or K=%d", j, st.K);
+    if (!aligned(st.x, el) || (st.x_mul && !aligned(st.x_mul, el))) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv_program_build: step %d: x misaligned", j);
+    for (int i = 0; i < st.n_ops; ++i)
+      if (int e = check_gemv_op(st.ops[i], fmt, "b200q_gemv_program_build")) return e;
+  }
+  return gemv_program_build(steps, n_steps, fmt, host_blob, blob_bytes);
+}
+
+size_t b200q_gemv_program_workspace_bytes(const void* host_blob) {
+  return host_blob ? gemv_program_workspace_bytes(host_blob) : 0;
+}
+
+int b200q_gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
+                           void* stream) {
+  if (!host_blob || !dev_blob || !workspace) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_run: NULL blob/workspace");
+  return gemv_program_run(host_blob, dev_blob, workspace, workspace_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,

@@ -39,18 +39,21 @@
 #include <cuda.h>
 
 #include "common.cuh"
+#include "gemv_device.cuh"
+#include "ptx.cuh"
 
 namespace b200q {
 
 namespace {
 
+using namespace ptx;
+using namespace gemvdev;
+
 constexpr int kConsumerWarps = 8;
 constexpr int kConsumerThreads = kConsumerWarps * 32;
 constexpr int kThreads = kConsumerThreads + 32;  // + producer warp
 constexpr int kMaxOps = 4;
-constexpr int kPanelCols = 128;
 constexpr int kBlockRows = 32;
-constexpr int kBoxCols = 32;                                   // one TMA box: 32 rows x 32 words, 128B rows
 constexpr int kBoxBytes = kBlockRows * kBoxCols * 4;           // 4096
 constexpr int kWordStageBytes = kBlockRows * kPanelCols * 4;   // 16384
 constexpr int kMaxStages = 12;
@@ -69,8 +72,7 @@ struct Stream {
   static constexpr int kScaleStageBytes = kGroupsPerBlock * kScalePitch;
   static constexpr int kStageTx = kWordStageBytes + kScaleStageBytes;       // bytes TMA delivers per stage
   static constexpr int kStageBytes = (kStageTx + 1023) / 1024 * 1024;       // swizzled boxes need 1024B alignment
-  // permuted activation bytes per packed word row
-  static constexpr int kXRowBytes = kF32 ? 32 : F::kQuads * 8;
+  static constexpr int kXRowBytes = XLayout<FMT>::kXRowBytes;
 };
 
 struct StreamOp {
@@ -104,200 +106,12 @@ struct StreamParams {
   int no_compute;  // debug: stream only
 };
 
-// ---- PTX helpers ---------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "LAB_WAIT:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-      "@P1 bra DONE;\n"
-      "bra LAB_WAIT;\n"
-      "DONE:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
+// ---- PTX helpers: ptx.cuh; shared device code: gemv_device.cuh -------------------------------------
 __device__ __forceinline__ void tma_2d(uint32_t dst, const CUtensorMap* tm, int c_inner, int c_outer, uint32_t bar,
                                        uint64_t pol) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%2, %3}], [%4], %5;"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c_inner), "r"(c_outer), "r"(bar), "l"(pol)
-      : "memory");
-}
-__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
+  tma_load_2d_hint(dst, tm, c_inner, c_outer, bar, pol);
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
-__device__ __forceinline__ uint4 lds128(uint32_t a) {
-  uint4 r;
-  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
-  return r;
-}
-__device__ __forceinline__ uint2 lds64(uint32_t a) {
-  uint2 r;
-  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(a));
-  return r;
-}
-__device__ __forceinline__ float ld_cg_f32(const float* p) {
-  float v;
-  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
-  return v;
-}
-
-__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
-                                         uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-      "{%0,%1,%2,%3};"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
-
-// ---- f16 formats: one packed row = 4 words (columns 4c..4c+3) of one lane -------------------------
-// acc[m][*]: MMA m covers columns (4c + 2m) [A rows 0-7] and (4c + 2m + 1) [A rows 8-15] of the
-// lane's column quad c; the four lanes of a quad own different rows (different k).
-__device__ __forceinline__ void split_scales(uint2 sc, __half2 (&s2)[4]) {
-  s2[0] = u32_as_h2(__byte_perm(sc.x, 0, 0x1010));
-  s2[1] = u32_as_h2(__byte_perm(sc.x, 0, 0x3232));
-  s2[2] = u32_as_h2(__byte_perm(sc.y, 0, 0x1010));
-  s2[3] = u32_as_h2(__byte_perm(sc.y, 0, 0x3232));
-}
-template <int FMT>
-__device__ __forceinline__ void compute_row_f16(uint4 w, const __half2 (&s2)[4], uint32_t xr, float (&acc)[2][4]) {
-  const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
-  if constexpr (FMT == B200Q_Q4F16_0) {
-    uint4 xv = lds128(xr);  // (x0,x4)(x1,x5)(x2,x6)(x3,x7)
-    __half2 h[4][4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) unpack_q4(wv[j], s2[j], h[j]);
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-               h2_as_u32(h[2 * m + 1][1]), xv.x, xv.y);
-      mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
-               h2_as_u32(h[2 * m + 1][3]), xv.z, xv.w);
-    }
-  } else if constexpr (FMT == B200Q_Q3F16_0) {
-    // (x0,x5)(x1,x6) | (x2,x7)(x3,x8) | (x4,x9)(0,0); rows are 24 bytes apart: 8-byte alignment
-    uint2 x01 = lds64(xr), x23 = lds64(xr + 8), xb = lds64(xr + 16);
-    __half2 h[4][5];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) unpack_q3(wv[j], s2[j], h[j]);
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-               h2_as_u32(h[2 * m + 1][1]), x01.x, x01.y);
-      mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]),
-               h2_as_u32(h[2 * m + 1][3]), x23.x, x23.y);
-      mma16816(acc[m], h2_as_u32(h[2 * m][4]), h2_as_u32(h[2 * m + 1][4]), 0u, 0u, xb.x, xb.y);
-    }
-  } else {  // Q8: (x0,x1)(x2,x3)
-    uint2 xv = lds64(xr);
-    __half2 h[4][2];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) unpack_q8(wv[j], s2[j], h[j]);
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]),
-               h2_as_u32(h[2 * m + 1][1]), xv.x, xv.y);
-    }
-  }
-}
-
-// ---- q4f32_0: f32 weights  fl32(f32(q - 7) * s), FFMA into four column accumulators ----------------
-// (q | 0x4B000000) is the f32 2^23 + q; subtracting 2^23 + 7 gives q - 7 exactly.
-__device__ __forceinline__ float nib_to_f32(uint32_t w, int t) {
-  uint32_t q = (w >> (4 * t)) & 0xFu;
-  return __uint_as_float(q | 0x4B000000u) - 8388615.0f;
-}
-__device__ __forceinline__ void compute_row_f32(uint4 w, uint4 sc, uint32_t xr, float (&acc)[4]) {
-  const float s[4] = {__uint_as_float(sc.x), __uint_as_float(sc.y), __uint_as_float(sc.z), __uint_as_float(sc.w)};
-  const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
-  uint4 xa = lds128(xr), xb = lds128(xr + 16);
-  const float xv[8] = {__uint_as_float(xa.x), __uint_as_float(xa.y), __uint_as_float(xa.z), __uint_as_float(xa.w),
-                       __uint_as_float(xb.x), __uint_as_float(xb.y), __uint_as_float(xb.z), __uint_as_float(xb.w)};
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-#pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      float wt = __fmul_rn(nib_to_f32(wv[j], t), s[j]);  // the reference's single rounding
-      acc[j] = fmaf(xv[t], wt, acc[j]);
-    }
-  }
-}
-
-// ---- activation staging: the whole x (optionally x * x_mul) into shared memory ---------------------
-// f16 formats: word row r -> xs[r][kXRowBytes] in the pair order the unpack produces.
-template <int FMT>
-__device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const void* xmul, int K, int rows) {
-  using S = Stream<FMT>;
-  using F = Fmt<FMT>;
-  if constexpr (S::kF32) {
-    const float* x = reinterpret_cast<const float*>(xg);
-    const float* m = reinterpret_cast<const float*>(xmul);
-    float* dst = reinterpret_cast<float*>(xs);
-    const int n = rows * 8;
-    for (int k = threadIdx.x; k < n; k += kConsumerThreads) {
-      float v = 0.f;
-      if (k < K) v = m ? __fmul_rn(x[k], m[k]) : x[k];
-      dst[k] = v;
-    }
-  } else {
-    const __half* x = reinterpret_cast<const __half*>(xg);
-    const __half* m = reinterpret_cast<const __half*>(xmul);
-    constexpr int XB = S::kXRowBytes;
-    const bool vec_ok = (F::kNpu == 8) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
-                        (m == nullptr || (reinterpret_cast<uintptr_t>(m) & 15) == 0);
-    for (int lr = threadIdx.x; lr < rows; lr += kConsumerThreads) {
-      const int k0 = lr * F::kNpu;
-      __align__(16) __half v[12];
-#pragma unroll
-      for (int t = 0; t < 12; ++t) v[t] = __ushort_as_half(0);
-      if (vec_ok && k0 + 8 <= K) {
-        *reinterpret_cast<uint4*>(v) = *reinterpret_cast<const uint4*>(x + k0);
-        if (m) {
-          __align__(16) __half mv[8];
-          *reinterpret_cast<uint4*>(mv) = *reinterpret_cast<const uint4*>(m + k0);
-#pragma unroll
-          for (int t = 0; t < 8; ++t) v[t] = __hmul(v[t], mv[t]);
-        }
-      } else {
-#pragma unroll
-        for (int t = 0; t < F::kNpu; ++t)
-          if (k0 + t < K) v[t] = m ? __hmul(x[k0 + t], m[k0 + t]) : x[k0 + t];
-      }
-      __align__(8) __half o[12];
-      if constexpr (FMT == B200Q_Q4F16_0) {
-        o[0] = v[0]; o[1] = v[4]; o[2] = v[1]; o[3] = v[5];
-        o[4] = v[2]; o[5] = v[6]; o[6] = v[3]; o[7] = v[7];
-      } else if constexpr (FMT == B200Q_Q3F16_0) {
-        o[0] = v[0]; o[1] = v[5]; o[2] = v[1]; o[3] = v[6];
-        o[4] = v[2]; o[5] = v[7]; o[6] = v[3]; o[7] = v[8];
-        o[8] = v[4]; o[9] = v[9]; o[10] = __ushort_as_half(0); o[11] = __ushort_as_half(0);
-      } else {
-        o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
-      }
-      unsigned char* d = xs + (size_t)lr * XB;
-#pragma unroll
-      for (int t = 0; t < XB / 8; ++t) reinterpret_cast<uint2*>(d)[t] = reinterpret_cast<const uint2*>(o)[t];
-    }
-  }
-}
-
 __device__ __forceinline__ int find_op(const StreamParams& p, int panel) {
   int oi = 0;
 #pragma unroll
@@ -342,7 +156,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, kConsumerWarps);
     }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_barrier_init();
   }
   __syncthreads();
 
@@ -382,7 +196,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
   const int rows_alloc = p.RB * kBlockRows;
 
   pdl_wait();  // x / x_mul / ep0 / out belong to the previous kernel until here
-  stage_x<FMT>(xs, p.x, p.x_mul, p.K, rows_alloc);
+  stage_x<FMT, kConsumerThreads>(xs, p.x, p.x_mul, p.K, rows_alloc);
   consumer_sync();
 
   // lane rows of the 16-row half: 2 tig + j + 8 m  (j, m in {0,1}); swizzled chunk = c ^ (row & 7)

@@ -83,18 +83,12 @@ class QuantWeight:
         self.packed, self.scale, self.K, self.N = packed, scale, K, N
 
 
-def synth_weight(spec: QuantSpec, K: int, N: int, seed: int, device, col_slice=None, row_slice=None) -> QuantWeight:
-    """Draw W[N, K] ~ N(0, 0.02^2) on the device, pack it with the library encoder, slice for TP.
+def shard_packed(packed, scale, spec: QuantSpec, K: int, N: int, col_slice=None, row_slice=None):
+    """Tensor-parallel shard of one packed Linear: pure indexing, no repacking.
 
-    col_slice=(r, tp): keep output columns [r*N/tp, (r+1)*N/tp)     (column parallel)
-    row_slice=(r, tp): keep input rows    [r*K/tp, (r+1)*K/tp)      (row parallel; K/tp % group == 0)"""
-    g = torch.Generator(device=device)
-    g.manual_seed(seed)
-    W = torch.empty((N, K), dtype=torch.float32, device=device)
-    W.normal_(0.0, 0.02, generator=g)
-    W = W.to(spec.torch_dtype)
-    packed, scale = ops.encode(W, spec, transpose=True)
-    del W
+    col_slice=(r, tp): output columns [r*N/tp, (r+1)*N/tp)  - packed[:, n0:n1], scale[:, n0:n1]
+    row_slice=(r, tp): input rows     [r*K/tp, (r+1)*K/tp)  - whole groups: packed word rows / scale rows
+    Works on any torch tensor (CPU tensors in the gloo tests).  Returns (packed, scale, K, N) of the shard."""
     if col_slice is not None:
         r, tp = col_slice
         n = N // tp
@@ -113,6 +107,22 @@ def synth_weight(spec: QuantSpec, K: int, N: int, seed: int, device, col_slice=N
         packed = packed[r * gk * wpg:(r + 1) * gk * wpg].contiguous()
         scale = scale[r * gk:(r + 1) * gk].contiguous()
         K = k
+    return packed, scale, K, N
+
+
+def synth_weight(spec: QuantSpec, K: int, N: int, seed: int, device, col_slice=None, row_slice=None) -> QuantWeight:
+    """Draw W[N, K] ~ N(0, 0.02^2) on the device, pack it with the library encoder, slice for TP.
+
+    col_slice=(r, tp): keep output columns [r*N/tp, (r+1)*N/tp)     (column parallel)
+    row_slice=(r, tp): keep input rows    [r*K/tp, (r+1)*K/tp)      (row parallel; K/tp % group == 0)"""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    W = torch.empty((N, K), dtype=torch.float32, device=device)
+    W.normal_(0.0, 0.02, generator=g)
+    W = W.to(spec.torch_dtype)
+    packed, scale = ops.encode(W, spec, transpose=True)
+    del W
+    packed, scale, K, N = shard_packed(packed, scale, spec, K, N, col_slice, row_slice)
     return QuantWeight(packed, scale, K, N)
 
 
@@ -126,7 +136,7 @@ class DecodeStack:
 
     def __init__(self, shape, spec, device=None, tp_rank: int = 0, tp_size: int = 1, seed: int = 0xB200,
                  layers: Optional[int] = None, process_group=None, fuse_qkv: bool = True, fuse_gate_up: bool = True,
-                 pdl: bool = True, use_graph: bool = True):
+                 pdl: bool = True, use_graph: bool = True, use_program: bool = False):
         self.shape = MODEL_SHAPES[shape] if isinstance(shape, str) else shape
         self.spec = SPECS[spec] if isinstance(spec, str) else spec
         self.device = torch.device(device if device is not None else "cuda")
@@ -141,6 +151,12 @@ class DecodeStack:
         self.graph = None
         self.launches_per_step = 0
         self.collectives_per_step = 0
+        # use_program: the whole GEMV chain as persistent program launches (one per all-reduce-free segment)
+        self.use_program = use_program
+        self._plan = None
+        self._steps = None
+        if use_program:
+            self._build_plan()
 
     # ------------------------------------------------------------------ weights
     def _build_weights(self, seed: int):
@@ -196,6 +212,11 @@ class DecodeStack:
     # ------------------------------------------------------------------ the launch sequence
     def _launch(self, items, x, x_mul=None):
         """One kernel launch: items = [(weight, epilogue, ep0, out), ...] all reading x (* x_mul)."""
+        if self._steps is not None:  # recording a program
+            self._steps.append(dict(weights=[(w.packed, w.scale) for w, _, _, _ in items], x=x, x_mul=x_mul,
+                                    epilogues=[ep for _, ep, _, _ in items], ep0s=[e0 for _, _, e0, _ in items],
+                                    outs=[o for _, _, _, o in items]))
+            return
         ops.gemv_multi([(w.packed, w.scale) for w, _, _, _ in items], x, self.spec,
                        epilogues=[ep for _, ep, _, _ in items], ep0s=[e0 for _, _, e0, _ in items],
                        outs=[o for _, _, _, o in items], pdl=self.pdl, x_mul=x_mul, ws=self.ws)
@@ -204,7 +225,40 @@ class DecodeStack:
     def _gemv(self, w: QuantWeight, x, ep, ep0, out):
         self._launch([(w, ep, ep0, out)], x)
 
+    def _flush_steps(self):
+        if self._steps:
+            self._plan.append(("program", ops.GemvProgram(self._steps, self.spec)))
+        self._steps = []
+
+    def _build_plan(self):
+        """Record the step's launches once: GEMV programs separated by the collectives."""
+        self._plan, self._steps = [], []
+        self._run_sequence()
+        self._flush_steps()
+        self._steps = None
+
+    def _run_plan(self):
+        import torch.distributed as dist
+
+        self.launches_per_step = 0
+        self.collectives_per_step = 0
+        for kind, obj in self._plan:
+            if kind == "program":
+                obj.run()
+                self.launches_per_step += 1
+            elif kind == "all_reduce":
+                dist.all_reduce(obj, group=self.pg)
+                self.collectives_per_step += 1
+            else:
+                dist.all_gather_into_tensor(obj[0], obj[1], group=self.pg)
+                self.collectives_per_step += 1
+        return self.logits
+
     def _all_reduce(self, t):
+        if self._steps is not None:
+            self._flush_steps()
+            self._plan.append(("all_reduce", t))
+            return
         import torch.distributed as dist
 
         dist.all_reduce(t, group=self.pg)
@@ -258,17 +312,26 @@ class DecodeStack:
             x = b["x2"]
         return x
 
-    def _run(self):
-        self.launches_per_step = 0
-        self.collectives_per_step = 0
+    def _run_sequence(self):
         x = self._run_llama() if self.shape.family == "llama" else self._run_neox()
         self._gemv(self.lm_head, x, "none" if self.spec.dtype == "float32" else "cast_f32", None, self.logits_part)
         if self.tp_size > 1:
+            if self._steps is not None:
+                self._flush_steps()
+                self._plan.append(("all_gather", (self.logits, self.logits_part)))
+                return self.logits
             import torch.distributed as dist
 
             dist.all_gather_into_tensor(self.logits, self.logits_part, group=self.pg)
             self.collectives_per_step += 1
         return self.logits
+
+    def _run(self):
+        if self._plan is not None:
+            return self._run_plan()
+        self.launches_per_step = 0
+        self.collectives_per_step = 0
+        return self._run_sequence()
 
     def capture(self):
         """Warm up on a side stream and capture the step into one CUDA graph."""

@@ -260,3 +260,66 @@ def nt_matmul(X, T, epilogue="none", ep0=None, ep1=None, ep2=None, out=None):
 
 def launch_count() -> int:
     return int(_lib.lib().b200q_launch_count())
+
+
+class GemvProgram:
+    """The GEMV chain of one decode step as ONE persistent launch (b200q_gemv_program_*).
+
+    steps: list of dicts with keys
+        weights   [(packed, scale), ...]   1..4 Linears that read the same activation
+        x         dtype[K]                 activation (may be the `out` of an earlier step)
+        x_mul     optional dtype[K]        activation = x * x_mul
+        epilogues optional list            per Linear ("none", "add", ...)
+        ep0s      optional list            per Linear epilogue operand or None
+        outs      list                     per Linear output tensor (destination passing)
+    Dependencies between steps are derived by the library from pointer overlap.  All tensors are kept
+    alive by this object; run() launches on torch's current stream and is CUDA-graph capturable."""
+
+    def __init__(self, steps, spec):
+        import numpy as np
+
+        spec = _spec(spec)
+        self.spec = spec
+        L = _lib.lib()
+        n = len(steps)
+        arr = (_lib.GemvStep * n)()
+        self._keep = []
+        dev = None
+        for j, st in enumerate(steps):
+            x = st["x"]
+            x_mul = st.get("x_mul")
+            weights = st["weights"]
+            eps = list(st.get("epilogues") or ["none"] * len(weights))
+            ep0s = list(st.get("ep0s") or [None] * len(weights))
+            outs = st["outs"]
+            K = x.shape[-1]
+            _need_cuda(x, x_mul)
+            if x.numel() != K or x.dtype != spec.torch_dtype:
+                raise ValueError(f"step {j}: x must be {spec.dtype}[K]")
+            dev = x.device
+            arr[j].n_ops = len(weights)
+            arr[j].x = x.data_ptr()
+            arr[j].x_mul = _ptr(x_mul)
+            arr[j].K = K
+            for i, (packed, scale) in enumerate(weights):
+                _need_cuda(packed, scale, ep0s[i], outs[i])
+                N = _check_weight(spec, packed, scale, K)
+                ep = _ep_id(eps[i])
+                odt = torch.float32 if (ep == EPILOGUES["cast_f32"] or spec.dtype == "float32") else torch.float16
+                if outs[i].numel() != N or outs[i].dtype != odt:
+                    raise ValueError(f"step {j}: out[{i}] must be {odt}[{N}]")
+                arr[j].ops[i] = _lib.GemvOp(packed.data_ptr(), scale.data_ptr(), _ptr(ep0s[i]), outs[i].data_ptr(), N, ep)
+                self._keep += [packed, scale, ep0s[i], outs[i]]
+            self._keep += [x, x_mul]
+        nbytes = int(L.b200q_gemv_program_bytes(n))
+        self._host = np.zeros(nbytes // 8 + 1, dtype=np.uint64)  # 8-byte aligned host blob
+        _lib.check(L.b200q_gemv_program_build(arr, n, spec.fmt_id, self._host.ctypes.data, nbytes))
+        self._dev = torch.from_numpy(self._host.view(np.uint8)[:nbytes].copy()).to(dev)  # torch allocations are >= 256-byte aligned
+        ws_bytes = int(L.b200q_gemv_program_workspace_bytes(self._host.ctypes.data))
+        self._ws = torch.zeros(ws_bytes, dtype=torch.uint8, device=dev)
+        self.n_steps = n
+
+    def run(self):
+        L = _lib.lib()
+        _lib.check(L.b200q_gemv_program_run(self._host.ctypes.data, self._dev.data_ptr(), self._ws.data_ptr(),
+                                            self._ws.numel(), _stream()))
