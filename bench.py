@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-per-shape", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
-    ap.add_argument("--no-program", action="store_true", help="one launch per Linear (PDL chain) instead of the persistent decode program")
+    ap.add_argument("--program", type=int, default=0, help="1: the persistent decode-program kernel (one cooperative launch per collective-free segment); 0: one launch per fused Linear group, PDL chain")
     ap.add_argument("--no-fuse-qkv", action="store_true")
     ap.add_argument("--no-fuse-gate-up", action="store_true")
     ap.add_argument("--tune", default="", help="ctas_per_sm,stages,dbg_flags for b200q_gemv_tune (experiments)")
@@ -242,7 +242,7 @@ def main():
 
     stack = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, layers=args.layers,
                         pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up,
-                        use_program=not args.no_program)
+                        use_program=bool(args.program))
     if args.tune:
         ops.gemv_tune(*[int(v) for v in args.tune.split(",")])
     stack.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(stack.dt))
@@ -353,8 +353,13 @@ def main():
             out["cpu_baseline"] = cb
         print(json.dumps(out))
     if world > 1:
+        # leave without tearing NCCL down: destroy_process_group() can block forever while CUDA graphs that
+        # captured collectives are still alive; every rank has finished its work at this barrier
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def bench_shapes(stack, spec, torch, iters: int = 20):
