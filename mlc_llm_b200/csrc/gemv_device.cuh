@@ -119,6 +119,21 @@ __device__ __forceinline__ void compute_row_f32(uint4 w, uint4 sc, uint32_t xr, 
 
 // ---- activation staging: the whole x (optionally x * x_mul) into shared memory ---------------------
 // f16 formats: word row r -> xs[r][kXRowBytes] in the pair order the unpack produces.
+// one packed word row of activations (kNpu values, zero padded to 12) -> the pair order the unpack produces
+template <int FMT>
+__device__ __forceinline__ void permute_x_row(const __half (&v)[12], __half (&o)[12]) {
+  if constexpr (FMT == B200Q_Q4F16_0) {
+    o[0] = v[0]; o[1] = v[4]; o[2] = v[1]; o[3] = v[5];
+    o[4] = v[2]; o[5] = v[6]; o[6] = v[3]; o[7] = v[7];
+  } else if constexpr (FMT == B200Q_Q3F16_0) {
+    o[0] = v[0]; o[1] = v[5]; o[2] = v[1]; o[3] = v[6];
+    o[4] = v[2]; o[5] = v[7]; o[6] = v[3]; o[7] = v[8];
+    o[8] = v[4]; o[9] = v[9]; o[10] = __ushort_as_half(0); o[11] = __ushort_as_half(0);
+  } else {
+    o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
+  }
+}
+
 // CG: read the activation with ld.global.cg (L2 only): required when another CTA of the SAME launch
 // produced it (the persistent decode-program kernel); L1 is not coherent across SMs.
 template <bool CG, typename T>
@@ -127,7 +142,8 @@ __device__ __forceinline__ T ldx(const T* p) {
   else return *p;
 }
 template <int FMT, int NT, bool CG = false>
-__device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const void* xmul, int K, int rows) {
+__device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const void* xmul, int K, int rows,
+                                        int tid = threadIdx.x) {
   using S = XLayout<FMT>;
   using F = Fmt<FMT>;
   if constexpr (S::kF32) {
@@ -135,7 +151,7 @@ __device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const
     const float* m = reinterpret_cast<const float*>(xmul);
     float* dst = reinterpret_cast<float*>(xs);
     const int n = rows * 8;
-    for (int k = threadIdx.x; k < n; k += NT) {
+    for (int k = tid; k < n; k += NT) {
       float v = 0.f;
       if (k < K) v = m ? __fmul_rn(ldx<CG>(x + k), ldx<CG>(m + k)) : ldx<CG>(x + k);
       dst[k] = v;
@@ -146,7 +162,7 @@ __device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const
     constexpr int XB = S::kXRowBytes;
     const bool vec_ok = (F::kNpu == 8) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
                         (m == nullptr || (reinterpret_cast<uintptr_t>(m) & 15) == 0);
-    for (int lr = threadIdx.x; lr < rows; lr += NT) {
+    for (int lr = tid; lr < rows; lr += NT) {
       const int k0 = lr * F::kNpu;
       __align__(16) __half v[12];
 #pragma unroll
@@ -165,16 +181,7 @@ __device__ __forceinline__ void stage_x(unsigned char* xs, const void* xg, const
           if (k0 + t < K) v[t] = m ? __hmul(ldx<CG>(x + k0 + t), ldx<CG>(m + k0 + t)) : ldx<CG>(x + k0 + t);
       }
       __align__(8) __half o[12];
-      if constexpr (FMT == B200Q_Q4F16_0) {
-        o[0] = v[0]; o[1] = v[4]; o[2] = v[1]; o[3] = v[5];
-        o[4] = v[2]; o[5] = v[6]; o[6] = v[3]; o[7] = v[7];
-      } else if constexpr (FMT == B200Q_Q3F16_0) {
-        o[0] = v[0]; o[1] = v[5]; o[2] = v[1]; o[3] = v[6];
-        o[4] = v[2]; o[5] = v[7]; o[6] = v[3]; o[7] = v[8];
-        o[8] = v[4]; o[9] = v[9]; o[10] = __ushort_as_half(0); o[11] = __ushort_as_half(0);
-      } else {
-        o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
-      }
+      permute_x_row<FMT>(v, o);
       unsigned char* d = xs + (size_t)lr * XB;
 #pragma unroll
       for (int t = 0; t < XB / 8; ++t) reinterpret_cast<uint2*>(d)[t] = reinterpret_cast<const uint2*>(o)[t];

@@ -18,12 +18,18 @@
 //     time), so the memory pipe does not drain at step boundaries;
 //   * 16 consumer warps in four groups of four; group g owns ring stages g, g+4, ... (one warp = a
 //     16-row x 32-column box, the lane mapping and exact-dequant mma.sync contraction of gemv.cu);
-//   * K-split panels: partial sums go to per-step slots, the last CTA to arrive adds them in CTA
-//     order (deterministic) and applies the epilogue;
-//   * dependencies: every finished panel increments done[step]; before staging its activation a CTA
-//     polls (ld.acquire.gpu) until the producer steps of x / x_mul / ep0 are complete.  Activations
-//     written inside the launch are read with ld.global.cg (L1 is not coherent across SMs).
-//   * the last CTA to leave clears the counters, so the launch is re-playable from a CUDA graph.
+//   * the compute warps never touch global memory: at the end of a panel segment they hand their sums
+//     to four helper warps through shared memory (double-buffered, mbarriers) and go on;
+//   * everything that flows between CTAs inside the launch is "LL" data, NCCL-style: every value is
+//     stored together with a launch tag ({f16 | tag} in one 32-bit word, {f32, tag} in one 64-bit word)
+//     and the reader polls the word itself - no counters, no atomics, no fences, one round trip:
+//       - K-split panels: contributors store tagged partial sums into per-step slots; the CTA that
+//         owns the panel's last block polls them, adds them in block order (deterministic), applies
+//         the epilogue, and stores the result both to the caller's `out` and to the LL activation array;
+//       - activations: the helper warps of every CTA poll the LL words of x (x_mul, ep0) of the next
+//         step and stage them into the other half of a double-buffered shared-memory activation;
+//   * the tag is a launch counter kept in the workspace (bumped by the last CTA to leave), so the same
+//     launch can be replayed from a CUDA graph without clearing anything.
 #include <cuda.h>
 
 #include <cstdlib>
@@ -48,15 +54,21 @@ using namespace gemvdev;
 constexpr int kGroups = 4;                    // consumer warp groups
 constexpr int kWarpsPerGroup = 4;             // one warp per 32-column box of the 128-column block
 constexpr int kConsWarps = kGroups * kWarpsPerGroup;
-constexpr int kConsThreads = kConsWarps * 32;  // 512
-constexpr int kProgThreads = kConsThreads + 32;  // + producer warp
+constexpr int kHelperWarps = 4;               // 128 helper threads = one per panel column
+constexpr int kHelperThreads = kHelperWarps * 32;
+constexpr int kProducerWarp = kConsWarps;     // warp 16
+constexpr int kFirstHelperWarp = kConsWarps + 1;
+constexpr int kProgThreads = (kConsWarps + 1 + kHelperWarps) * 32;  // 672
 constexpr int kRows = 16;                     // packed word rows per block
 constexpr int kBoxBytes = kRows * kBoxCols * 4;          // 2048
 constexpr int kWordBytes = kRows * kPanelCols * 4;       // 8192
 constexpr int kMaxStages = 24;
 constexpr int kMaxOps = 4;
-constexpr int kMaxDeps = 4;
-constexpr int kHeader = 4096;                 // barriers (2 x 24 x 8) + flag + red[4][128] f32 (2048)
+// shared-memory header: ring barriers [2 x 24], hand-off barriers [8], red[2][4][128] f32 at 1024
+constexpr int kBarRedFull = 2 * kMaxStages, kBarRedEmpty = kBarRedFull + 2, kBarXFull = kBarRedEmpty + 2,
+              kBarXEmpty = kBarXFull + 2;
+constexpr int kRedOff = 1024;
+constexpr int kHeader = kRedOff + 2 * kGroups * kPanelCols * 4;  // 5120
 constexpr int kSmemPerSm = 227 * 1024;
 
 template <int FMT>
@@ -70,15 +82,18 @@ struct PCfg {
   static constexpr int kStageTx = kWordBytes + kScaleBytes;
   static constexpr int kStageBytes = (kStageTx + 1023) / 1024 * 1024;
   static constexpr int kXRowBytes = XLayout<FMT>::kXRowBytes;
+  static constexpr int kLLBytes = kF32 ? 8 : 4;  // one LL activation element
 };
 
 struct ProgOp {
-  const void* ep0;
+  const void* ep0;  // plain epilogue operand (used when ep0_ll < 0)
   void* out;
   int N;
   int epilogue;
   int panel_begin;
   int pad_;
+  long long ep0_ll;  // LL element offset of the operand's producer, or -1
+  long long out_ll;  // LL element offset of this output, or -1 (f32 logits of an f16 model)
 };
 
 // one step of the program; lives in DEVICE memory (tensor maps must be 64-byte aligned)
@@ -86,8 +101,10 @@ struct alignas(64) ProgStep {
   CUtensorMap tm_w[kMaxOps];
   CUtensorMap tm_s[kMaxOps];
   ProgOp op[kMaxOps];
-  const void* x;
-  const void* x_mul;
+  const void* x;      // plain activation (used when x_ll < 0)
+  const void* x_mul;  // plain, optional
+  long long x_ll;     // LL element offset, or -1
+  long long xmul_ll;  // LL element offset, or -1 (x_mul == nullptr: unused)
   int n_ops;
   int K;
   int n_rows;    // packed word rows
@@ -95,34 +112,46 @@ struct alignas(64) ProgStep {
   int n_panels;  // over all ops of the step
   int T;         // blocks of the step
   int c_max;     // partial slots per panel
-  int n_deps;
-  int deps[kMaxDeps];          // step indices whose outputs this step reads (or overwrites)
-  unsigned counter_off;        // panel counters of this step: ws_counters + counter_off
-  unsigned pad_;
-  unsigned long long partial_off;  // float offset of this step's partial slots
+  int has_xmul;
+  unsigned long long partial_off;  // uint2 offset of this step's partial slots
 };
 
 struct ProgHeader {  // first 64 bytes of the blob
   int magic, n_steps, fmt, xs_bytes;
-  unsigned n_counters;             // panel counters in total
-  unsigned pad_;
-  unsigned long long partial_floats;  // partial-slot floats in total
-  unsigned long long reserved[4];
+  int G, pad_;
+  unsigned long long ll_elems;       // LL activation elements in total
+  unsigned long long partial_slots;  // {f32, tag} partial-sum words in total
+  unsigned long long reserved[3];
 };
 static_assert(sizeof(ProgHeader) == 64, "header is one cache line");
-constexpr int kMagic = 0xB2009E;
+constexpr int kMagic = 0xB2009F;
 
-// workspace layout: [done: n_steps u32][exit: 1 u32][panel counters][pad to 256][partials f32]
-__host__ __device__ inline size_t ws_partial_byte_off(int n_steps, unsigned n_counters) {
-  size_t b = ((size_t)n_steps + 1 + n_counters) * 4;
-  return (b + 255) / 256 * 256;
+// workspace layout: [epoch u32, exit u32, pad to 256][LL activations][pad to 256][partial slots uint2]
+inline size_t ws_ll_off() { return 256; }
+inline size_t ws_partial_off(unsigned long long ll_elems, int ll_bytes) {
+  return (256 + (size_t)ll_elems * ll_bytes + 255) / 256 * 256;
 }
 
-__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ uint32_t ld_vol_u32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint2 ld_vol_v2(const void* p) {
+  uint2 v;
+  asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_vol_u32(void* p, uint32_t v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_vol_v2(void* p, uint32_t a, uint32_t b) {
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(a), "r"(b) : "memory");
 }
 __device__ __forceinline__ int find_op(const ProgStep& st, int panel) {
   int oi = 0;
@@ -134,10 +163,104 @@ __device__ __forceinline__ int find_op(const ProgStep& st, int panel) {
 __device__ __forceinline__ int cta_begin(int T, int i, int G) { return (int)((long long)i * T / G); }
 __device__ __forceinline__ int block_owner(int T, int t, int G) { return (int)((((long long)t + 1) * G - 1) / T); }
 
+// ---- LL element access ------------------------------------------------------------------------------------
+// f16 models: one 32-bit word {tag << 16 | f16 bits}; f32 model (q4f32_0): one 64-bit word {f32 bits, tag}
+__device__ __forceinline__ __half ll_poll_f16(const uint32_t* p, uint32_t tag) {
+  uint32_t w;
+  do { w = ld_vol_u32(p); } while ((w >> 16) != tag);
+  return __ushort_as_half((unsigned short)(w & 0xFFFFu));
+}
+__device__ __forceinline__ float ll_poll_f32(const uint2* p, uint32_t tag) {
+  uint2 w;
+  do { w = ld_vol_v2(p); } while (w.y != tag);
+  return __uint_as_float(w.x);
+}
+// kNpu consecutive f16 LL elements (one packed word row of x); elements >= n_valid read as zero
+template <int NPU>
+__device__ __forceinline__ void ll_load_row_f16(const uint32_t* ll, int n_valid, uint32_t tag, __half (&v)[12]) {
+  uint32_t w[NPU];
+  bool ok;
+  do {
+    ok = true;
+#pragma unroll
+    for (int t = 0; t < NPU; t += 2) {
+      if (t + 1 < n_valid) {
+        const uint2 pr = ld_vol_v2(ll + t);  // rows start 8-byte aligned (NPU even, arrays 16-byte aligned)
+        w[t] = pr.x;
+        w[t + 1] = pr.y;
+      } else {
+        w[t] = (t < n_valid) ? ld_vol_u32(ll + t) : (tag << 16);
+        w[t + 1] = tag << 16;
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < NPU; ++t) ok = ok && ((w[t] >> 16) == tag);
+  } while (!ok);
+#pragma unroll
+  for (int t = 0; t < NPU; ++t) v[t] = __ushort_as_half((unsigned short)(w[t] & 0xFFFFu));
+}
+template <int NPU>
+__device__ __forceinline__ void plain_load_row_f16(const __half* x, int k0, int K, __half (&v)[12]) {
+#pragma unroll
+  for (int t = 0; t < NPU; ++t) v[t] = (k0 + t < K) ? __ldcg(x + k0 + t) : __ushort_as_half(0);
+}
+
+// helper warps: stage the activation of a step (x, optionally x * x_mul) into `xs`
+template <int FMT>
+__device__ __forceinline__ void helper_stage_x(unsigned char* xs, const ProgStep& st, const void* ws_ll, uint32_t tag,
+                                               int ht) {
+  using C = PCfg<FMT>;
+  using F = Fmt<FMT>;
+  const int K = st.K, rows = st.RB * kRows;
+  if constexpr (C::kF32) {
+    const uint2* ll = reinterpret_cast<const uint2*>(ws_ll);
+    const float* x = reinterpret_cast<const float*>(st.x);
+    const float* m = reinterpret_cast<const float*>(st.x_mul);
+    float* dst = reinterpret_cast<float*>(xs);
+    const int n = rows * 8;
+    for (int k = ht; k < n; k += kHelperThreads) {
+      float v = 0.f;
+      if (k < K) {
+        v = (st.x_ll >= 0) ? ll_poll_f32(ll + st.x_ll + k, tag) : __ldcg(x + k);
+        if (st.has_xmul) v = __fmul_rn(v, (st.xmul_ll >= 0) ? ll_poll_f32(ll + st.xmul_ll + k, tag) : __ldcg(m + k));
+      }
+      dst[k] = v;
+    }
+  } else {
+    const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
+    const __half* x = reinterpret_cast<const __half*>(st.x);
+    const __half* m = reinterpret_cast<const __half*>(st.x_mul);
+    constexpr int XB = C::kXRowBytes;
+    for (int lr = ht; lr < rows; lr += kHelperThreads) {
+      const int k0 = lr * F::kNpu;
+      const int n_valid = min(F::kNpu, max(0, K - k0));
+      __align__(16) __half v[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) v[t] = __ushort_as_half(0);
+      if (n_valid > 0) {
+        if (st.x_ll >= 0) ll_load_row_f16<F::kNpu>(ll + st.x_ll + k0, n_valid, tag, v);
+        else plain_load_row_f16<F::kNpu>(x, k0, K, v);
+        if (st.has_xmul) {
+          __align__(16) __half mv[12];
+          if (st.xmul_ll >= 0) ll_load_row_f16<F::kNpu>(ll + st.xmul_ll + k0, n_valid, tag, mv);
+          else plain_load_row_f16<F::kNpu>(m, k0, K, mv);
+#pragma unroll
+          for (int t = 0; t < F::kNpu; ++t) v[t] = __hmul(v[t], mv[t]);
+        }
+      }
+      __align__(8) __half o[12];
+      permute_x_row<FMT>(v, o);
+      unsigned char* d = xs + (size_t)lr * XB;
+#pragma unroll
+      for (int t = 0; t < XB / 8; ++t) reinterpret_cast<uint2*>(d)[t] = reinterpret_cast<const uint2*>(o)[t];
+    }
+  }
+}
+
 template <int FMT>
 __global__ void __launch_bounds__(kProgThreads, 1)
-gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __restrict__ ws_u32,
-                    float* __restrict__ ws_partial, int stages, int xs_bytes, int debug) {
+gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
+                    int stages, int xs_bytes) {
   using C = PCfg<FMT>;
   using F = Fmt<FMT>;
   using scale_t = typename C::scale_t;
@@ -146,26 +269,31 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
 
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);            // full[kMaxStages], empty[kMaxStages]
-  int* flag = reinterpret_cast<int*>(smem + 2 * kMaxStages * 8);  // byte 384
-  float* red = reinterpret_cast<float*>(smem + 2048);             // [kGroups][128]
-  unsigned char* xs = smem + kHeader;
-  const uint32_t stage_base = (smem_u32(smem + kHeader + xs_bytes) + 1023u) & ~1023u;
-  const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kMaxStages;
-  unsigned* done = ws_u32;
-  unsigned* exit_ctr = ws_u32 + n_steps;
-  unsigned* counters = ws_u32 + n_steps + 1;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  float* red = reinterpret_cast<float*>(smem + kRedOff);  // [2][kGroups][128]
+  unsigned char* xs0 = smem + kHeader;                    // two activation buffers of xs_bytes each
+  const uint32_t stage_base = (smem_u32(smem + kHeader + 2 * xs_bytes) + 1023u) & ~1023u;
+  const uint32_t bar0 = smem_u32(bars);
+  const uint32_t full0 = bar0, empty0 = bar0 + 8 * kMaxStages;
+  const uint32_t red_full = bar0 + 8 * kBarRedFull, red_empty = bar0 + 8 * kBarRedEmpty;
+  const uint32_t x_full = bar0 + 8 * kBarXFull, x_empty = bar0 + 8 * kBarXEmpty;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, kWarpsPerGroup);
     }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(red_full + 8 * i, kConsWarps);
+      mbar_init(red_empty + 8 * i, kHelperWarps);
+      mbar_init(x_full + 8 * i, kHelperWarps);
+      mbar_init(x_empty + 8 * i, kConsWarps);
+    }
     fence_barrier_init();
   }
   __syncthreads();
 
-  if (warp == kConsWarps) {
+  if (warp == kProducerWarp) {
     // ================= producer: never waits for a dependency (weights are constants) ==================
     const uint64_t pol = l2_evict_first_policy();
     int s = 0;
@@ -196,7 +324,100 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
     return;
   }
 
-  // ================= consumers ============================================================================
+  if (warp >= kFirstHelperWarp) {
+    // ================= helpers: activation staging, cross-CTA reduction, epilogue (all global traffic) =====
+    const int ht = threadIdx.x - kFirstHelperWarp * 32;  // 0..127 = panel column
+    const uint32_t epoch = ld_acquire_u32(ws_ctrl);
+    const uint32_t tag = (epoch % 65535u) + 1u;  // 1..65535: never the zero of a fresh workspace
+    int u = 0, sgi = 0;  // steps with work / segments handed over so far
+    for (int j = 0; j < n_steps; ++j) {
+      const ProgStep& st = prog[j];
+      const int T = st.T, RB = st.RB;
+      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
+      if (t0 >= t1) continue;
+      // ---- stage x of this step into buffer u & 1 (polls the LL words of its producers) -------------------
+      const int xb = u & 1;
+      mbar_wait(x_empty + 8 * xb, ((u >> 1) & 1) ^ 1);
+      helper_stage_x<FMT>(xs0 + (size_t)xb * xs_bytes, st, ws_ll, tag, ht);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(x_full + 8 * xb);
+      ++u;
+      // ---- the CTA's panel segments of this step, in the compute warps' order --------------------------------
+      int panel = t0 / RB, rb = t0 - panel * RB;
+      int t = t0;
+      while (t < t1) {
+        const int rb_begin = rb;
+        const int n_blk = min(t1 - t, RB - rb);
+        t += n_blk;
+        rb += n_blk;
+        const int rbuf = sgi & 1;
+        mbar_wait(red_full + 8 * rbuf, (sgi >> 1) & 1);
+        const float* r4 = red + rbuf * (kGroups * kPanelCols) + ht;
+        float sum = (r4[0] + r4[kPanelCols]) + (r4[2 * kPanelCols] + r4[3 * kPanelCols]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(red_empty + 8 * rbuf);
+        ++sgi;
+
+        const ProgOp& op = st.op[find_op(st, panel)];
+        const int n = (panel - op.panel_begin) * kPanelCols + ht;
+        const bool complete = (rb_begin == 0) && (rb == RB);
+        bool finalize = true;
+        if (!complete) {
+          // contributors of the panel in block order (T >= G: every CTA between the owners of the first and
+          // last block holds >= 1 block; T < G: every block is a different CTA); the owner of the LAST block
+          // finishes the panel
+          const int first = block_owner(T, panel * RB, G);
+          const bool sparse = (T < G);
+          uint2* slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
+          if (rb < RB) {
+            const int my_slot = sparse ? rb_begin : b - first;
+            st_vol_v2(slot0 + (size_t)my_slot * kPanelCols + ht, __float_as_uint(sum), tag);
+            finalize = false;
+          } else {
+            const int n_before = sparse ? rb_begin : b - first;  // contributors ahead of this CTA
+            float tot = 0.f;
+            for (int o = 0; o < n_before; ++o) tot += ll_poll_f32(slot0 + (size_t)o * kPanelCols + ht, tag);
+            sum = tot + sum;
+          }
+        }
+        if (finalize && n < op.N) {
+          if constexpr (C::kF32) {
+            float e0 = 0.f;
+            if (op.ep0_ll >= 0) e0 = ll_poll_f32(reinterpret_cast<const uint2*>(ws_ll) + op.ep0_ll + n, tag);
+            else if (op.ep0) e0 = __ldcg(reinterpret_cast<const float*>(op.ep0) + n);
+            const float y = ep_f32(sum, op.epilogue, &e0, 0);
+            reinterpret_cast<float*>(op.out)[n] = y;
+            if (op.out_ll >= 0) st_vol_v2(reinterpret_cast<uint2*>(ws_ll) + op.out_ll + n, __float_as_uint(y), tag);
+          } else if (op.epilogue == B200Q_EP_CAST_F32) {
+            reinterpret_cast<float*>(op.out)[n] = sum;
+          } else {
+            __half e0 = __ushort_as_half(0);
+            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag);
+            else if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
+            const __half y = ep_f16(sum, op.epilogue, &e0, 0);
+            reinterpret_cast<__half*>(op.out)[n] = y;
+            if (op.out_ll >= 0)
+              st_vol_u32(reinterpret_cast<uint32_t*>(ws_ll) + op.out_ll + n, (tag << 16) | (uint32_t)__half_as_ushort(y));
+          }
+        }
+        if (rb == RB) { rb = 0; ++panel; }
+      }
+    }
+    // ---- leave: the last CTA bumps the launch tag ------------------------------------------------------------
+    asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");
+    if (ht == 0) {
+      __threadfence();
+      const unsigned old = atomicAdd(ws_ctrl + 1, 1u);
+      if (old == (unsigned)(G - 1)) {
+        ws_ctrl[1] = 0u;
+        __threadfence();
+        ws_ctrl[0] = epoch + 1u;
+      }
+    }
+    return;
+  }
+
+  // ================= compute warps ===========================================================================
   const int grp = warp >> 2, cq = warp & 3;  // group (ring stages grp, grp + 4, ...), 32-column box
   const int c = lane >> 2, tig = lane & 3;
   // lane rows of the 16-row block: 2 tig + j + 8 m  (j, m in {0,1}); swizzled chunk = c ^ (row & 7)
@@ -206,12 +427,12 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
   const uint32_t s_col = (cq * 32 + c * 4) * (int)sizeof(scale_t);
   const uint32_t s_off0 = kWordBytes + g0 * C::kScalePitch + s_col;
   const uint32_t s_off1 = kWordBytes + g1 * C::kScalePitch + s_col;
-  const uint32_t xs_lane = smem_u32(xs) + (2 * tig) * C::kXRowBytes;
-  const int tc = threadIdx.x;
+  const uint32_t xs_lane0 = smem_u32(xs0) + (2 * tig) * C::kXRowBytes;
 
-  int qm = 0;       // (CTA-local block sequence number) & 3
-  int sg = grp;     // ring slot of this group's next block
+  int qm = 0;    // (CTA-local block sequence number) & 3
+  int sg = grp;  // ring slot of this group's next block
   uint32_t phg = 0;
+  int u = 0, sgi = 0;
 
   for (int j = 0; j < n_steps; ++j) {
     const ProgStep& st = prog[j];
@@ -219,20 +440,13 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
     const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
     if (t0 >= t1) continue;  // CTA-uniform
 
-    // ---- dependencies: the steps that produce x / x_mul / ep0 must be complete ------------------------
-    if (tc < st.n_deps && !(debug & 1)) {
-      const int d = st.deps[tc];
-      const unsigned need = (unsigned)prog[d].n_panels;
-      while (ld_acquire_u32(done + d) < need) __nanosleep(32);
-    }
-    cons_sync();
-    stage_x<FMT, kConsThreads, true>(xs, st.x, st.x_mul, st.K, RB * kRows);
-    cons_sync();
+    const int xb = u & 1;
+    mbar_wait(x_full + 8 * xb, (u >> 1) & 1);  // the helpers have staged this step's activation
+    const uint32_t xs_lane = xs_lane0 + xb * xs_bytes;
 
     int panel = t0 / RB, rb = t0 - panel * RB;
     int t = t0;
     while (t < t1) {
-      const int rb_begin = rb;
       const int seg_end = min(t1, t + (RB - rb));
       float acc[2][4];
 #pragma unroll
@@ -253,29 +467,6 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
             compute_row_f32(w01, sc0, xr + C::kXRowBytes, acc[0]);
             compute_row_f32(w10, sc1, xr + 8 * C::kXRowBytes, acc[0]);
             compute_row_f32(w11, sc1, xr + 9 * C::kXRowBytes, acc[0]);
-          } else if (debug & 6) {
-            // experiments: 2 = unpack only (no MMA), 4 = MMA only (no unpack); results are garbage
-            const uint4 ws4[4] = {w00, w01, w10, w11};
-            __half2 s2[4];
-            split_scales(lds64(sw + s_off0), s2);
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-              const uint32_t wv[4] = {ws4[r].x, ws4[r].y, ws4[r].z, ws4[r].w};
-              const uint4 xv = lds128(xr + (r & 1) * C::kXRowBytes + (r >> 1) * 8 * C::kXRowBytes);
-              if (debug & 2) {
-                __half2 h[4];
-#pragma unroll
-                for (int q4 = 0; q4 < 4; ++q4) {
-                  if constexpr (FMT == B200Q_Q4F16_0) unpack_q4(wv[q4], s2[q4], h);
-                  acc[0][q4] += __uint_as_float(h2_as_u32(h[0]) ^ h2_as_u32(h[1]) ^ h2_as_u32(h[2]) ^ h2_as_u32(h[3]) ^ xv.x);
-                }
-              } else {
-                mma16816(acc[0], wv[0], wv[1], wv[2], wv[3], xv.x, xv.y);
-                mma16816(acc[0], wv[1], wv[2], wv[3], wv[0], xv.z, xv.w);
-                mma16816(acc[1], wv[2], wv[3], wv[0], wv[1], xv.x, xv.y);
-                mma16816(acc[1], wv[3], wv[0], wv[1], wv[2], xv.z, xv.w);
-              }
-            }
           } else {
             __half2 s2[4];
             split_scales(lds64(sw + s_off0), s2);
@@ -293,7 +484,7 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
         qm = (qm + 1) & (kGroups - 1);
       }
 
-      // ---- reduce the segment over the four groups, then across CTAs ------------------------------------
+      // ---- hand the segment's sums to the helpers and go on -------------------------------------------------
       float4 v4;
       if constexpr (C::kF32) {
 #pragma unroll
@@ -305,79 +496,17 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* __
       } else {
         v4 = make_float4(acc[0][0], acc[0][2], acc[1][0], acc[1][2]);  // columns 4c .. 4c+3
       }
-      if (tig == 0) *reinterpret_cast<float4*>(red + grp * kPanelCols + cq * 32 + c * 4) = v4;
-      cons_sync();
-
-      const ProgOp& op = st.op[find_op(st, panel)];
-      const int n = (panel - op.panel_begin) * kPanelCols + tc;
-      const bool col_thread = (tc < kPanelCols);
-      float sum = 0.f;
-      if (col_thread) sum = (red[tc] + red[kPanelCols + tc]) + (red[2 * kPanelCols + tc] + red[3 * kPanelCols + tc]);
-      const bool complete = (rb_begin == 0) && (rb == RB);
-      bool finalize = true;  // CTA-uniform
-      if (!complete) {
-        // contributors of the panel, in block order.  T >= G: every CTA between the owners of the first
-        // and the last block holds at least one block; T < G: a CTA holds at most one block, so every
-        // block of the panel is a different contributor
-        const int first = block_owner(T, panel * RB, G);
-        const int last = block_owner(T, panel * RB + RB - 1, G);
-        const bool sparse = (T < G);
-        const int n_contrib = sparse ? RB : last - first + 1;
-        const int my_slot = sparse ? rb_begin : b - first;
-        float* slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
-        if (col_thread) {
-          slot0[(size_t)my_slot * kPanelCols + tc] = sum;
-          __threadfence();
-        }
-        cons_sync();
-        if (tc == 0) {
-          unsigned* ctr = counters + st.counter_off + panel;
-          const unsigned old = atomicAdd(ctr, 1u);
-          const int is_last = (old == (unsigned)(n_contrib - 1));
-          if (is_last) *ctr = 0u;  // self-cleaning
-          *flag = is_last;
-        }
-        cons_sync();
-        finalize = (*flag != 0);
-        if (finalize && col_thread) {
-          __threadfence();
-          sum = 0.f;
-          for (int o = 0; o < n_contrib; ++o) sum += ld_cg_f32(slot0 + (size_t)o * kPanelCols + tc);
-        }
-      }
-      if (finalize) {
-        if (col_thread && n < op.N) {
-          if constexpr (C::kF32) {
-            float e0 = 0.f;
-            if (op.ep0) e0 = __ldcg(reinterpret_cast<const float*>(op.ep0) + n);
-            reinterpret_cast<float*>(op.out)[n] = ep_f32(sum, op.epilogue, &e0, 0);
-          } else {
-            if (op.epilogue == B200Q_EP_CAST_F32) {
-              reinterpret_cast<float*>(op.out)[n] = sum;
-            } else {
-              __half e0 = __ushort_as_half(0);
-              if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
-              reinterpret_cast<__half*>(op.out)[n] = ep_f16(sum, op.epilogue, &e0, 0);
-            }
-          }
-        }
-        if (col_thread) __threadfence();
-        cons_sync();
-        if (tc == 0) atomicAdd(done + j, 1u);  // one finished panel
-      }
+      const int rbuf = sgi & 1;
+      mbar_wait(red_empty + 8 * rbuf, ((sgi >> 1) & 1) ^ 1);
+      if (tig == 0) *reinterpret_cast<float4*>(red + rbuf * (kGroups * kPanelCols) + grp * kPanelCols + cq * 32 + c * 4) = v4;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(red_full + 8 * rbuf);
+      ++sgi;
       if (rb == RB) { rb = 0; ++panel; }
     }
-  }
-
-  // ---- leave: the last CTA clears the step counters so the launch can be replayed ----------------------
-  if (tc == 0) {
-    __threadfence();
-    const unsigned old = atomicAdd(exit_ctr, 1u);
-    if (old == (unsigned)(G - 1)) {
-      for (int j = 0; j < n_steps; ++j) done[j] = 0u;
-      *exit_ctr = 0u;
-      __threadfence();
-    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(x_empty + 8 * xb);  // this warp is done with the step's activation
+    ++u;
   }
 }
 
@@ -398,6 +527,8 @@ int build_step(ProgStep& st, const b200q_gemv_step& in, int G) {
   st.n_ops = in.n_ops;
   st.x = in.x;
   st.x_mul = in.x_mul;
+  st.has_xmul = in.x_mul ? 1 : 0;
+  st.x_ll = st.xmul_ll = -1;
   st.K = in.K;
   st.n_rows = n_words(FMT, in.K);
   st.RB = ceil_div(st.n_rows, kRows);
@@ -410,6 +541,7 @@ int build_step(ProgStep& st, const b200q_gemv_step& in, int G) {
     st.op[i].N = o.N;
     st.op[i].epilogue = o.epilogue;
     st.op[i].panel_begin = panels;
+    st.op[i].ep0_ll = st.op[i].out_ll = -1;
     panels += ceil_div(o.N, kPanelCols);
     if (int e = make_tmap_2d(&st.tm_w[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, o.packed, o.N, st.n_rows, kBoxCols, kRows,
                              CU_TENSOR_MAP_SWIZZLE_128B))
@@ -439,6 +571,10 @@ int stage_bytes_for(int fmt) {
     default: return PCfg<B200Q_Q4F32_0>::kStageBytes;
   }
 }
+int stages_for(int fmt, int xs_bytes) {
+  int s = (kSmemPerSm - kHeader - 2 * xs_bytes - 1024) / stage_bytes_for(fmt);
+  return s > kMaxStages ? kMaxStages : s;
+}
 
 }  // namespace
 
@@ -449,14 +585,36 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
   if ((reinterpret_cast<uintptr_t>(host_blob) & 7) != 0) return set_error(B200Q_ERR_BAD_ALIGN, "gemv_program_build: blob must be 8-byte aligned");
   std::memset(host_blob, 0, gemv_program_bytes(n_steps));
   ProgHeader* h = reinterpret_cast<ProgHeader*>(host_blob);
-  // the step array is copied to a 64-byte aligned device address by the caller; fill through a bounce
-  // copy because the host blob itself need not be 64-byte aligned
   unsigned char* base = reinterpret_cast<unsigned char*>(host_blob) + sizeof(ProgHeader);
   const int G = device_sm_count();
   const size_t el = fmt_is_f32(fmt) ? 4 : 2;
-  unsigned n_counters = 0;
-  unsigned long long partial_floats = 0;
+  unsigned long long ll_elems = 0, partial_slots = 0;
   int xs_bytes = 0;
+  auto step_at = [&](int j, ProgStep& out) { std::memcpy(&out, base + (size_t)j * sizeof(ProgStep), sizeof(ProgStep)); };
+  // An input of step j is an LL input when it IS (same address, same length) the output of an earlier
+  // step; it is external when it overlaps no output at all.  Anything else (partial overlap, an output
+  // that aliases another step's input or output) cannot be ordered by the tags and is rejected.
+  auto resolve = [&](int j, const void* p, int len, long long& ll_off) -> int {
+    ll_off = -1;
+    if (!p) return B200Q_OK;
+    const Range r = range_of(p, el * len);
+    for (int i = j - 1; i >= 0; --i) {
+      ProgStep ps;
+      step_at(i, ps);
+      for (int a = 0; a < ps.n_ops; ++a) {
+        const size_t oel = (!fmt_is_f32(fmt) && ps.op[a].epilogue == B200Q_EP_CAST_F32) ? 4 : el;
+        const Range ro = range_of(ps.op[a].out, oel * ps.op[a].N);
+        if (!r.overlaps(ro)) continue;
+        if (ps.op[a].out == p && ps.op[a].N == len && ps.op[a].out_ll >= 0) {
+          ll_off = ps.op[a].out_ll;
+          return B200Q_OK;
+        }
+        return set_error(B200Q_ERR_UNSUPPORTED,
+                         "gemv_program_build: an input of step %d partially overlaps (or re-types) the output of step %d", j, i);
+      }
+    }
+    return B200Q_OK;
+  };
   for (int j = 0; j < n_steps; ++j) {
     alignas(64) ProgStep st;
     std::memset(&st, 0, sizeof(st));
@@ -469,76 +627,47 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
       default: return set_error(B200Q_ERR_UNSUPPORTED, "gemv_program_build: fmt %d", fmt);
     }
     if (e) return e;
-    st.counter_off = n_counters;
-    n_counters += (unsigned)st.n_panels;
-    st.partial_off = partial_floats;
-    partial_floats += (unsigned long long)st.n_panels * st.c_max * kPanelCols;
+    st.partial_off = partial_slots;
+    partial_slots += (unsigned long long)st.n_panels * st.c_max * kPanelCols;
     const int xb = xs_bytes_for(fmt, st.K);
     if (xb > xs_bytes) xs_bytes = xb;
-
-    // hazards against every earlier step: RAW (we read what it writes), WAW, WAR (we overwrite what it reads)
-    Range in_j[2 + kMaxOps], out_j[kMaxOps];
-    int n_in = 0;
-    in_j[n_in++] = range_of(steps[j].x, el * steps[j].K);
-    in_j[n_in++] = range_of(steps[j].x_mul, el * steps[j].K);
-    for (int i = 0; i < steps[j].n_ops; ++i) {
-      const b200q_gemv_op& o = steps[j].ops[i];
-      const size_t oel = (o.epilogue == B200Q_EP_CAST_F32) ? 4 : el;
-      in_j[n_in++] = range_of(o.ep0, el * o.N);
-      out_j[i] = range_of(o.out, oel * o.N);
-    }
-    int deps[kMaxDeps];
-    int n_deps = 0;
-    for (int i = j - 1; i >= 0; --i) {
-      bool hazard = false;
-      for (int a = 0; a < steps[i].n_ops && !hazard; ++a) {
-        const b200q_gemv_op& oi = steps[i].ops[a];
-        const Range out_i = range_of(oi.out, ((oi.epilogue == B200Q_EP_CAST_F32) ? 4 : el) * oi.N);
-        for (int q = 0; q < n_in; ++q) hazard |= out_i.overlaps(in_j[q]);
-        for (int q = 0; q < steps[j].n_ops; ++q) {
-          hazard |= out_i.overlaps(out_j[q]);
-          hazard |= out_j[q].overlaps(range_of(oi.ep0, el * oi.N));
-        }
-      }
-      for (int q = 0; q < steps[j].n_ops && !hazard; ++q)
-        hazard = out_j[q].overlaps(range_of(steps[i].x, el * steps[i].K)) ||
-                 out_j[q].overlaps(range_of(steps[i].x_mul, el * steps[i].K));
-      if (!hazard) continue;
-      // already implied by a dependency we hold?  (i is an ancestor of a held dep d if d depends on it, transitively)
-      bool implied = false;
-      for (int d = 0; d < n_deps && !implied; ++d) {
-        // walk the dependency DAG of deps[d] (steps are few; depth-first over recorded deps)
-        int stack[256];
-        int sp = 0;
-        stack[sp++] = deps[d];
-        while (sp > 0 && !implied) {
-          const ProgStep* ps = reinterpret_cast<const ProgStep*>(base + (size_t)stack[--sp] * sizeof(ProgStep));
-          ProgStep tmp;
-          std::memcpy(&tmp, ps, sizeof(tmp));
-          for (int q = 0; q < tmp.n_deps; ++q) {
-            if (tmp.deps[q] == i) implied = true;
-            else if (tmp.deps[q] > i && sp < 256) stack[sp++] = tmp.deps[q];
+    if (int e2 = resolve(j, steps[j].x, st.K, st.x_ll)) return e2;
+    if (int e2 = resolve(j, steps[j].x_mul, st.K, st.xmul_ll)) return e2;
+    for (int i = 0; i < st.n_ops; ++i) {
+      if (int e2 = resolve(j, st.op[i].ep0, st.op[i].N, st.op[i].ep0_ll)) return e2;
+      // outputs: must not alias anything an earlier step reads or writes, nor this step's own inputs
+      const size_t oel = (!fmt_is_f32(fmt) && st.op[i].epilogue == B200Q_EP_CAST_F32) ? 4 : el;
+      const Range ro = range_of(st.op[i].out, oel * st.op[i].N);
+      for (int q = 0; q <= j; ++q) {
+        const b200q_gemv_step& sq = steps[q];
+        bool bad = ro.overlaps(range_of(sq.x, el * sq.K)) || ro.overlaps(range_of(sq.x_mul, el * sq.K));
+        for (int a = 0; a < sq.n_ops; ++a) {
+          bad = bad || ro.overlaps(range_of(sq.ops[a].ep0, el * sq.ops[a].N));
+          if (q < j || a < i) {
+            const size_t ael = (!fmt_is_f32(fmt) && sq.ops[a].epilogue == B200Q_EP_CAST_F32) ? 4 : el;
+            bad = bad || ro.overlaps(range_of(sq.ops[a].out, ael * sq.ops[a].N));
           }
         }
+        if (bad)
+          return set_error(B200Q_ERR_UNSUPPORTED,
+                           "gemv_program_build: the output %d of step %d aliases a buffer used by step %d (every output "
+                           "of a program needs its own buffer)", i, j, q);
       }
-      if (implied) continue;
-      if (n_deps == kMaxDeps)
-        return set_error(B200Q_ERR_UNSUPPORTED, "gemv_program_build: step %d has more than %d independent producers", j, kMaxDeps);
-      deps[n_deps++] = i;
+      if (fmt_is_f32(fmt) || st.op[i].epilogue != B200Q_EP_CAST_F32) {
+        st.op[i].out_ll = (long long)ll_elems;
+        ll_elems += (unsigned long long)((st.op[i].N + 3) / 4 * 4);  // keep every array 16-byte aligned
+      }
     }
-    st.n_deps = n_deps;
-    for (int d = 0; d < n_deps; ++d) st.deps[d] = deps[d];
     std::memcpy(base + (size_t)j * sizeof(ProgStep), &st, sizeof(st));
   }
   h->magic = kMagic;
   h->n_steps = n_steps;
   h->fmt = fmt;
   h->xs_bytes = xs_bytes;
-  h->n_counters = n_counters;
-  h->partial_floats = partial_floats;
-  h->reserved[0] = (unsigned long long)G;
-  const int stages = (kSmemPerSm - kHeader - xs_bytes - 1024) / stage_bytes_for(fmt);
-  if (stages < 2 * kGroups)
+  h->G = G;
+  h->ll_elems = ll_elems;
+  h->partial_slots = partial_slots;
+  if (stages_for(fmt, xs_bytes) < 2 * kGroups)
     return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_build: K too large for the activation stage (%d bytes)", xs_bytes);
   return B200Q_OK;
 }
@@ -546,7 +675,7 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
 size_t gemv_program_workspace_bytes(const void* host_blob) {
   const ProgHeader* h = reinterpret_cast<const ProgHeader*>(host_blob);
   if (h->magic != kMagic) return 0;
-  return ws_partial_byte_off(h->n_steps, h->n_counters) + (size_t)h->partial_floats * 4;
+  return ws_partial_off(h->ll_elems, fmt_is_f32(h->fmt) ? 8 : 4) + (size_t)h->partial_slots * 8;
 }
 
 int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
@@ -556,18 +685,17 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   if ((reinterpret_cast<uintptr_t>(dev_blob) & 63) != 0) return set_error(B200Q_ERR_BAD_ALIGN, "gemv_program_run: device blob must be 64-byte aligned");
   if (workspace_bytes < gemv_program_workspace_bytes(host_blob) || (reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: workspace too small or not 256-byte aligned");
-  const int G = (int)h->reserved[0];
+  const int G = h->G;
   if (G != device_sm_count()) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: program was built for %d SMs", G);
-  int stages = (kSmemPerSm - kHeader - h->xs_bytes - 1024) / stage_bytes_for(h->fmt);
-  if (stages > kMaxStages) stages = kMaxStages;
-  const size_t smem = (size_t)kHeader + h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
+  int stages = stages_for(h->fmt, h->xs_bytes);
+  const size_t smem = (size_t)kHeader + 2 * (size_t)h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
 
   const ProgStep* prog = reinterpret_cast<const ProgStep*>(reinterpret_cast<const unsigned char*>(dev_blob) + sizeof(ProgHeader));
-  unsigned* ws_u32 = reinterpret_cast<unsigned*>(workspace);
-  float* ws_partial = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + ws_partial_byte_off(h->n_steps, h->n_counters));
+  unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
+  unsigned* ws_ctrl = reinterpret_cast<unsigned*>(ws);
+  void* ws_ll = ws + ws_ll_off();
+  uint2* ws_partial = reinterpret_cast<uint2*>(ws + ws_partial_off(h->ll_elems, fmt_is_f32(h->fmt) ? 8 : 4));
   int n_steps = h->n_steps, xs_bytes = h->xs_bytes;
-  static const int dbg_env = getenv("B200Q_PROG_DEBUG") ? atoi(getenv("B200Q_PROG_DEBUG")) : 0;  // experiments: 1 = ignore dependencies
-  int debug = dbg_env;
 
   const void* kern = nullptr;
   switch (h->fmt) {
@@ -588,7 +716,7 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   attrs[0].val.cooperative = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
-  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_u32, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes, (void*)&debug};
+  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes};
   e = cudaLaunchKernelExC(&cfg, kern, args);
   if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelExC(gemv program)");
   count_launch();
