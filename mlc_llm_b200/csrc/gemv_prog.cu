@@ -118,7 +118,7 @@ struct alignas(64) ProgStep {
 
 struct ProgHeader {  // first 64 bytes of the blob
   int magic, n_steps, fmt, xs_bytes;
-  int G, pad_;
+  int G, tc;  // tc: 1 = the tcgen05 kernel of gemv_tc.cuh (q4f16_0)
   unsigned long long ll_elems;       // LL activation elements in total
   unsigned long long partial_slots;  // {f32, tag} partial-sum words in total
   unsigned long long reserved[3];
@@ -510,6 +510,8 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws
   }
 }
 
+#include "gemv_tc.cuh"
+
 // ---- host side -----------------------------------------------------------------------------------------
 struct Range {
   uintptr_t lo, hi;
@@ -521,7 +523,7 @@ Range range_of(const void* p, size_t bytes) {
 }
 
 template <int FMT>
-int build_step(ProgStep& st, const b200q_gemv_step& in, int G) {
+int build_step(ProgStep& st, const b200q_gemv_step& in, int G, bool use_tc) {
   using C = PCfg<FMT>;
   using F = Fmt<FMT>;
   st.n_ops = in.n_ops;
@@ -543,8 +545,10 @@ int build_step(ProgStep& st, const b200q_gemv_step& in, int G) {
     st.op[i].panel_begin = panels;
     st.op[i].ep0_ll = st.op[i].out_ll = -1;
     panels += ceil_div(o.N, kPanelCols);
-    if (int e = make_tmap_2d(&st.tm_w[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, o.packed, o.N, st.n_rows, kBoxCols, kRows,
-                             CU_TENSOR_MAP_SWIZZLE_128B))
+    if (int e = use_tc ? make_tmap_2d(&st.tm_w[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, o.packed, o.N, st.n_rows, kPanelCols,
+                                      kRows, CU_TENSOR_MAP_SWIZZLE_NONE)
+                       : make_tmap_2d(&st.tm_w[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, o.packed, o.N, st.n_rows, kBoxCols, kRows,
+                                      CU_TENSOR_MAP_SWIZZLE_128B))
       return e;
     if (int e = make_tmap_2d(&st.tm_s[i], C::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
                              (int)sizeof(typename C::scale_t), o.scale, o.N, n_grp, kPanelCols, C::kGroupsPerBlock,
@@ -571,9 +575,18 @@ int stage_bytes_for(int fmt) {
     default: return PCfg<B200Q_Q4F32_0>::kStageBytes;
   }
 }
-int stages_for(int fmt, int xs_bytes) {
+int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
+  if (use_tc) {
+    int s = (kSmemPerSm - tc::kHeaderTc - tc::kABufs * tc::kBSlotBytes - 2 * xs_bytes - 256) / tc::kStageBytesTc;
+    return s > tc::kMaxStagesTc ? tc::kMaxStagesTc : s;
+  }
   int s = (kSmemPerSm - kHeader - 2 * xs_bytes - 1024) / stage_bytes_for(fmt);
   return s > kMaxStages ? kMaxStages : s;
+}
+bool want_tc(int fmt) {
+  if (fmt != B200Q_Q4F16_0) return false;
+  const char* e = std::getenv("B200Q_PROG_TC");
+  return !(e && e[0] == '0');
 }
 
 }  // namespace
@@ -590,6 +603,7 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
   const size_t el = fmt_is_f32(fmt) ? 4 : 2;
   unsigned long long ll_elems = 0, partial_slots = 0;
   int xs_bytes = 0;
+  const bool use_tc = want_tc(fmt);
   auto step_at = [&](int j, ProgStep& out) { std::memcpy(&out, base + (size_t)j * sizeof(ProgStep), sizeof(ProgStep)); };
   // An input of step j is an LL input when it IS (same address, same length) the output of an earlier
   // step; it is external when it overlaps no output at all.  Anything else (partial overlap, an output
@@ -620,16 +634,16 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
     std::memset(&st, 0, sizeof(st));
     int e;
     switch (fmt) {
-      case B200Q_Q4F16_0: e = build_step<B200Q_Q4F16_0>(st, steps[j], G); break;
-      case B200Q_Q3F16_0: e = build_step<B200Q_Q3F16_0>(st, steps[j], G); break;
-      case B200Q_Q8F16_0: e = build_step<B200Q_Q8F16_0>(st, steps[j], G); break;
-      case B200Q_Q4F32_0: e = build_step<B200Q_Q4F32_0>(st, steps[j], G); break;
+      case B200Q_Q4F16_0: e = build_step<B200Q_Q4F16_0>(st, steps[j], G, use_tc); break;
+      case B200Q_Q3F16_0: e = build_step<B200Q_Q3F16_0>(st, steps[j], G, false); break;
+      case B200Q_Q8F16_0: e = build_step<B200Q_Q8F16_0>(st, steps[j], G, false); break;
+      case B200Q_Q4F32_0: e = build_step<B200Q_Q4F32_0>(st, steps[j], G, false); break;
       default: return set_error(B200Q_ERR_UNSUPPORTED, "gemv_program_build: fmt %d", fmt);
     }
     if (e) return e;
     st.partial_off = partial_slots;
     partial_slots += (unsigned long long)st.n_panels * st.c_max * kPanelCols;
-    const int xb = xs_bytes_for(fmt, st.K);
+    const int xb = use_tc ? tc::xs_bytes_tc(st.K) : xs_bytes_for(fmt, st.K);
     if (xb > xs_bytes) xs_bytes = xb;
     if (int e2 = resolve(j, steps[j].x, st.K, st.x_ll)) return e2;
     if (int e2 = resolve(j, steps[j].x_mul, st.K, st.xmul_ll)) return e2;
@@ -665,9 +679,10 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
   h->fmt = fmt;
   h->xs_bytes = xs_bytes;
   h->G = G;
+  h->tc = use_tc ? 1 : 0;
   h->ll_elems = ll_elems;
   h->partial_slots = partial_slots;
-  if (stages_for(fmt, xs_bytes) < 2 * kGroups)
+  if (stages_for(fmt, xs_bytes, use_tc) < 2 * kGroups)
     return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_build: K too large for the activation stage (%d bytes)", xs_bytes);
   return B200Q_OK;
 }
@@ -687,8 +702,11 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
     return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: workspace too small or not 256-byte aligned");
   const int G = h->G;
   if (G != device_sm_count()) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: program was built for %d SMs", G);
-  int stages = stages_for(h->fmt, h->xs_bytes);
-  const size_t smem = (size_t)kHeader + 2 * (size_t)h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
+  const bool use_tc = h->tc != 0;
+  int stages = stages_for(h->fmt, h->xs_bytes, use_tc);
+  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kABufs * tc::kBSlotBytes + 2 * (size_t)h->xs_bytes + 256 +
+                                   (size_t)stages * tc::kStageBytesTc
+                             : (size_t)kHeader + 2 * (size_t)h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
 
   const ProgStep* prog = reinterpret_cast<const ProgStep*>(reinterpret_cast<const unsigned char*>(dev_blob) + sizeof(ProgHeader));
   unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
@@ -704,11 +722,12 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
     case B200Q_Q8F16_0: kern = (const void*)gemv_program_kernel<B200Q_Q8F16_0>; break;
     default: kern = (const void*)gemv_program_kernel<B200Q_Q4F32_0>; break;
   }
+  if (use_tc) kern = (const void*)tc::gemv_program_tc_kernel;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemv program smem)");
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(G, 1, 1);
-  cfg.blockDim = dim3(kProgThreads, 1, 1);
+  cfg.blockDim = dim3(use_tc ? tc::kThreadsTc : kProgThreads, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attrs[1];

@@ -1,0 +1,527 @@
+// q4f16_0 decode-program kernel on the 5th-generation tensor cores (included by gemv_prog.cu, inside its
+// anonymous namespace; uses ProgStep / ProgOp and the LL helpers defined there).
+//
+// Why: mma.sync.m16n8k16 occupies the issue port of its SM sub-partition for 8 cycles on sm_100a
+// (scripts/ubench/pipes2.cu), and the exact per-weight dequant needs 8 FMA-pipe half2 operations per
+// packed word at 2 cycles each: 25 issue cycles per lane-word against a budget of 22.9 at HBM speed
+// (scripts/ubench/unpack.cu).  A register-level contraction can therefore not keep up with HBM3e.
+// Here the contraction runs on tcgen05.mma, which costs no issue slots of the math warps:
+//
+//   * a "group tile" is one quantization group of 128 output columns: 4 packed-word rows x 128 columns
+//     = 32 k x 128 n.  Thread n of a 128-thread dequant slice reads the four words of ITS column from the
+//     TMA ring, turns each nibble pair into the two f16 numbers (1024 + 16 q) with one LOP3
+//     ((w >> s) & 0x00F000F0 | 0x64006400 - no floating-point instruction at all) and stores the 16
+//     registers with tcgen05.st into a TMEM operand buffer: lane n = output column, 16 columns = 32 k;
+//   * the MMA warp issues two  tcgen05.mma.kind::f16  (M128 N16 K16, A from TMEM, B from shared memory)
+//     per group tile.  B is the activation of the group, written into row p of an otherwise zero
+//     16-row operand, p = position of the group inside the current accumulator: column p of the f32
+//     accumulator receives  T[n] = sum_k (1024 + 16 q[k,n]) x[k]  of that group and the other 15 columns
+//     receive zeros, so ONE accumulator keeps 16 group sums apart without being read in between;
+//   * the four epilogue warps (thread = output column) read a finished accumulator with tcgen05.ld and
+//     fold it:  y[n] += s[g,n] * (T[g,n] - 1136 * X[g]),  X[g] = sum of the group's activations (computed
+//     once when the activation is staged).  T - 1136 X = 16 * sum (q - 7) x  exactly, so the group scale is
+//     applied ONCE per group to an f32 sum instead of once per weight in f16: closer to real arithmetic
+//     than the reference's  f16((q - 7) * s)  weights (tolerance: oracle/quant_oracle.py::tolerance);
+//   * everything else is the persistent program of gemv_prog.cu: stream-K division, TMA producer that
+//     never waits for a dependency, LL (value|tag) dataflow between CTAs, replayable from a CUDA graph.
+#pragma once
+
+namespace tc {
+
+constexpr int kDqWarps = 16;                 // 4 slices (group of a stage) x 4 TMEM lane quadrants
+constexpr int kHelperWarp0 = 16;             // warps 16..19: epilogue + staging + cross-CTA traffic
+constexpr int kProducerWarpTc = 20;
+constexpr int kMmaWarp = 21;
+constexpr int kThreadsTc = 22 * 32;          // 704
+constexpr int kABufs = 8;                    // TMEM operand buffers (16 columns each) / B slots
+constexpr int kNAcc = 4;                     // accumulators in flight (16 columns each)
+constexpr int kTmemCols = 256;               // A: columns [0,128), D: [128,192)
+constexpr int kDCol0 = 128;
+constexpr int kStageWordBytes = kRows * kPanelCols * 4;             // 8192: [16 rows][128 cols] u32, no swizzle
+constexpr int kStageScaleBytes = 4 * kPanelCols * 2;                // 1024: [4 groups][128 cols] f16
+constexpr int kStageBytesTc = kStageWordBytes + kStageScaleBytes;   // 9216
+constexpr int kBSlotBytes = 1024;            // two K16 operands of 16 rows: [h][kc][j / 8][j % 8][16 B]
+constexpr int kMaxStagesTc = 24;
+// barriers (8 bytes each) in the first 1024 bytes
+constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + kABufs,
+              kBarAccFull = kBarAFree + kABufs, kBarAccFree = kBarAccFull + kNAcc, kBarXFullTc = kBarAccFree + kNAcc,
+              kBarXEmptyTc = kBarXFullTc + 2, kNumBars = kBarXEmptyTc + 2;  // 76
+constexpr int kTmemPtrOff = 8 * kNumBars;    // 608
+constexpr int kHeaderTc = 1024;
+constexpr float kCorr = 1136.0f;             // 1024 + 16 * 7
+
+// bytes of one activation buffer: 16 bytes per packed word row + one f32 correction per group
+__host__ __device__ inline int xs_bytes_tc(int K) {
+  const int rows = ceil_div(n_words(B200Q_Q4F16_0, K), kRows) * kRows;
+  return (rows * 16 + rows + 127) / 128 * 128;
+}
+
+__device__ __forceinline__ uint4 ld_vol_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t r;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ uint32_t lds16(uint32_t a) {
+  unsigned short r;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ float lds_f32(uint32_t a) {
+  float r;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// one packed word row of an input vector: 8 f16 values, zero beyond K.  LL: poll until all tags match.
+struct Row8 {
+  uint4 lo, hi;  // LL: 8 x {tag << 16 | f16}; plain: lo = 8 halves
+};
+__device__ __forceinline__ bool ll_row_ready(const Row8& r, uint32_t tag) {
+  return ((r.lo.x >> 16) == tag) & ((r.lo.y >> 16) == tag) & ((r.lo.z >> 16) == tag) & ((r.lo.w >> 16) == tag) &
+         ((r.hi.x >> 16) == tag) & ((r.hi.y >> 16) == tag) & ((r.hi.z >> 16) == tag) & ((r.hi.w >> 16) == tag);
+}
+__device__ __forceinline__ uint4 ll_row_pack(const Row8& r) {  // 8 halves in k order
+  return make_uint4(__byte_perm(r.lo.x, r.lo.y, 0x5410), __byte_perm(r.lo.z, r.lo.w, 0x5410),
+                    __byte_perm(r.hi.x, r.hi.y, 0x5410), __byte_perm(r.hi.z, r.hi.w, 0x5410));
+}
+
+// ---- activation staging (helper warps, 128 threads): x (optionally x * x_mul) of one step -> `xs` ------------
+// xs: 16 bytes per packed word row in the pair order of the unpack, (x0,x4)(x1,x5)(x2,x6)(x3,x7), zero beyond
+// K; followed by one f32 per group: 1136 * (sum of the group's activations).  All LL loads of a batch of four
+// rows per thread are issued before the first tag is checked (one L2 round trip per batch when the data is there).
+__device__ __forceinline__ __half tc_fetch(const __half* plain, const uint32_t* ll, long long ll_off, int k, uint32_t tag) {
+  return (ll_off >= 0) ? ll_poll_f16(ll + ll_off + k, tag) : __ldcg(plain + k);
+}
+__device__ __forceinline__ uint4 tc_finish_row(Row8& r, const __half* plain, const uint32_t* ll, long long ll_off, int k0,
+                                               int n_valid, bool vec, uint32_t tag) {
+  if (n_valid == 8 && ll_off >= 0) {
+    while (!ll_row_ready(r, tag)) {
+      r.lo = ld_vol_v4(ll + ll_off + k0);
+      r.hi = ld_vol_v4(ll + ll_off + k0 + 4);
+    }
+    return ll_row_pack(r);
+  }
+  if (n_valid == 8 && vec) return __ldcg(reinterpret_cast<const uint4*>(plain + k0));
+  __align__(16) __half v[8];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) v[t] = (t < n_valid) ? tc_fetch(plain, ll, ll_off, k0 + t, tag) : __ushort_as_half(0);
+  return *reinterpret_cast<const uint4*>(v);
+}
+// rows i = base + r * 128 + ht of the CTA's compacted row list (R rows per thread in flight)
+template <int R, bool kHasM>
+__device__ __forceinline__ void tc_stage_batch(unsigned char* xs, float* corr, const ProgStep& st, const uint32_t* ll,
+                                               uint32_t tag, int ht, int base, int n_rows_needed, int rb0) {
+  const int K = st.K, RB = st.RB;
+  const __half* xp = reinterpret_cast<const __half*>(st.x);
+  const __half* mp = reinterpret_cast<const __half*>(st.x_mul);
+  const long long x_ll = st.x_ll, m_ll = kHasM ? st.xmul_ll : -1;
+  const bool x_vec = (reinterpret_cast<uintptr_t>(xp) & 15) == 0, m_vec = (reinterpret_cast<uintptr_t>(mp) & 15) == 0;
+  Row8 rx[R], rm[kHasM ? R : 1];
+  int lrs[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int i = base + r * kHelperThreads + ht;
+    int blk = rb0 + (i >> 4);
+    if (blk >= RB) blk -= RB;
+    const int lr = (i < n_rows_needed) ? blk * kRows + (i & 15) : -1;
+    lrs[r] = lr;
+    const bool full = lr >= 0 && (lr * 8 + 8 <= K);
+    rx[r].lo = rx[r].hi = make_uint4(0, 0, 0, 0);
+    if (full && x_ll >= 0) {
+      rx[r].lo = ld_vol_v4(ll + x_ll + lr * 8);
+      rx[r].hi = ld_vol_v4(ll + x_ll + lr * 8 + 4);
+    }
+    if constexpr (kHasM) {
+      rm[r].lo = rm[r].hi = make_uint4(0, 0, 0, 0);
+      if (full && m_ll >= 0) {
+        rm[r].lo = ld_vol_v4(ll + m_ll + lr * 8);
+        rm[r].hi = ld_vol_v4(ll + m_ll + lr * 8 + 4);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int lr = lrs[r];
+    const int k0 = lr * 8;
+    const int n_valid = lr >= 0 ? min(8, max(0, K - k0)) : 0;
+    __align__(16) __half v[8];
+    *reinterpret_cast<uint4*>(v) = make_uint4(0, 0, 0, 0);
+    if (n_valid > 0) {
+      *reinterpret_cast<uint4*>(v) = tc_finish_row(rx[r], xp, ll, x_ll, k0, n_valid, x_vec, tag);
+      if constexpr (kHasM) {
+        __align__(16) __half mv[8];
+        *reinterpret_cast<uint4*>(mv) = tc_finish_row(rm[r], mp, ll, m_ll, k0, n_valid, m_vec, tag);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) v[t] = __hmul(v[t], mv[t]);
+      }
+    }
+    float sm = 0.f;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) sm += __half2float(v[t]);
+    sm += __shfl_xor_sync(0xffffffffu, sm, 1);
+    sm += __shfl_xor_sync(0xffffffffu, sm, 2);
+    if (lr >= 0) {
+      __align__(16) __half o[8] = {v[0], v[4], v[1], v[5], v[2], v[6], v[3], v[7]};
+      *reinterpret_cast<uint4*>(xs + (size_t)lr * 16) = *reinterpret_cast<const uint4*>(o);
+      if ((lr & 3) == 0) corr[lr >> 2] = kCorr * sm;
+    }
+  }
+}
+// stages the row blocks [rb0, rb0 + nb) (cyclic in RB) of the step's activation: only what this CTA's share
+// of the step reads
+__device__ __forceinline__ void tc_stage_x(unsigned char* xs, const ProgStep& st, const void* ws_ll, uint32_t tag, int ht,
+                                           int rb0, int nb) {
+  float* corr = reinterpret_cast<float*>(xs + (size_t)st.RB * kRows * 16);
+  const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
+  const int n_rows_needed = nb * kRows;
+  if (st.has_xmul) {
+    for (int base = 0; base < n_rows_needed; base += 2 * kHelperThreads)
+      tc_stage_batch<2, true>(xs, corr, st, ll, tag, ht, base, n_rows_needed, rb0);
+  } else {
+    for (int base = 0; base < n_rows_needed; base += 4 * kHelperThreads)
+      tc_stage_batch<4, false>(xs, corr, st, ll, tag, ht, base, n_rows_needed, rb0);
+  }
+}
+
+// (w >> s) & 0x00F000F0 | 0x64006400: the f16 pair (1024 + 16 q_lo, 1024 + 16 q_hi) of nibbles s/4 and s/4 + 4
+__device__ __forceinline__ void unpack_q4_direct(uint32_t w, uint32_t* out) {
+  const uint32_t kMagic = 0x64006400u, kMask = 0x00F000F0u;
+  out[0] = lop3_and_or(w << 4, kMask, kMagic);  // (v0, v4)
+  out[1] = lop3_and_or(w, kMask, kMagic);       // (v1, v5)
+  out[2] = lop3_and_or(w >> 4, kMask, kMagic);  // (v2, v6)
+  out[3] = lop3_and_or(w >> 8, kMask, kMagic);  // (v3, v7)
+}
+
+// shared-memory map: [0,1024) barriers + TMEM pointer | B slots 8 x 1 KB | two activation buffers | ring
+__global__ void __launch_bounds__(kThreadsTc, 1)
+gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
+                       int stages, int xs_bytes) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int G = gridDim.x, b = blockIdx.x;
+
+  const uint32_t bar0 = smem_u32(smem);
+  const uint32_t full0 = bar0 + 8 * kBarFull, empty0 = bar0 + 8 * kBarEmpty;
+  const uint32_t aready0 = bar0 + 8 * kBarAReady, afree0 = bar0 + 8 * kBarAFree;
+  const uint32_t accfull0 = bar0 + 8 * kBarAccFull, accfree0 = bar0 + 8 * kBarAccFree;
+  const uint32_t xfull0 = bar0 + 8 * kBarXFullTc, xempty0 = bar0 + 8 * kBarXEmptyTc;
+  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + kTmemPtrOff);
+  unsigned char* bslots = smem + kHeaderTc;
+  unsigned char* xs0 = bslots + kABufs * kBSlotBytes;
+  const uint32_t stage_base = (smem_u32(xs0 + 2 * xs_bytes) + 127u) & ~127u;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, kDqWarps + kHelperWarps);
+    }
+    for (int i = 0; i < kABufs; ++i) {
+      mbar_init(aready0 + 8 * i, 4);
+      mbar_init(afree0 + 8 * i, 1);
+    }
+    for (int i = 0; i < kNAcc; ++i) {
+      mbar_init(accfull0 + 8 * i, 1);
+      mbar_init(accfree0 + 8 * i, kHelperWarps);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(xfull0 + 8 * i, kHelperWarps);
+      mbar_init(xempty0 + 8 * i, kDqWarps);
+    }
+    fence_barrier_init();
+  }
+  // the B slots start as zeros: only the four 16-byte activation chunks of a group are ever rewritten
+  for (int i = threadIdx.x; i < kABufs * kBSlotBytes / 16; i += kThreadsTc)
+    reinterpret_cast<uint4*>(bslots)[i] = make_uint4(0, 0, 0, 0);
+  if (warp == kMmaWarp) {
+    tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_ptr)), kTmemCols);
+    tmem_relinquish();
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == kProducerWarpTc) {
+    // ================= producer: never waits for a dependency (weights are constants) ==================
+    const uint64_t pol = l2_evict_first_policy();
+    int s = 0;
+    uint32_t ph = 0;
+    for (int j = 0; j < n_steps; ++j) {
+      const ProgStep& st = prog[j];
+      const int T = st.T, RB = st.RB;
+      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
+      int panel = t0 / RB, rb = t0 - panel * RB;
+      for (int t = t0; t < t1; ++t) {
+        const int oi = find_op(st, panel);
+        const int col0 = (panel - st.op[oi].panel_begin) * kPanelCols;
+        mbar_wait(empty0 + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          const uint32_t bar = full0 + 8 * s;
+          mbar_expect_tx(bar, (uint32_t)kStageBytesTc);
+          const uint32_t sw = stage_base + s * kStageBytesTc;
+          tma_load_2d_hint(sw, &st.tm_w[oi], col0, rb * kRows, bar, pol);
+          tma_load_2d_hint(sw + kStageWordBytes, &st.tm_s[oi], col0, rb * 4, bar, pol);
+        }
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1; }
+        if (++rb == RB) { rb = 0; ++panel; }
+      }
+    }
+  } else if (warp < kDqWarps) {
+    // ================= dequant warps: ring -> registers -> TMEM operand buffers ============================
+    const int q = warp & 3, sl = warp >> 2;  // TMEM lane quadrant (= warp id % 4), group of the stage
+    const int n = q * 32 + lane;
+    const uint32_t w_off = (uint32_t)(4 * sl) * (kPanelCols * 4) + (uint32_t)n * 4;
+    const uint32_t a_taddr0 = tmem_base + ((uint32_t)(q * 32) << 16);
+    int s = 0;
+    uint32_t ph = 0;
+    int m = 0, u = 0;
+    int jo0 = 0, jo1 = 0;
+    for (int j = 0; j < n_steps; ++j) {
+      const ProgStep& st = prog[j];
+      const int T = st.T, RB = st.RB;
+      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
+      if (t0 >= t1) continue;
+      const int xb = u & 1;
+      bool x_waited = false;
+      const uint32_t xs_u32 = smem_u32(xs0 + (size_t)xb * xs_bytes);
+      int panel = t0 / RB, rb = t0 - panel * RB;
+      int t = t0;
+      while (t < t1) {
+        const int n_blk = min(t1 - t, RB - rb);
+        for (int bseg = 0; bseg < n_blk; ++bseg, ++m) {
+          mbar_wait(full0 + 8 * s, ph);
+          const uint32_t sw = stage_base + s * kStageBytesTc + w_off;
+          const uint32_t w0 = lds32(sw), w1 = lds32(sw + 512), w2 = lds32(sw + 1024), w3 = lds32(sw + 1536);
+          uint32_t a[16];
+          unpack_q4_direct(w0, a);
+          unpack_q4_direct(w1, a + 4);
+          unpack_q4_direct(w2, a + 8);
+          unpack_q4_direct(w3, a + 12);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(empty0 + 8 * s);  // the words are in registers
+          const int buf = 4 * (m & 1) + sl;
+          mbar_wait(afree0 + 8 * buf, ((m >> 1) & 1) ^ 1);  // the MMAs of this buffer's previous group are done
+          tc_fence_after();
+          tmem_st_32x16(a_taddr0 + buf * 16, a);
+          if (q == 0) {
+            if (!x_waited) {
+              mbar_wait(xfull0 + 8 * xb, (u >> 1) & 1);
+              x_waited = true;
+            }
+            if (lane < 4) {
+              // activation row `lane` of the group -> row p of the B operand; zero the row of the previous use
+              const int p = 4 * (bseg & 3) + sl, po = (m & 1) ? jo1 : jo0;
+              const uint32_t slot = smem_u32(bslots) + buf * kBSlotBytes + (lane >> 1) * 512 + (lane & 1) * 256;
+              const uint4 xv = *reinterpret_cast<const uint4*>(xs0 + (size_t)xb * xs_bytes + (size_t)((rb + bseg) * kRows + 4 * sl + lane) * 16);
+              sts128(slot + (po >> 3) * 128 + (po & 7) * 16, make_uint4(0, 0, 0, 0));
+              sts128(slot + (p >> 3) * 128 + (p & 7) * 16, xv);
+            }
+            if (m & 1) jo1 = 4 * (bseg & 3) + sl; else jo0 = 4 * (bseg & 3) + sl;
+            fence_proxy_async_smem();
+          }
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(aready0 + 8 * buf);
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+        t += n_blk;
+        rb += n_blk;
+        if (rb == RB) { rb = 0; ++panel; }
+      }
+      (void)xs_u32;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(xempty0 + 8 * xb);
+      ++u;
+    }
+  } else if (warp == kMmaWarp) {
+    // ================= MMA warp: two tcgen05.mma per group tile ============================================
+    const uint32_t idesc = make_idesc_f16(128, 16, 0, 0);
+    const uint64_t bdesc_hi = make_smem_desc_nosw(0, 256, 128);  // everything but the start address
+    const uint32_t bslot_u32 = smem_u32(bslots);
+    int m = 0, a = 0;
+    for (int j = 0; j < n_steps; ++j) {
+      const ProgStep& st = prog[j];
+      const int T = st.T, RB = st.RB;
+      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
+      if (t0 >= t1) continue;
+      int rb = t0 % RB;
+      int t = t0;
+      while (t < t1) {
+        const int n_blk = min(t1 - t, RB - rb);
+        for (int bseg = 0; bseg < n_blk; ++bseg, ++m) {
+          const uint32_t d_taddr = tmem_base + kDCol0 + (a & (kNAcc - 1)) * 16;
+          if ((bseg & 3) == 0) {
+            mbar_wait(accfree0 + 8 * (a & (kNAcc - 1)), ((a / kNAcc) & 1) ^ 1);  // the epilogue has read it
+            tc_fence_after();
+          }
+#pragma unroll
+          for (int sl = 0; sl < 4; ++sl) {
+            const int buf = 4 * (m & 1) + sl;
+            mbar_wait(aready0 + 8 * buf, (m >> 1) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t a_taddr = tmem_base + buf * 16;
+              const uint32_t bs = bslot_u32 + buf * kBSlotBytes;
+              const uint32_t first = ((bseg & 3) == 0 && sl == 0) ? 0u : 1u;
+              umma_f16_ts(d_taddr, a_taddr, bdesc_hi | (uint64_t)((bs & 0x3FFFFu) >> 4), idesc, first);
+              umma_f16_ts(d_taddr, a_taddr + 8, bdesc_hi | (uint64_t)(((bs + 512) & 0x3FFFFu) >> 4), idesc, 1u);
+              umma_commit(afree0 + 8 * buf);
+            }
+            __syncwarp();
+          }
+          if ((bseg & 3) == 3 || bseg == n_blk - 1) {
+            if (elect_one()) umma_commit(accfull0 + 8 * (a & (kNAcc - 1)));
+            __syncwarp();
+            ++a;
+          }
+        }
+        t += n_blk;
+        rb += n_blk;
+        if (rb == RB) rb = 0;
+      }
+    }
+  } else {
+    // ================= helper warps: staging, accumulator read-out, cross-CTA reduction, epilogue ============
+    const int hq = warp - kHelperWarp0;  // TMEM lane quadrant (warp 16 + hq, (16 + hq) % 4 == hq)
+    const int ht = hq * 32 + lane;       // panel column
+    const uint32_t d_taddr0 = tmem_base + ((uint32_t)(hq * 32) << 16) + kDCol0;
+    const uint32_t epoch = ld_acquire_u32(ws_ctrl);
+    const uint32_t tag = (epoch % 65535u) + 1u;
+    int s = 0;
+    int m = 0, a = 0, u = 0;
+    for (int j = 0; j < n_steps; ++j) {
+      const ProgStep& st = prog[j];
+      const int T = st.T, RB = st.RB;
+      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
+      if (t0 >= t1) continue;
+      const int xb = u & 1;
+      unsigned char* xs = xs0 + (size_t)xb * xs_bytes;
+      mbar_wait(xempty0 + 8 * xb, ((u >> 1) & 1) ^ 1);
+      tc_stage_x(xs, st, ws_ll, tag, ht, t0 % RB, min(RB, t1 - t0));
+      asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");  // corr[] is read by all helper warps
+      if (lane == 0) mbar_arrive(xfull0 + 8 * xb);
+      ++u;
+      const uint32_t corr_u32 = smem_u32(xs + (size_t)RB * kRows * 16);
+
+      int panel = t0 / RB, rb = t0 - panel * RB;
+      int t = t0;
+      while (t < t1) {
+        const int rb_begin = rb;
+        const int n_blk = min(t1 - t, RB - rb);
+        float sum = 0.f;
+        for (int b0 = 0; b0 < n_blk; b0 += 4) {
+          const int cnt = min(4, n_blk - b0);
+          const int ai = a & (kNAcc - 1);
+          mbar_wait(accfull0 + 8 * ai, (a / kNAcc) & 1);
+          tc_fence_after();
+          uint32_t d[16];
+          tmem_ld_32x16(d_taddr0 + ai * 16, d);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(accfree0 + 8 * ai);
+          ++a;
+#pragma unroll
+          for (int bb = 0; bb < 4; ++bb) {
+            if (bb < cnt) {
+              const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
+              const uint32_t c_addr = corr_u32 + (uint32_t)((rb + b0 + bb) * 4) * 4;
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                const float sc = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
+                const float cg = lds_f32(c_addr + g * 4);
+                sum = fmaf(sc, __uint_as_float(d[4 * bb + g]) - cg, sum);
+              }
+              __syncwarp();
+              if (lane == 0) mbar_arrive(empty0 + 8 * s);
+              if (++s == stages) s = 0;
+              ++m;
+            }
+          }
+        }
+        sum *= 0.0625f;
+        t += n_blk;
+        rb += n_blk;
+
+        // ---- cross-CTA reduction + epilogue of the panel (as gemv_program_kernel's helpers) ---------------------
+        const ProgOp& op = st.op[find_op(st, panel)];
+        const int n = (panel - op.panel_begin) * kPanelCols + ht;
+        const bool complete = (rb_begin == 0) && (rb == RB);
+        bool finalize = true;
+        if (!complete) {
+          const int first = block_owner(T, panel * RB, G);
+          const bool sparse = (T < G);
+          uint2* slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
+          if (rb < RB) {
+            const int my_slot = sparse ? rb_begin : b - first;
+            st_vol_v2(slot0 + (size_t)my_slot * kPanelCols + ht, __float_as_uint(sum), tag);
+            finalize = false;
+          } else {
+            const int n_before = sparse ? rb_begin : b - first;
+            float tot = 0.f;
+            for (int o0 = 0; o0 < n_before; o0 += 4) {  // up to four polls in flight
+              uint2 pv[4];
+#pragma unroll
+              for (int o = 0; o < 4; ++o)
+                if (o0 + o < n_before) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
+#pragma unroll
+              for (int o = 0; o < 4; ++o)
+                if (o0 + o < n_before) {
+                  while (pv[o].y != tag) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
+                  tot += __uint_as_float(pv[o].x);
+                }
+            }
+            sum = tot + sum;
+          }
+        }
+        if (finalize && n < op.N) {
+          if (op.epilogue == B200Q_EP_CAST_F32) {
+            reinterpret_cast<float*>(op.out)[n] = sum;
+          } else {
+            __half e0 = __ushort_as_half(0);
+            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag);
+            else if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
+            const __half y = ep_f16(sum, op.epilogue, &e0, 0);
+            if (op.out_ll >= 0)
+              st_vol_u32(reinterpret_cast<uint32_t*>(ws_ll) + op.out_ll + n, (tag << 16) | (uint32_t)__half_as_ushort(y));
+            reinterpret_cast<__half*>(op.out)[n] = y;
+          }
+        }
+        if (rb == RB) { rb = 0; ++panel; }
+      }
+    }
+    // ---- leave: the last CTA bumps the launch tag ------------------------------------------------------------
+    asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");
+    if (ht == 0) {
+      __threadfence();
+      const unsigned old = atomicAdd(ws_ctrl + 1, 1u);
+      if (old == (unsigned)(G - 1)) {
+        ws_ctrl[1] = 0u;
+        __threadfence();
+        ws_ctrl[0] = epoch + 1u;
+      }
+    }
+    (void)m;
+  }
+
+  // every accumulator has been read (the helpers waited for the last commit): TMEM can go back
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace tc
