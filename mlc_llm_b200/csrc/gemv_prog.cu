@@ -34,6 +34,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <cstdio>
 
 #include "common.cuh"
 #include "gemv_device.cuh"
@@ -735,7 +736,9 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   attrs[0].val.cooperative = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
-  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes};
+  int dbg = 0;
+  if (const char* e = std::getenv("B200Q_TC_DBG")) dbg = std::atoi(e);
+  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes, (void*)&dbg};
   e = cudaLaunchKernelExC(&cfg, kern, args);
   if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelExC(gemv program)");
   count_launch();

@@ -31,22 +31,25 @@ namespace tc {
 constexpr int kDqWarps = 16;                 // 4 slices (group of a stage) x 4 TMEM lane quadrants
 constexpr int kHelperWarp0 = 16;             // warps 16..19: epilogue + staging + cross-CTA traffic
 constexpr int kProducerWarpTc = 20;
-constexpr int kMmaWarp = 21;
-constexpr int kThreadsTc = 22 * 32;          // 704
-constexpr int kABufs = 8;                    // TMEM operand buffers (16 columns each) / B slots
-constexpr int kNAcc = 4;                     // accumulators in flight (16 columns each)
-constexpr int kTmemCols = 256;               // A: columns [0,128), D: [128,192)
-constexpr int kDCol0 = 128;
+constexpr int kMmaWarp = 21;                 // blocks with even sequence number
+constexpr int kBWriterWarp = 22;             // fills the B operand slots (activation rows)
+constexpr int kMmaWarp2 = 23;                // blocks with odd sequence number
+constexpr int kThreadsTc = 24 * 32;          // 768
+constexpr int kASets = 4;                    // stages of operand buffers in flight
+constexpr int kABufs = 4 * kASets;           // TMEM operand buffers (16 columns each) / B slots
+constexpr int kNAcc = 8;                     // accumulators in flight (one per block, 16 columns each)
+constexpr int kTmemCols = 512;               // A: columns [0,256), D: [256,384)
+constexpr int kDCol0 = 256;
 constexpr int kStageWordBytes = kRows * kPanelCols * 4;             // 8192: [16 rows][128 cols] u32, no swizzle
 constexpr int kStageScaleBytes = 4 * kPanelCols * 2;                // 1024: [4 groups][128 cols] f16
 constexpr int kStageBytesTc = kStageWordBytes + kStageScaleBytes;   // 9216
 constexpr int kBSlotBytes = 1024;            // two K16 operands of 16 rows: [h][kc][j / 8][j % 8][16 B]
 constexpr int kMaxStagesTc = 24;
 // barriers (8 bytes each) in the first 1024 bytes
-constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + kABufs,
-              kBarAccFull = kBarAFree + kABufs, kBarAccFree = kBarAccFull + kNAcc, kBarXFullTc = kBarAccFree + kNAcc,
-              kBarXEmptyTc = kBarXFullTc + 2, kNumBars = kBarXEmptyTc + 2;  // 76
-constexpr int kTmemPtrOff = 8 * kNumBars;    // 608
+constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + kASets,
+              kBarAccFull = kBarAFree + kASets, kBarAccFree = kBarAccFull + kNAcc, kBarXFullTc = kBarAccFree + kNAcc,
+              kBarXEmptyTc = kBarXFullTc + 2, kNumBars = kBarXEmptyTc + 2;  // 68
+constexpr int kTmemPtrOff = 8 * kNumBars;    // 544
 constexpr int kHeaderTc = 1024;
 constexpr float kCorr = 1136.0f;             // 1024 + 16 * 7
 
@@ -200,10 +203,24 @@ __device__ __forceinline__ void unpack_q4_direct(uint32_t w, uint32_t* out) {
   out[3] = lop3_and_or(w >> 8, kMask, kMagic);  // (v3, v7)
 }
 
-// shared-memory map: [0,1024) barriers + TMEM pointer | B slots 8 x 1 KB | two activation buffers | ring
+#ifdef B200Q_TC_TIMING
+#define TC_T0() long long _t0 = clock64()
+#define TC_ACC(v) do { long long _t1 = clock64(); (v) += _t1 - _t0; _t0 = _t1; } while (0)
+#else
+#define TC_T0() do { } while (0)
+#define TC_ACC(v) do { } while (0)
+#endif
+
+// shared-memory map: [0,1024) barriers + TMEM pointer | B slots 16 x 1 KB | two activation buffers | ring
+//
+// Block m (CTA-local sequence number of a 16-row x 128-column stage) is handled by
+//   dequant slice  m % 4  (warps 4 sl .. 4 sl + 3; thread = output column): its four groups -> operand set m % 4,
+//   MMA warp       m % 2,  accumulator m % 8 (group g in column g),
+// so the four warps that share an SM sub-partition (same lane quadrant, different slice) work on different
+// blocks and are never in the same phase of their loop.
 __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
-                       int stages, int xs_bytes) {
+                       int stages, int xs_bytes, int dbg) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
@@ -221,10 +238,10 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, kDqWarps + kHelperWarps);
+      mbar_init(empty0 + 8 * s, 4 + kHelperWarps);  // the block's dequant slice + the epilogue warps
     }
-    for (int i = 0; i < kABufs; ++i) {
-      mbar_init(aready0 + 8 * i, 4);
+    for (int i = 0; i < kASets; ++i) {
+      mbar_init(aready0 + 8 * i, 4 + 1);  // dequant slice + B writer
       mbar_init(afree0 + 8 * i, 1);
     }
     for (int i = 0; i < kNAcc; ++i) {
@@ -233,11 +250,11 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(xfull0 + 8 * i, kHelperWarps);
-      mbar_init(xempty0 + 8 * i, kDqWarps);
+      mbar_init(xempty0 + 8 * i, 1);
     }
     fence_barrier_init();
   }
-  // the B slots start as zeros: only the four 16-byte activation chunks of a group are ever rewritten
+  // the B slots start as zeros: slot (set, g) only ever gets activation rows written into operand row g
   for (int i = threadIdx.x; i < kABufs * kBSlotBytes / 16; i += kThreadsTc)
     reinterpret_cast<uint4*>(bslots)[i] = make_uint4(0, 0, 0, 0);
   if (warp == kMmaWarp) {
@@ -252,146 +269,126 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
 
   if (warp == kProducerWarpTc) {
     // ================= producer: never waits for a dependency (weights are constants) ==================
-    const uint64_t pol = l2_evict_first_policy();
-    int s = 0;
-    uint32_t ph = 0;
-    for (int j = 0; j < n_steps; ++j) {
-      const ProgStep& st = prog[j];
-      const int T = st.T, RB = st.RB;
-      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
-      int panel = t0 / RB, rb = t0 - panel * RB;
-      for (int t = t0; t < t1; ++t) {
-        const int oi = find_op(st, panel);
-        const int col0 = (panel - st.op[oi].panel_begin) * kPanelCols;
-        mbar_wait(empty0 + 8 * s, ph ^ 1);
-        if (elect_one()) {
+    // (the whole loop runs in ONE elected lane: an elect + branch + __syncwarp per iteration costs ~100 cycles,
+    // scripts/ubench/umma_small.cu)
+    if (elect_one()) {
+      const uint64_t pol = l2_evict_first_policy();
+      int s = 0;
+      uint32_t ph = 0;
+      for (int j = 0; j < n_steps; ++j) {
+        const ProgStep& st = prog[j];
+        const int T = st.T, RB = st.RB;
+        const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
+        int panel = t0 / RB, rb = t0 - panel * RB;
+        for (int t = t0; t < t1; ++t) {
+          const int oi = find_op(st, panel);
+          const int col0 = (panel - st.op[oi].panel_begin) * kPanelCols;
+          mbar_wait(empty0 + 8 * s, ph ^ 1);
           const uint32_t bar = full0 + 8 * s;
           mbar_expect_tx(bar, (uint32_t)kStageBytesTc);
           const uint32_t sw = stage_base + s * kStageBytesTc;
           tma_load_2d_hint(sw, &st.tm_w[oi], col0, rb * kRows, bar, pol);
           tma_load_2d_hint(sw + kStageWordBytes, &st.tm_s[oi], col0, rb * 4, bar, pol);
+          if (++s == stages) { s = 0; ph ^= 1; }
+          if (++rb == RB) { rb = 0; ++panel; }
         }
-        __syncwarp();
-        if (++s == stages) { s = 0; ph ^= 1; }
-        if (++rb == RB) { rb = 0; ++panel; }
       }
     }
+    __syncwarp();
   } else if (warp < kDqWarps) {
     // ================= dequant warps: ring -> registers -> TMEM operand buffers ============================
-    const int q = warp & 3, sl = warp >> 2;  // TMEM lane quadrant (= warp id % 4), group of the stage
+    const int q = warp & 3, sl = warp >> 2;  // TMEM lane quadrant (= warp id % 4), slice = operand set
     const int n = q * 32 + lane;
-    const uint32_t w_off = (uint32_t)(4 * sl) * (kPanelCols * 4) + (uint32_t)n * 4;
-    const uint32_t a_taddr0 = tmem_base + ((uint32_t)(q * 32) << 16);
-    int s = 0;
-    uint32_t ph = 0;
+    const uint32_t a_taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + sl * 64;
+    // total number of blocks of this CTA (the slice takes every fourth)
+    int n_total = 0;
+    for (int j = 0; j < n_steps; ++j) n_total += cta_begin(prog[j].T, b + 1, G) - cta_begin(prog[j].T, b, G);
+    uint32_t use = 0;
+    for (int m = sl; m < n_total; m += 4, ++use) {
+      const int s = m % stages;
+      const uint32_t ph = (uint32_t)(m / stages) & 1u;
+      mbar_wait(full0 + 8 * s, ph);
+      const uint32_t sw = stage_base + s * kStageBytesTc + (uint32_t)n * 4;
+      mbar_wait(afree0 + 8 * sl, (use & 1u) ^ 1u);  // the MMAs of this set's previous block are done
+      tc_fence_after();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint32_t sg = sw + g * (4 * kPanelCols * 4);
+        const uint32_t w0 = lds32(sg), w1 = lds32(sg + 512), w2 = lds32(sg + 1024), w3 = lds32(sg + 1536);
+        uint32_t a[16];
+        unpack_q4_direct(w0, a);
+        unpack_q4_direct(w1, a + 4);
+        unpack_q4_direct(w2, a + 8);
+        unpack_q4_direct(w3, a + 12);
+        if (!(dbg & 2)) tmem_st_32x16(a_taddr0 + g * 16, a);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(aready0 + 8 * sl);
+        mbar_arrive(empty0 + 8 * s);  // the words have left shared memory
+      }
+    }
+  } else if (warp == kBWriterWarp) {
+    // ================= B writer: activation rows of the block's four groups -> their B slots ================
+    // lane = 4 * g + c (16 lanes): 16-byte chunk c (one packed word row) of group g goes to operand row g of slot
+    // (set, g); every other row of the slot stays zero.  One generic->async proxy fence per block.
+    const int g = (lane >> 2) & 3, c = lane & 3;
     int m = 0, u = 0;
-    int jo0 = 0, jo1 = 0;
     for (int j = 0; j < n_steps; ++j) {
       const ProgStep& st = prog[j];
       const int T = st.T, RB = st.RB;
       const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
       if (t0 >= t1) continue;
       const int xb = u & 1;
-      bool x_waited = false;
-      const uint32_t xs_u32 = smem_u32(xs0 + (size_t)xb * xs_bytes);
-      int panel = t0 / RB, rb = t0 - panel * RB;
-      int t = t0;
-      while (t < t1) {
-        const int n_blk = min(t1 - t, RB - rb);
-        for (int bseg = 0; bseg < n_blk; ++bseg, ++m) {
-          mbar_wait(full0 + 8 * s, ph);
-          const uint32_t sw = stage_base + s * kStageBytesTc + w_off;
-          const uint32_t w0 = lds32(sw), w1 = lds32(sw + 512), w2 = lds32(sw + 1024), w3 = lds32(sw + 1536);
-          uint32_t a[16];
-          unpack_q4_direct(w0, a);
-          unpack_q4_direct(w1, a + 4);
-          unpack_q4_direct(w2, a + 8);
-          unpack_q4_direct(w3, a + 12);
-          __syncwarp();
-          if (lane == 0) mbar_arrive(empty0 + 8 * s);  // the words are in registers
-          const int buf = 4 * (m & 1) + sl;
-          mbar_wait(afree0 + 8 * buf, ((m >> 1) & 1) ^ 1);  // the MMAs of this buffer's previous group are done
-          tc_fence_after();
-          tmem_st_32x16(a_taddr0 + buf * 16, a);
-          if (q == 0) {
-            if (!x_waited) {
-              mbar_wait(xfull0 + 8 * xb, (u >> 1) & 1);
-              x_waited = true;
-            }
-            if (lane < 4) {
-              // activation row `lane` of the group -> row p of the B operand; zero the row of the previous use
-              const int p = 4 * (bseg & 3) + sl, po = (m & 1) ? jo1 : jo0;
-              const uint32_t slot = smem_u32(bslots) + buf * kBSlotBytes + (lane >> 1) * 512 + (lane & 1) * 256;
-              const uint4 xv = *reinterpret_cast<const uint4*>(xs0 + (size_t)xb * xs_bytes + (size_t)((rb + bseg) * kRows + 4 * sl + lane) * 16);
-              sts128(slot + (po >> 3) * 128 + (po & 7) * 16, make_uint4(0, 0, 0, 0));
-              sts128(slot + (p >> 3) * 128 + (p & 7) * 16, xv);
-            }
-            if (m & 1) jo1 = 4 * (bseg & 3) + sl; else jo0 = 4 * (bseg & 3) + sl;
-            fence_proxy_async_smem();
-          }
-          tmem_st_wait();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(aready0 + 8 * buf);
-          if (++s == stages) { s = 0; ph ^= 1; }
+      mbar_wait(xfull0 + 8 * xb, (u >> 1) & 1);
+      const unsigned char* xs = xs0 + (size_t)xb * xs_bytes;
+      int rb = t0 % RB;
+      for (int t = t0; t < t1; ++t, ++m) {
+        const int set = m & (kASets - 1);
+        mbar_wait(afree0 + 8 * set, ((m / kASets) & 1) ^ 1);
+        if (lane < 16) {
+          const uint32_t dst = smem_u32(bslots) + (4 * set + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
+          sts128(dst, *reinterpret_cast<const uint4*>(xs + (size_t)(rb * kRows + 4 * g + c) * 16));
         }
-        t += n_blk;
-        rb += n_blk;
-        if (rb == RB) { rb = 0; ++panel; }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(aready0 + 8 * set);
+        if (++rb == RB) rb = 0;
       }
-      (void)xs_u32;
       __syncwarp();
       if (lane == 0) mbar_arrive(xempty0 + 8 * xb);
       ++u;
     }
-  } else if (warp == kMmaWarp) {
-    // ================= MMA warp: two tcgen05.mma per group tile ============================================
+  } else if (warp == kMmaWarp || warp == kMmaWarp2) {
+    // ================= MMA warps: eight tcgen05.mma per block (two per group), whole loop in one lane ========
     const uint32_t idesc = make_idesc_f16(128, 16, 0, 0);
-    const uint64_t bdesc_hi = make_smem_desc_nosw(0, 256, 128);  // everything but the start address
-    const uint32_t bslot_u32 = smem_u32(bslots);
-    int m = 0, a = 0;
-    for (int j = 0; j < n_steps; ++j) {
-      const ProgStep& st = prog[j];
-      const int T = st.T, RB = st.RB;
-      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
-      if (t0 >= t1) continue;
-      int rb = t0 % RB;
-      int t = t0;
-      while (t < t1) {
-        const int n_blk = min(t1 - t, RB - rb);
-        for (int bseg = 0; bseg < n_blk; ++bseg, ++m) {
-          const uint32_t d_taddr = tmem_base + kDCol0 + (a & (kNAcc - 1)) * 16;
-          if ((bseg & 3) == 0) {
-            mbar_wait(accfree0 + 8 * (a & (kNAcc - 1)), ((a / kNAcc) & 1) ^ 1);  // the epilogue has read it
-            tc_fence_after();
-          }
+    const uint64_t bdesc0 = make_smem_desc_nosw(smem_u32(bslots), 256, 128);
+    if (elect_one()) {
+      int n_total = 0;
+      for (int j = 0; j < n_steps; ++j) n_total += cta_begin(prog[j].T, b + 1, G) - cta_begin(prog[j].T, b, G);
+      for (int m = (warp == kMmaWarp) ? 0 : 1; m < n_total; m += 2) {
+        const int set = m & (kASets - 1), ai = m & (kNAcc - 1);
+        const uint32_t d_taddr = tmem_base + kDCol0 + ai * 16;
+        const uint32_t a_taddr = tmem_base + set * 64;
+        const uint64_t bd = bdesc0 + (uint64_t)(set * (4 * kBSlotBytes / 16));
+        mbar_wait(accfree0 + 8 * ai, ((m / kNAcc) & 1) ^ 1);  // the epilogue has read this accumulator
+        mbar_wait(aready0 + 8 * set, (m / kASets) & 1);
+        tc_fence_after();
+        if (!(dbg & 1)) {
 #pragma unroll
-          for (int sl = 0; sl < 4; ++sl) {
-            const int buf = 4 * (m & 1) + sl;
-            mbar_wait(aready0 + 8 * buf, (m >> 1) & 1);
-            tc_fence_after();
-            if (elect_one()) {
-              const uint32_t a_taddr = tmem_base + buf * 16;
-              const uint32_t bs = bslot_u32 + buf * kBSlotBytes;
-              const uint32_t first = ((bseg & 3) == 0 && sl == 0) ? 0u : 1u;
-              umma_f16_ts(d_taddr, a_taddr, bdesc_hi | (uint64_t)((bs & 0x3FFFFu) >> 4), idesc, first);
-              umma_f16_ts(d_taddr, a_taddr + 8, bdesc_hi | (uint64_t)(((bs + 512) & 0x3FFFFu) >> 4), idesc, 1u);
-              umma_commit(afree0 + 8 * buf);
-            }
-            __syncwarp();
-          }
-          if ((bseg & 3) == 3 || bseg == n_blk - 1) {
-            if (elect_one()) umma_commit(accfull0 + 8 * (a & (kNAcc - 1)));
-            __syncwarp();
-            ++a;
+          for (int g = 0; g < 4; ++g) {
+            umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
+            umma_f16_ts(d_taddr, a_taddr + g * 16 + 8, bd + (uint64_t)(g * (kBSlotBytes / 16) + 512 / 16), idesc, 1u);
           }
         }
-        t += n_blk;
-        rb += n_blk;
-        if (rb == RB) rb = 0;
+        umma_commit(afree0 + 8 * set);
+        umma_commit(accfull0 + 8 * ai);
       }
     }
-  } else {
+    __syncwarp();
+  } else if (warp >= kHelperWarp0 && warp < kHelperWarp0 + kHelperWarps) {
     // ================= helper warps: staging, accumulator read-out, cross-CTA reduction, epilogue ============
     const int hq = warp - kHelperWarp0;  // TMEM lane quadrant (warp 16 + hq, (16 + hq) % 4 == hq)
     const int ht = hq * 32 + lane;       // panel column
@@ -399,7 +396,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const uint32_t epoch = ld_acquire_u32(ws_ctrl);
     const uint32_t tag = (epoch % 65535u) + 1u;
     int s = 0;
-    int m = 0, a = 0, u = 0;
+    int m = 0, u = 0;
     for (int j = 0; j < n_steps; ++j) {
       const ProgStep& st = prog[j];
       const int T = st.T, RB = st.RB;
@@ -420,69 +417,67 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         const int rb_begin = rb;
         const int n_blk = min(t1 - t, RB - rb);
         float sum = 0.f;
-        for (int b0 = 0; b0 < n_blk; b0 += 4) {
-          const int cnt = min(4, n_blk - b0);
-          const int ai = a & (kNAcc - 1);
-          mbar_wait(accfull0 + 8 * ai, (a / kNAcc) & 1);
+        for (int bb = 0; bb < n_blk; ++bb, ++m) {
+          const int ai = m & (kNAcc - 1);
+          mbar_wait(accfull0 + 8 * ai, (m / kNAcc) & 1);
           tc_fence_after();
-          uint32_t d[16];
-          tmem_ld_32x16(d_taddr0 + ai * 16, d);
+          uint32_t d[4];
+          tmem_ld_32x4(d_taddr0 + ai * 16, d);
+          // scales and corrections of the block while the TMEM load is in flight
+          const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
+          const uint32_t c_addr = corr_u32 + (uint32_t)((rb + bb) * 4) * 4;
+          float sc[4], cg[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
+            cg[g] = lds_f32(c_addr + g * 4);
+          }
           tmem_ld_wait();
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(accfree0 + 8 * ai);
-          ++a;
-#pragma unroll
-          for (int bb = 0; bb < 4; ++bb) {
-            if (bb < cnt) {
-              const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
-              const uint32_t c_addr = corr_u32 + (uint32_t)((rb + b0 + bb) * 4) * 4;
-#pragma unroll
-              for (int g = 0; g < 4; ++g) {
-                const float sc = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
-                const float cg = lds_f32(c_addr + g * 4);
-                sum = fmaf(sc, __uint_as_float(d[4 * bb + g]) - cg, sum);
-              }
-              __syncwarp();
-              if (lane == 0) mbar_arrive(empty0 + 8 * s);
-              if (++s == stages) s = 0;
-              ++m;
-            }
+          if (lane == 0) {
+            mbar_arrive(accfree0 + 8 * ai);
+            mbar_arrive(empty0 + 8 * s);
           }
+          if (!(dbg & 8)) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
+          }
+          if (++s == stages) s = 0;
         }
         sum *= 0.0625f;
         t += n_blk;
         rb += n_blk;
-
         // ---- cross-CTA reduction + epilogue of the panel (as gemv_program_kernel's helpers) ---------------------
         const ProgOp& op = st.op[find_op(st, panel)];
         const int n = (panel - op.panel_begin) * kPanelCols + ht;
         const bool complete = (rb_begin == 0) && (rb == RB);
         bool finalize = true;
         if (!complete) {
+          // K-split panel.  The owner of the panel's FIRST block finishes it: that segment is the last of its
+          // owner's range, so by then the other contributors (whose ranges end at the same time, or - the owner
+          // of the panel's tail - much earlier) have published; a CTA never waits in the middle of its range.
           const int first = block_owner(T, panel * RB, G);
-          const bool sparse = (T < G);
+          const bool sparse = (T < G);  // every block of the step is a different CTA
           uint2* slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
-          if (rb < RB) {
+          if (rb_begin > 0) {
             const int my_slot = sparse ? rb_begin : b - first;
             st_vol_v2(slot0 + (size_t)my_slot * kPanelCols + ht, __float_as_uint(sum), tag);
             finalize = false;
           } else {
-            const int n_before = sparse ? rb_begin : b - first;
-            float tot = 0.f;
-            for (int o0 = 0; o0 < n_before; o0 += 4) {  // up to four polls in flight
+            const int n_contrib = sparse ? RB : block_owner(T, panel * RB + RB - 1, G) - first + 1;
+            for (int o0 = 1; o0 < n_contrib; o0 += 4) {  // up to four polls in flight; added in block order
               uint2 pv[4];
 #pragma unroll
               for (int o = 0; o < 4; ++o)
-                if (o0 + o < n_before) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
+                if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
 #pragma unroll
               for (int o = 0; o < 4; ++o)
-                if (o0 + o < n_before) {
+                if (o0 + o < n_contrib) {
                   while (pv[o].y != tag) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
-                  tot += __uint_as_float(pv[o].x);
+                  sum += __uint_as_float(pv[o].x);
                 }
             }
-            sum = tot + sum;
           }
         }
         if (finalize && n < op.N) {

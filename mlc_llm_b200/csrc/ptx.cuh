@@ -148,6 +148,12 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld_32x4(uint32_t taddr, uint32_t (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr)
+               : "memory");
+}
 // no-swizzle ("interleave") K-major operand: 8-row x 16-byte core matrices; LBO = byte distance between
 // the two core matrices along K, SBO = between 8-row groups along M/N
 __device__ __forceinline__ uint64_t make_smem_desc_nosw(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
