@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-per-shape", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
-    ap.add_argument("--program", type=int, default=0, help="1: the persistent decode-program kernel (one cooperative launch per collective-free segment); 0: one launch per fused Linear group, PDL chain")
+    ap.add_argument("--program", type=int, default=-1, help="1: the persistent decode-program kernel (one cooperative launch per collective-free segment; tcgen05 kernel for q4f16_0); 0: one launch per fused Linear group, PDL chain; -1: auto (program for q4f16_0)")
     ap.add_argument("--no-fuse-qkv", action="store_true")
     ap.add_argument("--no-fuse-gate-up", action="store_true")
     ap.add_argument("--tune", default="", help="ctas_per_sm,stages,dbg_flags for b200q_gemv_tune (experiments)")
@@ -242,7 +242,7 @@ def main():
 
     stack = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, layers=args.layers,
                         pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up,
-                        use_program=bool(args.program))
+                        use_program=(args.fmt == "q4f16_0") if args.program < 0 else bool(args.program))
     if args.tune:
         ops.gemv_tune(*[int(v) for v in args.tune.split(",")])
     stack.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(stack.dt))
@@ -318,9 +318,10 @@ def main():
         achieved = step_bytes / (ms_per_step * 1e-3) / 1e9
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": ncu_traffic("gemv_q4f16_0_4096x11008_dram_bytes"),
-            "kernel": ("b200q::gemv_program_kernel (persistent: every GEMV of the step in one cooperative launch per "
-                       "collective-free segment)") if stack.use_program else "b200q::gemv_stream_kernel (one launch per fused Linear group, PDL chain)",
+            "traffic": ncu_traffic("gemv_program_tc_llama7b_token_dram_bytes") if (stack.use_program and args.fmt == "q4f16_0" and world == 1 and args.model == "llama-7b") else None,
+            "kernel": (("b200q::tc::gemv_program_tc_kernel" if args.fmt == "q4f16_0" else "b200q::gemv_program_kernel") +
+                       " (persistent: every GEMV of the step in one cooperative launch per collective-free segment" +
+                       ("; tcgen05.mma with the unpacked weights as TMEM operand" if args.fmt == "q4f16_0" else "") + ")") if stack.use_program else "b200q::gemv_stream_kernel (one launch per fused Linear group, PDL chain)",
             "gemv_steps_per_launch": (sum(o.n_steps for k, o in stack._plan if k == "program") / max(1, launches)) if stack.use_program else 1,
             "bytes_per_step_per_rank": step_bytes, "launches_per_step": launches,
             "avg_launch_us": ms_per_step * 1e3 / launches,

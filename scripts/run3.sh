@@ -1,3 +1,1 @@
-timeout -s KILL 100 python scripts/dbg_tc.py 4096 4096 2>&1 | tail -2
-timeout -s KILL 100 python scripts/dbg_tc.py 11008 4096 2>&1 | tail -1
-timeout -s KILL 100 python scripts/prog_sweep.py q4f16_0 2>&1 | tail -5
+timeout -s KILL 300 python -m pytest tests/test_gemv_program_gpu.py -x -q > gpurun_out/t_prog.log 2>&1; tail -12 gpurun_out/t_prog.log

@@ -30,9 +30,14 @@ def test_single_step_matches_gemv_and_oracle(name):
         prog = ops.GemvProgram([dict(weights=[(pd, sd)], x=xd, outs=[out])], name)
         prog.run()
         y = host(out)
-        check_gemv_tolerance(y, p, s, x, fmt, out_f32=f32, what=f"{name} {K}x{N}")
+        tc = name == "q4f16_0"  # tcgen05 program: group scale applied to the f32 group sum
+        check_gemv_tolerance(y, p, s, x, fmt, out_f32=f32, what=f"{name} {K}x{N}", group_scaled=tc)
         y1 = host(ops.gemv(pd, sd, xd, name)).reshape(-1)
-        if not f32:
+        if tc:
+            # same value up to the per-weight f16 rounding the single-op kernel reproduces: a few f16 ulps
+            d = np.abs(y.astype(np.float64) - y1.astype(np.float64))
+            assert d.max() <= 2.0**-8 * np.abs(y1.astype(np.float64)).max()
+        elif not f32:
             assert (np.abs(y.view(np.int16).astype(np.int32) - y1.view(np.int16).astype(np.int32)) <= 1).mean() > 0.99
         out.zero_()
         prog.run()  # replay: the workspace must have been left clean

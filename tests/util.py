@@ -31,11 +31,11 @@ def rand_weight(fmt: qo.Fmt, K: int, N: int, seed: int):
     return packed, scale
 
 
-def check_gemv_tolerance(y, packed, scale, x, fmt, out_f32, K=None, what=""):
+def check_gemv_tolerance(y, packed, scale, x, fmt, out_f32, K=None, what="", group_scaled=False):
     """|y - y64| <= rel*|y64| + 2^-14 * sum|x w| + 2^-24 against the f64 evaluation
     of the SAME dequantized weights."""
     y64, ab = co.gemv_f64(packed, scale, x, fmt, K)
-    tol = qo.tolerance(y64, ab, out_f32)
+    tol = qo.tolerance(y64, ab, out_f32, group_scaled)
     err = np.abs(y.astype(np.float64).reshape(-1) - y64)
     worst = float((err / tol).max())
     assert worst <= 1.0, f"{what}: error/tolerance = {worst:.3f} (max abs err {err.max():.3e})"
