@@ -58,6 +58,9 @@ PROTOTYPES = {
     "b200q_gemv_program_build": (c_int, [ctypes.POINTER(GemvStep), c_int, c_int, c_void_p, ctypes.c_size_t]),
     "b200q_gemv_program_workspace_bytes": (ctypes.c_size_t, [c_void_p]),
     "b200q_gemv_program_run": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
+    "b200q_gemv_program_build_tp": (c_int, [ctypes.POINTER(GemvStep), c_int, c_int, c_void_p, c_int, c_int, c_void_p,
+                                            ctypes.c_size_t]),
+    "b200q_gemv_program_run_tp": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.c_size_t, c_void_p, c_void_p]),
     "b200q_gemv_tune": (None, [c_int, c_int, c_int]),
     "b200q_gemv_host": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_dequant": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),

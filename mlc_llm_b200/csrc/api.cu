@@ -30,10 +30,11 @@ int gemv_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* 
 void gemv_tune(int ctas_per_sm, int stages, int flags);
 size_t gemv_workspace_bytes();
 size_t gemv_program_bytes(int n_steps);
-int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes);
+int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes,
+                       const unsigned char* reduce_mask, int tp_rank, int tp_size);
 size_t gemv_program_workspace_bytes(const void* host_blob);
 int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
-                     cudaStream_t stream);
+                     void* const* peer_workspaces, cudaStream_t stream);
 int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
                    cudaStream_t stream);
 int take_decode_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
@@ -125,6 +126,11 @@ int b200q_gemv(const void* packed, const void* scale, const void* x, const void*
 size_t b200q_gemv_program_bytes(int n_steps) { return n_steps > 0 ? gemv_program_bytes(n_steps) : 0; }
 
 int b200q_gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes) {
+  return b200q_gemv_program_build_tp(steps, n_steps, fmt, nullptr, 0, 1, host_blob, blob_bytes);
+}
+
+int b200q_gemv_program_build_tp(const b200q_gemv_step* steps, int n_steps, int fmt, const unsigned char* reduce_mask,
+                                int tp_rank, int tp_size, void* host_blob, size_t blob_bytes) {
   if (int e = check_fmt(fmt, "b200q_gemv_program_build")) return e;
   if (!steps || !host_blob) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_build: NULL steps/blob");
   if (n_steps < 1 || n_steps > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_program_build: n_steps=%d", n_steps);
@@ -137,7 +143,7 @@ int b200q_gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt,
     for (int i = 0; i < st.n_ops; ++i)
       if (int e = check_gemv_op(st.ops[i], fmt, "b200q_gemv_program_build")) return e;
   }
-  return gemv_program_build(steps, n_steps, fmt, host_blob, blob_bytes);
+  return gemv_program_build(steps, n_steps, fmt, host_blob, blob_bytes, reduce_mask, tp_rank, tp_size);
 }
 
 size_t b200q_gemv_program_workspace_bytes(const void* host_blob) {
@@ -146,8 +152,13 @@ size_t b200q_gemv_program_workspace_bytes(const void* host_blob) {
 
 int b200q_gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
                            void* stream) {
+  return b200q_gemv_program_run_tp(host_blob, dev_blob, workspace, workspace_bytes, nullptr, stream);
+}
+
+int b200q_gemv_program_run_tp(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
+                              void* const* peer_workspaces, void* stream) {
   if (!host_blob || !dev_blob || !workspace) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_run: NULL blob/workspace");
-  return gemv_program_run(host_blob, dev_blob, workspace, workspace_bytes, reinterpret_cast<cudaStream_t>(stream));
+  return gemv_program_run(host_blob, dev_blob, workspace, workspace_bytes, peer_workspaces, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,

@@ -92,7 +92,7 @@ struct ProgOp {
   int N;
   int epilogue;
   int panel_begin;
-  int pad_;
+  int tp_reduce;  // 1: row-parallel op - the value is summed over the tensor-parallel ranks inside the program
   long long ep0_ll;  // LL element offset of the operand's producer, or -1
   long long out_ll;  // LL element offset of this output, or -1 (f32 logits of an f16 model)
 };
@@ -115,6 +115,7 @@ struct alignas(64) ProgStep {
   int c_max;     // partial slots per panel
   int has_xmul;
   unsigned long long partial_off;  // uint2 offset of this step's partial slots
+  unsigned long long tp_partial_off;  // uint2 offset of the step's [panel][rank][128] cross-GPU partial slots
 };
 
 struct ProgHeader {  // first 64 bytes of the blob
@@ -122,7 +123,8 @@ struct ProgHeader {  // first 64 bytes of the blob
   int G, tc;  // tc: 1 = the tcgen05 kernel of gemv_tc.cuh (q4f16_0)
   unsigned long long ll_elems;       // LL activation elements in total
   unsigned long long partial_slots;  // {f32, tag} partial-sum words in total
-  unsigned long long reserved[3];
+  int tp_rank, tp_size;
+  unsigned long long reserved[2];
 };
 static_assert(sizeof(ProgHeader) == 64, "header is one cache line");
 constexpr int kMagic = 0xB2009F;
@@ -511,6 +513,13 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws
   }
 }
 
+// tensor-parallel peers of a program launch: every rank's workspace (same layout everywhere), by value
+struct TpInfo {
+  int rank, size;
+  unsigned long long ll_off, partial_off;  // byte offsets of the LL activations / partial slots inside a workspace
+  unsigned char* ws[8];
+};
+
 #include "gemv_tc.cuh"
 
 // ---- host side -----------------------------------------------------------------------------------------
@@ -594,7 +603,8 @@ bool want_tc(int fmt) {
 
 size_t gemv_program_bytes(int n_steps) { return sizeof(ProgHeader) + (size_t)n_steps * sizeof(ProgStep); }
 
-int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes) {
+int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes,
+                       const unsigned char* reduce_mask, int tp_rank, int tp_size) {
   if (blob_bytes < gemv_program_bytes(n_steps)) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_build: blob too small");
   if ((reinterpret_cast<uintptr_t>(host_blob) & 7) != 0) return set_error(B200Q_ERR_BAD_ALIGN, "gemv_program_build: blob must be 8-byte aligned");
   std::memset(host_blob, 0, gemv_program_bytes(n_steps));
@@ -605,6 +615,10 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
   unsigned long long ll_elems = 0, partial_slots = 0;
   int xs_bytes = 0;
   const bool use_tc = want_tc(fmt);
+  if (tp_size > 1 && !use_tc)
+    return set_error(B200Q_ERR_UNSUPPORTED, "gemv_program_build: in-program tensor-parallel reduction needs the q4f16_0 tcgen05 program");
+  if (tp_size < 1 || tp_size > 8 || tp_rank < 0 || tp_rank >= tp_size)
+    return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_build: tp rank %d of %d", tp_rank, tp_size);
   auto step_at = [&](int j, ProgStep& out) { std::memcpy(&out, base + (size_t)j * sizeof(ProgStep), sizeof(ProgStep)); };
   // An input of step j is an LL input when it IS (same address, same length) the output of an earlier
   // step; it is external when it overlaps no output at all.  Anything else (partial overlap, an output
@@ -644,6 +658,11 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
     if (e) return e;
     st.partial_off = partial_slots;
     partial_slots += (unsigned long long)st.n_panels * st.c_max * kPanelCols;
+    st.tp_partial_off = partial_slots;
+    if (tp_size > 1 && reduce_mask && reduce_mask[j]) {
+      partial_slots += (unsigned long long)st.n_panels * tp_size * kPanelCols;
+      for (int i = 0; i < st.n_ops; ++i) st.op[i].tp_reduce = (reduce_mask[j] >> i) & 1;
+    }
     const int xb = use_tc ? tc::xs_bytes_tc(st.K) : xs_bytes_for(fmt, st.K);
     if (xb > xs_bytes) xs_bytes = xb;
     if (int e2 = resolve(j, steps[j].x, st.K, st.x_ll)) return e2;
@@ -681,6 +700,8 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
   h->xs_bytes = xs_bytes;
   h->G = G;
   h->tc = use_tc ? 1 : 0;
+  h->tp_rank = tp_rank;
+  h->tp_size = tp_size;
   h->ll_elems = ll_elems;
   h->partial_slots = partial_slots;
   if (stages_for(fmt, xs_bytes, use_tc) < 2 * kGroups)
@@ -695,7 +716,7 @@ size_t gemv_program_workspace_bytes(const void* host_blob) {
 }
 
 int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
-                     cudaStream_t stream) {
+                     void* const* peer_workspaces, cudaStream_t stream) {
   const ProgHeader* h = reinterpret_cast<const ProgHeader*>(host_blob);
   if (h->magic != kMagic) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: not a program blob");
   if ((reinterpret_cast<uintptr_t>(dev_blob) & 63) != 0) return set_error(B200Q_ERR_BAD_ALIGN, "gemv_program_run: device blob must be 64-byte aligned");
@@ -736,9 +757,25 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   attrs[0].val.cooperative = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
+  TpInfo tp{};
+  tp.rank = h->tp_rank;
+  tp.size = h->tp_size;
+  tp.ll_off = ws_ll_off();
+  tp.partial_off = ws_partial_off(h->ll_elems, fmt_is_f32(h->fmt) ? 8 : 4);
+  for (int r = 0; r < 8; ++r) tp.ws[r] = nullptr;
+  if (h->tp_size > 1) {
+    if (!peer_workspaces) return set_error(B200Q_ERR_NULL, "gemv_program_run: a tensor-parallel program needs the peers' workspaces");
+    for (int r = 0; r < h->tp_size; ++r) {
+      tp.ws[r] = reinterpret_cast<unsigned char*>(peer_workspaces[r]);
+      if (!tp.ws[r]) return set_error(B200Q_ERR_NULL, "gemv_program_run: NULL workspace of rank %d", r);
+    }
+    if (tp.ws[h->tp_rank] != ws) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: peer_workspaces[rank] must be this rank's workspace");
+  } else {
+    tp.ws[0] = ws;
+  }
   int dbg = 0;
   if (const char* e = std::getenv("B200Q_TC_DBG")) dbg = std::atoi(e);
-  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes, (void*)&dbg};
+  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes, (void*)&dbg, (void*)&tp};
   e = cudaLaunchKernelExC(&cfg, kern, args);
   if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelExC(gemv program)");
   count_launch();

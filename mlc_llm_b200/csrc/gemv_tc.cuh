@@ -46,10 +46,10 @@ constexpr int kStageBytesTc = kStageWordBytes + kStageScaleBytes;   // 9216
 constexpr int kBSlotBytes = 1024;            // two K16 operands of 16 rows: [h][kc][j / 8][j % 8][16 B]
 constexpr int kMaxStagesTc = 24;
 // barriers (8 bytes each) in the first 1024 bytes
-constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + kASets,
-              kBarAccFull = kBarAFree + kASets, kBarAccFree = kBarAccFull + kNAcc, kBarXFullTc = kBarAccFree + kNAcc,
-              kBarXEmptyTc = kBarXFullTc + 2, kNumBars = kBarXEmptyTc + 2;  // 68
-constexpr int kTmemPtrOff = 8 * kNumBars;    // 544
+constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + 2 * kASets,
+              kBarAccFull = kBarAFree + 2 * kASets, kBarAccFree = kBarAccFull + kNAcc, kBarXFullTc = kBarAccFree + kNAcc,
+              kBarXEmptyTc = kBarXFullTc + 2, kNumBars = kBarXEmptyTc + 2;  // 76
+constexpr int kTmemPtrOff = 8 * kNumBars;    // 608
 constexpr int kHeaderTc = 1024;
 constexpr float kCorr = 1136.0f;             // 1024 + 16 * 7
 
@@ -220,7 +220,7 @@ __device__ __forceinline__ void unpack_q4_direct(uint32_t w, uint32_t* out) {
 // blocks and are never in the same phase of their loop.
 __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
-                       int stages, int xs_bytes, int dbg) {
+                       int stages, int xs_bytes, int dbg, const __grid_constant__ TpInfo tp) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
@@ -240,7 +240,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, 4 + kHelperWarps);  // the block's dequant slice + the epilogue warps
     }
-    for (int i = 0; i < kASets; ++i) {
+    for (int i = 0; i < 2 * kASets; ++i) {  // one pair per half block (two groups)
       mbar_init(aready0 + 8 * i, 4 + 1);  // dequant slice + B writer
       mbar_init(afree0 + 8 * i, 1);
     }
@@ -309,25 +309,31 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       const uint32_t ph = (uint32_t)(m / stages) & 1u;
       mbar_wait(full0 + 8 * s, ph);
       const uint32_t sw = stage_base + s * kStageBytesTc + (uint32_t)n * 4;
-      mbar_wait(afree0 + 8 * sl, (use & 1u) ^ 1u);  // the MMAs of this set's previous block are done
-      tc_fence_after();
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const uint32_t sg = sw + g * (4 * kPanelCols * 4);
-        const uint32_t w0 = lds32(sg), w1 = lds32(sg + 512), w2 = lds32(sg + 1024), w3 = lds32(sg + 1536);
-        uint32_t a[16];
-        unpack_q4_direct(w0, a);
-        unpack_q4_direct(w1, a + 4);
-        unpack_q4_direct(w2, a + 8);
-        unpack_q4_direct(w3, a + 12);
-        if (!(dbg & 2)) tmem_st_32x16(a_taddr0 + g * 16, a);
-      }
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(aready0 + 8 * sl);
-        mbar_arrive(empty0 + 8 * s);  // the words have left shared memory
+      for (int h = 0; h < 2; ++h) {
+        // half a block = two groups = one x32 tcgen05.st (a store costs its warp ~150 cycles whatever its width).
+        // The halves are handed to the MMA warp separately: the tensor core works on one while the slice
+        // unpacks the other.
+        uint32_t a[32];
+#pragma unroll
+        for (int gg = 0; gg < 2; ++gg) {
+          const uint32_t sg = sw + (2 * h + gg) * (4 * kPanelCols * 4);
+          const uint32_t w0 = lds32(sg), w1 = lds32(sg + 512), w2 = lds32(sg + 1024), w3 = lds32(sg + 1536);
+          unpack_q4_direct(w0, a + 16 * gg);
+          unpack_q4_direct(w1, a + 16 * gg + 4);
+          unpack_q4_direct(w2, a + 16 * gg + 8);
+          unpack_q4_direct(w3, a + 16 * gg + 12);
+        }
+        mbar_wait(afree0 + 8 * (2 * sl + h), (use & 1u) ^ 1u);  // the MMAs of this half set's previous block are done
+        tc_fence_after();
+        if (!(dbg & 2)) tmem_st_32x32(a_taddr0 + h * 32, a);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(aready0 + 8 * (2 * sl + h));
+          if (h == 1) mbar_arrive(empty0 + 8 * s);  // the words have left shared memory
+        }
       }
     }
   } else if (warp == kBWriterWarp) {
@@ -347,14 +353,18 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       int rb = t0 % RB;
       for (int t = t0; t < t1; ++t, ++m) {
         const int set = m & (kASets - 1);
-        mbar_wait(afree0 + 8 * set, ((m / kASets) & 1) ^ 1);
+        mbar_wait(afree0 + 8 * (2 * set), ((m / kASets) & 1) ^ 1);
+        mbar_wait(afree0 + 8 * (2 * set + 1), ((m / kASets) & 1) ^ 1);
         if (lane < 16) {
           const uint32_t dst = smem_u32(bslots) + (4 * set + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
           sts128(dst, *reinterpret_cast<const uint4*>(xs + (size_t)(rb * kRows + 4 * g + c) * 16));
         }
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) mbar_arrive(aready0 + 8 * set);
+        if (lane == 0) {
+          mbar_arrive(aready0 + 8 * (2 * set));
+          mbar_arrive(aready0 + 8 * (2 * set + 1));
+        }
         if (++rb == RB) rb = 0;
       }
       __syncwarp();
@@ -374,16 +384,19 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         const uint32_t a_taddr = tmem_base + set * 64;
         const uint64_t bd = bdesc0 + (uint64_t)(set * (4 * kBSlotBytes / 16));
         mbar_wait(accfree0 + 8 * ai, ((m / kNAcc) & 1) ^ 1);  // the epilogue has read this accumulator
-        mbar_wait(aready0 + 8 * set, (m / kASets) & 1);
-        tc_fence_after();
-        if (!(dbg & 1)) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
-            umma_f16_ts(d_taddr, a_taddr + g * 16 + 8, bd + (uint64_t)(g * (kBSlotBytes / 16) + 512 / 16), idesc, 1u);
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(aready0 + 8 * (2 * set + h), (m / kASets) & 1);
+          tc_fence_after();
+          if (!(dbg & 1)) {
+#pragma unroll
+            for (int g = 2 * h; g < 2 * h + 2; ++g) {
+              umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
+              umma_f16_ts(d_taddr, a_taddr + g * 16 + 8, bd + (uint64_t)(g * (kBSlotBytes / 16) + 512 / 16), idesc, 1u);
+            }
           }
+          umma_commit(afree0 + 8 * (2 * set + h));
         }
-        umma_commit(afree0 + 8 * set);
         umma_commit(accfull0 + 8 * ai);
       }
     }
@@ -480,7 +493,37 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             }
           }
         }
-        if (finalize && n < op.N) {
+        if (finalize && n < op.N && op.tp_reduce && tp.size > 1) {
+          // row-parallel op: `sum` is this rank's partial.  The ranks take turns owning panels: the others push
+          // their f32 partial to the owner's slots over NVLink; the owner adds them in rank order, applies the
+          // epilogue ONCE and pushes the finished {f16 | tag} word into every rank's activation array - the
+          // all-reduce of the sharded block, inside the launch (no collective kernel, no launch boundary).
+          const int pl = panel - op.panel_begin;
+          const int owner = pl % tp.size;
+          const size_t slot = st.tp_partial_off + ((size_t)panel * tp.size) * kPanelCols + ht;
+          if (tp.rank != owner) {
+            uint2* dst = reinterpret_cast<uint2*>(tp.ws[owner] + tp.partial_off) + slot + (size_t)tp.rank * kPanelCols;
+            st_vol_v2(dst, __float_as_uint(sum), tag);
+          } else {
+            const uint2* src = ws_partial + slot;
+            float tot = 0.f;
+            for (int r = 0; r < tp.size; ++r) {
+              if (r == tp.rank) { tot += sum; continue; }
+              uint2 pv = ld_vol_v2(src + (size_t)r * kPanelCols);
+              while (pv.y != tag) pv = ld_vol_v2(src + (size_t)r * kPanelCols);
+              tot += __uint_as_float(pv.x);
+            }
+            __half e0 = __ushort_as_half(0);
+            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag);
+            else if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
+            const __half y = ep_f16(tot, op.epilogue, &e0, 0);
+            const uint32_t word = (tag << 16) | (uint32_t)__half_as_ushort(y);
+            if (op.out_ll >= 0)
+              for (int r = 0; r < tp.size; ++r)
+                st_vol_u32(reinterpret_cast<uint32_t*>(tp.ws[r] + tp.ll_off) + op.out_ll + n, word);
+            reinterpret_cast<__half*>(op.out)[n] = y;
+          }
+        } else if (finalize && n < op.N) {
           if (op.epilogue == B200Q_EP_CAST_F32) {
             reinterpret_cast<float*>(op.out)[n] = sum;
           } else {

@@ -22,6 +22,8 @@ from __future__ import annotations
 import dataclasses
 from typing import Dict, List, Optional, Tuple
 
+import os
+
 import torch
 
 from . import _lib, ops
@@ -153,6 +155,10 @@ class DecodeStack:
         self.collectives_per_step = 0
         # use_program: the whole GEMV chain as persistent program launches (one per all-reduce-free segment)
         self.use_program = use_program
+        # tensor parallel + program + q4f16_0: the per-block all-reduce is fused into the program (one launch per
+        # token and rank; only the final logits all-gather is an NCCL call)
+        self.fused_tp = bool(use_program and tp_size > 1 and self.spec.name == "q4f16_0" and
+                             os.environ.get("B200Q_FUSED_TP", "1") != "0")
         self._plan = None
         self._steps = None
         if use_program:
@@ -210,12 +216,12 @@ class DecodeStack:
         self.logits = self.logits_part if tp == 1 else e(sh.vocab, torch.float32)
 
     # ------------------------------------------------------------------ the launch sequence
-    def _launch(self, items, x, x_mul=None):
+    def _launch(self, items, x, x_mul=None, reduce=False):
         """One kernel launch: items = [(weight, epilogue, ep0, out), ...] all reading x (* x_mul)."""
         if self._steps is not None:  # recording a program
             self._steps.append(dict(weights=[(w.packed, w.scale) for w, _, _, _ in items], x=x, x_mul=x_mul,
                                     epilogues=[ep for _, ep, _, _ in items], ep0s=[e0 for _, _, e0, _ in items],
-                                    outs=[o for _, _, _, o in items]))
+                                    outs=[o for _, _, _, o in items], reduces=[reduce] * len(items)))
             return
         ops.gemv_multi([(w.packed, w.scale) for w, _, _, _ in items], x, self.spec,
                        epilogues=[ep for _, ep, _, _ in items], ep0s=[e0 for _, _, e0, _ in items],
@@ -227,7 +233,8 @@ class DecodeStack:
 
     def _flush_steps(self):
         if self._steps:
-            self._plan.append(("program", ops.GemvProgram(self._steps, self.spec)))
+            tp = (self.tp_rank, self.tp_size, self.pg) if self.fused_tp else None
+            self._plan.append(("program", ops.GemvProgram(self._steps, self.spec, tp=tp)))
         self._steps = []
 
     def _build_plan(self):
@@ -267,6 +274,11 @@ class DecodeStack:
     def _row_parallel(self, w, x, residual, out, ep_single, x_mul=None):
         """o / down: out = residual + sum_ranks(x_r @ w_r).  Rank 0 carries the residual (or bias)
         into the sum so the reduction result is the final value."""
+        if self.fused_tp and self._steps is not None:
+            # the reduction over the ranks happens inside the program launch (peer pushes over NVLink): the
+            # epilogue is applied once, by the rank that owns the output panel, to the f32 sum of the partials
+            self._launch([(w, ep_single, residual, out)], x, x_mul, reduce=True)
+            return
         if self.tp_size == 1 or self.tp_rank == 0:
             self._launch([(w, ep_single, residual, out)], x, x_mul)
         else:

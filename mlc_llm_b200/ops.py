@@ -272,10 +272,15 @@ class GemvProgram:
         epilogues optional list            per Linear ("none", "add", ...)
         ep0s      optional list            per Linear epilogue operand or None
         outs      list                     per Linear output tensor (destination passing)
+        reduces   optional list of bool    per Linear: row-parallel (tensor parallel; summed over the ranks in-program)
+    tp = (rank, size, process_group): tensor-parallel program (b200q_gemv_program_build_tp / _run_tp): the
+    workspace is allocated as symmetric memory so that the peers can push partial sums / finished values into it.
     Dependencies between steps are derived by the library from pointer overlap.  All tensors are kept
     alive by this object; run() launches on torch's current stream and is CUDA-graph capturable."""
 
-    def __init__(self, steps, spec):
+    def __init__(self, steps, spec, tp=None):
+        import ctypes
+
         import numpy as np
 
         spec = _spec(spec)
@@ -283,6 +288,8 @@ class GemvProgram:
         L = _lib.lib()
         n = len(steps)
         arr = (_lib.GemvStep * n)()
+        tp_rank, tp_size, tp_group = tp if tp is not None else (0, 1, None)
+        mask = np.zeros(n, dtype=np.uint8)
         self._keep = []
         dev = None
         for j, st in enumerate(steps):
@@ -292,6 +299,9 @@ class GemvProgram:
             eps = list(st.get("epilogues") or ["none"] * len(weights))
             ep0s = list(st.get("ep0s") or [None] * len(weights))
             outs = st["outs"]
+            for i, r in enumerate(st.get("reduces") or []):
+                if r:
+                    mask[j] |= 1 << i
             K = x.shape[-1]
             _need_cuda(x, x_mul)
             if x.numel() != K or x.dtype != spec.torch_dtype:
@@ -313,13 +323,31 @@ class GemvProgram:
             self._keep += [x, x_mul]
         nbytes = int(L.b200q_gemv_program_bytes(n))
         self._host = np.zeros(nbytes // 8 + 1, dtype=np.uint64)  # 8-byte aligned host blob
-        _lib.check(L.b200q_gemv_program_build(arr, n, spec.fmt_id, self._host.ctypes.data, nbytes))
+        self._mask = mask
+        _lib.check(L.b200q_gemv_program_build_tp(arr, n, spec.fmt_id, mask.ctypes.data, tp_rank, tp_size,
+                                                 self._host.ctypes.data, nbytes))
         self._dev = torch.from_numpy(self._host.view(np.uint8)[:nbytes].copy()).to(dev)  # torch allocations are >= 256-byte aligned
         ws_bytes = int(L.b200q_gemv_program_workspace_bytes(self._host.ctypes.data))
-        self._ws = torch.zeros(ws_bytes, dtype=torch.uint8, device=dev)
+        self._peers = None
+        if tp_size > 1:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm_mem
+
+            # symmetric allocation: the peers write partial sums and finished activations straight into it
+            self._ws = symm_mem.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            self._ws.zero_()
+            self._hdl = symm_mem.rendezvous(self._ws, group=tp_group if tp_group is not None else dist.group.WORLD)
+            ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+            if ptrs[tp_rank] != self._ws.data_ptr():
+                raise RuntimeError("symmetric memory: buffer_ptrs[rank] is not the local workspace")
+            self._peers = (ctypes.c_void_p * tp_size)(*ptrs)
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=tp_group)  # every rank's workspace is zeroed before anyone launches
+        else:
+            self._ws = torch.zeros(ws_bytes, dtype=torch.uint8, device=dev)
         self.n_steps = n
 
     def run(self):
         L = _lib.lib()
-        _lib.check(L.b200q_gemv_program_run(self._host.ctypes.data, self._dev.data_ptr(), self._ws.data_ptr(),
-                                            self._ws.numel(), _stream()))
+        _lib.check(L.b200q_gemv_program_run_tp(self._host.ctypes.data, self._dev.data_ptr(), self._ws.data_ptr(),
+                                               self._ws.numel(), self._peers, _stream()))
