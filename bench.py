@@ -327,7 +327,7 @@ def main():
             "avg_launch_us": ms_per_step * 1e3 / launches,
             "peak_source": peak_src + (" of measured" if "measured" in peak_src else " of fallback"),
             "note": "achieved = algorithmic bytes of the step's GEMV launches (packed + scales + x + out + epilogue operand, "
-                    "SURVEY.md 8d) / CUDA-event time of the step" + ("; includes the all-reduces" if world > 1 else ""),
+                    "SURVEY.md 8d) / CUDA-event time of the step" + (("; the per-block reductions run inside the program launch (peer pushes over NVLink), the logits all-gather is NCCL" if getattr(stack, "fused_tp", False) else "; includes the all-reduces") if world > 1 else ""),
         }
 
     if rank == 0:
