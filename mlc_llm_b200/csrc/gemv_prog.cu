@@ -587,7 +587,7 @@ int stage_bytes_for(int fmt) {
 }
 int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
   if (use_tc) {
-    int s = (kSmemPerSm - tc::kHeaderTc - tc::kABufs * tc::kBSlotBytes - 2 * xs_bytes - 256) / tc::kStageBytesTc;
+    int s = (kSmemPerSm - tc::kHeaderTc - tc::kBSlots * tc::kBSlotBytes - 512) / tc::kStageBytesTc;  // no activation staging
     return s > tc::kMaxStagesTc ? tc::kMaxStagesTc : s;
   }
   int s = (kSmemPerSm - kHeader - 2 * xs_bytes - 1024) / stage_bytes_for(fmt);
@@ -663,7 +663,7 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
       partial_slots += (unsigned long long)st.n_panels * tp_size * kPanelCols;
       for (int i = 0; i < st.n_ops; ++i) st.op[i].tp_reduce = (reduce_mask[j] >> i) & 1;
     }
-    const int xb = use_tc ? tc::xs_bytes_tc(st.K) : xs_bytes_for(fmt, st.K);
+    const int xb = use_tc ? 0 : xs_bytes_for(fmt, st.K);  // the tcgen05 kernel reads activations per block
     if (xb > xs_bytes) xs_bytes = xb;
     if (int e2 = resolve(j, steps[j].x, st.K, st.x_ll)) return e2;
     if (int e2 = resolve(j, steps[j].x_mul, st.K, st.xmul_ll)) return e2;
@@ -726,8 +726,7 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   if (G != device_sm_count()) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: program was built for %d SMs", G);
   const bool use_tc = h->tc != 0;
   int stages = stages_for(h->fmt, h->xs_bytes, use_tc);
-  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kABufs * tc::kBSlotBytes + 2 * (size_t)h->xs_bytes + 256 +
-                                   (size_t)stages * tc::kStageBytesTc
+  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kBSlots * tc::kBSlotBytes + 512 + (size_t)stages * tc::kStageBytesTc
                              : (size_t)kHeader + 2 * (size_t)h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
 
   const ProgStep* prog = reinterpret_cast<const ProgStep*>(reinterpret_cast<const unsigned char*>(dev_blob) + sizeof(ProgHeader));

@@ -32,11 +32,12 @@ constexpr int kDqWarps = 16;                 // 4 slices (group of a stage) x 4 
 constexpr int kHelperWarp0 = 16;             // warps 16..19: epilogue + staging + cross-CTA traffic
 constexpr int kProducerWarpTc = 20;
 constexpr int kMmaWarp = 21;                 // blocks with even sequence number
-constexpr int kBWriterWarp = 22;             // fills the B operand slots (activation rows)
-constexpr int kMmaWarp2 = 23;                // blocks with odd sequence number
-constexpr int kThreadsTc = 24 * 32;          // 768
+constexpr int kMmaWarp2 = 22;                // blocks with odd sequence number
+constexpr int kXWarp0 = 23;                  // warps 23..26: one activation warp per dequant slice (B operand of its blocks)
+constexpr int kThreadsTc = 27 * 32;          // 864
 constexpr int kASets = 4;                    // stages of operand buffers in flight
-constexpr int kABufs = 4 * kASets;           // TMEM operand buffers (16 columns each) / B slots
+constexpr int kABufs = 4 * kASets;           // TMEM operand buffers (16 columns each)
+constexpr int kBSlots = 2 * kABufs;          // B operand slots: two per (slice, group), so the next block's is written early
 constexpr int kNAcc = 8;                     // accumulators in flight (one per block, 16 columns each)
 constexpr int kTmemCols = 512;               // A: columns [0,256), D: [256,384)
 constexpr int kDCol0 = 256;
@@ -47,17 +48,10 @@ constexpr int kBSlotBytes = 1024;            // two K16 operands of 16 rows: [h]
 constexpr int kMaxStagesTc = 24;
 // barriers (8 bytes each) in the first 1024 bytes
 constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + 2 * kASets,
-              kBarAccFull = kBarAFree + 2 * kASets, kBarAccFree = kBarAccFull + kNAcc, kBarXFullTc = kBarAccFree + kNAcc,
-              kBarXEmptyTc = kBarXFullTc + 2, kNumBars = kBarXEmptyTc + 2;  // 76
-constexpr int kTmemPtrOff = 8 * kNumBars;    // 608
+              kBarAccFull = kBarAFree + 2 * kASets, kBarAccFree = kBarAccFull + kNAcc, kBarBReady = kBarAccFree + kNAcc,
+              kBarBFree = kBarBReady + 2 * kASets, kNumBars = kBarBFree + 2 * kASets;  // 96
+constexpr int kTmemPtrOff = 8 * kNumBars;    // 768
 constexpr int kHeaderTc = 1024;
-constexpr float kCorr = 1136.0f;             // 1024 + 16 * 7
-
-// bytes of one activation buffer: 16 bytes per packed word row + one f32 correction per group
-__host__ __device__ inline int xs_bytes_tc(int K) {
-  const int rows = ceil_div(n_words(B200Q_Q4F16_0, K), kRows) * kRows;
-  return (rows * 16 + rows + 127) / 128 * 128;
-}
 
 __device__ __forceinline__ uint4 ld_vol_v4(const void* p) {
   uint4 v;
@@ -96,10 +90,7 @@ __device__ __forceinline__ uint4 ll_row_pack(const Row8& r) {  // 8 halves in k 
                     __byte_perm(r.hi.x, r.hi.y, 0x5410), __byte_perm(r.hi.z, r.hi.w, 0x5410));
 }
 
-// ---- activation staging (helper warps, 128 threads): x (optionally x * x_mul) of one step -> `xs` ------------
-// xs: 16 bytes per packed word row in the pair order of the unpack, (x0,x4)(x1,x5)(x2,x6)(x3,x7), zero beyond
-// K; followed by one f32 per group: 1136 * (sum of the group's activations).  All LL loads of a batch of four
-// rows per thread are issued before the first tag is checked (one L2 round trip per batch when the data is there).
+// ---- activation rows: 8 values of one packed word row from an LL array (polled) or a plain f16 vector -----------
 __device__ __forceinline__ __half tc_fetch(const __half* plain, const uint32_t* ll, long long ll_off, int k, uint32_t tag) {
   return (ll_off >= 0) ? ll_poll_f16(ll + ll_off + k, tag) : __ldcg(plain + k);
 }
@@ -118,100 +109,32 @@ __device__ __forceinline__ uint4 tc_finish_row(Row8& r, const __half* plain, con
   for (int t = 0; t < 8; ++t) v[t] = (t < n_valid) ? tc_fetch(plain, ll, ll_off, k0 + t, tag) : __ushort_as_half(0);
   return *reinterpret_cast<const uint4*>(v);
 }
-// rows i = base + r * 128 + ht of the CTA's compacted row list (R rows per thread in flight)
-template <int R, bool kHasM>
-__device__ __forceinline__ void tc_stage_batch(unsigned char* xs, float* corr, const ProgStep& st, const uint32_t* ll,
-                                               uint32_t tag, int ht, int base, int n_rows_needed, int rb0) {
-  const int K = st.K, RB = st.RB;
-  const __half* xp = reinterpret_cast<const __half*>(st.x);
-  const __half* mp = reinterpret_cast<const __half*>(st.x_mul);
-  const long long x_ll = st.x_ll, m_ll = kHasM ? st.xmul_ll : -1;
-  const bool x_vec = (reinterpret_cast<uintptr_t>(xp) & 15) == 0, m_vec = (reinterpret_cast<uintptr_t>(mp) & 15) == 0;
-  Row8 rx[R], rm[kHasM ? R : 1];
-  int lrs[R];
-#pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const int i = base + r * kHelperThreads + ht;
-    int blk = rb0 + (i >> 4);
-    if (blk >= RB) blk -= RB;
-    const int lr = (i < n_rows_needed) ? blk * kRows + (i & 15) : -1;
-    lrs[r] = lr;
-    const bool full = lr >= 0 && (lr * 8 + 8 <= K);
-    rx[r].lo = rx[r].hi = make_uint4(0, 0, 0, 0);
-    if (full && x_ll >= 0) {
-      rx[r].lo = ld_vol_v4(ll + x_ll + lr * 8);
-      rx[r].hi = ld_vol_v4(ll + x_ll + lr * 8 + 4);
-    }
-    if constexpr (kHasM) {
-      rm[r].lo = rm[r].hi = make_uint4(0, 0, 0, 0);
-      if (full && m_ll >= 0) {
-        rm[r].lo = ld_vol_v4(ll + m_ll + lr * 8);
-        rm[r].hi = ld_vol_v4(ll + m_ll + lr * 8 + 4);
-      }
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const int lr = lrs[r];
-    const int k0 = lr * 8;
-    const int n_valid = lr >= 0 ? min(8, max(0, K - k0)) : 0;
-    __align__(16) __half v[8];
-    *reinterpret_cast<uint4*>(v) = make_uint4(0, 0, 0, 0);
-    if (n_valid > 0) {
-      *reinterpret_cast<uint4*>(v) = tc_finish_row(rx[r], xp, ll, x_ll, k0, n_valid, x_vec, tag);
-      if constexpr (kHasM) {
-        __align__(16) __half mv[8];
-        *reinterpret_cast<uint4*>(mv) = tc_finish_row(rm[r], mp, ll, m_ll, k0, n_valid, m_vec, tag);
-#pragma unroll
-        for (int t = 0; t < 8; ++t) v[t] = __hmul(v[t], mv[t]);
-      }
-    }
-    float sm = 0.f;
-#pragma unroll
-    for (int t = 0; t < 8; ++t) sm += __half2float(v[t]);
-    sm += __shfl_xor_sync(0xffffffffu, sm, 1);
-    sm += __shfl_xor_sync(0xffffffffu, sm, 2);
-    if (lr >= 0) {
-      __align__(16) __half o[8] = {v[0], v[4], v[1], v[5], v[2], v[6], v[3], v[7]};
-      *reinterpret_cast<uint4*>(xs + (size_t)lr * 16) = *reinterpret_cast<const uint4*>(o);
-      if ((lr & 3) == 0) corr[lr >> 2] = kCorr * sm;
-    }
-  }
-}
-// stages the row blocks [rb0, rb0 + nb) (cyclic in RB) of the step's activation: only what this CTA's share
-// of the step reads
-__device__ __forceinline__ void tc_stage_x(unsigned char* xs, const ProgStep& st, const void* ws_ll, uint32_t tag, int ht,
-                                           int rb0, int nb) {
-  float* corr = reinterpret_cast<float*>(xs + (size_t)st.RB * kRows * 16);
-  const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
-  const int n_rows_needed = nb * kRows;
-  if (st.has_xmul) {
-    for (int base = 0; base < n_rows_needed; base += 2 * kHelperThreads)
-      tc_stage_batch<2, true>(xs, corr, st, ll, tag, ht, base, n_rows_needed, rb0);
-  } else {
-    for (int base = 0; base < n_rows_needed; base += 4 * kHelperThreads)
-      tc_stage_batch<4, false>(xs, corr, st, ll, tag, ht, base, n_rows_needed, rb0);
-  }
-}
-
-// (w >> s) & 0x00F000F0 | 0x64006400: the f16 pair (1024 + 16 q_lo, 1024 + 16 q_hi) of nibbles s/4 and s/4 + 4
+// One packed word -> four f16 pairs with five integer instructions and no floating-point one: a nibble in mantissa
+// bits 0..3 under the exponent of 1024 is the f16 number 1024 + q, a nibble in bits 4..7 under the exponent of 64 is
+// 64 + q.  Even nibbles (0,4 | 2,6) take the first form, odd ones (1,5 | 3,7) the second; the offsets leave with
+// the correction term  sum_k off(k) x[k]  (kOffEven / kOffOdd below, which also carry the -7 of the format).
 __device__ __forceinline__ void unpack_q4_direct(uint32_t w, uint32_t* out) {
-  const uint32_t kMagic = 0x64006400u, kMask = 0x00F000F0u;
-  out[0] = lop3_and_or(w << 4, kMask, kMagic);  // (v0, v4)
-  out[1] = lop3_and_or(w, kMask, kMagic);       // (v1, v5)
-  out[2] = lop3_and_or(w >> 4, kMask, kMagic);  // (v2, v6)
-  out[3] = lop3_and_or(w >> 8, kMask, kMagic);  // (v3, v7)
+  const uint32_t t = w >> 8;
+  out[0] = lop3_and_or(w, 0x000F000Fu, 0x64006400u);  // (1024 + v0, 1024 + v4)
+  out[1] = lop3_and_or(w, 0x00F000F0u, 0x54005400u);  // (64 + v1, 64 + v5)
+  out[2] = lop3_and_or(t, 0x000F000Fu, 0x64006400u);  // (1024 + v2, 1024 + v6)
+  out[3] = lop3_and_or(t, 0x00F000F0u, 0x54005400u);  // (64 + v3, 64 + v7)
 }
+constexpr float kOffEven = 1024.0f + 7.0f, kOffOdd = 64.0f + 7.0f;
 
 #ifdef B200Q_TC_TIMING
 #define TC_T0() long long _t0 = clock64()
 #define TC_ACC(v) do { long long _t1 = clock64(); (v) += _t1 - _t0; _t0 = _t1; } while (0)
+#define TC_DECL(...) long long __VA_ARGS__
+#define TC_PRINT(cond, ...) do { if (cond) printf(__VA_ARGS__); } while (0)
 #else
+#define TC_DECL(...) do { } while (0)
+#define TC_PRINT(cond, ...) do { } while (0)
 #define TC_T0() do { } while (0)
 #define TC_ACC(v) do { } while (0)
 #endif
 
-// shared-memory map: [0,1024) barriers + TMEM pointer | B slots 16 x 1 KB | two activation buffers | ring
+// shared-memory map: [0,1024) barriers + TMEM pointer | B slots 16 x 1 KB | group-sum ring 256 B | weight ring
 //
 // Block m (CTA-local sequence number of a 16-row x 128-column stage) is handled by
 //   dequant slice  m % 4  (warps 4 sl .. 4 sl + 3; thread = output column): its four groups -> operand set m % 4,
@@ -229,11 +152,12 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   const uint32_t full0 = bar0 + 8 * kBarFull, empty0 = bar0 + 8 * kBarEmpty;
   const uint32_t aready0 = bar0 + 8 * kBarAReady, afree0 = bar0 + 8 * kBarAFree;
   const uint32_t accfull0 = bar0 + 8 * kBarAccFull, accfree0 = bar0 + 8 * kBarAccFree;
-  const uint32_t xfull0 = bar0 + 8 * kBarXFullTc, xempty0 = bar0 + 8 * kBarXEmptyTc;
+  const uint32_t bready0 = bar0 + 8 * kBarBReady, bfree0 = bar0 + 8 * kBarBFree;  // [slice][slot set of the slice]
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + kTmemPtrOff);
   unsigned char* bslots = smem + kHeaderTc;
-  unsigned char* xs0 = bslots + kABufs * kBSlotBytes;
-  const uint32_t stage_base = (smem_u32(xs0 + 2 * xs_bytes) + 127u) & ~127u;
+  float* corr_s = reinterpret_cast<float*>(bslots + kBSlots * kBSlotBytes);  // [16 blocks][4 groups]: 1136 * sum of the group's x
+  const uint32_t stage_base = (smem_u32(corr_s + 64) + 127u) & ~127u;
+  (void)xs_bytes;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -241,21 +165,21 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       mbar_init(empty0 + 8 * s, 4 + kHelperWarps);  // the block's dequant slice + the epilogue warps
     }
     for (int i = 0; i < 2 * kASets; ++i) {  // one pair per half block (two groups)
-      mbar_init(aready0 + 8 * i, 4 + 1);  // dequant slice + B writer
+      mbar_init(aready0 + 8 * i, 4);  // the four warps of the dequant slice
       mbar_init(afree0 + 8 * i, 1);
     }
     for (int i = 0; i < kNAcc; ++i) {
       mbar_init(accfull0 + 8 * i, 1);
       mbar_init(accfree0 + 8 * i, kHelperWarps);
     }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(xfull0 + 8 * i, kHelperWarps);
-      mbar_init(xempty0 + 8 * i, 1);
+    for (int i = 0; i < 2 * kASets; ++i) {
+      mbar_init(bready0 + 8 * i, 1);
+      mbar_init(bfree0 + 8 * i, 1);
     }
     fence_barrier_init();
   }
   // the B slots start as zeros: slot (set, g) only ever gets activation rows written into operand row g
-  for (int i = threadIdx.x; i < kABufs * kBSlotBytes / 16; i += kThreadsTc)
+  for (int i = threadIdx.x; i < kBSlots * kBSlotBytes / 16; i += kThreadsTc)
     reinterpret_cast<uint4*>(bslots)[i] = make_uint4(0, 0, 0, 0);
   if (warp == kMmaWarp) {
     tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_ptr)), kTmemCols);
@@ -304,10 +228,13 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     int n_total = 0;
     for (int j = 0; j < n_steps; ++j) n_total += cta_begin(prog[j].T, b + 1, G) - cta_begin(prog[j].T, b, G);
     uint32_t use = 0;
+    TC_DECL(tq_full = 0, tq_unp = 0, tq_afree = 0, tq_st = 0);
+    TC_T0();
     for (int m = sl; m < n_total; m += 4, ++use) {
       const int s = m % stages;
       const uint32_t ph = (uint32_t)(m / stages) & 1u;
       mbar_wait(full0 + 8 * s, ph);
+      TC_ACC(tq_full);
       const uint32_t sw = stage_base + s * kStageBytesTc + (uint32_t)n * 4;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
@@ -324,7 +251,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           unpack_q4_direct(w2, a + 16 * gg + 8);
           unpack_q4_direct(w3, a + 16 * gg + 12);
         }
+        TC_ACC(tq_unp);
         mbar_wait(afree0 + 8 * (2 * sl + h), (use & 1u) ^ 1u);  // the MMAs of this half set's previous block are done
+        TC_ACC(tq_afree);
         tc_fence_after();
         if (!(dbg & 2)) tmem_st_32x32(a_taddr0 + h * 32, a);
         tmem_st_wait();
@@ -334,43 +263,145 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           mbar_arrive(aready0 + 8 * (2 * sl + h));
           if (h == 1) mbar_arrive(empty0 + 8 * s);  // the words have left shared memory
         }
+        TC_ACC(tq_st);
       }
     }
-  } else if (warp == kBWriterWarp) {
-    // ================= B writer: activation rows of the block's four groups -> their B slots ================
-    // lane = 4 * g + c (16 lanes): 16-byte chunk c (one packed word row) of group g goes to operand row g of slot
-    // (set, g); every other row of the slot stays zero.  One generic->async proxy fence per block.
+    TC_PRINT(b == 0 && warp == 0 && lane == 0, "dq: n=%d full %lld unpack %lld afree %lld st %lld\n", (int)use, tq_full / (use + 1),
+             tq_unp / (use + 1), tq_afree / (use + 1), tq_st / (use + 1));
+  } else if (warp >= kXWarp0) {
+    // ================= activation warps: the B operand of the blocks of one dequant slice =====================
+    // B part (16 lanes, lane = 4 g + c): the 8 activations of packed word row c of group g are read straight from
+    // their producer's LL words (polled here, per block: a block starts as soon as ITS 128 activations exist) or
+    // from a plain input, multiplied by x_mul if the step has one, and written in the unpack's pair order into
+    // operand row g of B slot (slice, g); the other rows of the slot stay zero.  The group's activation sum
+    // (x 1136) goes to the epilogue warps through a small ring.  One generic->async proxy fence per block.
+    // Every slice has two slot sets and the loads of the block after the next are in the air, so the warp runs up
+    // to eight blocks ahead of the tensor core and a block of the next step starts as soon as ITS row block exists.
+    const int sl = warp - kXWarp0;
     const int g = (lane >> 2) & 3, c = lane & 3;
-    int m = 0, u = 0;
-    for (int j = 0; j < n_steps; ++j) {
-      const ProgStep& st = prog[j];
-      const int T = st.T, RB = st.RB;
-      const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
-      if (t0 >= t1) continue;
-      const int xb = u & 1;
-      mbar_wait(xfull0 + 8 * xb, (u >> 1) & 1);
-      const unsigned char* xs = xs0 + (size_t)xb * xs_bytes;
-      int rb = t0 % RB;
-      for (int t = t0; t < t1; ++t, ++m) {
-        const int set = m & (kASets - 1);
-        mbar_wait(afree0 + 8 * (2 * set), ((m / kASets) & 1) ^ 1);
-        mbar_wait(afree0 + 8 * (2 * set + 1), ((m / kASets) & 1) ^ 1);
-        if (lane < 16) {
-          const uint32_t dst = smem_u32(bslots) + (4 * set + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
-          sts128(dst, *reinterpret_cast<const uint4*>(xs + (size_t)(rb * kRows + 4 * g + c) * 16));
+    const uint32_t my_slot = smem_u32(bslots) + (4 * sl + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
+    const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
+    const uint32_t tag = (ld_acquire_u32(ws_ctrl) % 65535u) + 1u;
+    // iterator over this CTA's blocks; the slice takes those with m % 4 == sl
+    // (the step table lives in global memory and there is no L1 to speak of next to 227 KB of shared memory:
+    // every field read is an L2 round trip, so the fields are cached in registers when the iterator enters a step)
+    int it_j = -1, it_t = 0, it_t1 = 0, it_rb = 0, it_RB = 1, it_m = 0, it_K = 0;
+    long long it_xll = -1, it_mll = -1;
+    const __half* it_xp = nullptr;
+    const __half* it_mp = nullptr;
+    bool it_hasm = false;
+    bool it_valid = false;
+    auto seek = [&]() {  // move to the next own block at or after the current position
+      for (;;) {
+        if (it_t >= it_t1) {
+          if (++it_j >= n_steps) { it_valid = false; return; }
+          const ProgStep& st = prog[it_j];
+          const int T = st.T;
+          it_RB = st.RB;
+          it_K = st.K;
+          it_hasm = st.has_xmul != 0;
+          it_xll = st.x_ll;
+          it_mll = it_hasm ? st.xmul_ll : -1;
+          it_xp = reinterpret_cast<const __half*>(st.x);
+          it_mp = reinterpret_cast<const __half*>(st.x_mul);
+          it_t = cta_begin(T, b, G);
+          it_t1 = cta_begin(T, b + 1, G);
+          it_rb = it_t % it_RB;
+          continue;
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(aready0 + 8 * (2 * set));
-          mbar_arrive(aready0 + 8 * (2 * set + 1));
-        }
-        if (++rb == RB) rb = 0;
+        if ((it_m & 3) == sl) { it_valid = true; return; }
+        ++it_t; ++it_m;
+        if (++it_rb == it_RB) it_rb = 0;
       }
+    };
+    // the activation row of this lane for the block under the iterator: loads issued, not yet checked
+    Row8 rx, rm;
+    int p_k0 = 0, p_nvalid = 0, p_m = 0;
+    long long p_xll = -1, p_mll = -1;
+    const __half* p_xp = nullptr;
+    const __half* p_mp = nullptr;
+    bool p_hasm = false;
+    auto preload = [&]() {
+      p_m = it_m;
+      p_xll = it_xll; p_mll = it_mll; p_xp = it_xp; p_mp = it_mp; p_hasm = it_hasm;
+      p_k0 = (it_rb * kRows + 4 * g + c) * 8;
+      p_nvalid = (lane < 16) ? min(8, max(0, it_K - p_k0)) : 0;
+      rx.lo = rx.hi = rm.lo = rm.hi = make_uint4(0, 0, 0, 0);
+      if (p_nvalid == 8 && p_xll >= 0) {
+        rx.lo = ld_vol_v4(ll + p_xll + p_k0);
+        rx.hi = ld_vol_v4(ll + p_xll + p_k0 + 4);
+      } else if (p_nvalid == 8 && (reinterpret_cast<uintptr_t>(p_xp) & 15) == 0) {
+        rx.lo = __ldcg(reinterpret_cast<const uint4*>(p_xp + p_k0));
+      }
+      if (p_nvalid == 8 && p_hasm) {
+        if (p_mll >= 0) {
+          rm.lo = ld_vol_v4(ll + p_mll + p_k0);
+          rm.hi = ld_vol_v4(ll + p_mll + p_k0 + 4);
+        } else if ((reinterpret_cast<uintptr_t>(p_mp) & 15) == 0) {
+          rm.lo = __ldcg(reinterpret_cast<const uint4*>(p_mp + p_k0));
+        }
+      }
+    };
+    // B part for the block whose loads were issued by the last preload(), into the slot set `par` of this slice
+    auto bpart = [&](int par) {
+      const __half* xp = p_xp;
+      const __half* mp = p_mp;
+      const long long x_ll = p_xll, m_ll = p_mll;
+      const bool x_vec = (reinterpret_cast<uintptr_t>(xp) & 15) == 0, m_vec = (reinterpret_cast<uintptr_t>(mp) & 15) == 0;
+      __align__(16) __half v[8];
+      *reinterpret_cast<uint4*>(v) = make_uint4(0, 0, 0, 0);
+      if (p_nvalid > 0) {
+        if (p_nvalid == 8 && x_ll < 0 && x_vec) *reinterpret_cast<uint4*>(v) = rx.lo;  // plain row, loaded by preload()
+        else *reinterpret_cast<uint4*>(v) = tc_finish_row(rx, xp, ll, x_ll, p_k0, p_nvalid, x_vec, tag);
+        if (p_hasm) {
+          __align__(16) __half mv[8];
+          if (p_nvalid == 8 && m_ll < 0 && m_vec) *reinterpret_cast<uint4*>(mv) = rm.lo;
+          else *reinterpret_cast<uint4*>(mv) = tc_finish_row(rm, mp, ll, m_ll, p_k0, p_nvalid, m_vec, tag);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = __hmul(v[i], mv[i]);
+        }
+      }
+      float sm_e = 0.f, sm_o = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; i += 2) {
+        sm_e += __half2float(v[i]);
+        sm_o += __half2float(v[i + 1]);
+      }
+      float sm = fmaf(kOffEven, sm_e, kOffOdd * sm_o);
+      sm += __shfl_xor_sync(0xffffffffu, sm, 1);
+      sm += __shfl_xor_sync(0xffffffffu, sm, 2);
+      if (lane < 16) {
+        __align__(16) __half o[8] = {v[0], v[4], v[1], v[5], v[2], v[6], v[3], v[7]};
+        sts128(my_slot + par * (kABufs * kBSlotBytes), *reinterpret_cast<const uint4*>(o));
+        if (c == 0) corr_s[(p_m & 15) * 4 + g] = sm;
+      }
+      fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(xempty0 + 8 * xb);
-      ++u;
+    };
+    auto advance = [&]() {
+      ++it_t; ++it_m;
+      if (++it_rb == it_RB) it_rb = 0;
+      seek();
+    };
+    seek();
+    if (it_valid) preload();
+    TC_DECL(tx_bfree = 0, tx_b = 0, tx_adv = 0);
+    TC_T0();
+    uint32_t use = 0;
+    for (; it_valid; ++use) {
+      const int par = (int)(use & 1u);
+      // the MMAs of the block that used this slot set two uses ago are done (first two uses: passes at once)
+      mbar_wait(bfree0 + 8 * (2 * sl + par), ((use >> 1) & 1u) ^ 1u);
+      TC_ACC(tx_bfree);
+      bpart(par);
+      if (lane == 0) mbar_arrive(bready0 + 8 * (2 * sl + par));
+      TC_ACC(tx_b);
+      advance();
+      if (it_valid) preload();
+      TC_ACC(tx_adv);
     }
+    TC_PRINT(b == 0 && sl == 0 && lane == 0, "x: n=%d bfree %lld bpart %lld advance+preload %lld\n", (int)use, tx_bfree / (use + 1),
+             tx_b / (use + 1), tx_adv / (use + 1));
   } else if (warp == kMmaWarp || warp == kMmaWarp2) {
     // ================= MMA warps: eight tcgen05.mma per block (two per group), whole loop in one lane ========
     const uint32_t idesc = make_idesc_f16(128, 16, 0, 0);
@@ -378,15 +409,23 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     if (elect_one()) {
       int n_total = 0;
       for (int j = 0; j < n_steps; ++j) n_total += cta_begin(prog[j].T, b + 1, G) - cta_begin(prog[j].T, b, G);
-      for (int m = (warp == kMmaWarp) ? 0 : 1; m < n_total; m += 2) {
+      TC_DECL(tm_accfree = 0, tm_bready = 0, tm_a0 = 0, tm_a1 = 0, tm_issue = 0);
+      TC_T0();
+      int cnt = 0;
+      for (int m = (warp == kMmaWarp) ? 0 : 1; m < n_total; m += 2, ++cnt) {
         const int set = m & (kASets - 1), ai = m & (kNAcc - 1);
+        const uint32_t use = (uint32_t)m / kASets, par = use & 1u;
         const uint32_t d_taddr = tmem_base + kDCol0 + ai * 16;
         const uint32_t a_taddr = tmem_base + set * 64;
-        const uint64_t bd = bdesc0 + (uint64_t)(set * (4 * kBSlotBytes / 16));
+        const uint64_t bd = bdesc0 + (uint64_t)((par * kABufs + set * 4) * (kBSlotBytes / 16));
         mbar_wait(accfree0 + 8 * ai, ((m / kNAcc) & 1) ^ 1);  // the epilogue has read this accumulator
+        TC_ACC(tm_accfree);
+        mbar_wait(bready0 + 8 * (2 * set + par), (use >> 1) & 1u);
+        TC_ACC(tm_bready);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          mbar_wait(aready0 + 8 * (2 * set + h), (m / kASets) & 1);
+          mbar_wait(aready0 + 8 * (2 * set + h), use & 1u);
+          if (h == 0) TC_ACC(tm_a0); else TC_ACC(tm_a1);
           tc_fence_after();
           if (!(dbg & 1)) {
 #pragma unroll
@@ -397,8 +436,12 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           }
           umma_commit(afree0 + 8 * (2 * set + h));
         }
+        umma_commit(bfree0 + 8 * (2 * set + par));
         umma_commit(accfull0 + 8 * ai);
+        TC_ACC(tm_issue);
       }
+      TC_PRINT(b == 0 && warp == kMmaWarp, "mma: n=%d accfree %lld bready %lld aready0 %lld aready1 %lld issue %lld\n", cnt,
+               tm_accfree / (cnt + 1), tm_bready / (cnt + 1), tm_a0 / (cnt + 1), tm_a1 / (cnt + 1), tm_issue / (cnt + 1));
     }
     __syncwarp();
   } else if (warp >= kHelperWarp0 && warp < kHelperWarp0 + kHelperWarps) {
@@ -409,21 +452,14 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const uint32_t epoch = ld_acquire_u32(ws_ctrl);
     const uint32_t tag = (epoch % 65535u) + 1u;
     int s = 0;
-    int m = 0, u = 0;
+    int m = 0;
+    TC_DECL(th_accfull = 0, th_blk = 0, th_fin = 0);
+    TC_T0();
     for (int j = 0; j < n_steps; ++j) {
       const ProgStep& st = prog[j];
       const int T = st.T, RB = st.RB;
       const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
       if (t0 >= t1) continue;
-      const int xb = u & 1;
-      unsigned char* xs = xs0 + (size_t)xb * xs_bytes;
-      mbar_wait(xempty0 + 8 * xb, ((u >> 1) & 1) ^ 1);
-      tc_stage_x(xs, st, ws_ll, tag, ht, t0 % RB, min(RB, t1 - t0));
-      asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");  // corr[] is read by all helper warps
-      if (lane == 0) mbar_arrive(xfull0 + 8 * xb);
-      ++u;
-      const uint32_t corr_u32 = smem_u32(xs + (size_t)RB * kRows * 16);
-
       int panel = t0 / RB, rb = t0 - panel * RB;
       int t = t0;
       while (t < t1) {
@@ -432,13 +468,15 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         float sum = 0.f;
         for (int bb = 0; bb < n_blk; ++bb, ++m) {
           const int ai = m & (kNAcc - 1);
+          TC_ACC(th_fin);
           mbar_wait(accfull0 + 8 * ai, (m / kNAcc) & 1);
+          TC_ACC(th_accfull);
           tc_fence_after();
           uint32_t d[4];
           tmem_ld_32x4(d_taddr0 + ai * 16, d);
           // scales and corrections of the block while the TMEM load is in flight
           const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
-          const uint32_t c_addr = corr_u32 + (uint32_t)((rb + bb) * 4) * 4;
+          const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & 15) * 4) * 4;
           float sc[4], cg[4];
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -457,8 +495,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             for (int g = 0; g < 4; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
           }
           if (++s == stages) s = 0;
+          TC_ACC(th_blk);
         }
-        sum *= 0.0625f;
         t += n_blk;
         rb += n_blk;
         // ---- cross-CTA reduction + epilogue of the panel (as gemv_program_kernel's helpers) ---------------------
@@ -539,6 +577,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         if (rb == RB) { rb = 0; ++panel; }
       }
     }
+    TC_PRINT(b == 0 && ht == 0, "helper: n=%d accfull %lld block %lld finalize+step %lld (totals / blocks)\n", m, th_accfull / (m + 1),
+             th_blk / (m + 1), th_fin / (m + 1));
     // ---- leave: the last CTA bumps the launch tag ------------------------------------------------------------
     asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");
     if (ht == 0) {
