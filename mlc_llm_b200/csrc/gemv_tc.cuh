@@ -122,6 +122,18 @@ __device__ __forceinline__ void unpack_q4_direct(uint32_t w, uint32_t* out) {
 }
 constexpr float kOffEven = 1024.0f + 7.0f, kOffOdd = 64.0f + 7.0f;
 
+// event trace of a few steps (scripts/trace_steps.py reads the printed lines): build with EXTRA=-DB200Q_TC_TRACE
+#ifdef B200Q_TC_TRACE
+constexpr int kTrStep0 = 41, kTrSteps = 8;
+__device__ __forceinline__ unsigned long long tc_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define TC_EV(j, e) do { if ((j) >= kTrStep0 && (j) < kTrStep0 + kTrSteps) tc_trace[(j) - kTrStep0][e] = tc_globaltimer(); } while (0)
+#else
+#define TC_EV(j, e) do { } while (0)
+#endif
 #ifdef B200Q_TC_TIMING
 #define TC_T0() long long _t0 = clock64()
 #define TC_ACC(v) do { long long _t1 = clock64(); (v) += _t1 - _t0; _t0 = _t1; } while (0)
@@ -145,6 +157,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
                        int stages, int xs_bytes, int dbg, const __grid_constant__ TpInfo tp) {
   extern __shared__ __align__(128) unsigned char smem[];
+#ifdef B200Q_TC_TRACE
+  __shared__ unsigned long long tc_trace[kTrSteps][6];
+#endif
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
 
@@ -291,6 +306,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const __half* it_mp = nullptr;
     bool it_hasm = false;
     bool it_valid = false;
+    bool p_first = false;  // (trace) first block of the CTA's share of a step
+    int p_j = 0, it_t0 = 0;
     auto seek = [&]() {  // move to the next own block at or after the current position
       for (;;) {
         if (it_t >= it_t1) {
@@ -307,6 +324,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           it_t = cta_begin(T, b, G);
           it_t1 = cta_begin(T, b + 1, G);
           it_rb = it_t % it_RB;
+          it_t0 = it_t;
           continue;
         }
         if ((it_m & 3) == sl) { it_valid = true; return; }
@@ -323,6 +341,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     bool p_hasm = false;
     auto preload = [&]() {
       p_m = it_m;
+      p_first = (it_t == it_t0); p_j = it_j;
       p_xll = it_xll; p_mll = it_mll; p_xp = it_xp; p_mp = it_mp; p_hasm = it_hasm;
       p_k0 = (it_rb * kRows + 4 * g + c) * 8;
       p_nvalid = (lane < 16) ? min(8, max(0, it_K - p_k0)) : 0;
@@ -393,8 +412,10 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       // the MMAs of the block that used this slot set two uses ago are done (first two uses: passes at once)
       mbar_wait(bfree0 + 8 * (2 * sl + par), ((use >> 1) & 1u) ^ 1u);
       TC_ACC(tx_bfree);
+      if (p_first && lane == 0) TC_EV(p_j, 5);
       bpart(par);
       if (lane == 0) mbar_arrive(bready0 + 8 * (2 * sl + par));
+      if (p_first && lane == 0) TC_EV(p_j, 0);
       TC_ACC(tx_b);
       advance();
       if (it_valid) preload();
@@ -465,12 +486,41 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       while (t < t1) {
         const int rb_begin = rb;
         const int n_blk = min(t1 - t, RB - rb);
+        // ---- everything the panel's epilogue needs is fetched NOW: the step table, the epilogue operand and the
+        // other contributors' partial sums are L2 round trips (no L1 next to 227 KB of shared memory) that would
+        // otherwise line up behind the segment's last block, on the critical path of the next step
+        const ProgOp& op = st.op[find_op(st, panel)];
+        const int op_N = op.N, op_ep = op.epilogue, op_reduce = op.tp_reduce;
+        const long long op_ep0_ll = op.ep0_ll, op_out_ll = op.out_ll;
+        void* const op_out = op.out;
+        const void* const op_ep0 = op.ep0;
+        const int n = (panel - op.panel_begin) * kPanelCols + ht;
+        const bool complete = (rb_begin == 0) && (rb + n_blk == RB);
+        // K-split panel.  The owner of the panel's FIRST block finishes it: that segment is the last of its
+        // owner's range, so by then the other contributors (whose ranges end at the same time, or - the owner
+        // of the panel's tail - much earlier) have published; a CTA never waits in the middle of its range.
+        const int first = complete ? 0 : block_owner(T, panel * RB, G);
+        const bool sparse = (T < G);  // every block of the step is a different CTA
+        uint2* const slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
+        const int n_contrib = (complete || rb_begin > 0) ? 1 : (sparse ? RB : block_owner(T, panel * RB + RB - 1, G) - first + 1);
+        uint32_t e0w = tag << 16;  // {tag | f16 epilogue operand}
+        uint2 pv[4];
+#pragma unroll
+        for (int o = 0; o < 4; ++o) pv[o] = make_uint2(0u, 0u);
+        if (rb_begin == 0 && n < op_N) {
+          if (op_ep0_ll >= 0) e0w = ld_vol_u32(reinterpret_cast<const uint32_t*>(ws_ll) + op_ep0_ll + n);
+          else if (op_ep0) e0w |= (uint32_t)__half_as_ushort(__ldcg(reinterpret_cast<const __half*>(op_ep0) + n));
+#pragma unroll
+          for (int o = 0; o < 4; ++o)
+            if (1 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(1 + o) * kPanelCols + ht);
+        }
         float sum = 0.f;
         for (int bb = 0; bb < n_blk; ++bb, ++m) {
           const int ai = m & (kNAcc - 1);
           TC_ACC(th_fin);
           mbar_wait(accfull0 + 8 * ai, (m / kNAcc) & 1);
           TC_ACC(th_accfull);
+          if (ht == 0 && t == t0 && bb == 0) TC_EV(j, 2);
           tc_fence_after();
           uint32_t d[4];
           tmem_ld_32x4(d_taddr0 + ai * 16, d);
@@ -497,85 +547,79 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           if (++s == stages) s = 0;
           TC_ACC(th_blk);
         }
+        if (ht == 0 && t + n_blk == t1) TC_EV(j, 3);
         t += n_blk;
         rb += n_blk;
         // ---- cross-CTA reduction + epilogue of the panel (as gemv_program_kernel's helpers) ---------------------
-        const ProgOp& op = st.op[find_op(st, panel)];
-        const int n = (panel - op.panel_begin) * kPanelCols + ht;
-        const bool complete = (rb_begin == 0) && (rb == RB);
         bool finalize = true;
         if (!complete) {
-          // K-split panel.  The owner of the panel's FIRST block finishes it: that segment is the last of its
-          // owner's range, so by then the other contributors (whose ranges end at the same time, or - the owner
-          // of the panel's tail - much earlier) have published; a CTA never waits in the middle of its range.
-          const int first = block_owner(T, panel * RB, G);
-          const bool sparse = (T < G);  // every block of the step is a different CTA
-          uint2* slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
           if (rb_begin > 0) {
             const int my_slot = sparse ? rb_begin : b - first;
             st_vol_v2(slot0 + (size_t)my_slot * kPanelCols + ht, __float_as_uint(sum), tag);
             finalize = false;
           } else {
-            const int n_contrib = sparse ? RB : block_owner(T, panel * RB + RB - 1, G) - first + 1;
-            for (int o0 = 1; o0 < n_contrib; o0 += 4) {  // up to four polls in flight; added in block order
-              uint2 pv[4];
+            for (int o0 = 1; o0 < n_contrib; o0 += 4) {  // four polls in flight (the first four since the segment began)
+              if (o0 > 1) {
+#pragma unroll
+                for (int o = 0; o < 4; ++o)
+                  if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
+              }
 #pragma unroll
               for (int o = 0; o < 4; ++o)
-                if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
-#pragma unroll
-              for (int o = 0; o < 4; ++o)
-                if (o0 + o < n_contrib) {
+                if (o0 + o < n_contrib) {  // added in block order
                   while (pv[o].y != tag) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
                   sum += __uint_as_float(pv[o].x);
                 }
             }
           }
         }
-        if (finalize && n < op.N && op.tp_reduce && tp.size > 1) {
-          // row-parallel op: `sum` is this rank's partial.  The ranks take turns owning panels: the others push
-          // their f32 partial to the owner's slots over NVLink; the owner adds them in rank order, applies the
-          // epilogue ONCE and pushes the finished {f16 | tag} word into every rank's activation array - the
-          // all-reduce of the sharded block, inside the launch (no collective kernel, no launch boundary).
-          const int pl = panel - op.panel_begin;
-          const int owner = pl % tp.size;
-          const size_t slot = st.tp_partial_off + ((size_t)panel * tp.size) * kPanelCols + ht;
-          if (tp.rank != owner) {
-            uint2* dst = reinterpret_cast<uint2*>(tp.ws[owner] + tp.partial_off) + slot + (size_t)tp.rank * kPanelCols;
-            st_vol_v2(dst, __float_as_uint(sum), tag);
-          } else {
-            const uint2* src = ws_partial + slot;
-            float tot = 0.f;
-            for (int r = 0; r < tp.size; ++r) {
-              if (r == tp.rank) { tot += sum; continue; }
-              uint2 pv = ld_vol_v2(src + (size_t)r * kPanelCols);
-              while (pv.y != tag) pv = ld_vol_v2(src + (size_t)r * kPanelCols);
-              tot += __uint_as_float(pv.x);
+        if (finalize && n < op_N) {
+          if (op_reduce && tp.size > 1) {
+            // row-parallel op: `sum` is this rank's partial.  The ranks take turns owning panels: the others push
+            // their f32 partial to the owner's slots over NVLink; the owner adds them in rank order, applies the
+            // epilogue ONCE and pushes the finished {f16 | tag} word into every rank's activation array - the
+            // all-reduce of the sharded block, inside the launch (no collective kernel, no launch boundary).
+            const int owner = (panel - op.panel_begin) % tp.size;
+            const size_t slot = st.tp_partial_off + ((size_t)panel * tp.size) * kPanelCols + ht;
+            if (tp.rank != owner) {
+              uint2* dst = reinterpret_cast<uint2*>(tp.ws[owner] + tp.partial_off) + slot + (size_t)tp.rank * kPanelCols;
+              st_vol_v2(dst, __float_as_uint(sum), tag);
+              finalize = false;
+            } else {
+              const uint2* src = ws_partial + slot;
+              float tot = 0.f;
+              for (int r = 0; r < tp.size; ++r) {
+                if (r == tp.rank) { tot += sum; continue; }
+                uint2 rv = ld_vol_v2(src + (size_t)r * kPanelCols);
+                while (rv.y != tag) rv = ld_vol_v2(src + (size_t)r * kPanelCols);
+                tot += __uint_as_float(rv.x);
+              }
+              sum = tot;
             }
-            __half e0 = __ushort_as_half(0);
-            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag);
-            else if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
-            const __half y = ep_f16(tot, op.epilogue, &e0, 0);
-            const uint32_t word = (tag << 16) | (uint32_t)__half_as_ushort(y);
-            if (op.out_ll >= 0)
-              for (int r = 0; r < tp.size; ++r)
-                st_vol_u32(reinterpret_cast<uint32_t*>(tp.ws[r] + tp.ll_off) + op.out_ll + n, word);
-            reinterpret_cast<__half*>(op.out)[n] = y;
           }
-        } else if (finalize && n < op.N) {
-          if (op.epilogue == B200Q_EP_CAST_F32) {
-            reinterpret_cast<float*>(op.out)[n] = sum;
-          } else {
-            __half e0 = __ushort_as_half(0);
-            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag);
-            else if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
-            const __half y = ep_f16(sum, op.epilogue, &e0, 0);
-            if (op.out_ll >= 0)
-              st_vol_u32(reinterpret_cast<uint32_t*>(ws_ll) + op.out_ll + n, (tag << 16) | (uint32_t)__half_as_ushort(y));
-            reinterpret_cast<__half*>(op.out)[n] = y;
+          if (finalize) {
+            if (op_ep == B200Q_EP_CAST_F32) {
+              reinterpret_cast<float*>(op_out)[n] = sum;
+            } else {
+              while ((e0w >> 16) != tag) e0w = ld_vol_u32(reinterpret_cast<const uint32_t*>(ws_ll) + op_ep0_ll + n);
+              const __half e0 = __ushort_as_half((unsigned short)(e0w & 0xFFFFu));
+              const __half y = ep_f16(sum, op_ep, &e0, 0);
+              if (op_out_ll >= 0) {
+                const uint32_t word = (tag << 16) | (uint32_t)__half_as_ushort(y);
+                if (op_reduce && tp.size > 1) {
+                  for (int r = 0; r < tp.size; ++r)
+                    st_vol_u32(reinterpret_cast<uint32_t*>(tp.ws[r] + tp.ll_off) + op_out_ll + n, word);
+                } else {
+                  st_vol_u32(reinterpret_cast<uint32_t*>(ws_ll) + op_out_ll + n, word);
+                }
+              }
+              reinterpret_cast<__half*>(op_out)[n] = y;
+            }
           }
         }
         if (rb == RB) { rb = 0; ++panel; }
       }
+      if (ht == 0) TC_EV(j, 4);
     }
     TC_PRINT(b == 0 && ht == 0, "helper: n=%d accfull %lld block %lld finalize+step %lld (totals / blocks)\n", m, th_accfull / (m + 1),
              th_blk / (m + 1), th_fin / (m + 1));
@@ -596,6 +640,11 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   // every accumulator has been read (the helpers waited for the last commit): TMEM can go back
   tc_fence_before();
   __syncthreads();
+#ifdef B200Q_TC_TRACE
+  if (threadIdx.x < kTrSteps && n_steps > kTrStep0 + kTrSteps)
+    printf("TR %d %d %llu %llu %llu %llu %llu %llu\n", b, kTrStep0 + (int)threadIdx.x, tc_trace[threadIdx.x][0], tc_trace[threadIdx.x][1],
+           tc_trace[threadIdx.x][2], tc_trace[threadIdx.x][3], tc_trace[threadIdx.x][4], tc_trace[threadIdx.x][5]);
+#endif
   if (warp == kMmaWarp) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);

@@ -1,3 +1,4 @@
-timeout -s KILL 60 python scripts/prog_sweep.py q4f16_0 4096x32000 2>&1 | tail -6
-timeout -s KILL 60 python scripts/prog_sweep.py q4f16_0 4096x4096 2>&1 | tail -6
-timeout -s KILL 90 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-per-shape 2>/dev/null | grep -E "^(dq|x|mma|helper):" | tail -5
+timeout -s KILL 90 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-per-shape 2>/dev/null > gpurun_out/trace_raw.txt
+grep -c "^TR" gpurun_out/trace_raw.txt
+tail -n 2400 gpurun_out/trace_raw.txt | grep "^TR" | tail -n 1184 > gpurun_out/trace.txt
+wc -l gpurun_out/trace.txt
