@@ -587,7 +587,7 @@ int stage_bytes_for(int fmt) {
 }
 int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
   if (use_tc) {
-    int s = (kSmemPerSm - tc::kHeaderTc - tc::kBSlots * tc::kBSlotBytes - 512) / tc::kStageBytesTc;  // no activation staging
+    int s = (kSmemPerSm - tc::kHeaderTc - tc::kBSlots * tc::kBSlotBytes - 1024) / tc::kStageBytesTc;  // no activation staging
     return s > tc::kMaxStagesTc ? tc::kMaxStagesTc : s;
   }
   int s = (kSmemPerSm - kHeader - 2 * xs_bytes - 1024) / stage_bytes_for(fmt);
@@ -726,7 +726,7 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   if (G != device_sm_count()) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: program was built for %d SMs", G);
   const bool use_tc = h->tc != 0;
   int stages = stages_for(h->fmt, h->xs_bytes, use_tc);
-  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kBSlots * tc::kBSlotBytes + 512 + (size_t)stages * tc::kStageBytesTc
+  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kBSlots * tc::kBSlotBytes + 1024 + (size_t)stages * tc::kStageBytesTc
                              : (size_t)kHeader + 2 * (size_t)h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
 
   const ProgStep* prog = reinterpret_cast<const ProgStep*>(reinterpret_cast<const unsigned char*>(dev_blob) + sizeof(ProgHeader));

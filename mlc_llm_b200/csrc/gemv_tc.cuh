@@ -50,6 +50,9 @@ constexpr int kMaxStagesTc = 24;
 constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStagesTc, kBarAFree = kBarAReady + 2 * kASets,
               kBarAccFull = kBarAFree + 2 * kASets, kBarAccFree = kBarAccFull + kNAcc, kBarBReady = kBarAccFree + kNAcc,
               kBarBFree = kBarBReady + 2 * kASets, kNumBars = kBarBFree + 2 * kASets;  // 96
+// the scalar tail of a ProgStep (everything behind the tensor maps) is mirrored in shared memory by the epilogue warps
+constexpr int kTailOff = (int)offsetof(ProgStep, op);
+constexpr int kTailWords = ((int)sizeof(ProgStep) - kTailOff) / 4;  // 80
 constexpr int kTmemPtrOff = 8 * kNumBars;    // 768
 constexpr int kHeaderTc = 1024;
 
@@ -131,8 +134,12 @@ __device__ __forceinline__ unsigned long long tc_globaltimer() {
   return t;
 }
 #define TC_EV(j, e) do { if ((j) >= kTrStep0 && (j) < kTrStep0 + kTrSteps) tc_trace[(j) - kTrStep0][e] = tc_globaltimer(); } while (0)
+// per-block events (SM clock) of the CTA-local blocks [kTrBlk0, kTrBlk0 + kTrBlks)
+constexpr int kTrBlk0 = 870, kTrBlks = 64;
+#define TC_BEV(m, e) do { if ((m) >= kTrBlk0 && (m) < kTrBlk0 + kTrBlks) tc_btrace[(m) - kTrBlk0][e] = (unsigned)clock(); } while (0)
 #else
 #define TC_EV(j, e) do { } while (0)
+#define TC_BEV(m, e) do { } while (0)
 #endif
 #ifdef B200Q_TC_TIMING
 #define TC_T0() long long _t0 = clock64()
@@ -159,6 +166,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   extern __shared__ __align__(128) unsigned char smem[];
 #ifdef B200Q_TC_TRACE
   __shared__ unsigned long long tc_trace[kTrSteps][6];
+  __shared__ unsigned tc_btrace[kTrBlks][8];
 #endif
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
@@ -171,7 +179,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + kTmemPtrOff);
   unsigned char* bslots = smem + kHeaderTc;
   float* corr_s = reinterpret_cast<float*>(bslots + kBSlots * kBSlotBytes);  // [16 blocks][4 groups]: 1136 * sum of the group's x
-  const uint32_t stage_base = (smem_u32(corr_s + 64) + 127u) & ~127u;
+  uint32_t* stepc = reinterpret_cast<uint32_t*>(corr_s + 64);  // [2][kTailWords]: step tails, see the epilogue warps
+  const uint32_t stage_base = (smem_u32(stepc + 2 * kTailWords) + 127u) & ~127u;
   (void)xs_bytes;
 
   if (threadIdx.x == 0) {
@@ -193,6 +202,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     }
     fence_barrier_init();
   }
+#ifdef B200Q_TC_TRACE
+  for (int i = threadIdx.x; i < kTrBlks * 8; i += kThreadsTc) (&tc_btrace[0][0])[i] = 0u;
+#endif
   // the B slots start as zeros: slot (set, g) only ever gets activation rows written into operand row g
   for (int i = threadIdx.x; i < kBSlots * kBSlotBytes / 16; i += kThreadsTc)
     reinterpret_cast<uint4*>(bslots)[i] = make_uint4(0, 0, 0, 0);
@@ -219,17 +231,24 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         const int T = st.T, RB = st.RB;
         const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
         int panel = t0 / RB, rb = t0 - panel * RB;
-        for (int t = t0; t < t1; ++t) {
+        for (int t = t0; t < t1;) {
+          // one panel segment: the tensor maps and the column are fixed, the inner loop is the bare minimum
           const int oi = find_op(st, panel);
           const int col0 = (panel - st.op[oi].panel_begin) * kPanelCols;
-          mbar_wait(empty0 + 8 * s, ph ^ 1);
-          const uint32_t bar = full0 + 8 * s;
-          mbar_expect_tx(bar, (uint32_t)kStageBytesTc);
-          const uint32_t sw = stage_base + s * kStageBytesTc;
-          tma_load_2d_hint(sw, &st.tm_w[oi], col0, rb * kRows, bar, pol);
-          tma_load_2d_hint(sw + kStageWordBytes, &st.tm_s[oi], col0, rb * 4, bar, pol);
-          if (++s == stages) { s = 0; ph ^= 1; }
-          if (++rb == RB) { rb = 0; ++panel; }
+          const CUtensorMap* tmw = &st.tm_w[oi];
+          const CUtensorMap* tms = &st.tm_s[oi];
+          const int rb_end = min(RB, rb + (t1 - t));
+          t += rb_end - rb;
+          for (; rb < rb_end; ++rb) {
+            mbar_wait(empty0 + 8 * s, ph ^ 1);
+            const uint32_t bar = full0 + 8 * s;
+            mbar_expect_tx(bar, (uint32_t)kStageBytesTc);
+            const uint32_t sw = stage_base + s * kStageBytesTc;
+            tma_load_2d_hint(sw, tmw, col0, rb * kRows, bar, pol);
+            tma_load_2d_hint(sw + kStageWordBytes, tms, col0, rb * 4, bar, pol);
+            if (++s == stages) { s = 0; ph ^= 1; }
+          }
+          if (rb == RB) { rb = 0; ++panel; }
         }
       }
     }
@@ -250,6 +269,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       const uint32_t ph = (uint32_t)(m / stages) & 1u;
       mbar_wait(full0 + 8 * s, ph);
       TC_ACC(tq_full);
+      if (q == 0 && lane == 0) TC_BEV(m, 0);
       const uint32_t sw = stage_base + s * kStageBytesTc + (uint32_t)n * 4;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
@@ -269,6 +289,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         TC_ACC(tq_unp);
         mbar_wait(afree0 + 8 * (2 * sl + h), (use & 1u) ^ 1u);  // the MMAs of this half set's previous block are done
         TC_ACC(tq_afree);
+        if (q == 0 && lane == 0 && h == 0) TC_BEV(m, 1);
         tc_fence_after();
         if (!(dbg & 2)) tmem_st_32x32(a_taddr0 + h * 32, a);
         tmem_st_wait();
@@ -277,6 +298,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         if (lane == 0) {
           mbar_arrive(aready0 + 8 * (2 * sl + h));
           if (h == 1) mbar_arrive(empty0 + 8 * s);  // the words have left shared memory
+          if (q == 0 && h == 1) TC_BEV(m, 2);
         }
         TC_ACC(tq_st);
       }
@@ -285,144 +307,130 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
              tq_unp / (use + 1), tq_afree / (use + 1), tq_st / (use + 1));
   } else if (warp >= kXWarp0) {
     // ================= activation warps: the B operand of the blocks of one dequant slice =====================
-    // B part (16 lanes, lane = 4 g + c): the 8 activations of packed word row c of group g are read straight from
-    // their producer's LL words (polled here, per block: a block starts as soon as ITS 128 activations exist) or
-    // from a plain input, multiplied by x_mul if the step has one, and written in the unpack's pair order into
-    // operand row g of B slot (slice, g); the other rows of the slot stay zero.  The group's activation sum
-    // (x 1136) goes to the epilogue warps through a small ring.  One generic->async proxy fence per block.
-    // Every slice has two slot sets and the loads of the block after the next are in the air, so the warp runs up
-    // to eight blocks ahead of the tensor core and a block of the next step starts as soon as ITS row block exists.
+    // Lane 4 g + c of the LOWER half warp owns packed word row c of group g: its 8 activations are read straight
+    // from their producer's LL words (polled here, per block: a block starts as soon as ITS 128 activations
+    // exist) or from a plain input; the UPPER half warp fetches the matching x_mul rows, if the step has one, and
+    // hands them down with four shuffles.  The row goes, in the unpack's pair order, into operand row g of B slot
+    // (slot set, slice, g); the other rows of the slot stay zero.  The group's correction  sum_k off(k) x[k]
+    // goes to the epilogue warps through a small ring.  One generic->async proxy fence per block.
+    // Every slice has two slot sets and the loads of the next block are in the air during this one, so the warp
+    // runs up to eight blocks ahead of the tensor core.  These warps share their SM sub-partitions with the
+    // dequant warps (an instruction costs ~5 cycles here): the common case is kept short.
     const int sl = warp - kXWarp0;
-    const int g = (lane >> 2) & 3, c = lane & 3;
-    const uint32_t my_slot = smem_u32(bslots) + (4 * sl + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
+    const int upper = lane >> 4, g = (lane >> 2) & 3, c = lane & 3;
+    const uint32_t slot_lane = smem_u32(bslots) + (4 * sl + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
     const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
     const uint32_t tag = (ld_acquire_u32(ws_ctrl) % 65535u) + 1u;
-    // iterator over this CTA's blocks; the slice takes those with m % 4 == sl
-    // (the step table lives in global memory and there is no L1 to speak of next to 227 KB of shared memory:
-    // every field read is an L2 round trip, so the fields are cached in registers when the iterator enters a step)
-    int it_j = -1, it_t = 0, it_t1 = 0, it_rb = 0, it_RB = 1, it_m = 0, it_K = 0;
-    long long it_xll = -1, it_mll = -1;
-    const __half* it_xp = nullptr;
-    const __half* it_mp = nullptr;
-    bool it_hasm = false;
-    bool it_valid = false;
-    bool p_first = false;  // (trace) first block of the CTA's share of a step
-    int p_j = 0, it_t0 = 0;
-    auto seek = [&]() {  // move to the next own block at or after the current position
-      for (;;) {
-        if (it_t >= it_t1) {
-          if (++it_j >= n_steps) { it_valid = false; return; }
-          const ProgStep& st = prog[it_j];
-          const int T = st.T;
-          it_RB = st.RB;
-          it_K = st.K;
-          it_hasm = st.has_xmul != 0;
-          it_xll = st.x_ll;
-          it_mll = it_hasm ? st.xmul_ll : -1;
-          it_xp = reinterpret_cast<const __half*>(st.x);
-          it_mp = reinterpret_cast<const __half*>(st.x_mul);
-          it_t = cta_begin(T, b, G);
-          it_t1 = cta_begin(T, b + 1, G);
-          it_rb = it_t % it_RB;
-          it_t0 = it_t;
-          continue;
-        }
-        if ((it_m & 3) == sl) { it_valid = true; return; }
-        ++it_t; ++it_m;
-        if (++it_rb == it_RB) it_rb = 0;
+    // iterator: the slice's next block (CTA-local number it_m, it_m % 4 == sl) = block it_t of step it_j.
+    // (The step table is in global memory and there is no L1 to speak of next to 227 KB of shared memory: every
+    // field read is an L2 round trip, so the fields live in registers while the iterator is inside a step.)
+    int it_j = -1, it_t = sl, it_t1 = 0, it_t0 = 0, it_rb = 0, it_RB = 1, it_m = sl, it_K = 0;
+    long long it_ll = -1;            // this lane's source: LL element offset, or -1: plain vector it_ptr
+    const __half* it_ptr = nullptr;
+    bool it_hasm = false, it_valid = true;
+    auto settle = [&]() {  // it_t may have run past the end of the step: carry the excess into the following steps
+      while (it_t >= it_t1) {
+        const int carry = it_t - it_t1;
+        if (++it_j >= n_steps) { it_valid = false; return; }
+        const ProgStep& st = prog[it_j];
+        const int T = st.T;
+        it_RB = st.RB;
+        it_K = st.K;
+        it_hasm = st.has_xmul != 0;
+        it_ll = upper ? (it_hasm ? st.xmul_ll : -1) : st.x_ll;
+        it_ptr = reinterpret_cast<const __half*>(upper ? st.x_mul : st.x);
+        it_t0 = cta_begin(T, b, G);
+        it_t1 = cta_begin(T, b + 1, G);
+        it_t = it_t0 + carry;
+        it_rb = it_t % it_RB;
       }
     };
-    // the activation row of this lane for the block under the iterator: loads issued, not yet checked
-    Row8 rx, rm;
-    int p_k0 = 0, p_nvalid = 0, p_m = 0;
-    long long p_xll = -1, p_mll = -1;
-    const __half* p_xp = nullptr;
-    const __half* p_mp = nullptr;
-    bool p_hasm = false;
+    // this lane's row of the block under the iterator: loads issued, not yet checked; then the iterator moves on
+    Row8 row;
+    int p_k0 = 0, p_nvalid = 0, p_m = 0, p_j = 0;
+    long long p_ll = -1;
+    const __half* p_ptr = nullptr;
+    bool p_hasm = false, p_first = false;
     auto preload = [&]() {
+      p_first = (it_t == it_t0);
+      p_j = it_j;
       p_m = it_m;
-      p_first = (it_t == it_t0); p_j = it_j;
-      p_xll = it_xll; p_mll = it_mll; p_xp = it_xp; p_mp = it_mp; p_hasm = it_hasm;
+      p_ll = it_ll; p_ptr = it_ptr; p_hasm = it_hasm;
       p_k0 = (it_rb * kRows + 4 * g + c) * 8;
-      p_nvalid = (lane < 16) ? min(8, max(0, it_K - p_k0)) : 0;
-      rx.lo = rx.hi = rm.lo = rm.hi = make_uint4(0, 0, 0, 0);
-      if (p_nvalid == 8 && p_xll >= 0) {
-        rx.lo = ld_vol_v4(ll + p_xll + p_k0);
-        rx.hi = ld_vol_v4(ll + p_xll + p_k0 + 4);
-      } else if (p_nvalid == 8 && (reinterpret_cast<uintptr_t>(p_xp) & 15) == 0) {
-        rx.lo = __ldcg(reinterpret_cast<const uint4*>(p_xp + p_k0));
-      }
-      if (p_nvalid == 8 && p_hasm) {
-        if (p_mll >= 0) {
-          rm.lo = ld_vol_v4(ll + p_mll + p_k0);
-          rm.hi = ld_vol_v4(ll + p_mll + p_k0 + 4);
-        } else if ((reinterpret_cast<uintptr_t>(p_mp) & 15) == 0) {
-          rm.lo = __ldcg(reinterpret_cast<const uint4*>(p_mp + p_k0));
+      p_nvalid = (upper == 0 || it_hasm) ? min(8, max(0, it_K - p_k0)) : 0;
+      row.lo = row.hi = make_uint4(0, 0, 0, 0);
+      if (p_nvalid == 8) {
+        if (p_ll >= 0) {
+          row.lo = ld_vol_v4(ll + p_ll + p_k0);
+          row.hi = ld_vol_v4(ll + p_ll + p_k0 + 4);
+        } else if ((reinterpret_cast<uintptr_t>(p_ptr) & 15) == 0) {
+          row.lo = __ldcg(reinterpret_cast<const uint4*>(p_ptr + p_k0));
         }
       }
+      it_t += 4;
+      it_m += 4;
+      it_rb += 4;
+      while (it_rb >= it_RB) it_rb -= it_RB;
+      settle();
     };
-    // B part for the block whose loads were issued by the last preload(), into the slot set `par` of this slice
-    auto bpart = [&](int par) {
-      const __half* xp = p_xp;
-      const __half* mp = p_mp;
-      const long long x_ll = p_xll, m_ll = p_mll;
-      const bool x_vec = (reinterpret_cast<uintptr_t>(xp) & 15) == 0, m_vec = (reinterpret_cast<uintptr_t>(mp) & 15) == 0;
-      __align__(16) __half v[8];
-      *reinterpret_cast<uint4*>(v) = make_uint4(0, 0, 0, 0);
-      if (p_nvalid > 0) {
-        if (p_nvalid == 8 && x_ll < 0 && x_vec) *reinterpret_cast<uint4*>(v) = rx.lo;  // plain row, loaded by preload()
-        else *reinterpret_cast<uint4*>(v) = tc_finish_row(rx, xp, ll, x_ll, p_k0, p_nvalid, x_vec, tag);
-        if (p_hasm) {
-          __align__(16) __half mv[8];
-          if (p_nvalid == 8 && m_ll < 0 && m_vec) *reinterpret_cast<uint4*>(mv) = rm.lo;
-          else *reinterpret_cast<uint4*>(mv) = tc_finish_row(rm, mp, ll, m_ll, p_k0, p_nvalid, m_vec, tag);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = __hmul(v[i], mv[i]);
+    // B operand of the preloaded block, into slot set `par` of this slice
+    auto bpart = [&](uint32_t par) {
+      const bool vec = (reinterpret_cast<uintptr_t>(p_ptr) & 15) == 0;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (p_nvalid == 8 && p_ll >= 0) {  // the common case: a whole row of LL words
+        while (!ll_row_ready(row, tag)) {
+          row.lo = ld_vol_v4(ll + p_ll + p_k0);
+          row.hi = ld_vol_v4(ll + p_ll + p_k0 + 4);
         }
+        v = ll_row_pack(row);
+      } else if (p_nvalid == 8 && vec) {
+        v = row.lo;  // plain row, loaded by preload()
+      } else if (p_nvalid > 0) {
+        v = tc_finish_row(row, p_ptr, ll, p_ll, p_k0, p_nvalid, vec, tag);
       }
-      float sm_e = 0.f, sm_o = 0.f;
-#pragma unroll
-      for (int i = 0; i < 8; i += 2) {
-        sm_e += __half2float(v[i]);
-        sm_o += __half2float(v[i + 1]);
+      uint4 mv;
+      mv.x = __shfl_down_sync(0xffffffffu, v.x, 16);
+      mv.y = __shfl_down_sync(0xffffffffu, v.y, 16);
+      mv.z = __shfl_down_sync(0xffffffffu, v.z, 16);
+      mv.w = __shfl_down_sync(0xffffffffu, v.w, 16);
+      if (p_hasm) {
+        v.x = h2_as_u32(__hmul2(u32_as_h2(v.x), u32_as_h2(mv.x)));
+        v.y = h2_as_u32(__hmul2(u32_as_h2(v.y), u32_as_h2(mv.y)));
+        v.z = h2_as_u32(__hmul2(u32_as_h2(v.z), u32_as_h2(mv.z)));
+        v.w = h2_as_u32(__hmul2(u32_as_h2(v.w), u32_as_h2(mv.w)));
       }
-      float sm = fmaf(kOffEven, sm_e, kOffOdd * sm_o);
+      // v = (x0,x1)(x2,x3)(x4,x5)(x6,x7); even k carry the offset 1024 + 7, odd k 64 + 7
+      const float2 f0 = __half22float2(u32_as_h2(v.x)), f1 = __half22float2(u32_as_h2(v.y));
+      const float2 f2 = __half22float2(u32_as_h2(v.z)), f3 = __half22float2(u32_as_h2(v.w));
+      float sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
       sm += __shfl_xor_sync(0xffffffffu, sm, 1);
       sm += __shfl_xor_sync(0xffffffffu, sm, 2);
       if (lane < 16) {
-        __align__(16) __half o[8] = {v[0], v[4], v[1], v[5], v[2], v[6], v[3], v[7]};
-        sts128(my_slot + par * (kABufs * kBSlotBytes), *reinterpret_cast<const uint4*>(o));
+        // the unpack's pair order: (x0,x4)(x1,x5)(x2,x6)(x3,x7)
+        sts128(slot_lane + par * (kABufs * kBSlotBytes),
+               make_uint4(__byte_perm(v.x, v.z, 0x5410), __byte_perm(v.x, v.z, 0x7632), __byte_perm(v.y, v.w, 0x5410),
+                          __byte_perm(v.y, v.w, 0x7632)));
         if (c == 0) corr_s[(p_m & 15) * 4 + g] = sm;
       }
       fence_proxy_async_smem();
       __syncwarp();
     };
-    auto advance = [&]() {
-      ++it_t; ++it_m;
-      if (++it_rb == it_RB) it_rb = 0;
-      seek();
-    };
-    seek();
-    if (it_valid) preload();
-    TC_DECL(tx_bfree = 0, tx_b = 0, tx_adv = 0);
-    TC_T0();
-    uint32_t use = 0;
-    for (; it_valid; ++use) {
-      const int par = (int)(use & 1u);
-      // the MMAs of the block that used this slot set two uses ago are done (first two uses: passes at once)
-      mbar_wait(bfree0 + 8 * (2 * sl + par), ((use >> 1) & 1u) ^ 1u);
-      TC_ACC(tx_bfree);
-      if (p_first && lane == 0) TC_EV(p_j, 5);
-      bpart(par);
-      if (lane == 0) mbar_arrive(bready0 + 8 * (2 * sl + par));
-      if (p_first && lane == 0) TC_EV(p_j, 0);
-      TC_ACC(tx_b);
-      advance();
-      if (it_valid) preload();
-      TC_ACC(tx_adv);
+    settle();
+    if (it_valid) {
+      preload();  // p_*: the block to serve; the iterator is already one block further
+      for (uint32_t use = 0;; ++use) {
+        const uint32_t par = use & 1u;
+        // the MMAs of the block that used this slot set two uses ago are done (first two uses: passes at once)
+        mbar_wait(bfree0 + 8 * (2 * sl + par), ((use >> 1) & 1u) ^ 1u);
+        if (p_first && lane == 0) TC_EV(p_j, 5);
+        bpart(par);
+        if (lane == 0) mbar_arrive(bready0 + 8 * (2 * sl + par));
+        if (p_first && lane == 0) TC_EV(p_j, 0);
+        if (lane == 0) TC_BEV(p_m, 3);
+        if (!it_valid) break;
+        preload();
+      }
     }
-    TC_PRINT(b == 0 && sl == 0 && lane == 0, "x: n=%d bfree %lld bpart %lld advance+preload %lld\n", (int)use, tx_bfree / (use + 1),
-             tx_b / (use + 1), tx_adv / (use + 1));
   } else if (warp == kMmaWarp || warp == kMmaWarp2) {
     // ================= MMA warps: eight tcgen05.mma per block (two per group), whole loop in one lane ========
     const uint32_t idesc = make_idesc_f16(128, 16, 0, 0);
@@ -447,6 +455,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         for (int h = 0; h < 2; ++h) {
           mbar_wait(aready0 + 8 * (2 * set + h), use & 1u);
           if (h == 0) TC_ACC(tm_a0); else TC_ACC(tm_a1);
+          if (h == 1) TC_BEV(m, 4);
           tc_fence_after();
           if (!(dbg & 1)) {
 #pragma unroll
@@ -476,11 +485,22 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     int m = 0;
     TC_DECL(th_accfull = 0, th_blk = 0, th_fin = 0);
     TC_T0();
+    // The step table is in global memory and there is no L1 to speak of next to 227 KB of shared memory: every
+    // field read is an L2 round trip (~0.4 us), and a segment needs several dependent ones.  The 128 epilogue
+    // threads therefore mirror the scalar tail of the CURRENT step in shared memory (one word per thread) and
+    // fetch the next step's while the current one is processed.
+    auto tail_word = [&](int j) -> uint32_t {
+      return (ht < kTailWords && j < n_steps)
+                 ? __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const unsigned char*>(prog + j) + kTailOff) + ht) : 0u;
+    };
+    if (ht < kTailWords) stepc[ht] = tail_word(0);
+    asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");
     for (int j = 0; j < n_steps; ++j) {
-      const ProgStep& st = prog[j];
+      // (only the tail of this reference is real - the tensor maps are never read through it)
+      const ProgStep& st = *reinterpret_cast<const ProgStep*>(reinterpret_cast<const unsigned char*>(stepc + (j & 1) * kTailWords) - kTailOff);
+      const uint32_t next_word = tail_word(j + 1);
       const int T = st.T, RB = st.RB;
       const int t0 = cta_begin(T, b, G), t1 = cta_begin(T, b + 1, G);
-      if (t0 >= t1) continue;
       int panel = t0 / RB, rb = t0 - panel * RB;
       int t = t0;
       while (t < t1) {
@@ -619,7 +639,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         }
         if (rb == RB) { rb = 0; ++panel; }
       }
-      if (ht == 0) TC_EV(j, 4);
+      if (ht == 0 && t0 < t1) TC_EV(j, 4);
+      if (ht < kTailWords) stepc[((j + 1) & 1) * kTailWords + ht] = next_word;
+      asm volatile("bar.sync 2, %0;" ::"n"(kHelperThreads) : "memory");
     }
     TC_PRINT(b == 0 && ht == 0, "helper: n=%d accfull %lld block %lld finalize+step %lld (totals / blocks)\n", m, th_accfull / (m + 1),
              th_blk / (m + 1), th_fin / (m + 1));
@@ -642,6 +664,10 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   __syncthreads();
 #ifdef B200Q_TC_TRACE
   if (threadIdx.x < kTrSteps && n_steps > kTrStep0 + kTrSteps)
+    if (b == 5 || b == 77)
+      for (int i = threadIdx.x; i < kTrBlks; i += kTrSteps)
+        printf("BT %d %d %u %u %u %u %u %u %u %u\n", b, kTrBlk0 + i, tc_btrace[i][0], tc_btrace[i][1], tc_btrace[i][2], tc_btrace[i][3],
+               tc_btrace[i][4], tc_btrace[i][5], tc_btrace[i][6], tc_btrace[i][7]);
     printf("TR %d %d %llu %llu %llu %llu %llu %llu\n", b, kTrStep0 + (int)threadIdx.x, tc_trace[threadIdx.x][0], tc_trace[threadIdx.x][1],
            tc_trace[threadIdx.x][2], tc_trace[threadIdx.x][3], tc_trace[threadIdx.x][4], tc_trace[threadIdx.x][5]);
 #endif
