@@ -264,9 +264,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     uint32_t use = 0;
     TC_DECL(tq_full = 0, tq_unp = 0, tq_afree = 0, tq_st = 0);
     TC_T0();
+    int s = sl;        // ring stage of block m = m % stages, phase = (m / stages) & 1 (kept incrementally: a division
+    uint32_t ph = 0;   // by a run-time number costs ~20 of the ~120 instructions of a block)
     for (int m = sl; m < n_total; m += 4, ++use) {
-      const int s = m % stages;
-      const uint32_t ph = (uint32_t)(m / stages) & 1u;
       mbar_wait(full0 + 8 * s, ph);
       TC_ACC(tq_full);
       if (q == 0 && lane == 0) TC_BEV(m, 0);
@@ -302,6 +302,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         }
         TC_ACC(tq_st);
       }
+      s += 4;
+      if (s >= stages) { s -= stages; ph ^= 1u; }
     }
     TC_PRINT(b == 0 && warp == 0 && lane == 0, "dq: n=%d full %lld unpack %lld afree %lld st %lld\n", (int)use, tq_full / (use + 1),
              tq_unp / (use + 1), tq_afree / (use + 1), tq_st / (use + 1));
@@ -547,12 +549,11 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           // scales and corrections of the block while the TMEM load is in flight
           const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
           const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & 15) * 4) * 4;
-          float sc[4], cg[4];
+          float sc[4];
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
-            cg[g] = lds_f32(c_addr + g * 4);
-          }
+          for (int g = 0; g < 4; ++g) sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
+          const uint4 cg4 = gemvdev::lds128(c_addr);
+          const float cg[4] = {__uint_as_float(cg4.x), __uint_as_float(cg4.y), __uint_as_float(cg4.z), __uint_as_float(cg4.w)};
           tmem_ld_wait();
           tc_fence_before();
           __syncwarp();
