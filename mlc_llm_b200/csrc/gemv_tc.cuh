@@ -144,6 +144,13 @@ constexpr int kTrBlk0 = 870, kTrBlks = 64;
 #define TC_EV(j, e) do { } while (0)
 #define TC_BEV(m, e) do { } while (0)
 #endif
+// B200Q_TC_DBG=<bits> (environment) switches pipeline stages off for bisecting, only in -DB200Q_TC_DBGFLAGS builds:
+// the tests cost the dequant loop two instructions per half block
+#ifdef B200Q_TC_DBGFLAGS
+#define TC_DBG(bit) (dbg & (bit))
+#else
+#define TC_DBG(bit) false
+#endif
 #ifdef B200Q_TC_TIMING
 #define TC_T0() long long _t0 = clock64()
 #define TC_ACC(v) do { long long _t1 = clock64(); (v) += _t1 - _t0; _t0 = _t1; } while (0)
@@ -173,6 +180,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
 #endif
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
+  (void)dbg;
 
   const uint32_t bar0 = smem_u32(smem);
   const uint32_t full0 = bar0 + 8 * kBarFull, empty0 = bar0 + 8 * kBarEmpty;
@@ -294,7 +302,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         TC_ACC(tq_afree);
         if (q == 0 && lane == 0 && h == 0) TC_BEV(m, 1);
         tc_fence_after();
-        if (!(dbg & 2)) tmem_st_32x32(a_taddr0 + h * 32, a);
+        if (!TC_DBG(2)) tmem_st_32x32(a_taddr0 + h * 32, a);
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
@@ -462,7 +470,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           if (h == 0) TC_ACC(tm_a0); else TC_ACC(tm_a1);
           if (h == 1) TC_BEV(m, 4);
           tc_fence_after();
-          if (!(dbg & 1)) {
+          if (!TC_DBG(1)) {
 #pragma unroll
             for (int g = 2 * h; g < 2 * h + 2; ++g) {
               umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
@@ -564,7 +572,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             mbar_arrive(accfree0 + 8 * ai);
             mbar_arrive(empty0 + 8 * s);
           }
-          if (!(dbg & 8)) {
+          if (!TC_DBG(8)) {
 #pragma unroll
             for (int g = 0; g < 4; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
           }
