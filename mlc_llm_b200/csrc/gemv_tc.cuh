@@ -303,9 +303,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         if (q == 0 && lane == 0 && h == 0) TC_BEV(m, 1);
         tc_fence_after();
         if (!TC_DBG(2)) tmem_st_32x32(a_taddr0 + h * 32, a);
-        tmem_st_wait();
+        tmem_st_wait();  // (.sync.aligned: the whole warp's stores are done - no __syncwarp needed before lane 0 signals)
         tc_fence_before();
-        __syncwarp();
         if (lane == 0) {
           mbar_arrive(aready0 + 8 * (2 * sl + h));
           if (h == 1) mbar_arrive(empty0 + 8 * s);  // the words have left shared memory
@@ -565,9 +564,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           for (int g = 0; g < 4; ++g) sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
           const uint4 cg4 = gemvdev::lds128(c_addr);
           const float cg[4] = {__uint_as_float(cg4.x), __uint_as_float(cg4.y), __uint_as_float(cg4.z), __uint_as_float(cg4.w)};
-          tmem_ld_wait();
+          tmem_ld_wait();  // (.sync.aligned, like the shared-memory loads above: warp-wide)
           tc_fence_before();
-          __syncwarp();
           if (lane == 0) {
             mbar_arrive(accfree0 + 8 * ai);
             mbar_arrive(empty0 + 8 * s);
