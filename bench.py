@@ -433,7 +433,36 @@ def bench_shapes(stack, spec, torch, iters: int = 20):
     us = ts[len(ts) // 2]
     res.append({"shape": f"lm_head {stack.lm_head.K}->{stack.lm_head.N} f32 (L2 flushed, event-timed single launch)", "us": round(us, 3),
                 "gbs": round(nbytes / us / 1e3, 1), "bytes": nbytes})
+    if spec.name == "q4f16_0":
+        res.append(stream_rate(spec, torch, stack.device))
     return res
+
+
+def stream_rate(spec, torch, dev, K: int = 4096, N: int = 32000, n: int = 9, iters: int = 10):
+    """Streaming rate of the tcgen05 decode-program kernel without dependency bubbles: n INDEPENDENT
+    K x N GEMVs (distinct weights, n * 73.8 MB >> L2) as the steps of one program launch."""
+    from mlc_llm_b200 import ops
+    x = (torch.randn(K, device=dev) * 0.05).to(spec.torch_dtype)
+    steps = []
+    for _ in range(n):
+        p = torch.randint(-2**31, 2**31 - 1, (spec.n_words(K), N), dtype=torch.int32, device=dev)
+        sc = (torch.rand((spec.n_groups(K), N), device=dev) * 0.01).to(spec.torch_dtype)
+        steps.append(dict(weights=[(p, sc)], x=x, outs=[torch.empty(N, dtype=spec.torch_dtype, device=dev)]))
+    prog = ops.GemvProgram(steps, spec.name)
+    for _ in range(3):
+        prog.run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        prog.run()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / iters / n
+    nbytes = spec.gemv_bytes(K, N)
+    peak, _ = measured_peaks()
+    return {"shape": f"stream: {n} independent {K}->{N} GEMVs as steps of one program launch (no dependency bubbles, weights >> L2)",
+            "us": round(us, 3), "gbs": round(nbytes / us / 1e3, 1), "bytes": nbytes, "frac_of_peak": round(nbytes / us / 1e3 / peak, 4)}
 
 
 if __name__ == "__main__":

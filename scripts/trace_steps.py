@@ -3,8 +3,9 @@
 (relative to the step's earliest event, in us) the CTAs reach each event:
   5 activation warp starts waiting for the first block's rows   0 its B operand is written
   2 epilogue sees the first accumulator   3 last block of the CTA's share read   4 share finalized/published"""
-import sys, collections
+import sys, collections, warnings
 import numpy as np
+warnings.simplefilter('ignore')
 rows = collections.defaultdict(dict)
 for ln in open(sys.argv[1]):
     f = ln.split()
