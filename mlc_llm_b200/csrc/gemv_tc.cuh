@@ -536,15 +536,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         uint2* const slot0 = ws_partial + st.partial_off + (size_t)panel * st.c_max * kPanelCols;
         const int n_contrib = (complete || rb_begin > 0) ? 1 : (sparse ? RB : block_owner(T, panel * RB + RB - 1, G) - first + 1);
         uint32_t e0w = tag << 16;  // {tag | f16 epilogue operand}
-        uint2 pv[4];
-#pragma unroll
-        for (int o = 0; o < 4; ++o) pv[o] = make_uint2(0u, 0u);
         if (rb_begin == 0 && n < op_N) {
           if (op_ep0_ll >= 0) e0w = ld_vol_u32(reinterpret_cast<const uint32_t*>(ws_ll) + op_ep0_ll + n);
           else if (op_ep0) e0w |= (uint32_t)__half_as_ushort(__ldcg(reinterpret_cast<const __half*>(op_ep0) + n));
-#pragma unroll
-          for (int o = 0; o < 4; ++o)
-            if (1 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(1 + o) * kPanelCols + ht);
         }
         float sum = 0.f;
         for (int bb = 0; bb < n_blk; ++bb, ++m) {
@@ -588,12 +582,13 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             st_vol_v2(slot0 + (size_t)my_slot * kPanelCols + ht, __float_as_uint(sum), tag);
             finalize = false;
           } else {
-            for (int o0 = 1; o0 < n_contrib; o0 += 4) {  // four polls in flight (the first four since the segment began)
-              if (o0 > 1) {
+            // the other contributors finish their last block of the panel about now: all their slots are polled
+            // at once (one L2 round trip when the sums are there), four at a time
+            for (int o0 = 1; o0 < n_contrib; o0 += 4) {
+              uint2 pv[4];
 #pragma unroll
-                for (int o = 0; o < 4; ++o)
-                  if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
-              }
+              for (int o = 0; o < 4; ++o)
+                if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
 #pragma unroll
               for (int o = 0; o < 4; ++o)
                 if (o0 + o < n_contrib) {  // added in block order
