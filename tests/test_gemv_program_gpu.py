@@ -117,3 +117,16 @@ def test_program_in_cuda_graph_and_full_stack():
     ref.capture()
     y3 = ref.decode_step()
     assert (y1 - y3).abs().max().item() <= 2e-2 * max(1.0, y3.abs().max().item())
+
+
+def test_launch_tag_wraps_around():
+    """The LL tag is (launch epoch % 65535) + 1: more than 65535 replays of one program must keep giving the
+    same bits (every word is rewritten by every launch, so a tag can never be confused with a stale one)."""
+    stack = DecodeStack("llama-7b", "q4f16_0", layers=1, use_program=True)
+    stack.x_in.copy_((torch.randn(4096, device="cuda") * 0.05).half())
+    stack.capture()
+    y0 = stack.decode_step().clone()
+    for i in range(66000):
+        stack.decode_step()
+    torch.cuda.synchronize()
+    assert torch.equal(stack.decode_step(), y0)
