@@ -88,8 +88,15 @@ struct Row8 {
   uint4 lo, hi;  // LL: 8 x {tag << 16 | f16}; plain: lo = 8 halves
 };
 __device__ __forceinline__ bool ll_row_ready(const Row8& r, uint32_t tag) {
-  return ((r.lo.x >> 16) == tag) & ((r.lo.y >> 16) == tag) & ((r.lo.z >> 16) == tag) & ((r.lo.w >> 16) == tag) &
-         ((r.hi.x >> 16) == tag) & ((r.hi.y >> 16) == tag) & ((r.hi.z >> 16) == tag) & ((r.hi.w >> 16) == tag);
+  const uint32_t t = tag << 16;  // one LOP3 per word: the tag halves of all eight words equal `tag`
+  uint32_t acc = (r.lo.x ^ t) | (r.lo.y ^ t);
+  acc |= (r.lo.z ^ t);
+  acc |= (r.lo.w ^ t);
+  acc |= (r.hi.x ^ t);
+  acc |= (r.hi.y ^ t);
+  acc |= (r.hi.z ^ t);
+  acc |= (r.hi.w ^ t);
+  return (acc & 0xFFFF0000u) == 0u;
 }
 __device__ __forceinline__ uint4 ll_row_pack(const Row8& r) {  // 8 halves in k order
   return make_uint4(__byte_perm(r.lo.x, r.lo.y, 0x5410), __byte_perm(r.lo.z, r.lo.w, 0x5410),
@@ -400,12 +407,12 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       } else if (p_nvalid > 0) {
         v = tc_finish_row(row, p_ptr, ll, p_ll, p_k0, p_nvalid, vec, tag);
       }
-      uint4 mv;
-      mv.x = __shfl_down_sync(0xffffffffu, v.x, 16);
-      mv.y = __shfl_down_sync(0xffffffffu, v.y, 16);
-      mv.z = __shfl_down_sync(0xffffffffu, v.z, 16);
-      mv.w = __shfl_down_sync(0xffffffffu, v.w, 16);
-      if (p_hasm) {
+      if (p_hasm) {  // (warp-uniform)
+        uint4 mv;
+        mv.x = __shfl_down_sync(0xffffffffu, v.x, 16);
+        mv.y = __shfl_down_sync(0xffffffffu, v.y, 16);
+        mv.z = __shfl_down_sync(0xffffffffu, v.z, 16);
+        mv.w = __shfl_down_sync(0xffffffffu, v.w, 16);
         v.x = h2_as_u32(__hmul2(u32_as_h2(v.x), u32_as_h2(mv.x)));
         v.y = h2_as_u32(__hmul2(u32_as_h2(v.y), u32_as_h2(mv.y)));
         v.z = h2_as_u32(__hmul2(u32_as_h2(v.z), u32_as_h2(mv.z)));
