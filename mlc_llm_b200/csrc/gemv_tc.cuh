@@ -419,16 +419,16 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         v.w = h2_as_u32(__hmul2(u32_as_h2(v.w), u32_as_h2(mv.w)));
       }
       // v = (x0,x1)(x2,x3)(x4,x5)(x6,x7); even k carry the offset 1024 + 7, odd k 64 + 7
-      const float2 f0 = __half22float2(u32_as_h2(v.x)), f1 = __half22float2(u32_as_h2(v.y));
-      const float2 f2 = __half22float2(u32_as_h2(v.z)), f3 = __half22float2(u32_as_h2(v.w));
-      float sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
-      sm += __shfl_xor_sync(0xffffffffu, sm, 1);
-      sm += __shfl_xor_sync(0xffffffffu, sm, 2);
-      if (lane < 16) {
+      if (lane < 16) {  // (the upper half warp only supplies x_mul rows: it takes no part in the reduction below)
         // the unpack's pair order: (x0,x4)(x1,x5)(x2,x6)(x3,x7)
         sts128(slot_lane + par * (kABufs * kBSlotBytes),
                make_uint4(__byte_perm(v.x, v.z, 0x5410), __byte_perm(v.x, v.z, 0x7632), __byte_perm(v.y, v.w, 0x5410),
                           __byte_perm(v.y, v.w, 0x7632)));
+        const float2 f0 = __half22float2(u32_as_h2(v.x)), f1 = __half22float2(u32_as_h2(v.y));
+        const float2 f2 = __half22float2(u32_as_h2(v.z)), f3 = __half22float2(u32_as_h2(v.w));
+        float sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
+        sm += __shfl_xor_sync(0x0000ffffu, sm, 1);
+        sm += __shfl_xor_sync(0x0000ffffu, sm, 2);
         if (c == 0) corr_s[(p_m & 15) * 4 + g] = sm;
       }
       fence_proxy_async_smem();
