@@ -11,10 +11,17 @@ norms and sampling are not part of this path and are NOT in the timed region (st
 The 3.7 GB of distinct packed weights is far larger than the 126 MB L2, so every step streams its
 weights from HBM (config.l2: "inputs larger than L2").
 
-N > 1 (torchrun): tensor parallel - q/k/v/gate/up column-sharded, o/down row-sharded, one all-reduce
+N > 1 (torchrun): tensor parallel - q/k/v/gate/up column-sharded, o/down row-sharded, one reduction
 per sharded block (total work fixed => "scaling": "strong").
 
-Prints ONE JSON line (rank 0).
+Prints ONE JSON line (rank 0).  Besides the contract's keys the line carries, all measured OUTSIDE the timed
+region of the headline:
+  parity     a 2-layer stack of the same shapes on the same ranks through the same kernel path, every fused
+             dequant-GEMV re-evaluated by the CPU oracle from the bits it read (oracle/stack_check.py)
+  segmented  the same token with the program cut at the reference's non-GEMV call sites (what a drop-in behind
+             the reference's operator boundary gets today)
+  prefill    BASELINE config 3: dolly-v2-3b q3f16_0, 2048 prompt tokens, tcgen05 dequant-GEMM, TFLOP/s
+  extra      BASELINE configs 1 / 4 / 5 as they fit the N of this run
 """
 from __future__ import annotations
 
@@ -50,6 +57,14 @@ def parse_args():
     ap.add_argument("--no-fuse-qkv", action="store_true")
     ap.add_argument("--no-fuse-gate-up", action="store_true")
     ap.add_argument("--tune", default="", help="ctas_per_sm,stages,dbg_flags for b200q_gemv_tune (experiments)")
+    ap.add_argument("--segments", default="fused", choices=["fused", "reference"],
+                    help="headline launch granularity: fused = one program per token (default); reference = cut at the "
+                         "reference's non-GEMV call sites (the other one is reported beside it either way)")
+    ap.add_argument("--headline-only", action="store_true", help="skip parity / segmented / prefill / extra records")
+    ap.add_argument("--no-prefill", action="store_true")
+    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--ref-budget-s", type=float, default=150.0, help="wall-clock budget of the whole --impl reference run")
     return ap.parse_args()
 
 
@@ -141,76 +156,295 @@ def ncu_traffic(key: str):
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU baseline / reference arm: the reference's algorithm (f16-accumulating fused GEMV) on host cores
+# CPU baseline / reference arm: the reference's algorithm (dtype-accumulating fused GEMV) on host cores
 # ------------------------------------------------------------------------------------------------
-def cpu_sample(model: str, fmt_name: str):
-    """One layer of the workload (its 7 quantized Linears), weights packed by the oracle encoder."""
-    import numpy as np
-
-    from mlc_llm_b200.decode_stack import MODEL_SHAPES, linear_list, token_macs
-    from oracle import quant_oracle as qo
-
-    shape = MODEL_SHAPES[model]
-    fmt = qo.FORMATS[fmt_name]
-    ops_ = []
-    for j, (name, K, N, ep) in enumerate(linear_list(shape)):
-        W = qo.synth_weight(N, K, fmt, seed=qo.SEED + j)
-        packed, scale = qo.encode_sym(W, fmt)
-        x = qo.synth_act(K, fmt, seed=qo.SEED + 100 + j)
-        ep0 = qo.synth_act(N, fmt, seed=qo.SEED + 200 + j)
-        ops_.append((packed, scale, x, qo.EPILOGUES[ep], ep0))
-    macs = sum(K * N for _, K, N, _ in linear_list(shape))
-    return fmt, ops_, macs / token_macs(shape)
+def host_threads() -> int:
+    """Host cores this process may use (torchrun exports OMP_NUM_THREADS=1: never trust the OpenMP default)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
-def cpu_run_sample(fmt, ops_):
+class CpuSample:
+    """A bounded sample of one token's quantized-Linear work for the CPU port: EVERY Linear of one decoder layer
+    plus 1/L of lm_head's output columns = exactly 1/L of a token (L layers), weights packed by the oracle
+    encoder.  `col_frac` < 1 evaluates only the leading fraction of every operator's output columns (the cost of
+    the reference's loop nest is proportional to N), so that a run of many steps stays inside its time budget."""
+
+    def __init__(self, model: str, fmt_name: str):
+        import numpy as np
+
+        from mlc_llm_b200.decode_stack import MODEL_SHAPES, linear_list, token_macs
+        from oracle import quant_oracle as qo
+
+        self.shape = MODEL_SHAPES[model]
+        self.fmt = qo.FORMATS[fmt_name]
+        self.token_macs = token_macs(self.shape)
+        items = list(linear_list(self.shape))
+        n_lm = max(8, (self.shape.vocab // self.shape.layers) // 8 * 8)
+        items.append(("lm_head", self.shape.hidden, n_lm, "none" if self.fmt.dtype == "float32" else "cast_f32"))
+        self.ops = []
+        for j, (name, K, N, ep) in enumerate(items):
+            W = qo.synth_weight(N, K, self.fmt, seed=qo.SEED + j)
+            packed, scale = qo.encode_sym(W, self.fmt)
+            x = qo.synth_act(K, self.fmt, seed=qo.SEED + 100 + j)
+            ep0 = qo.synth_act(N, self.fmt, seed=qo.SEED + 200 + j)
+            self.ops.append((name, K, N, packed, scale, x, qo.EPILOGUES[ep], ep0))
+        self.col_frac = 1.0
+        self._np = np
+        self._sliced = None
+
+    def set_col_frac(self, f: float):
+        self.col_frac = min(1.0, max(1.0 / 64, f))
+        self._sliced = None
+
+    def _prepare(self):
+        np = self._np
+        out = []
+        macs = 0
+        for name, K, N, packed, scale, x, ep, ep0 in self.ops:
+            n = N if self.col_frac >= 1.0 else max(8, int(N * self.col_frac) // 8 * 8)
+            out.append((np.ascontiguousarray(packed[:, :n]), np.ascontiguousarray(scale[:, :n]), x, ep, np.ascontiguousarray(ep0[:n])))
+            macs += K * n
+        self._sliced = out
+        self.fraction_of_token = macs / self.token_macs
+
+    def run(self) -> float:
+        from oracle import c_oracle as co
+
+        if self._sliced is None:
+            self._prepare()
+        t = time.perf_counter()
+        for packed, scale, x, ep, ep0 in self._sliced:
+            co.gemv_ref(packed, scale, x, self.fmt, ep, ep0)
+        return time.perf_counter() - t
+
+    def describe(self, steps: int, t: float) -> str:
+        cf = "" if self.col_frac >= 1.0 else f", leading {self.col_frac * 100:.1f}% of every operator's output columns"
+        return (f"every quantized Linear of one decoder layer + 1/{self.shape.layers} of lm_head{cf} = "
+                f"{self.fraction_of_token * 100:.3f}% of a token's MACs per step, {steps} timed steps, {t:.3f} s each, "
+                "tokens/s = fraction / time; oracle/oracle.c (C/OpenMP port of the reference's dtype-accumulating "
+                "fused_decode*_matmul* loop nest, mlc_llm/dispatch/dispatch_tir_operator_adreno.py:5-23)")
+
+
+def cpu_baseline(model: str, fmt_name: str, steps: int = 3, warmup: int = 1, budget_s: float = 20.0):
     from oracle import c_oracle as co
 
-    t = time.perf_counter()
-    for packed, scale, x, ep, ep0 in ops_:
-        co.gemv_ref(packed, scale, x, fmt, ep, ep0)
-    return time.perf_counter() - t
-
-
-def cpu_baseline(model: str, fmt_name: str, steps: int = 3, warmup: int = 1):
-    from oracle import c_oracle as co
-
-    fmt, ops_, frac = cpu_sample(model, fmt_name)
-    for _ in range(warmup):
-        cpu_run_sample(fmt, ops_)
-    ts = [cpu_run_sample(fmt, ops_) for _ in range(steps)]
+    co.set_threads(host_threads())
+    sample = CpuSample(model, fmt_name)
+    t1 = sample.run()  # calibration (also the first warm-up)
+    if (steps + warmup) * t1 > budget_s:
+        sample.set_col_frac(budget_s / ((steps + warmup) * t1))
+    for _ in range(max(0, warmup - 1)):
+        sample.run()
+    ts = [sample.run() for _ in range(steps)]
     t = sum(ts) / len(ts)
     return {
-        "value": frac / t,
+        "value": sample.fraction_of_token / t,
         "unit": UNIT,
         "cores": co.num_threads(),
         "kind": "port",
-        "sample": f"one decoder layer (7 fused dequant-GEMVs, {frac * 100:.2f}% of a token's MACs), "
-                  f"{steps} runs, {t:.2f} s each, scaled to a whole token; oracle/oracle.c (C/OpenMP port of the "
-                  "reference's f16-accumulating fused_decode*_matmul* loop nest)",
-    }, t
+        "sample": sample.describe(steps, t),
+    }, t, sample
 
 
 def run_reference(args):
+    """The reference arm: the reference's own CPU algorithm for the path, all host threads, K steps after W
+    warm-up steps, each step a bounded sample of the workload (see CpuSample)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 5))
-    warmup = max(1, min(args.warmup, 1))
-    cb, t = cpu_baseline(args.model, args.fmt, steps=steps, warmup=warmup)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    t_begin = time.time()
+    cb, t, sample = cpu_baseline(args.model, args.fmt, steps=steps, warmup=max(1, warmup), budget_s=args.ref_budget_s)
     out = {
         "impl": "reference",
         "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
-        "ms_per_step": 1000.0 / cb["value"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f16", "data": "synthetic", "config": workload_config(args, 1),
+        "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f16" if sample.fmt.dtype == "float16" else "f32", "data": "synthetic",
+        "config": workload_config(args, args.gpus),
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "sample_fraction_of_token": sample.fraction_of_token,
+        "wall_s": round(time.time() - t_begin, 2),
         "note": "reference arm = the reference's CPU algorithm (build.py --target llvm hands LLVM the unscheduled loop "
-                "nest; LLVM-enabled TVM is not available, so the C/OpenMP port in oracle/ is timed on all host cores); "
-                "ms_per_step is per whole token, extrapolated from the bounded sample",
+                "nest; an LLVM-enabled TVM is not available here, so the C/OpenMP port in oracle/ is timed on all host "
+                "threads - it is FASTER than the reference's own TVM-C build of the same PrimFunc, which runs one "
+                "4096x4096 GEMV in ~2 s on one thread); one step = the bounded sample described in cpu_baseline.sample "
+                "(ms_per_step is the measured time of that sample; value = sample_fraction_of_token / step time); the host "
+                "path does not change with --gpus: rank 0 runs it with every host thread at every N",
     }
     print(json.dumps(out))
+
+
+# ------------------------------------------------------------------------------------------------
+# records measured outside the headline's timed region
+# ------------------------------------------------------------------------------------------------
+def time_steps(torch, fn, steps: int, warmup: int, barrier, max_over_ranks) -> float:
+    """ms per call of fn(): CUDA events on the current stream, barrier + synchronize on both sides, max over ranks."""
+    for _ in range(max(warmup, 3)):
+        fn()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    barrier()
+    return max_over_ranks(e0.elapsed_time(e1)) / steps
+
+
+def parity_record(args, torch, dist, dev, rank, world, use_program: bool):
+    """A 2-layer stack of the SAME shapes on the SAME ranks through the SAME kernel path as the headline; every
+    fused dequant-GEMV it launched is re-evaluated by the CPU oracle (oracle/stack_check.py) from the bits it
+    read.  At N > 1 the shards are gathered and checked against the full (unsharded) weights regenerated on
+    rank 0 from the same seeds - the only way a tensor-parallel line can carry correctness."""
+    from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack
+
+    shape = MODEL_SHAPES[args.model]
+    st = DecodeStack(shape, args.fmt, device=dev, tp_rank=rank, tp_size=world, layers=2, use_program=use_program,
+                     pdl=not args.no_pdl, segments=args.segments)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234)
+    st.x_in.copy_((torch.randn(shape.hidden, device=dev, generator=g) * 0.05).to(st.dt))
+    st.capture()
+    st.decode_step()
+    st.decode_step()
+    snap = st.snapshot()
+    group_scaled = bool(use_program and args.fmt == "q4f16_0" and os.environ.get("B200Q_PROG_TC", "1") != "0")
+    rec = None
+    if rank == 0:
+        from oracle import quant_oracle as qo
+        from oracle import stack_check
+
+        full = st if world == 1 else DecodeStack(shape, args.fmt, device=dev, layers=2, use_program=False)
+
+        def weights(li, nm):
+            w = full.lm_head if nm == "lm_head" else full.layers[li][nm]
+            return w.packed.cpu().numpy().view("uint32"), w.scale.cpu().numpy()
+
+        rec = stack_check.check_launches(snap, weights, qo.FORMATS[args.fmt], group_scaled)
+        rec["what"] = (f"{args.model} shapes, 2 layers + lm_head, {args.fmt}, " + ("program" if use_program else "PDL chain") +
+                       (f", tp{world} (fused in-program reduction)" if getattr(st, "fused_tp", False) else (f", tp{world} (NCCL all-reduce)" if world > 1 else "")) +
+                       ": every launched fused dequant-GEMV vs the f64 oracle on the bits it read")
+        del full
+    del st
+    torch.cuda.empty_cache()
+    return rec
+
+
+def prefill_record(args, torch, dev, clocks_fn):
+    """BASELINE config 3: dolly-v2-3b (GPT-NeoX shape), q3f16_0, 2048 prompt tokens: the 6 Linears x 32 layers of one
+    `encoding` call through the tcgen05 dequant-GEMM (ops.gemm -> b200q_gemm) with their fused epilogues; beside
+    it the reference's own CUDA route rebuilt from library parts (b200q_dequant to [N,K] + cuBLAS NT matmul +
+    the same epilogue as torch ops) and the CPU port on a row sample."""
+    from mlc_llm_b200 import ops
+    from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack
+    from mlc_llm_b200.prefill_stack import PrefillStack
+
+    model, fmt, M = "dolly-v2-3b", "q3f16_0", 2048
+    st = DecodeStack(MODEL_SHAPES[model], fmt, device=dev, use_program=False)
+    pf = PrefillStack(st, M)
+    g = torch.Generator(device=dev)
+    g.manual_seed(7)
+    pf.x_in.copy_((torch.randn(M, st.shape.hidden, device=dev, generator=g) * 0.05).half())
+    ident = lambda v: v
+    t_wall0 = time.time()
+    n0 = ops.launch_count()
+    ms = time_steps(torch, pf.run, 10, 3, torch.cuda.synchronize, ident)
+    launches = (ops.launch_count() - n0) // 13
+    clocks = clocks_fn(t_wall0, time.time())
+    flops = pf.flops()
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak = float(peaks.get("bf16_tflops_sustained", 1379.4))
+    burst = float(peaks.get("bf16_tflops", 1639.4))
+    tf = flops / (ms * 1e-3) / 1e12
+    rec = {
+        "metric": "dolly_v2_3b_q3f16_0_prefill2048_linear_tflops", "value": tf, "unit": "TFLOP/s", "ms_per_pass": ms,
+        "config": {"workload": f"{model} {fmt} prefill, M={M}: 6 quantized Linears x {st.n_layers} layers with fused epilogues "
+                               "(bias, bias+GELU, bias+2 residual adds); attention / norms excluded", "flop": flops,
+                   "l2": "192 GEMMs over 1.1 GB of distinct packed weights per pass"},
+        "roofline": {"bound": "tensor", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
+                     "frac_of_burst": tf / burst, "kernel": "b200q::gemm_tc_kernel<q3f16_0> (tcgen05.mma, dequant in the B-operand warps)",
+                     "flop_per_launch": flops / max(1, launches), "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (burst beside it)"},
+        "gpu_launches_per_pass": launches, "clocks": clocks,
+    }
+    # per-shape TFLOP/s of the three distinct GEMMs
+    shapes = []
+    w0 = st.layers[0]
+    for label, w, ep in (("2560->2560 +bias", w0["q"], "bias"), ("2560->10240 +bias+gelu", w0["h_to_4h"], "bias_gelu"),
+                         ("10240->2560 +bias", w0["4h_to_h"], "bias")):
+        X = (torch.randn(M, w.K, device=dev, generator=g) * 0.05).half()
+        bias = torch.zeros(w.N, dtype=torch.float16, device=dev)
+        Y = torch.empty(M, w.N, dtype=torch.float16, device=dev)
+        f = lambda: ops.gemm(w.packed, w.scale, X, fmt, ep, bias, out=Y)
+        t = time_steps(torch, f, 20, 3, torch.cuda.synchronize, ident)
+        # the reference's CUDA route from library parts: dequantize to [N, K] in HBM, then a dense NT matmul (cuBLAS)
+        Wt = torch.empty(w.N, w.K, dtype=torch.float16, device=dev)
+
+        def ref_route():
+            ops.dequantize(w.packed, w.scale, w.K, fmt, True, out=Wt)
+            torch.matmul(X, Wt.t(), out=Y)
+
+        t_ref = time_steps(torch, ref_route, 20, 3, torch.cuda.synchronize, ident)
+        fl = 2.0 * M * w.K * w.N
+        shapes.append({"shape": f"{M}x{label}", "us": round(t * 1e3, 2), "tflops": round(fl / t / 1e9, 1),
+                       "dequant_plus_cublas_us": round(t_ref * 1e3, 2), "dequant_plus_cublas_tflops": round(fl / t_ref / 1e9, 1)})
+    rec["per_shape"] = shapes
+    # CPU port on a row sample: the reference's f16-accumulating NT matmul loop nest on the dequantized weight
+    if not args.no_cpu_baseline:
+        import numpy as np
+
+        from oracle import c_oracle as co
+        from oracle import quant_oracle as qo
+
+        co.set_threads(host_threads())
+        f3 = qo.FORMATS[fmt]
+        rows = 8
+        tot, macs = 0.0, 0
+        for w in (w0["q"], w0["h_to_4h"], w0["4h_to_h"]):
+            pk, sc = w.packed.cpu().numpy().view(np.uint32), w.scale.cpu().numpy()
+            T = co.decode(pk, sc, w.K, f3, transpose_output=True)
+            Xs = qo.synth_act((rows, w.K), f3, seed=5)
+            co.nt_matmul_ref_f16(Xs, T)
+            t0 = time.perf_counter()
+            co.nt_matmul_ref_f16(Xs, T)
+            tot += time.perf_counter() - t0
+            macs += rows * w.K * w.N
+        rec["cpu_baseline"] = {"value": 2.0 * macs / tot / 1e12, "unit": "TFLOP/s", "cores": co.num_threads(), "kind": "port",
+                               "sample": f"{rows} of the {M} rows through the three distinct GEMM shapes of one layer (NT_matmul only, weight "
+                                         "already dequantized), oracle/oracle.c f16-accumulating loop nest"}
+    del pf, st
+    torch.cuda.empty_cache()
+    return rec
+
+
+def decode_extra(args, torch, dist, dev, rank, world, model, fmt, barrier, max_over_ranks, steps=30, cpu=False):
+    """One more decode configuration of BASELINE.json on the ranks of this run (same protocol, fewer steps)."""
+    from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack, token_bytes
+    from mlc_llm_b200.quant_spec import SPECS
+
+    shape, spec = MODEL_SHAPES[model], SPECS[fmt]
+    st = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, use_program=True)
+    st.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(st.dt))
+    st.capture()
+    ms = time_steps(torch, st.decode_step, steps, 5, barrier, max_over_ranks)
+    nbytes = token_bytes(shape, spec, world)
+    peak, _ = measured_peaks()
+    rec = {"metric": f"{model}_{fmt}_batch1_decode_linear_stream_tokens_per_s", "value": 1000.0 / ms, "unit": UNIT,
+           "n_gpus": world, "ms_per_step": ms, "steps": steps,
+           "config": {"workload": f"{model} {fmt} batch-1 decode: quantized-Linear stream of one token", "parallelism": "single" if world == 1 else f"tp{world}",
+                      "reduction": ("in-program (peer pushes over NVLink)" if getattr(st, "fused_tp", False) else ("NCCL all-reduce per sharded block" if world > 1 else "none"))},
+           "bytes_per_step_per_rank": nbytes, "gbs_per_rank": nbytes / ms / 1e6, "frac_of_hbm_peak": nbytes / ms / 1e6 / peak,
+           "launches_per_step": st.launches_per_step, "collectives_per_step": st.collectives_per_step}
+    if cpu and rank == 0 and not args.no_cpu_baseline:
+        cb, _, _ = cpu_baseline(model, fmt, steps=2, warmup=1, budget_s=15.0)
+        rec["cpu_baseline"] = cb
+    del st
+    torch.cuda.empty_cache()
+    return rec
 
 
 # ------------------------------------------------------------------------------------------------
@@ -239,10 +473,11 @@ def main():
     n_gpus = world
     spec = SPECS[args.fmt]
     shape = MODEL_SHAPES[args.model]
+    use_program = (args.fmt == "q4f16_0") if args.program < 0 else bool(args.program)
 
     stack = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, layers=args.layers,
                         pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up,
-                        use_program=(args.fmt == "q4f16_0") if args.program < 0 else bool(args.program))
+                        use_program=use_program, segments=args.segments)
     if args.tune:
         ops.gemv_tune(*[int(v) for v in args.tune.split(",")])
     stack.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(stack.dt))
@@ -278,7 +513,6 @@ def main():
         stack.decode_step()
     ev1.record()
     barrier()
-    t_wall1 = time.time()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     ms_per_step = ms / args.steps
     tok_s = 1000.0 / ms_per_step
@@ -301,34 +535,85 @@ def main():
     clocks = None
     if rank == 0:
         time.sleep(0.15)
-        sampler.stop()
         clocks = sampler.summary(t_wall0, t_wall2)
+
+    def clocks_between(t0, t1):
+        time.sleep(0.15)
+        return sampler.summary(t0, t1) if rank == 0 else None
+
+    full_run = args.layers is None and not args.headline_only
+    launches = stack.launches_per_step
+    collectives = stack.collectives_per_step
+
+    # ---- the other launch granularity beside the headline (same weights, same protocol) ----------------
+    segmented = None
+    if full_run and use_program and world == 1:
+        other = "reference" if args.segments == "fused" else "fused"
+        st2 = DecodeStack(shape, spec, device=dev, use_program=True, segments=other, weights_from=stack)
+        st2.x_in.copy_(stack.x_in)
+        st2.capture()
+        ms2 = time_steps(torch, st2.decode_step, min(args.steps, 100), 5, barrier, max_over_ranks)
+        segmented = {"segments": other, "value": 1000.0 / ms2, "unit": UNIT, "ms_per_step": ms2,
+                     "launches_per_step": st2.launches_per_step,
+                     "what": ("program cut wherever the reference's `decoding` has a non-GEMV call_tir between two fused GEMVs "
+                              "(after q|k|v, after o, after down: mlc_llm/relax_model/llama.py:340-401): 3 launches per layer + lm_head, "
+                              "every segment starts from a plain buffer - what a drop-in behind the reference's operator boundary "
+                              "gets today") if other == "reference" else "one program launch per token"}
+        if (stack.logits - st2.logits).abs().max().item() != 0.0:
+            segmented["logits_equal_to_headline"] = False
+        else:
+            segmented["logits_equal_to_headline"] = True
+        del st2
+        torch.cuda.empty_cache()
 
     # ---- per-shape GB/s (weights rotate through all layers => every byte from HBM) -----------------
     per_shape = []
-    if rank == 0 and world == 1 and not args.no_per_shape and stack.n_layers >= 8:
+    if rank == 0 and world == 1 and not args.no_per_shape and stack.n_layers >= 8 and not args.headline_only:
         per_shape = bench_shapes(stack, spec, torch)
 
     # ---- roofline of the dominant kernel (the GEMV) -----------------------------------------------
     step_bytes = token_bytes(shape, spec, world) if args.layers is None else None
     peak, peak_src = measured_peaks()
-    launches = stack.launches_per_step
     roofline = None
     if step_bytes is not None:
         achieved = step_bytes / (ms_per_step * 1e-3) / 1e9
+        tc = use_program and args.fmt == "q4f16_0"
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": ncu_traffic("gemv_program_tc_llama7b_token_dram_bytes") if (stack.use_program and args.fmt == "q4f16_0" and world == 1 and args.model == "llama-7b") else None,
-            "kernel": (("b200q::tc::gemv_program_tc_kernel" if args.fmt == "q4f16_0" else "b200q::gemv_program_kernel") +
+            "traffic": ncu_traffic("gemv_program_tc_llama7b_token_dram_bytes") if (tc and world == 1 and args.model == "llama-7b" and args.segments == "fused") else None,
+            "traffic_source": "profiles/roofline_traffic.json (dram__bytes_read + dram__bytes_write of one launch, ncu --set full of this command; not re-measured by this run)",
+            "kernel": (("b200q::tc::gemv_program_tc_kernel" if tc else "b200q::gemv_program_kernel") +
                        " (persistent: every GEMV of the step in one cooperative launch per collective-free segment" +
-                       ("; tcgen05.mma with the unpacked weights as TMEM operand" if args.fmt == "q4f16_0" else "") + ")") if stack.use_program else "b200q::gemv_stream_kernel (one launch per fused Linear group, PDL chain)",
-            "gemv_steps_per_launch": (sum(o.n_steps for k, o in stack._plan if k == "program") / max(1, launches)) if stack.use_program else 1,
+                       ("; tcgen05.mma with the unpacked weights as TMEM operand" if tc else "") + ")") if use_program else "b200q::gemv_stream_kernel (one launch per fused Linear group, PDL chain)",
+            "gemv_steps_per_launch": (sum(o.n_steps for k, o in stack._plan if k == "program") / max(1, launches)) if use_program else 1,
             "bytes_per_step_per_rank": step_bytes, "launches_per_step": launches,
-            "avg_launch_us": ms_per_step * 1e3 / launches,
+            "avg_launch_us": ms_per_step * 1e3 / max(1, launches),
             "peak_source": peak_src + (" of measured" if "measured" in peak_src else " of fallback"),
             "note": "achieved = algorithmic bytes of the step's GEMV launches (packed + scales + x + out + epilogue operand, "
                     "SURVEY.md 8d) / CUDA-event time of the step" + (("; the per-block reductions run inside the program launch (peer pushes over NVLink), the logits all-gather is NCCL" if getattr(stack, "fused_tp", False) else "; includes the all-reduces") if world > 1 else ""),
         }
+    graph_used = stack.graph is not None
+    n_launched = int(ops.launch_count() - n0)
+
+    # ---- records outside the timed region ------------------------------------------------------------------
+    del stack
+    torch.cuda.empty_cache()
+    parity = None
+    if not args.no_parity and not args.headline_only:
+        parity = parity_record(args, torch, dist, dev, rank, world, use_program)
+    prefill = None
+    if full_run and world == 1 and not args.no_prefill:
+        prefill = prefill_record(args, torch, dev, clocks_between)
+    extra = []
+    if full_run and not args.no_extra:
+        if world == 1 and (args.model, args.fmt) != ("redpajama-3b", "q4f32_0"):
+            extra.append(decode_extra(args, torch, dist, dev, rank, world, "redpajama-3b", "q4f32_0", barrier, max_over_ranks, cpu=True))
+        if (args.model, args.fmt) != ("llama-13b", "q8f16_0"):
+            extra.append(decode_extra(args, torch, dist, dev, rank, world, "llama-13b", "q8f16_0", barrier, max_over_ranks))
+        if world == 8:
+            extra.append(decode_extra(args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks, steps=20))
+    if rank == 0:
+        sampler.stop()
 
     if rank == 0:
         out = {
@@ -341,26 +626,41 @@ def main():
                     "h2d_bytes_per_step": x_host.numel() * x_host.element_size(),
                     "d2h_bytes_per_step": logits_host.numel() * logits_host.element_size(),
                     "api": "DecodeStack.decode_step_host(x_host, logits_host): pinned hidden state in, f32 logits out, stream sync"},
-            "gpu_launches": int(ops.launch_count() - n0) if stack.graph is None else launches * args.steps,
-            "collectives_per_step": stack.collectives_per_step,
+            "gpu_launches": n_launched if not graph_used else launches * args.steps,
+            "collectives_per_step": collectives,
             "clocks": clocks,
             "aggregate_gbs": (step_bytes * world / (ms_per_step * 1e-3) / 1e9) if step_bytes else None,
+            "parity": parity,
+            "segmented": segmented,
             "per_shape": per_shape,
+            "prefill": prefill,
+            "extra": extra,
         }
         if args.layers is not None:
             out["invalid"] = "debug run with --layers: not the named config"
         if world == 1 and not args.no_cpu_baseline:
-            cb, _ = cpu_baseline(args.model, args.fmt, steps=2, warmup=1)
+            cb, _, _ = cpu_baseline(args.model, args.fmt, steps=3, warmup=1, budget_s=20.0)
             out["cpu_baseline"] = cb
         print(json.dumps(out))
     if world > 1:
-        # leave without tearing NCCL down: destroy_process_group() can block forever while CUDA graphs that
-        # captured collectives are still alive; every rank has finished its work at this barrier
+        # every CUDA graph that captured a collective (and every symmetric-memory workspace) was released above;
+        # tear NCCL down cleanly, but never let a stuck teardown hang the run: every rank has finished its work at
+        # this barrier and the JSON line is out
         dist.barrier()
         torch.cuda.synchronize()
         sys.stdout.flush()
         sys.stderr.flush()
-        os._exit(0)
+        done = threading.Event()
+
+        def _teardown():
+            try:
+                dist.destroy_process_group()
+            finally:
+                done.set()
+
+        threading.Thread(target=_teardown, daemon=True).start()
+        if not done.wait(timeout=20.0):
+            os._exit(0)
 
 
 def bench_shapes(stack, spec, torch, iters: int = 20):

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 100 /* major*100 + minor */
+#define B200Q_VERSION 101 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -140,8 +140,18 @@ B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* 
  * dependencies between steps from pointer overlap (a step waits for the steps that write its x /
  * x_mul / ep0, or whose inputs / outputs it overwrites) and runs everything in one cooperative,
  * persistent kernel: weights of later steps stream into shared memory while earlier steps finish.
- * Results are identical to running the steps one by one through b200q_gemv_multi with a workspace
- * (same kernels' arithmetic, same deterministic split-K order for a given SM count).
+ * Arithmetic: q3f16_0 / q8f16_0 / q4f32_0 programs (and q4f16_0 with B200Q_PROG_TC=0 in the environment) use
+ * the per-weight arithmetic of b200q_gemv_multi (every weight rounded to dtype exactly like the reference's
+ * decode, exact products, f32 accumulation; results differ from the step-by-step launches only by the f32
+ * summation order of the K split).  The DEFAULT q4f16_0 program runs on tcgen05: it accumulates
+ * T[g,n] = sum_k (off_k + q[k,n]) x[k] per quantization group in f32 and applies s[g,n] * (T - C[g]) once per
+ * group (C[g] = sum_k (off_k + 7) x[k], rounded to f32 separately), i.e. the group scale multiplies an f32 group
+ * sum instead of every weight being rounded to f16 first.  It is therefore NOT bit-equal to b200q_gemv_multi or
+ * to the reference; it is closer to real arithmetic than both (tests/test_program_parity_gpu.py: against the f64
+ * sum of the UNROUNDED (q-7)*s it meets the 2^-14 bound that the per-weight kernels meet against the rounded
+ * weights), and the T - C cancellation costs accuracy only when |sum_k x[k]| of a group is large against
+ * |sum_k (q-7) x[k]| (bounded and tested with shifted / outlier activations).  Every program is deterministic:
+ * replays give identical bits for a given SM count.
  *
  *   1. b200q_gemv_program_build fills a HOST blob of b200q_gemv_program_bytes(n_steps) bytes
  *      (tensor-map descriptors + step table; needs a CUDA context but launches nothing);
@@ -179,6 +189,19 @@ B200Q_API int b200q_gemv_program_build_tp(const b200q_gemv_step* steps, int n_st
                                 size_t blob_bytes);
 B200Q_API int b200q_gemv_program_run_tp(const void* host_blob, const void* dev_blob, void* workspace,
                               size_t workspace_bytes, void* const* peer_workspaces, void* stream);
+
+/* Watchdog of the program kernels.  Everything that flows between CTAs (and, for a tensor-parallel program,
+ * between GPUs) inside a program launch is polled in place; a poll that stays unsatisfied - a peer rank that
+ * never launched or replayed a different number of times, a workspace shared by two programs - would otherwise
+ * spin forever.  Every such wait is bounded: after timeout_ns the kernel writes
+ *     status = 0xDEAD | site << 16 | (uint64)step << 32      (site: 1 activation, 2 K-split partial sum,
+ *                                                             3 epilogue operand, 4 peer GPU partial sum,
+ *                                                             5 workspace belongs to another program)
+ * to *status_word (8 bytes; pass PINNED HOST memory mapped into the device so that it survives the context)
+ * and traps: the launch fails with B200Q_ERR_CUDA at the next synchronization instead of hanging.
+ * timeout_ns < 0: the default (environment B200Q_WATCHDOG_MS, else 10 s); 0: unbounded.  status_word may be NULL.
+ * Process-wide; a launch (or a CUDA graph capture of it) takes the settings in force when it is issued. */
+B200Q_API void b200q_gemv_program_set_watchdog(void* status_word, long long timeout_ns);
 
 /* Tuning override for experiments (0 = default).  ctas_per_sm: 1 or 2 persistent CTAs per SM;
  * stages: cap of the shared-memory ring depth; dbg_flags bit 0: stream only, skip the math

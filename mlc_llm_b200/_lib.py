@@ -11,7 +11,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200q.so")
+# B200Q_LIB: another build of the SAME library (kernel experiments: EXTRA=-D... OUT=...); never a fallback
+LIB_PATH = os.environ.get("B200Q_LIB") or os.path.join(_HERE, "libb200q.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 c_void_p, c_int, c_uint, c_ll, c_ull = (
@@ -61,6 +62,7 @@ PROTOTYPES = {
     "b200q_gemv_program_build_tp": (c_int, [ctypes.POINTER(GemvStep), c_int, c_int, c_void_p, c_int, c_int, c_void_p,
                                             ctypes.c_size_t]),
     "b200q_gemv_program_run_tp": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.c_size_t, c_void_p, c_void_p]),
+    "b200q_gemv_program_set_watchdog": (None, [c_void_p, c_ll]),
     "b200q_gemv_tune": (None, [c_int, c_int, c_int]),
     "b200q_gemv_host": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_dequant": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),

@@ -33,6 +33,7 @@ size_t gemv_program_bytes(int n_steps);
 int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes,
                        const unsigned char* reduce_mask, int tp_rank, int tp_size);
 size_t gemv_program_workspace_bytes(const void* host_blob);
+void gemv_program_set_watchdog(unsigned long long* status, long long timeout_ns);
 int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
                      void* const* peer_workspaces, cudaStream_t stream);
 int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
@@ -51,6 +52,31 @@ static bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_
 
 static int check_fmt(int fmt, const char* who) {
   if (fmt < 0 || fmt >= B200Q_NUM_FMT) return set_error(B200Q_ERR_UNSUPPORTED, "%s: unknown fmt %d", who, fmt);
+  return B200Q_OK;
+}
+
+// tir.noalias (dispatch_tir_operator_adreno.py:7): an output never overlaps an input or another output.  With
+// stream-K a panel owner writes out[n] while other CTAs (or a PDL-overlapped launch) still read x, so an
+// in-place call would race silently: reject it.
+static bool overlaps(const void* a, size_t na, const void* b, size_t nb) {
+  if (!a || !b || na == 0 || nb == 0) return false;
+  const uintptr_t a0 = reinterpret_cast<uintptr_t>(a), b0 = reinterpret_cast<uintptr_t>(b);
+  return a0 < b0 + nb && b0 < a0 + na;
+}
+static int check_gemv_alias(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K, int fmt,
+                            const char* who) {
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  for (int i = 0; i < n_ops; ++i) {
+    const size_t ob = ((ops[i].epilogue == B200Q_EP_CAST_F32) ? 4 : el) * (size_t)ops[i].N;
+    if (overlaps(ops[i].out, ob, x, el * K) || overlaps(ops[i].out, ob, x_mul, el * K))
+      return set_error(B200Q_ERR_UNSUPPORTED, "%s: out of op %d aliases the activation (outputs never alias inputs)", who, i);
+    for (int j = 0; j < n_ops; ++j) {
+      if (overlaps(ops[i].out, ob, ops[j].ep0, el * (size_t)ops[j].N))
+        return set_error(B200Q_ERR_UNSUPPORTED, "%s: out of op %d aliases the epilogue operand of op %d", who, i, j);
+      if (j < i && overlaps(ops[i].out, ob, ops[j].out, ((ops[j].epilogue == B200Q_EP_CAST_F32) ? 4 : el) * (size_t)ops[j].N))
+        return set_error(B200Q_ERR_UNSUPPORTED, "%s: the outputs of ops %d and %d overlap", who, j, i);
+    }
+  }
   return B200Q_OK;
 }
 
@@ -112,6 +138,7 @@ int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, const v
   if (workspace && !aligned(workspace, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv: workspace must be 16-byte aligned");
   for (int i = 0; i < n_ops; ++i)
     if (int e = check_gemv_op(ops[i], fmt, "b200q_gemv")) return e;
+  if (int e = check_gemv_alias(ops, n_ops, x, x_mul, K, fmt, "b200q_gemv")) return e;
   return gemv_launch(ops, n_ops, x, x_mul, K, fmt, flags, workspace, workspace ? workspace_bytes : 0,
                      reinterpret_cast<cudaStream_t>(stream));
 }
@@ -159,6 +186,10 @@ int b200q_gemv_program_run_tp(const void* host_blob, const void* dev_blob, void*
                               void* const* peer_workspaces, void* stream) {
   if (!host_blob || !dev_blob || !workspace) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_run: NULL blob/workspace");
   return gemv_program_run(host_blob, dev_blob, workspace, workspace_bytes, peer_workspaces, reinterpret_cast<cudaStream_t>(stream));
+}
+
+void b200q_gemv_program_set_watchdog(void* status_word, long long timeout_ns) {
+  gemv_program_set_watchdog(reinterpret_cast<unsigned long long*>(status_word), timeout_ns);
 }
 
 int b200q_gemv_host(const void* packed, const void* scale, const void* x_host, const void* ep0,

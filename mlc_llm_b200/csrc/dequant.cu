@@ -170,11 +170,18 @@ __global__ void __launch_bounds__(256) take_decode_kernel(const uint32_t* __rest
   using T = typename D::T;
   constexpr int kRowsPerGroup = Fmt<FMT>::kRowsPerGroup;
   const int i = blockIdx.y;
-  int id = ids[i];
-  if (id < 0 || id >= V) return;  // out-of-range ids leave the row untouched (TVM take: undefined)
+  const int id = ids[i];
+  // an out-of-range id is undefined in the reference (TVM take reads out of bounds); here the row is zero-filled
+  // so that a caller-allocated (uninitialised) output never leaks stale memory
+  const bool bad = (id < 0 || id >= V);
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
     T o[D::kNpu];
-    D::run(packed_rm[(size_t)id * n_rows + r], scale_rm[(size_t)id * n_grp + r / kRowsPerGroup], o);
+    if (bad) {
+#pragma unroll
+      for (int t = 0; t < D::kNpu; ++t) o[t] = T(0.0f);
+    } else {
+      D::run(packed_rm[(size_t)id * n_rows + r], scale_rm[(size_t)id * n_grp + r / kRowsPerGroup], o);
+    }
     const int k0 = r * D::kNpu;
 #pragma unroll
     for (int t = 0; t < D::kNpu; ++t)

@@ -29,6 +29,8 @@
 // boundaries, so the int3 word geometry never has to line up with the 128-byte swizzle atom of X.
 #include <cuda.h>
 
+#include <atomic>
+
 #include <cstdlib>
 
 #include "common.cuh"
@@ -453,11 +455,13 @@ int launch_gemm(GemmParams& p, cudaStream_t stream) {
   if (grid > n_tiles) grid = n_tiles;
   const size_t smem = (size_t)S::kBytes + 1024;  // + alignment slack
   auto kern = gemm_tc_kernel<MODE>;
-  static thread_local bool attr_set = false;  // per instantiation
-  if (!attr_set) {
+  static std::atomic<bool> attr_set[64];  // per instantiation and device (the opt-in is a per-device setting)
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+  if (dev < 0 || !attr_set[dev].load(std::memory_order_relaxed)) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemm smem)");
-    attr_set = true;
+    if (dev >= 0) attr_set[dev].store(true, std::memory_order_relaxed);
   }
   kern<<<grid, kGemmThreads, smem, stream>>>(p);
   cudaError_t e = cudaGetLastError();

@@ -38,6 +38,8 @@
 // the eight lanes of a quarter warp hit eight distinct bank groups.
 #include <cuda.h>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "gemv_device.cuh"
 #include "ptx.cuh"
@@ -316,13 +318,24 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
 // ---- host side --------------------------------------------------------------------------------------
 thread_local int g_tune_ctas_per_sm = 0, g_tune_stages = 0, g_tune_flags = 0;
 
+// per-device caches (one process may drive several GPUs): SM count and the dynamic-smem opt-in, which
+// cudaFuncSetAttribute records per device
+constexpr int kMaxDevices = 64;
+int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return -1;
+  return dev;
+}
 int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
+  static std::atomic<int> cache[kMaxDevices];
+  const int dev = current_device();
+  if (dev >= 0) {
+    const int c = cache[dev].load(std::memory_order_relaxed);
+    if (c > 0) return c;
   }
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev < 0 ? 0 : dev) != cudaSuccess || n <= 0) n = 148;
+  if (dev >= 0) cache[dev].store(n, std::memory_order_relaxed);
   return n;
 }
 
@@ -415,11 +428,12 @@ int launch_stream(StreamParams& p, unsigned flags, void* workspace, size_t works
   p.no_compute = (g_tune_flags & 1);
 
   auto kern = gemv_stream_kernel<FMT>;
-  static thread_local size_t smem_set = 0;  // per instantiation
-  if (smem > smem_set) {
+  static std::atomic<size_t> smem_set[kMaxDevices];  // per instantiation and device
+  const int dev = current_device();
+  if (dev < 0 || smem > smem_set[dev].load(std::memory_order_relaxed)) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemv smem)");
-    smem_set = smem;
+    if (dev >= 0) smem_set[dev].store(smem, std::memory_order_relaxed);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(G, 1, 1);

@@ -32,6 +32,7 @@
 //     launch can be replayed from a CUDA graph without clearing anything.
 #include <cuda.h>
 
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <cstdio>
@@ -124,7 +125,9 @@ struct ProgHeader {  // first 64 bytes of the blob
   unsigned long long ll_elems;       // LL activation elements in total
   unsigned long long partial_slots;  // {f32, tag} partial-sum words in total
   int tp_rank, tp_size;
-  unsigned long long reserved[2];
+  unsigned prog_id;  // non-zero hash of the step table: stamped into / checked against ws_ctrl[3] by every launch
+  unsigned reserved0;
+  unsigned long long reserved1;
 };
 static_assert(sizeof(ProgHeader) == 64, "header is one cache line");
 constexpr int kMagic = 0xB2009F;
@@ -133,6 +136,42 @@ constexpr int kMagic = 0xB2009F;
 inline size_t ws_ll_off() { return 256; }
 inline size_t ws_partial_off(unsigned long long ll_elems, int ll_bytes) {
   return (256 + (size_t)ll_elems * ll_bytes + 255) / 256 * 256;
+}
+
+// ---- watchdog: every cross-CTA / cross-GPU spin of the program kernels is bounded ---------------------------
+// A poll that has not been satisfied after `ns` nanoseconds (a peer rank that never launched or replayed a
+// different number of times, a workspace shared between two programs, a corrupted tag) writes a status word
+// {0xDEAD | site << 16, step} through `status` (normally pinned host memory, so it survives the dead context)
+// and traps: the launch fails with a CUDA error instead of hanging the GPU.  All of it sits on the retry path
+// of the polls; a poll that is satisfied at once costs nothing.
+struct Wd {
+  unsigned long long* status;  // may be NULL
+  unsigned long long ns;       // 0: no bound
+};
+enum WdSite { kWdActivation = 1, kWdPartial = 2, kWdEpOperand = 3, kWdTpPartial = 4, kWdProgId = 5 };
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __noinline__ void wd_expired(const Wd& wd, unsigned site, unsigned step) {
+  if (wd.status) {
+    *reinterpret_cast<volatile unsigned long long*>(wd.status) =
+        ((unsigned long long)step << 32) | ((unsigned long long)site << 16) | 0xDEADull;
+    __threadfence_system();
+  }
+  asm volatile("trap;");
+}
+struct WdSpin {
+  unsigned spins = 0;
+  unsigned long long t0 = 0;
+};
+__device__ __forceinline__ void wd_poll(WdSpin& w, const Wd& wd, unsigned site, unsigned step) {
+  if ((++w.spins & 63u) == 0u) {
+    const unsigned long long now = globaltimer_ns();
+    if (w.spins == 64u) w.t0 = now;
+    else if (wd.ns != 0ull && now - w.t0 > wd.ns) wd_expired(wd, site, step);
+  }
 }
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
@@ -166,24 +205,48 @@ __device__ __forceinline__ int find_op(const ProgStep& st, int panel) {
 __device__ __forceinline__ int cta_begin(int T, int i, int G) { return (int)((long long)i * T / G); }
 __device__ __forceinline__ int block_owner(int T, int t, int G) { return (int)((((long long)t + 1) * G - 1) / T); }
 
+// A workspace belongs to ONE program: the first launch stamps the program's id into ws_ctrl[3], every later launch
+// checks it (a workspace reused by another program would pick up stale tags silently).
+__device__ __forceinline__ void check_prog_id(unsigned* ws_ctrl, unsigned prog_id, const Wd& wd, bool elected) {
+  if (elected) {
+    const unsigned old = atomicCAS(ws_ctrl + 3, 0u, prog_id);
+    if (old != 0u && old != prog_id) wd_expired(wd, kWdProgId, 0u);
+  }
+}
+
 // ---- LL element access ------------------------------------------------------------------------------------
 // f16 models: one 32-bit word {tag << 16 | f16 bits}; f32 model (q4f32_0): one 64-bit word {f32 bits, tag}
-__device__ __forceinline__ __half ll_poll_f16(const uint32_t* p, uint32_t tag) {
-  uint32_t w;
-  do { w = ld_vol_u32(p); } while ((w >> 16) != tag);
+__device__ __forceinline__ __half ll_poll_f16(const uint32_t* p, uint32_t tag, const Wd& wd, unsigned site, unsigned step) {
+  uint32_t w = ld_vol_u32(p);
+  if ((w >> 16) != tag) {
+    WdSpin sp;
+    do {
+      wd_poll(sp, wd, site, step);
+      w = ld_vol_u32(p);
+    } while ((w >> 16) != tag);
+  }
   return __ushort_as_half((unsigned short)(w & 0xFFFFu));
 }
-__device__ __forceinline__ float ll_poll_f32(const uint2* p, uint32_t tag) {
-  uint2 w;
-  do { w = ld_vol_v2(p); } while (w.y != tag);
+__device__ __forceinline__ float ll_poll_f32(const uint2* p, uint32_t tag, const Wd& wd, unsigned site, unsigned step) {
+  uint2 w = ld_vol_v2(p);
+  if (w.y != tag) {
+    WdSpin sp;
+    do {
+      wd_poll(sp, wd, site, step);
+      w = ld_vol_v2(p);
+    } while (w.y != tag);
+  }
   return __uint_as_float(w.x);
 }
 // kNpu consecutive f16 LL elements (one packed word row of x); elements >= n_valid read as zero
 template <int NPU>
-__device__ __forceinline__ void ll_load_row_f16(const uint32_t* ll, int n_valid, uint32_t tag, __half (&v)[12]) {
+__device__ __forceinline__ void ll_load_row_f16(const uint32_t* ll, int n_valid, uint32_t tag, __half (&v)[12], const Wd& wd,
+                                                unsigned step) {
   uint32_t w[NPU];
   bool ok;
+  WdSpin sp;
   do {
+    wd_poll(sp, wd, kWdActivation, step);
     ok = true;
 #pragma unroll
     for (int t = 0; t < NPU; t += 2) {
@@ -211,7 +274,7 @@ __device__ __forceinline__ void plain_load_row_f16(const __half* x, int k0, int 
 // helper warps: stage the activation of a step (x, optionally x * x_mul) into `xs`
 template <int FMT>
 __device__ __forceinline__ void helper_stage_x(unsigned char* xs, const ProgStep& st, const void* ws_ll, uint32_t tag,
-                                               int ht) {
+                                               int ht, const Wd& wd, unsigned step) {
   using C = PCfg<FMT>;
   using F = Fmt<FMT>;
   const int K = st.K, rows = st.RB * kRows;
@@ -224,8 +287,9 @@ __device__ __forceinline__ void helper_stage_x(unsigned char* xs, const ProgStep
     for (int k = ht; k < n; k += kHelperThreads) {
       float v = 0.f;
       if (k < K) {
-        v = (st.x_ll >= 0) ? ll_poll_f32(ll + st.x_ll + k, tag) : __ldcg(x + k);
-        if (st.has_xmul) v = __fmul_rn(v, (st.xmul_ll >= 0) ? ll_poll_f32(ll + st.xmul_ll + k, tag) : __ldcg(m + k));
+        v = (st.x_ll >= 0) ? ll_poll_f32(ll + st.x_ll + k, tag, wd, kWdActivation, step) : __ldcg(x + k);
+        if (st.has_xmul)
+          v = __fmul_rn(v, (st.xmul_ll >= 0) ? ll_poll_f32(ll + st.xmul_ll + k, tag, wd, kWdActivation, step) : __ldcg(m + k));
       }
       dst[k] = v;
     }
@@ -241,11 +305,11 @@ __device__ __forceinline__ void helper_stage_x(unsigned char* xs, const ProgStep
 #pragma unroll
       for (int t = 0; t < 12; ++t) v[t] = __ushort_as_half(0);
       if (n_valid > 0) {
-        if (st.x_ll >= 0) ll_load_row_f16<F::kNpu>(ll + st.x_ll + k0, n_valid, tag, v);
+        if (st.x_ll >= 0) ll_load_row_f16<F::kNpu>(ll + st.x_ll + k0, n_valid, tag, v, wd, step);
         else plain_load_row_f16<F::kNpu>(x, k0, K, v);
         if (st.has_xmul) {
           __align__(16) __half mv[12];
-          if (st.xmul_ll >= 0) ll_load_row_f16<F::kNpu>(ll + st.xmul_ll + k0, n_valid, tag, mv);
+          if (st.xmul_ll >= 0) ll_load_row_f16<F::kNpu>(ll + st.xmul_ll + k0, n_valid, tag, mv, wd, step);
           else plain_load_row_f16<F::kNpu>(m, k0, K, mv);
 #pragma unroll
           for (int t = 0; t < F::kNpu; ++t) v[t] = __hmul(v[t], mv[t]);
@@ -263,7 +327,7 @@ __device__ __forceinline__ void helper_stage_x(unsigned char* xs, const ProgStep
 template <int FMT>
 __global__ void __launch_bounds__(kProgThreads, 1)
 gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
-                    int stages, int xs_bytes) {
+                    int stages, int xs_bytes, unsigned prog_id, const __grid_constant__ Wd wd) {
   using C = PCfg<FMT>;
   using F = Fmt<FMT>;
   using scale_t = typename C::scale_t;
@@ -332,6 +396,7 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws
     const int ht = threadIdx.x - kFirstHelperWarp * 32;  // 0..127 = panel column
     const uint32_t epoch = ld_acquire_u32(ws_ctrl);
     const uint32_t tag = (epoch % 65535u) + 1u;  // 1..65535: never the zero of a fresh workspace
+    check_prog_id(ws_ctrl, prog_id, wd, b == 0 && ht == 0);
     int u = 0, sgi = 0;  // steps with work / segments handed over so far
     for (int j = 0; j < n_steps; ++j) {
       const ProgStep& st = prog[j];
@@ -341,7 +406,7 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws
       // ---- stage x of this step into buffer u & 1 (polls the LL words of its producers) -------------------
       const int xb = u & 1;
       mbar_wait(x_empty + 8 * xb, ((u >> 1) & 1) ^ 1);
-      helper_stage_x<FMT>(xs0 + (size_t)xb * xs_bytes, st, ws_ll, tag, ht);
+      helper_stage_x<FMT>(xs0 + (size_t)xb * xs_bytes, st, ws_ll, tag, ht, wd, (unsigned)j);
       __syncwarp();
       if (lane == 0) mbar_arrive(x_full + 8 * xb);
       ++u;
@@ -379,14 +444,14 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws
           } else {
             const int n_before = sparse ? rb_begin : b - first;  // contributors ahead of this CTA
             float tot = 0.f;
-            for (int o = 0; o < n_before; ++o) tot += ll_poll_f32(slot0 + (size_t)o * kPanelCols + ht, tag);
+            for (int o = 0; o < n_before; ++o) tot += ll_poll_f32(slot0 + (size_t)o * kPanelCols + ht, tag, wd, kWdPartial, (unsigned)j);
             sum = tot + sum;
           }
         }
         if (finalize && n < op.N) {
           if constexpr (C::kF32) {
             float e0 = 0.f;
-            if (op.ep0_ll >= 0) e0 = ll_poll_f32(reinterpret_cast<const uint2*>(ws_ll) + op.ep0_ll + n, tag);
+            if (op.ep0_ll >= 0) e0 = ll_poll_f32(reinterpret_cast<const uint2*>(ws_ll) + op.ep0_ll + n, tag, wd, kWdEpOperand, (unsigned)j);
             else if (op.ep0) e0 = __ldcg(reinterpret_cast<const float*>(op.ep0) + n);
             const float y = ep_f32(sum, op.epilogue, &e0, 0);
             reinterpret_cast<float*>(op.out)[n] = y;
@@ -395,7 +460,7 @@ gemv_program_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws
             reinterpret_cast<float*>(op.out)[n] = sum;
           } else {
             __half e0 = __ushort_as_half(0);
-            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag);
+            if (op.ep0_ll >= 0) e0 = ll_poll_f16(reinterpret_cast<const uint32_t*>(ws_ll) + op.ep0_ll + n, tag, wd, kWdEpOperand, (unsigned)j);
             else if (op.ep0) e0 = __ldcg(reinterpret_cast<const __half*>(op.ep0) + n);
             const __half y = ep_f16(sum, op.epilogue, &e0, 0);
             reinterpret_cast<__half*>(op.out)[n] = y;
@@ -593,13 +658,47 @@ int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
   int s = (kSmemPerSm - kHeader - 2 * xs_bytes - 1024) / stage_bytes_for(fmt);
   return s > kMaxStages ? kMaxStages : s;
 }
-bool want_tc(int fmt) {
-  if (fmt != B200Q_Q4F16_0) return false;
-  const char* e = std::getenv("B200Q_PROG_TC");
-  return !(e && e[0] == '0');
+// environment switches are read ONCE per process (never on the launch path)
+struct EnvConfig {
+  bool prog_tc = true;          // B200Q_PROG_TC=0: q4f16_0 programs use the exact per-weight mma.sync kernel
+  int tc_dbg = 0;               // B200Q_TC_DBG (only honoured by -DB200Q_TC_DBGFLAGS builds)
+  long long watchdog_ms = 10000;  // B200Q_WATCHDOG_MS: bound of one cross-CTA / cross-GPU wait; 0 = unbounded
+};
+const EnvConfig& env_config() {
+  static const EnvConfig cfg = [] {
+    EnvConfig c;
+    if (const char* e = std::getenv("B200Q_PROG_TC")) c.prog_tc = !(e[0] == '0');
+    if (const char* e = std::getenv("B200Q_TC_DBG")) c.tc_dbg = std::atoi(e);
+    if (const char* e = std::getenv("B200Q_WATCHDOG_MS")) c.watchdog_ms = std::atoll(e);
+    return c;
+  }();
+  return cfg;
+}
+bool want_tc(int fmt) { return fmt == B200Q_Q4F16_0 && env_config().prog_tc; }
+
+// watchdog settings of the process (b200q_gemv_program_set_watchdog); a launch captures them by value
+std::atomic<unsigned long long*> g_wd_status{nullptr};
+std::atomic<long long> g_wd_ns{-1};  // -1: the B200Q_WATCHDOG_MS default
+
+// cudaFuncSetAttribute is a per-device setting: remember the largest opt-in per (device, kernel)
+constexpr int kMaxDevices = 64;
+int set_max_smem(const void* kern, int kern_id, size_t smem) {
+  static std::atomic<size_t> done[kMaxDevices][8];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) dev = -1;
+  if (dev >= 0 && done[dev][kern_id].load(std::memory_order_relaxed) >= smem) return B200Q_OK;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemv program smem)");
+  if (dev >= 0) done[dev][kern_id].store(smem, std::memory_order_relaxed);
+  return B200Q_OK;
 }
 
 }  // namespace
+
+void gemv_program_set_watchdog(unsigned long long* status, long long timeout_ns) {
+  g_wd_status.store(status, std::memory_order_relaxed);
+  g_wd_ns.store(timeout_ns, std::memory_order_relaxed);
+}
 
 size_t gemv_program_bytes(int n_steps) { return sizeof(ProgHeader) + (size_t)n_steps * sizeof(ProgStep); }
 
@@ -704,6 +803,12 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
   h->tp_size = tp_size;
   h->ll_elems = ll_elems;
   h->partial_slots = partial_slots;
+  {
+    unsigned hsh = 2166136261u;  // FNV-1a over the step table
+    const size_t nb = (size_t)n_steps * sizeof(ProgStep);
+    for (size_t i = 0; i < nb; ++i) hsh = (hsh ^ base[i]) * 16777619u;
+    h->prog_id = hsh ? hsh : 1u;
+  }
   if (stages_for(fmt, xs_bytes, use_tc) < 2 * kGroups)
     return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_build: K too large for the activation stage (%d bytes)", xs_bytes);
   return B200Q_OK;
@@ -744,8 +849,7 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
     default: kern = (const void*)gemv_program_kernel<B200Q_Q4F32_0>; break;
   }
   if (use_tc) kern = (const void*)tc::gemv_program_tc_kernel;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemv program smem)");
+  if (int e2 = set_max_smem(kern, use_tc ? 4 : h->fmt, smem)) return e2;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(G, 1, 1);
   cfg.blockDim = dim3(use_tc ? tc::kThreadsTc : kProgThreads, 1, 1);
@@ -772,10 +876,17 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   } else {
     tp.ws[0] = ws;
   }
-  int dbg = 0;
-  if (const char* e = std::getenv("B200Q_TC_DBG")) dbg = std::atoi(e);
-  void* args[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages, (void*)&xs_bytes, (void*)&dbg, (void*)&tp};
-  e = cudaLaunchKernelExC(&cfg, kern, args);
+  int dbg = env_config().tc_dbg;
+  unsigned prog_id = h->prog_id;
+  Wd wd{};
+  wd.status = g_wd_status.load(std::memory_order_relaxed);
+  const long long wd_ns = g_wd_ns.load(std::memory_order_relaxed);
+  wd.ns = wd_ns >= 0 ? (unsigned long long)wd_ns : (unsigned long long)env_config().watchdog_ms * 1000000ull;
+  void* args_tc[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages,
+                     (void*)&xs_bytes, (void*)&dbg, (void*)&prog_id, (void*)&wd, (void*)&tp};
+  void* args_gen[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages,
+                      (void*)&xs_bytes, (void*)&prog_id, (void*)&wd};
+  cudaError_t e = cudaLaunchKernelExC(&cfg, kern, use_tc ? args_tc : args_gen);
   if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelExC(gemv program)");
   count_launch();
   return B200Q_OK;

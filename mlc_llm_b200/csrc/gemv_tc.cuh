@@ -56,6 +56,7 @@ constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStage
 // the scalar tail of a ProgStep (everything behind the tensor maps) is mirrored in shared memory by the epilogue warps
 constexpr int kTailOff = (int)offsetof(ProgStep, op);
 constexpr int kTailWords = ((int)sizeof(ProgStep) - kTailOff) / 4;  // 80
+static_assert(kTailWords <= kHelperThreads, "the step tail is mirrored one word per helper thread");
 constexpr int kTmemPtrOff = 8 * kNumBars;    // 768
 constexpr int kHeaderTc = 1024;
 
@@ -104,13 +105,16 @@ __device__ __forceinline__ uint4 ll_row_pack(const Row8& r) {  // 8 halves in k 
 }
 
 // ---- activation rows: 8 values of one packed word row from an LL array (polled) or a plain f16 vector -----------
-__device__ __forceinline__ __half tc_fetch(const __half* plain, const uint32_t* ll, long long ll_off, int k, uint32_t tag) {
-  return (ll_off >= 0) ? ll_poll_f16(ll + ll_off + k, tag) : __ldcg(plain + k);
+__device__ __forceinline__ __half tc_fetch(const __half* plain, const uint32_t* ll, long long ll_off, int k, uint32_t tag,
+                                           const Wd& wd, unsigned step) {
+  return (ll_off >= 0) ? ll_poll_f16(ll + ll_off + k, tag, wd, kWdActivation, step) : __ldcg(plain + k);
 }
 __device__ __forceinline__ uint4 tc_finish_row(Row8& r, const __half* plain, const uint32_t* ll, long long ll_off, int k0,
-                                               int n_valid, bool vec, uint32_t tag) {
+                                               int n_valid, bool vec, uint32_t tag, const Wd& wd, unsigned step) {
   if (n_valid == 8 && ll_off >= 0) {
+    WdSpin sp;
     while (!ll_row_ready(r, tag)) {
+      wd_poll(sp, wd, kWdActivation, step);
       r.lo = ld_vol_v4(ll + ll_off + k0);
       r.hi = ld_vol_v4(ll + ll_off + k0 + 4);
     }
@@ -119,7 +123,7 @@ __device__ __forceinline__ uint4 tc_finish_row(Row8& r, const __half* plain, con
   if (n_valid == 8 && vec) return __ldcg(reinterpret_cast<const uint4*>(plain + k0));
   __align__(16) __half v[8];
 #pragma unroll
-  for (int t = 0; t < 8; ++t) v[t] = (t < n_valid) ? tc_fetch(plain, ll, ll_off, k0 + t, tag) : __ushort_as_half(0);
+  for (int t = 0; t < 8; ++t) v[t] = (t < n_valid) ? tc_fetch(plain, ll, ll_off, k0 + t, tag, wd, step) : __ushort_as_half(0);
   return *reinterpret_cast<const uint4*>(v);
 }
 // One packed word -> four f16 pairs with five integer instructions and no floating-point one: a nibble in mantissa
@@ -179,7 +183,8 @@ constexpr int kTrBlk0 = 870, kTrBlks = 64;
 // blocks and are never in the same phase of their loop.
 __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
-                       int stages, int xs_bytes, int dbg, const __grid_constant__ TpInfo tp) {
+                       int stages, int xs_bytes, int dbg, unsigned prog_id, const __grid_constant__ Wd wd,
+                       const __grid_constant__ TpInfo tp) {
   extern __shared__ __align__(128) unsigned char smem[];
 #ifdef B200Q_TC_TRACE
   __shared__ unsigned long long tc_trace[kTrSteps][6];
@@ -397,15 +402,19 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       const bool vec = (reinterpret_cast<uintptr_t>(p_ptr) & 15) == 0;
       uint4 v = make_uint4(0, 0, 0, 0);
       if (p_nvalid == 8 && p_ll >= 0) {  // the common case: a whole row of LL words
-        while (!ll_row_ready(row, tag)) {
-          row.lo = ld_vol_v4(ll + p_ll + p_k0);
-          row.hi = ld_vol_v4(ll + p_ll + p_k0 + 4);
+        if (!ll_row_ready(row, tag)) {
+          WdSpin sp;
+          do {
+            wd_poll(sp, wd, kWdActivation, (unsigned)p_j);
+            row.lo = ld_vol_v4(ll + p_ll + p_k0);
+            row.hi = ld_vol_v4(ll + p_ll + p_k0 + 4);
+          } while (!ll_row_ready(row, tag));
         }
         v = ll_row_pack(row);
       } else if (p_nvalid == 8 && vec) {
         v = row.lo;  // plain row, loaded by preload()
       } else if (p_nvalid > 0) {
-        v = tc_finish_row(row, p_ptr, ll, p_ll, p_k0, p_nvalid, vec, tag);
+        v = tc_finish_row(row, p_ptr, ll, p_ll, p_k0, p_nvalid, vec, tag, wd, (unsigned)p_j);
       }
       if (p_hasm) {  // (warp-uniform)
         uint4 mv;
@@ -500,6 +509,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const uint32_t d_taddr0 = tmem_base + ((uint32_t)(hq * 32) << 16) + kDCol0;
     const uint32_t epoch = ld_acquire_u32(ws_ctrl);
     const uint32_t tag = (epoch % 65535u) + 1u;
+    check_prog_id(ws_ctrl, prog_id, wd, b == 0 && ht == 0);
     int s = 0;
     int m = 0;
     TC_DECL(th_accfull = 0, th_blk = 0, th_fin = 0);
@@ -599,7 +609,13 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
 #pragma unroll
               for (int o = 0; o < 4; ++o)
                 if (o0 + o < n_contrib) {  // added in block order
-                  while (pv[o].y != tag) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
+                  if (pv[o].y != tag) {
+                    WdSpin sp;
+                    do {
+                      wd_poll(sp, wd, kWdPartial, (unsigned)j);
+                      pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
+                    } while (pv[o].y != tag);
+                  }
                   sum += __uint_as_float(pv[o].x);
                 }
             }
@@ -623,7 +639,13 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
               for (int r = 0; r < tp.size; ++r) {
                 if (r == tp.rank) { tot += sum; continue; }
                 uint2 rv = ld_vol_v2(src + (size_t)r * kPanelCols);
-                while (rv.y != tag) rv = ld_vol_v2(src + (size_t)r * kPanelCols);
+                if (rv.y != tag) {
+                  WdSpin sp;
+                  do {
+                    wd_poll(sp, wd, kWdTpPartial, (unsigned)j);
+                    rv = ld_vol_v2(src + (size_t)r * kPanelCols);
+                  } while (rv.y != tag);
+                }
                 tot += __uint_as_float(rv.x);
               }
               sum = tot;
@@ -633,7 +655,13 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             if (op_ep == B200Q_EP_CAST_F32) {
               reinterpret_cast<float*>(op_out)[n] = sum;
             } else {
-              while ((e0w >> 16) != tag) e0w = ld_vol_u32(reinterpret_cast<const uint32_t*>(ws_ll) + op_ep0_ll + n);
+              if ((e0w >> 16) != tag) {
+                WdSpin sp;
+                do {
+                  wd_poll(sp, wd, kWdEpOperand, (unsigned)j);
+                  e0w = ld_vol_u32(reinterpret_cast<const uint32_t*>(ws_ll) + op_ep0_ll + n);
+                } while ((e0w >> 16) != tag);
+              }
               const __half e0 = __ushort_as_half((unsigned short)(e0w & 0xFFFFu));
               const __half y = ep_f16(sum, op_ep, &e0, 0);
               if (op_out_ll >= 0) {

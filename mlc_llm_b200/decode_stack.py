@@ -138,7 +138,8 @@ class DecodeStack:
 
     def __init__(self, shape, spec, device=None, tp_rank: int = 0, tp_size: int = 1, seed: int = 0xB200,
                  layers: Optional[int] = None, process_group=None, fuse_qkv: bool = True, fuse_gate_up: bool = True,
-                 pdl: bool = True, use_graph: bool = True, use_program: bool = False):
+                 pdl: bool = True, use_graph: bool = True, use_program: bool = False, segments: str = "fused",
+                 weights_from: Optional["DecodeStack"] = None):
         self.shape = MODEL_SHAPES[shape] if isinstance(shape, str) else shape
         self.spec = SPECS[spec] if isinstance(spec, str) else spec
         self.device = torch.device(device if device is not None else "cuda")
@@ -148,7 +149,21 @@ class DecodeStack:
         if tp_size > 1 and self.spec.dtype != "float16":
             raise NotImplementedError("tensor parallel decode is wired for the f16 schemes")
         self.dt = self.spec.torch_dtype
-        self._build_weights(seed)
+        # segments: where a program launch ends.  "fused": only at collectives (the GEMV chain of a whole token is one
+        # launch).  "reference": additionally wherever the reference's `decoding` function has a non-GEMV call_tir
+        # between two fused dequant-GEMVs (attention after q|k|v, the norm after o and after down;
+        # mlc_llm/relax_model/llama.py:340-401) - what a drop-in behind the reference's operator boundary can do
+        # today, because those foreign kernels read and write plain buffers, not the program's tagged words.
+        if segments not in ("fused", "reference"):
+            raise ValueError("segments: 'fused' or 'reference'")
+        self.segments = segments
+        if weights_from is not None:  # share the packed tensors of another stack (same shape / scheme / sharding)
+            o = weights_from
+            if (o.shape, o.spec, o.tp_rank, o.tp_size, o.n_layers) != (self.shape, self.spec, tp_rank, tp_size, self.n_layers):
+                raise ValueError("weights_from: stacks differ")
+            self.layers, self.biases, self.lm_head = o.layers, o.biases, o.lm_head
+        else:
+            self._build_weights(seed)
         self._build_buffers()
         self.graph = None
         self.launches_per_step = 0
@@ -161,6 +176,11 @@ class DecodeStack:
                              os.environ.get("B200Q_FUSED_TP", "1") != "0")
         self._plan = None
         self._steps = None
+        # launch trace for snapshot(): which Linear(s) every launch runs on which buffers, and how every buffer is
+        # laid out over the tensor-parallel ranks
+        self._trace: Optional[list] = None
+        self._layout: Dict[int, str] = {}
+        self._row_ep: Dict[int, tuple] = {}
         if use_program:
             self._build_plan()
 
@@ -216,8 +236,16 @@ class DecodeStack:
         self.logits = self.logits_part if tp == 1 else e(sh.vocab, torch.float32)
 
     # ------------------------------------------------------------------ the launch sequence
-    def _launch(self, items, x, x_mul=None, reduce=False):
+    def _launch(self, items, x, x_mul=None, reduce=False, row=False):
         """One kernel launch: items = [(weight, epilogue, ep0, out), ...] all reading x (* x_mul)."""
+        if self._trace is not None:
+            self._trace.append(dict(x=x, x_mul=x_mul, row=row,
+                                    ops=[dict(w=w, epilogue=ep, ep0=e0, out=o) for w, ep, e0, o in items]))
+            for _, _, _, o in items:
+                if self.tp_size > 1:
+                    self._layout[o.data_ptr()] = ("row_fused" if reduce else "rep") if row else "col"
+            if self._trace_only:
+                return
         if self._steps is not None:  # recording a program
             self._steps.append(dict(weights=[(w.packed, w.scale) for w, _, _, _ in items], x=x, x_mul=x_mul,
                                     epilogues=[ep for _, ep, _, _ in items], ep0s=[e0 for _, _, e0, _ in items],
@@ -236,6 +264,11 @@ class DecodeStack:
             tp = (self.tp_rank, self.tp_size, self.pg) if self.fused_tp else None
             self._plan.append(("program", ops.GemvProgram(self._steps, self.spec, tp=tp)))
         self._steps = []
+
+    def _segment_break(self):
+        """A call site of the reference's `decoding` where a non-GEMV kernel sits between two fused GEMVs."""
+        if self.segments == "reference" and self._steps is not None and not self._trace_only:
+            self._flush_steps()
 
     def _build_plan(self):
         """Record the step's launches once: GEMV programs separated by the collectives."""
@@ -262,6 +295,8 @@ class DecodeStack:
         return self.logits
 
     def _all_reduce(self, t):
+        if self._trace is not None and self._trace_only:
+            return
         if self._steps is not None:
             self._flush_steps()
             self._plan.append(("all_reduce", t))
@@ -274,15 +309,16 @@ class DecodeStack:
     def _row_parallel(self, w, x, residual, out, ep_single, x_mul=None):
         """o / down: out = residual + sum_ranks(x_r @ w_r).  Rank 0 carries the residual (or bias)
         into the sum so the reduction result is the final value."""
-        if self.fused_tp and self._steps is not None:
+        if self.fused_tp and (self._steps is not None or self._trace_only):
             # the reduction over the ranks happens inside the program launch (peer pushes over NVLink): the
             # epilogue is applied once, by the rank that owns the output panel, to the f32 sum of the partials
-            self._launch([(w, ep_single, residual, out)], x, x_mul, reduce=True)
+            self._launch([(w, ep_single, residual, out)], x, x_mul, reduce=True, row=True)
             return
+        self._row_ep[out.data_ptr()] = (ep_single, residual)
         if self.tp_size == 1 or self.tp_rank == 0:
-            self._launch([(w, ep_single, residual, out)], x, x_mul)
+            self._launch([(w, ep_single, residual, out)], x, x_mul, row=True)
         else:
-            self._launch([(w, "none", None, out)], x, x_mul)
+            self._launch([(w, "none", None, out)], x, x_mul, row=True)
         if self.tp_size > 1:
             self._all_reduce(out)
 
@@ -295,8 +331,10 @@ class DecodeStack:
             else:
                 for n in ("q", "k", "v"):
                     self._gemv(w[n], x, "none", None, b[n])
+            self._segment_break()  # rotary + KV append + attention + softmax (llama.py:233-290)
             attn = b["q"]  # stand-in for the attention output (same shape, same dependency)
             self._row_parallel(w["o"], attn, x, b["x1"], "add")
+            self._segment_break()  # post_attention_layernorm (llama.py:387)
             if self.fuse_gate_up:
                 # gate|up in one launch; the SwiGLU product silu(gate) * up is formed while down_proj
                 # stages its activation (bit-identical to the reference's `multiply` epilogue)
@@ -306,6 +344,7 @@ class DecodeStack:
                 self._gemv(w["gate"], b["x1"], "silu", None, b["g"])
                 self._gemv(w["up"], b["x1"], "multiply", b["g"], b["a"])
                 self._row_parallel(w["down"], b["a"], b["x1"], b["x2"], "add")
+            self._segment_break()  # the next layer's input_layernorm / the final norm (llama.py:361, 523)
             x = b["x2"]
         return x
 
@@ -318,9 +357,12 @@ class DecodeStack:
             else:
                 for n in ("q", "k", "v"):
                     self._gemv(w[n], x, "bias", bias[n], b[n])
+            self._segment_break()  # attention (gpt_neox.py:134-200)
             self._row_parallel(w["dense"], b["q"], bias["dense"], b["x1"], "bias")
+            self._segment_break()  # post_attention_layernorm
             self._gemv(w["h_to_4h"], b["x1"], "bias_gelu", bias["h_to_4h"], b["a"])
             self._row_parallel(w["4h_to_h"], b["a"], bias["4h_to_h"], b["x2"], "bias")
+            self._segment_break()  # next layer's input_layernorm / final_layer_norm
             x = b["x2"]
         return x
 
@@ -328,6 +370,8 @@ class DecodeStack:
         x = self._run_llama() if self.shape.family == "llama" else self._run_neox()
         self._gemv(self.lm_head, x, "none" if self.spec.dtype == "float32" else "cast_f32", None, self.logits_part)
         if self.tp_size > 1:
+            if self._trace is not None and self._trace_only:
+                return self.logits
             if self._steps is not None:
                 self._flush_steps()
                 self._plan.append(("all_gather", (self.logits, self.logits_part)))
@@ -344,6 +388,70 @@ class DecodeStack:
         self.launches_per_step = 0
         self.collectives_per_step = 0
         return self._run_sequence()
+
+    # ------------------------------------------------------------------ verification support
+    _trace_only = False
+
+    def _record_trace(self):
+        """Walk the launch sequence once without launching anything: which Linear runs on which buffers."""
+        steps, plan = self._steps, self._plan
+        self._steps, self._plan = None, None
+        self._trace, self._trace_only = [], True
+        try:
+            self._run_sequence()
+        finally:
+            self._trace_only = False
+            self._steps, self._plan = steps, plan
+        trace, self._trace = self._trace, None
+        return trace
+
+    def _weight_name(self, w: "QuantWeight"):
+        for li, ws in enumerate(self.layers):
+            for name, cand in ws.items():
+                if cand is w:
+                    return li, name
+        return self.n_layers, "lm_head"
+
+    def _full_host(self, t: Optional[torch.Tensor]):
+        """The complete (unsharded) tensor as a host array: column-parallel outputs are concatenated over the
+        ranks, outputs of an in-program row-parallel reduction are taken panel by panel from their owner rank."""
+        if t is None:
+            return None
+        kind = self._layout.get(t.data_ptr(), "rep") if self.tp_size > 1 else "rep"
+        if kind == "rep":
+            return t.detach().cpu().numpy().copy()
+        import torch.distributed as dist
+
+        parts = [torch.empty_like(t) for _ in range(self.tp_size)]
+        dist.all_gather(parts, t.contiguous(), group=self.pg)
+        if kind == "col":
+            return torch.cat([p.reshape(-1) for p in parts]).cpu().numpy()
+        full = parts[0].reshape(-1).clone()  # row_fused: 128-column panel p was finished by rank p % tp
+        for p in range((full.numel() + 127) // 128):
+            full[p * 128:(p + 1) * 128] = parts[p % self.tp_size].reshape(-1)[p * 128:(p + 1) * 128]
+        return full.cpu().numpy()
+
+    def snapshot(self):
+        """After a decode_step(): for every launch of the step, the host copies of the FULL activation it read
+        and of the FULL outputs it wrote (every rank must call this - tensor-parallel shards are gathered; the
+        checker, which is not part of this package, compares them operator by operator with the CPU oracle)."""
+        torch.cuda.synchronize(self.device)
+        trace = self._record_trace()
+        out = []
+        for ln in trace:
+            x = self._full_host(ln["x"])
+            x_mul = self._full_host(ln["x_mul"])
+            ops_ = []
+            for op in ln["ops"]:
+                li, name = self._weight_name(op["w"])
+                ep = op["epilogue"]
+                ep0 = op["ep0"]
+                if self.tp_size > 1 and ln["row"] and not self.fused_tp:
+                    # NCCL chain: rank 0 carries the residual / bias into the all-reduced sum
+                    ep, ep0 = self._row_ep.get(op["out"].data_ptr(), (ep, ep0))
+                ops_.append(dict(layer=li, name=name, epilogue=ep, ep0=self._full_host(ep0), out=self._full_host(op["out"])))
+            out.append(dict(x=x, x_mul=x_mul, ops=ops_))
+        return out
 
     def capture(self):
         """Warm up on a side stream and capture the step into one CUDA graph."""

@@ -77,3 +77,29 @@ def lookup_decode(spec, K: int, N: int, transpose_output: bool) -> Optional[Call
 
     decode_op.__name__ = f"decode_{spec.name}_k{K}_n{N}" + ("_T" if transpose_output else "")
     return decode_op
+
+
+def lookup_program(spec, call_sites) -> Optional["ops.GemvProgram"]:
+    """The whole fused-GEMV chain of one `decoding` call as ONE operator.
+
+    The reference dispatches PrimFunc by PrimFunc (lookup_func, mlc_llm/dispatch/llama/main.py:6452-6458); a
+    B200-native drop-in can additionally take the LIST of consecutive fused_decode*_matmul* call sites of the
+    compiled `decoding` function (mlc_llm/relax_model/llama.py:581-611) and run them as one persistent launch.
+    call_sites: [{"weights": [(packed, scale), ...], "x": tensor, "x_mul": tensor | None,
+                  "epilogues": [...], "ep0s": [...], "outs": [...]}, ...]   (ops.GemvProgram's step format:
+    every entry = the 1..4 GEMVs that read one activation).  Consecutive call sites only: a non-GEMV kernel
+    between two of them ends the list (DecodeStack(segments="reference") shows the cut points).
+    Returns None - the reference's miss - when any call site is outside what `lookup` handles."""
+    if isinstance(spec, str):
+        spec = SPECS.get(spec)
+    if spec is None or not call_sites:
+        return None
+    for cs in call_sites:
+        K = cs["x"].shape[-1]
+        eps = cs.get("epilogues") or ["none"] * len(cs["weights"])
+        if not (1 <= len(cs["weights"]) <= 4):
+            return None
+        for (packed, _), ep in zip(cs["weights"], eps):
+            if lookup(spec, K, packed.shape[1], ep, m_is_one=True) is None:
+                return None
+    return ops.GemvProgram(list(call_sites), spec)

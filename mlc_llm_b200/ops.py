@@ -262,6 +262,21 @@ def launch_count() -> int:
     return int(_lib.lib().b200q_launch_count())
 
 
+_WATCHDOG_STATUS = None
+
+
+def program_watchdog(status: Optional[torch.Tensor] = None, timeout_ms: float = -1.0) -> None:
+    """b200q_gemv_program_set_watchdog: bound every cross-CTA / cross-GPU wait of the program kernels.
+    status: a pinned-host int64[1] tensor that receives 0xDEAD | site << 16 | step << 32 when a wait expires (the
+    kernel then traps, so the launch fails instead of hanging); timeout_ms < 0: the default (10 s), 0: unbounded."""
+    global _WATCHDOG_STATUS
+    if status is not None and (status.dtype != torch.int64 or status.numel() < 1 or not status.is_pinned()):
+        raise ValueError("status must be a pinned int64 tensor")
+    _WATCHDOG_STATUS = status  # keep it alive
+    _lib.lib().b200q_gemv_program_set_watchdog(None if status is None else status.data_ptr(),
+                                               int(timeout_ms * 1e6) if timeout_ms >= 0 else -1)
+
+
 class GemvProgram:
     """The GEMV chain of one decode step as ONE persistent launch (b200q_gemv_program_*).
 

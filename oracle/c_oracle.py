@@ -85,6 +85,18 @@ def gemv_f64(packed, scale, x, fmt: qo.Fmt, K=None):
     return y, a
 
 
+def gemv_f64_unrounded(packed, scale, x, fmt: qo.Fmt, K=None):
+    """C version of quant_oracle.gemv_f64_unrounded (f16 formats): (y, sum|x w|, cancellation magnitude)."""
+    assert fmt.dtype == "float16"
+    N = packed.shape[1]
+    K = x.size if K is None else K
+    y, a, c = np.empty(N, np.float64), np.empty(N, np.float64), np.empty(N, np.float64)
+    x = np.ascontiguousarray(x.reshape(-1))
+    lib().orc_gemv_f64u_f16(_p(np.ascontiguousarray(packed)), _p(np.ascontiguousarray(scale)), _p(x), _p(y), _p(a), _p(c),
+                            K, N, fmt.nbit, fmt.group)
+    return y, a, c
+
+
 def nt_matmul_ref_f16(X, T):
     M, K = X.shape
     N = T.shape[0]

@@ -166,6 +166,37 @@ DEF_GEMV(f32, float)
 DEF_GEMV64(f16, half)
 DEF_GEMV64(f32, float)
 
+/* ---- f64 truth of the UNROUNDED weights (q - maxint) * s  (f16 formats) ----------------------
+ * y, sum |x w| and the cancellation magnitude sum_k off_k |x_k| s of the tcgen05 decode program
+ * (off_k = 1024 + maxint for even positions of a word, 64 + maxint for odd ones); see
+ * quant_oracle.gemv_f64_unrounded / tolerance_group_scaled. */
+void orc_gemv_f64u_f16(const uint32_t* packed, const half* scale, const half* x, double* y, double* abs_sum,
+                       double* cancel_sum, int K, int N, int nbit, int group) {
+  fmt_t f = make_fmt(nbit, group);
+  uint32_t mask = (1u << nbit) - 1u;
+#pragma omp parallel for schedule(static)
+  for (int n0 = 0; n0 < N; n0 += 256) {
+    int nn = N - n0 < 256 ? N - n0 : 256;
+    double a[256], b[256], c[256];
+    for (int j = 0; j < nn; ++j) a[j] = b[j] = c[j] = 0.0;
+    for (int k = 0; k < K; ++k) {
+      const uint32_t* prow = packed + (size_t)(k / f.npu) * N + n0;
+      const half* srow = scale + (size_t)(k / group) * N + n0;
+      uint32_t sh = (uint32_t)(k % f.npu) * nbit;
+      double xk = (double)x[k];
+      double off = ((k % f.npu) % 2 == 0 ? 1024.0 : 64.0) + (double)f.maxint;
+      for (int j = 0; j < nn; ++j) {
+        double w = ((double)((prow[j] >> sh) & mask) - (double)f.maxint) * (double)srow[j];
+        double t = xk * w;
+        a[j] += t;
+        b[j] += fabs(t);
+        c[j] += fabs(xk) * off * fabs((double)srow[j]);
+      }
+    }
+    for (int j = 0; j < nn; ++j) { y[n0 + j] = a[j]; abs_sum[n0 + j] = b[j]; cancel_sum[n0 + j] = c[j]; }
+  }
+}
+
 /* ---- a7: dense NT matmul, reference semantics (accumulate in half) -------------------------- */
 void orc_nt_matmul_ref_f16(const half* X, const half* T_, half* Y, int M, int K, int N) {
 #pragma omp parallel for collapse(2) schedule(static)

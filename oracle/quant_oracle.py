@@ -254,6 +254,43 @@ def gemv_f64(packed, scale, x, fmt: Fmt, K=None):
     return xv @ w, np.abs(xv) @ np.abs(w)
 
 
+def gemv_f64_unrounded(packed, scale, x, fmt: Fmt, K=None, chunk: int = 2048):
+    """f64 evaluation with the UNROUNDED weights (q - maxint) * s (s = the stored scale, exact in f64): what the
+    format means in real arithmetic, before the reference rounds every weight to dtype (quantization.py:222-224).
+    Returns (y, sum_k |x_k w_kn|, sum_k off_k |x_k| s_kn) where off_k is the integer offset the tcgen05 decode
+    program carries through its tensor-core sum for element k (1024 + maxint for even nibbles of a word, 64 + maxint
+    for odd ones; csrc/gemv_tc.cuh) - the magnitude that cancels in  T - C  and bounds that kernel's extra error."""
+    K = x.size if K is None else K
+    xv = x.reshape(-1).astype(np.float64)[:K]
+    N = packed.shape[1]
+    k = np.arange(K)
+    shift = ((k % fmt.npu) * fmt.nbit).astype(np.uint32)[:, None]
+    off = np.where((k % fmt.npu) % 2 == 0, 1024.0 + fmt.maxint, 64.0 + fmt.maxint)
+    y = np.empty(N, np.float64)
+    ab = np.empty(N, np.float64)
+    cc = np.empty(N, np.float64)
+    for n0 in range(0, N, chunk):
+        sl = slice(n0, min(N, n0 + chunk))
+        q = (packed[k // fmt.npu, sl] >> shift) & np.uint32((1 << fmt.nbit) - 1)
+        sc = scale[k // fmt.group, sl].astype(np.float64)
+        w = (q.astype(np.float64) - fmt.maxint) * sc
+        y[sl] = xv @ w
+        ab[sl] = np.abs(xv) @ np.abs(w)
+        cc[sl] = (np.abs(xv) * off) @ np.abs(sc)
+    return y, ab, cc
+
+
+def tolerance_group_scaled(y64u, abs_sum_u, cancel_sum, out_f32: bool) -> np.ndarray:
+    """Bound of the tcgen05 decode program against the UNROUNDED truth (gemv_f64_unrounded):
+        |y - y64u| <= rel*|y64u| + 2^-14 * sum|x w| + 2^-22 * sum_k off_k |x_k| s + 2^-24
+    the SURVEY 8c(ii) bound plus the cancellation term: T = sum (off + q) x and C = sum (off + maxint) x are each
+    rounded to f32 (relative 2^-24 per accumulation step of a magnitude <= sum off |x|) before they are
+    subtracted.  For zero-mean activations the third term is about as large as the second; it dominates when a
+    group's activations share a sign (large mean, outlier channels) or when |q - maxint| is small."""
+    rel = 2.0**-22 if out_f32 else 2.0**-10
+    return rel * np.abs(y64u) + 2.0**-14 * abs_sum_u + 2.0**-22 * cancel_sum + 2.0**-24
+
+
 # --------------------------------------------------------------------------------------
 # a7: prefill dense NT GEMM  (transform/transpose_matmul.py:34-101; main.py:3884-3898)
 # --------------------------------------------------------------------------------------

@@ -31,7 +31,7 @@ def test_header_symbols_exported_and_bound():
 
 def test_version_and_layout_helpers_match_oracle():
     L = _lib.lib()
-    assert L.b200q_version() == 100
+    assert L.b200q_version() == 101
     for name, spec in SPECS.items():
         f = qo.FORMATS[name]
         assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3}[name]
@@ -70,6 +70,12 @@ def test_argument_validation_codes():
     assert L.b200q_gemv(a + 4, a, a, None, a, 4096, 4096, 0, 0, 0, None, 0, st) == -2
     assert L.b200q_gemv(a, a, a, None, a, 4096, 4096, 0, 0, 0, a + 8, 1 << 20, st) == -2  # workspace
     assert L.b200q_gemv_workspace_bytes() >= 1 << 20
+    # tir.noalias: an output that overlaps the activation / an epilogue operand / another output is rejected
+    b, c = 0x200000, 0x300000
+    assert L.b200q_gemv(a, a, b, None, b, 4096, 4096, 0, 0, 0, None, 0, st) == -3
+    assert b"aliases" in L.b200q_last_error()
+    assert L.b200q_gemv(a, a, b, c, c, 4096, 4096, 0, 1, 0, None, 0, st) == -3
+    assert L.b200q_gemv(a, a, b, None, b + 8192 - 16, 4096, 4096, 0, 0, 0, None, 0, st) == -3  # partial overlap
     assert L.b200q_dequant(a, a, a, 4096, 4100, 0, 0, st) == -1
     assert L.b200q_gemm(a, a, a, None, None, None, a, 16, 4096, 4096, 2, 0, 0, st) == -3  # f32 GEMM
     assert L.b200q_take_decode(a, a, a, a, 0, 10, 64, 0, st) == 0  # empty gather is a no-op
