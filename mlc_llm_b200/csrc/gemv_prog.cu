@@ -167,6 +167,9 @@ struct WdSpin {
   unsigned long long t0 = 0;
 };
 __device__ __forceinline__ void wd_poll(WdSpin& w, const Wd& wd, unsigned site, unsigned step) {
+#ifdef B200Q_NO_WATCHDOG  // A/B builds only
+  return;
+#endif
   if ((++w.spins & 63u) == 0u) {
     const unsigned long long now = globaltimer_ns();
     if (w.spins == 64u) w.t0 = now;

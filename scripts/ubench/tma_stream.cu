@@ -27,7 +27,7 @@ struct P {
 __global__ void __launch_bounds__(64, 1) k(const __grid_constant__ P p, unsigned long long* sink) {
   extern __shared__ __align__(1024) unsigned char smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
-  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + 32);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + 64);  // up to 64 stages
   const uint32_t stage0 = (smem_u32(smem) + 1024u + 1023u) & ~1023u;
   const int G = gridDim.x, b = blockIdx.x;
   if (threadIdx.x == 0) {
@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(64, 1) k(const __grid_constant__ P p, unsigned
 }
 
 int main(int argc, char** argv) {
+  setvbuf(stdout, nullptr, _IONBF, 0);
   const size_t total = (size_t)2 << 30;  // 2 GiB matrix >> L2
   unsigned char* d; cudaMalloc(&d, total); cudaMemset(d, 1, total);
   unsigned long long* sink; cudaMalloc(&sink, 8);
@@ -99,6 +100,7 @@ int main(int argc, char** argv) {
     p.stage_bytes = c.bc * c.br * 4; p.order = c.order; p.box_rows = c.br; p.box_cols = c.bc;
     const size_t smem = 2048 + (size_t)c.stages * p.stage_bytes + 1024;
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    printf("N %5d box %3d w x %2d rows order %d stages %2d: ", c.N, c.bc, c.br, c.order, c.stages);
     k<<<sms, 64, smem>>>(p, sink);
     cudaDeviceSynchronize();
     cudaEventRecord(e0);
@@ -106,8 +108,8 @@ int main(int argc, char** argv) {
     cudaEventRecord(e1); cudaDeviceSynchronize();
     float ms; cudaEventElapsedTime(&ms, e0, e1);
     const double bytes = (double)p.T * p.stage_bytes * 3;
-    printf("N %5d box %3d w x %2d rows order %d stages %2d (%3zu KB ring): %7.1f GB/s  [%s]\n", c.N, c.bc, c.br, c.order, c.stages,
-           ((size_t)c.stages * p.stage_bytes) >> 10, bytes / ms / 1e6, cudaGetErrorString(cudaGetLastError()));
+    printf("(%3zu KB ring): %7.1f GB/s  [%s]\n", ((size_t)c.stages * p.stage_bytes) >> 10, bytes / ms / 1e6,
+           cudaGetErrorString(cudaGetLastError()));
   }
   return 0;
 }
