@@ -84,6 +84,12 @@ typedef enum {
                              (constant) packed weights before waiting on the previous kernel in the
                              stream.  Only legal when no earlier kernel in flight WRITES packed/scale. */
 
+/* b200q_gemm tile selection (default: chosen per shape): the single-CTA 128 x 256 kernel, or the CTA-pair
+ * (cta_group::2, M = 256) kernel with 256 x 128 / 256 x 256 tiles.  For tests and experiments. */
+#define B200Q_FLAG_GEMM_SINGLE 2u
+#define B200Q_FLAG_GEMM_PAIR128 4u
+#define B200Q_FLAG_GEMM_PAIR256 8u
+
 /* ---- introspection ------------------------------------------------------------------------- */
 B200Q_API int b200q_version(void);
 B200Q_API const char* b200q_last_error(void);
@@ -200,6 +206,8 @@ B200Q_API int b200q_gemv_program_run_tp(const void* host_blob, const void* dev_b
  * to *status_word (8 bytes; pass PINNED HOST memory mapped into the device so that it survives the context)
  * and traps: the launch fails with B200Q_ERR_CUDA at the next synchronization instead of hanging.
  * timeout_ns < 0: the default (environment B200Q_WATCHDOG_MS, else 10 s); 0: unbounded.  status_word may be NULL.
+ * The bound is kept as a poll count (timeout / 0.35 us, the minimum round trip of one poll): a wait expires no
+ * earlier than timeout_ns and at most a few times later.
  * Process-wide; a launch (or a CUDA graph capture of it) takes the settings in force when it is issued. */
 B200Q_API void b200q_gemv_program_set_watchdog(void* status_word, long long timeout_ns);
 

@@ -84,6 +84,7 @@ struct GemmParams {
   int n_rows;    // packed word rows
   int epilogue;
   int tiles_m, tiles_n;
+  unsigned flags;  // B200Q_FLAG_GEMM_*: tile selection override
   int debug;  // experiments (B200Q_GEMM_DEBUG): 1 = operands are not loaded / unpacked (protocol intact, data garbage), 2 = epilogue does not store
 };
 
@@ -91,14 +92,15 @@ struct GemmParams {
 // w[8]: the words of columns n0..n0+7 of word row r; s[4]: their scales as half2 pairs (n, n+1).
 // Writes kNpu k-rows; k row `kl` (stage-local) of chunk `chunk` (8 columns) lives at
 //   (kl / 8) * kKAtomBytes + (chunk / 8) * 1024 + (kl % 8) * 128 + ((chunk % 8) ^ (kl % 8)) * 16
+template <int KATOM = kKAtomBytes>
 __device__ __forceinline__ uint32_t b_chunk_addr(uint32_t stage, int kl, int chunk) {
-  return stage + (kl >> 3) * kKAtomBytes + (chunk >> 3) * 1024 + (kl & 7) * 128 + ((((chunk & 7) ^ (kl & 7))) << 4);
+  return stage + (kl >> 3) * KATOM + (chunk >> 3) * 1024 + (kl & 7) * 128 + ((((chunk & 7) ^ (kl & 7))) << 4);
 }
 __device__ __forceinline__ void sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
 
-template <int FMT>
+template <int FMT, int KATOM = kKAtomBytes>
 __device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint32_t (&s)[4], uint32_t stage, int kl0,
                                               int chunk) {
   const uint32_t kMagic = 0x64006400u;
@@ -121,7 +123,7 @@ __device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint
       }
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) sts128(b_chunk_addr(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+    for (int i = 0; i < 8; ++i) sts128(b_chunk_addr<KATOM>(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
   } else if constexpr (FMT == B200Q_Q3F16_0) {
     const __half2 kSub1 = u32_as_h2(0xE403E403u);   // -(1024 + 3)
     const __half2 kMul8 = u32_as_h2(0x30003000u);   // 1/8
@@ -145,7 +147,7 @@ __device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint
       }
     }
 #pragma unroll
-    for (int i = 0; i < 10; ++i) sts128(b_chunk_addr(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+    for (int i = 0; i < 10; ++i) sts128(b_chunk_addr<KATOM>(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
   } else {  // Q8: 4 values per word
     const __half2 kSub = u32_as_h2(0xE47FE47Fu);  // -(1024 + 127)
     uint32_t o[4][4];
@@ -165,7 +167,7 @@ __device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint
       o[3][j] = h2_as_u32(__hmul2(__hadd2(u32_as_h2(v3), kSub), s2));
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) sts128(b_chunk_addr(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+    for (int i = 0; i < 4; ++i) sts128(b_chunk_addr<KATOM>(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
   }
 }
 
@@ -313,37 +315,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     const uint32_t da_lo0 = (uint32_t)make_smem_desc_sw128(0, 16, 1024);
     const uint32_t db_lo0 = (uint32_t)(kDenseB ? make_smem_desc_sw128(0, 16, 1024) : make_smem_desc_sw128(0, 1024, kKAtomBytes));
     constexpr uint32_t kBStep = kDenseB ? 32u : 2u * kKAtomBytes;  // bytes per 16-k step inside a B stage
-    int sa = 0, sb = 0, it = 0;
-    uint32_t pa = 0, pb = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
-      mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
-      tc_fence_after();
-      const uint32_t d = tmem_base + acc * kBN;
-      int ka = 0, kb = 0;  // k-step inside the current A / B stage
-      for (int ks = 0; ks < n_ksteps; ++ks) {
-        if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
-        if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
-        if (ka == 0 || kb == 0) tc_fence_after();
-        // A: K-major SW128, 8-row groups 1024 B apart; +32 B per 16-k step inside the swizzle row
-        // B: MN-major SW128: 64-column atoms 1024 B apart (LBO), 8-k slabs kKAtomBytes apart (SBO)
-        const uint32_t a_addr = a_ring + sa * kAStageBytes + ka * 32;
-        const uint32_t b_addr = b_ring + sb * B::kStageBytes + kb * kBStep;
-        const uint64_t da = da_hi | (uint64_t)(da_lo0 | ((a_addr & 0x3FFFFu) >> 4));
-        const uint64_t db = db_hi | (uint64_t)(db_lo0 | ((b_addr & 0x3FFFFu) >> 4));
-        const bool last = (ks == n_ksteps - 1);
-        const bool rel_a = (ka == 3) || last, rel_b = (kb == B::kKSteps - 1) || last;
-        if (elect_one()) {
+    // the whole loop runs in ONE elected lane: an elect + branch + __syncwarp per 16-k step costs ~100 cycles of
+    // issue latency, and a 128 x 256 x 16 MMA lasts only ~176 - the tensor pipe would wait for its issuer
+    if (elect_one()) {
+      int sa = 0, sb = 0, it = 0;
+      uint32_t pa = 0, pb = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + acc * kBN;
+        int ka = 0, kb = 0;  // k-step inside the current A / B stage
+        for (int ks = 0; ks < n_ksteps; ++ks) {
+          if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
+          if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
+          if (ka == 0 || kb == 0) tc_fence_after();
+          // A: K-major SW128, 8-row groups 1024 B apart; +32 B per 16-k step inside the swizzle row
+          // B: MN-major SW128: 64-column atoms 1024 B apart (LBO), 8-k slabs kKAtomBytes apart (SBO)
+          const uint32_t a_addr = a_ring + sa * kAStageBytes + ka * 32;
+          const uint32_t b_addr = b_ring + sb * B::kStageBytes + kb * kBStep;
+          const uint64_t da = da_hi | (uint64_t)(da_lo0 | ((a_addr & 0x3FFFFu) >> 4));
+          const uint64_t db = db_hi | (uint64_t)(db_lo0 | ((b_addr & 0x3FFFFu) >> 4));
+          const bool last = (ks == n_ksteps - 1);
+          const bool rel_a = (ka == 3) || last, rel_b = (kb == B::kKSteps - 1) || last;
           umma_f16(d, da, db, idesc, ks > 0 ? 1u : 0u);
           if (rel_a) umma_commit(a_empty + 8 * sa);
           if (rel_b) umma_commit(b_empty + 8 * sb);
           if (last) umma_commit(t_full + 8 * acc);
+          if (rel_a) { ka = 0; if (++sa == kAStages) { sa = 0; pa ^= 1; } } else { ++ka; }
+          if (rel_b) { kb = 0; if (++sb == B::kStages) { sb = 0; pb ^= 1; } } else { ++kb; }
         }
-        __syncwarp();
-        if (rel_a) { ka = 0; if (++sa == kAStages) { sa = 0; pa ^= 1; } } else { ++ka; }
-        if (rel_b) { kb = 0; if (++sb == B::kStages) { sb = 0; pb ^= 1; } } else { ++kb; }
       }
     }
+    __syncwarp();
   } else if (warp < kFirstDqWarp) {
     // ================= epilogue ============================================================================
     const int quarter = warp & 3;  // TMEM lanes [32 * quarter, +32) are the ones this warp may read
@@ -432,6 +436,269 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   }
 }
 
+
+// =====================================================================================================================
+// CTA-pair variant (cta_group::2): one cluster = the two SMs of a TPC works on a 256 x BN output tile.
+//   * every CTA keeps ITS 128 rows of X (TMA) and dequantizes ITS HALF of the weight tile's columns: the unpack work
+//     and the shared-memory B traffic per SM are half of the single-CTA kernel's (128 x 256 tiles are shared-memory
+//     bound: 139 B/cycle of operand traffic against 128 B/cycle of bandwidth; the pair needs 91);
+//   * ONE tcgen05.mma.cta_group::2 (M = 256) issued by the leader's MMA lane reads A from both CTAs and the two B
+//     halves; each CTA's TMEM receives the accumulator of its own 128 rows; each CTA's epilogue warps drain it;
+//   * barriers: "full" barriers and the accumulator-free barrier live in the LEADER (the peer's TMA counts its bytes
+//     there through the pair form of cp.async.bulk.tensor, the peer's dequant / epilogue warps arrive remotely);
+//     "empty" barriers and accumulator-full barriers exist in both CTAs and are signalled by multicast commits.
+// Warp roles per CTA: 0 TMA producer, 1 MMA issue (leader) + TMEM alloc (both), 2-5 epilogue, 6.. dequant.
+template <int MODE, int BN>
+struct Pair {
+  using B = BCfg<MODE>;
+  static constexpr bool kDenseB = (MODE == kDense);
+  static constexpr int kHalfN = BN / 2;                 // columns of B this CTA owns
+  static constexpr int kAtoms = kHalfN / 64;            // 64-column swizzle atoms: 2 (BN 256) or 1 (BN 128)
+  static constexpr int kKAtom = kAtoms * 1024;          // one 8-k slab of a B stage
+  static constexpr int kChunks = kHalfN / 8;            // 16-byte column chunks per k row: 16 or 8
+  static constexpr int kRowsPerPass = 32 / kChunks;     // word rows one warp covers per pass: 2 or 4
+  static constexpr int kDq = 8 / kRowsPerPass;          // dequant warps per B stage: 4 or 2 (8 word rows per pass)
+  static constexpr int kDqGroups = 8 / kDq;             // warp groups: group g fills the stages c with c % groups == g, so
+                                                        // a warp has `groups` stage times per stage of its own (its global
+                                                        // loads run that far ahead) - with one group the warps sat on the
+                                                        // L2 latency of their packed words (issue slots 12 % busy)
+  static constexpr int kDqWarpsAll = kDq * kDqGroups;   // 8
+  static constexpr int kBK = B::kBK;
+  static constexpr int kRows = kDenseB ? 8 : B::kRows;  // packed word rows per stage: 8 / 8 / 16
+  static constexpr int kItems = kRows / 8;              // passes per stage: 1 (2 for int8)
+  static constexpr int kBStage = kHalfN * kBK * 2;      // 16 KB (20 KB int3) / half of it for BN 128
+  static constexpr int kBStages = (BN == 256) ? 6 : 8;  // a multiple of kDqGroups
+  static constexpr int kThreads = (kFirstDqWarp + (kDenseB ? 0 : kDqWarpsAll)) * 32;
+  static constexpr int kAOff = 0;
+  static constexpr int kBOff = kAStages * kAStageBytes;
+  static constexpr int kBarOff = kBOff + kBStages * kBStage;
+  static constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 4;
+  static constexpr int kBytes = kBarOff + kNumBars * 8 + 16;
+  static constexpr int kTmemCols = 2 * BN;              // two accumulators: 512 or 256 columns
+};
+
+template <int MODE, int BN>
+__global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(const __grid_constant__ GemmParams p) {
+  using C = Pair<MODE, BN>;
+  using B = BCfg<MODE>;
+  constexpr bool kDenseB = C::kDenseB;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t a_ring = base + C::kAOff, b_ring = base + C::kBOff;
+  const uint32_t bars = base + C::kBarOff;
+  const uint32_t a_full = bars, a_empty = a_full + 8 * kAStages;
+  const uint32_t b_full = a_empty + 8 * kAStages, b_empty = b_full + 8 * C::kBStages;
+  const uint32_t t_full = b_empty + 8 * C::kBStages, t_empty = t_full + 16;
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(base_ptr + C::kBarOff + C::kNumBars * 8);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();  // 0 = leader
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int tiles_m = (p.M + 255) >> 8;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int n_tiles = tiles_m * tiles_n;
+  const int n_ksteps = (p.K + 15) >> 4;
+  const int n_a_stages = (n_ksteps + 3) >> 2;
+  const int n_b_stages = (n_ksteps + B::kKSteps - 1) / B::kKSteps;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tm_a);
+    if constexpr (kDenseB) prefetch_tmap(&p.tm_b);
+    for (int s = 0; s < kAStages; ++s) {
+      mbar_init(a_full + 8 * s, 1);   // the leader's expect_tx arrive; both CTAs' TMA bytes
+      mbar_init(a_empty + 8 * s, 1);  // multicast commit
+    }
+    for (int s = 0; s < C::kBStages; ++s) {
+      mbar_init(b_full + 8 * s, kDenseB ? 1 : 2 * C::kDq);  // the dequant warps of BOTH CTAs
+      mbar_init(b_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(t_full + 8 * s, 1);
+      mbar_init(t_empty + 8 * s, 2 * kEpWarps);  // the epilogue warps of BOTH CTAs
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc2(smem_u32(const_cast<uint32_t*>(tmem_ptr_smem)), C::kTmemCols);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // both CTAs' barriers exist before anything is signalled across the pair
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ================= TMA producer: this CTA's 128 rows of X (and, dense mode, its BN/2 rows of T) ==============
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+      const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tile / tiles_m) * BN + (int)rank * C::kHalfN;
+      for (int i = 0; i < n_a_stages; ++i) {
+        mbar_wait(a_empty + 8 * sa, pa ^ 1);
+        if (elect_one()) {
+          if (rank == 0) mbar_expect_tx(a_full + 8 * sa, 2 * kAStageBytes);
+          tma_load_2d_pair(a_ring + sa * kAStageBytes, &p.tm_a, i * kAK, m0, a_full + 8 * sa);
+        }
+        if (++sa == kAStages) { sa = 0; pa ^= 1; }
+        if constexpr (kDenseB) {
+          mbar_wait(b_empty + 8 * sb, pb ^ 1);
+          if (elect_one()) {
+            if (rank == 0) mbar_expect_tx(b_full + 8 * sb, 2 * C::kBStage);
+            tma_load_2d_pair(b_ring + sb * C::kBStage, &p.tm_b, i * kAK, n0, b_full + 8 * sb);
+          }
+          if (++sb == C::kBStages) { sb = 0; pb ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issue: the leader's elected lane, for the pair ==========================================
+    if (rank == 0) {
+      const uint32_t idesc = make_idesc_f16(256, BN, 0, kDenseB ? 0 : 1);
+      const uint64_t da_hi = make_smem_desc_sw128(0, 16, 1024) & 0xFFFFFFFF00000000ull;
+      const uint64_t db_hi = (kDenseB ? make_smem_desc_sw128(0, 16, 1024) : make_smem_desc_sw128(0, 1024, C::kKAtom)) &
+                             0xFFFFFFFF00000000ull;
+      const uint32_t da_lo0 = (uint32_t)make_smem_desc_sw128(0, 16, 1024);
+      const uint32_t db_lo0 = (uint32_t)(kDenseB ? make_smem_desc_sw128(0, 16, 1024) : make_smem_desc_sw128(0, 1024, C::kKAtom));
+      constexpr uint32_t kBStep = kDenseB ? 32u : 2u * C::kKAtom;  // bytes per 16-k step inside a B stage
+      if (elect_one()) {  // (the whole loop in one lane, see the single-CTA kernel)
+        int sa = 0, sb = 0, it = 0;
+        uint32_t pa = 0, pb = 0;
+        for (int tile = pair; tile < n_tiles; tile += n_pairs, ++it) {
+          const int acc = it & 1;
+          mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d = tmem_base + acc * BN;
+          int ka = 0, kb = 0;
+          for (int ks = 0; ks < n_ksteps; ++ks) {
+            if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
+            if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
+            if (ka == 0 || kb == 0) tc_fence_after();
+            const uint32_t a_addr = a_ring + sa * kAStageBytes + ka * 32;
+            const uint32_t b_addr = b_ring + sb * C::kBStage + kb * kBStep;
+            const uint64_t da = da_hi | (uint64_t)(da_lo0 | ((a_addr & 0x3FFFFu) >> 4));
+            const uint64_t db = db_hi | (uint64_t)(db_lo0 | ((b_addr & 0x3FFFFu) >> 4));
+            const bool last = (ks == n_ksteps - 1);
+            const bool rel_a = (ka == 3) || last, rel_b = (kb == B::kKSteps - 1) || last;
+            umma_f16_pair(d, da, db, idesc, ks > 0 ? 1u : 0u);
+            if (rel_a) umma_commit_pair(a_empty + 8 * sa);
+            if (rel_b) umma_commit_pair(b_empty + 8 * sb);
+            if (last) umma_commit_pair(t_full + 8 * acc);
+            if (rel_a) { ka = 0; if (++sa == kAStages) { sa = 0; pa ^= 1; } } else { ++ka; }
+            if (rel_b) { kb = 0; if (++sb == C::kBStages) { sb = 0; pb ^= 1; } } else { ++kb; }
+          }
+        }
+      }
+      __syncwarp();
+    }
+  } else if (warp < kFirstDqWarp) {
+    // ================= epilogue: this CTA's 128 rows of the pair's tile ============================================
+    const int quarter = warp & 3;
+    int it = 0;
+    for (int tile = pair; tile < n_tiles; tile += n_pairs, ++it) {
+      const int acc = it & 1;
+      const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tile / tiles_m) * BN;
+      mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
+      tc_fence_after();
+      const int m = m0 + quarter * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c, v);
+        tmem_ld_wait();
+        if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) mbar_arrive(t_empty + 8 * acc);
+        else mbar_arrive_cluster(t_empty + 8 * acc, 0);
+      }
+    }
+  } else {
+    // ================= dequantizers: this CTA's BN/2 columns of the weight tile ====================================
+    if constexpr (!kDenseB) {
+      using F = Fmt<MODE>;
+      static_assert(C::kBStages % C::kDqGroups == 0, "a warp group owns a fixed subset of the ring slots");
+      const int dwa = warp - kFirstDqWarp;
+      const int grp = dwa / C::kDq, dw = dwa % C::kDq;
+      const int sub = lane / C::kChunks, chunk = lane % C::kChunks;  // word row of the pass, 8-column chunk
+      uint32_t w[C::kItems][8], s[C::kItems][4];
+      auto row_of = [&](int t) { return dw * C::kRowsPerPass + sub + 8 * t; };  // stage-local word row
+      auto load_stage = [&](int n0, int i) {
+#pragma unroll
+        for (int t = 0; t < C::kItems; ++t) {
+          const int r = i * C::kRows + row_of(t);
+          const int n = n0 + chunk * 8;
+          if (r < p.n_rows && n < p.N) {
+            const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)r * p.N + n);
+            const uint4 lo = __ldg(src), hi = __ldg(src + 1);
+            w[t][0] = lo.x; w[t][1] = lo.y; w[t][2] = lo.z; w[t][3] = lo.w;
+            w[t][4] = hi.x; w[t][5] = hi.y; w[t][6] = hi.z; w[t][7] = hi.w;
+            const uint4 sv = __ldg(reinterpret_cast<const uint4*>(p.scale + (size_t)(r / F::kRowsPerGroup) * p.N + n));
+            s[t][0] = sv.x; s[t][1] = sv.y; s[t][2] = sv.z; s[t][3] = sv.w;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[t][j] = 0u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s[t][j] = 0u;
+          }
+        }
+      };
+      // c = running number of B stages of this CTA over all its tiles; this group takes those with c % groups == grp
+      long long c0 = 0;  // stages before the current tile
+      // first own stage: find it, load it
+      auto n0_of = [&](int tile) { return (tile / tiles_m) * BN + (int)rank * C::kHalfN; };
+      int tile = pair;
+      int i = (int)((grp - c0 % C::kDqGroups + C::kDqGroups) % C::kDqGroups);  // first own stage index inside the tile
+      auto settle = [&]() {  // move (tile, i) to the next tile while i runs past the tile's stages
+        while (tile < n_tiles && i >= n_b_stages) {
+          i -= n_b_stages;
+          c0 += n_b_stages;
+          tile += n_pairs;
+        }
+      };
+      settle();
+      if (tile < n_tiles) load_stage(n0_of(tile), i);
+      while (tile < n_tiles) {
+        const long long c = c0 + i;
+        const int sb = (int)(c % C::kBStages);
+        const uint32_t pb = (uint32_t)((c / C::kBStages) & 1);
+        uint32_t wc[C::kItems][8], sc[C::kItems][4];
+#pragma unroll
+        for (int t = 0; t < C::kItems; ++t) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) wc[t][j] = w[t][j];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) sc[t][j] = s[t][j];
+        }
+        // this group's next stage (possibly in the next tile): its loads are in flight during this stage's unpack
+        i += C::kDqGroups;
+        settle();
+        if (tile < n_tiles) load_stage(n0_of(tile), i);
+        mbar_wait(b_empty + 8 * sb, pb ^ 1);
+        const uint32_t stage = b_ring + sb * C::kBStage;
+#pragma unroll
+        for (int t = 0; t < C::kItems; ++t) dequant_chunk<MODE, C::kKAtom>(wc[t], sc[t], stage, row_of(t) * F::kNpu, chunk);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          if (rank == 0) mbar_arrive(b_full + 8 * sb);
+          else mbar_arrive_cluster(b_full + 8 * sb, 0);
+        }
+      }
+    }
+  }
+
+  // ---- teardown: nobody leaves while the other CTA may still signal into this one ------------------------------
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, C::kTmemCols);
+  }
+}
+
 }  // namespace
 
 // gemv.cu
@@ -441,9 +708,72 @@ int device_sm_count();
 
 namespace {
 
+// environment switches, read once: B200Q_GEMM_PAIR = 0 (single-CTA kernel only) | 128 | 256 (force the pair tile N)
+int gemm_pair_mode() {
+  static const int mode = [] {
+    const char* e = getenv("B200Q_GEMM_PAIR");
+    return e ? atoi(e) : -1;
+  }();
+  return mode;
+}
+
+template <int MODE, int BN>
+int launch_gemm_pair(GemmParams& p, int n_pairs, cudaStream_t stream) {
+  using C = Pair<MODE, BN>;
+  const int n_tiles = ceil_div(p.M, 256) * ceil_div(p.N, BN);
+  if (n_pairs > n_tiles) n_pairs = n_tiles;
+  const size_t smem = (size_t)C::kBytes + 1024;
+  auto kern = gemm_tc2_kernel<MODE, BN>;
+  static std::atomic<bool> attr_set[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+  if (dev < 0 || !attr_set[dev].load(std::memory_order_relaxed)) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemm pair smem)");
+    if (dev >= 0) attr_set[dev].store(true, std::memory_order_relaxed);
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * n_pairs, 1, 1);
+  cfg.blockDim = dim3(C::kThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;  // the two CTAs of a cluster run on the two SMs of one TPC
+  attrs[0].val.clusterDim.x = 2;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
+  if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelEx(gemm pair)");
+  count_launch();
+  return B200Q_OK;
+}
+
+// tile choice: the CTA-pair kernel with 256 x 256 tiles whenever there is more than one 128-row block (measured on
+// B200, M = 2048: 1.05-1.16x the single-CTA kernel on every Llama / NeoX shape); 256 x 128 pair tiles have twice the
+// X traffic per FLOP and lose everywhere (kept behind B200Q_FLAG_GEMM_PAIR128 for experiments).  Returns 0: use the
+// single-CTA kernel.
+int pick_pair_bn(int M, int N, int n_pairs, unsigned flags = 0) {
+  int mode = gemm_pair_mode();
+  if (flags & B200Q_FLAG_GEMM_SINGLE) mode = 0;
+  if (flags & B200Q_FLAG_GEMM_PAIR128) mode = 128;
+  if (flags & B200Q_FLAG_GEMM_PAIR256) mode = 256;
+  (void)N;
+  if (mode == 0 || n_pairs < 1) return 0;
+  if (mode == 128 || mode == 256) return mode;
+  return M > kBM ? 256 : 0;
+}
+
 template <int MODE>
 int launch_gemm(GemmParams& p, cudaStream_t stream) {
   using S = Smem<MODE>;
+  {
+    const int n_pairs = device_sm_count() / 2;
+    const int bn = pick_pair_bn(p.M, p.N, n_pairs, p.flags);
+    if (bn == 256) return launch_gemm_pair<MODE, 256>(p, n_pairs, stream);
+    if (bn == 128) return launch_gemm_pair<MODE, 128>(p, n_pairs, stream);
+  }
   p.tiles_m = ceil_div(p.M, kBM);
   p.tiles_n = ceil_div(p.N, kBN);
   const int n_tiles = p.tiles_m * p.tiles_n;
@@ -483,7 +813,7 @@ int check_epilogue_operands(int epilogue, const void* ep0, const void* ep1, cons
 }  // namespace
 
 int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
-                const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned /*flags*/,
+                const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
                 cudaStream_t stream) {
   if (K % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm: K=%d must be a multiple of 8 (16-byte rows of X)", K);
   if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_gemm")) return e;
@@ -497,6 +827,7 @@ int gemm_launch(const void* packed, const void* scale, const void* X, const void
   p.M = M; p.K = K; p.N = N;
   p.n_rows = n_words(fmt, K);
   p.epilogue = epilogue;
+  p.flags = flags;
   if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
   switch (fmt) {
     case B200Q_Q4F16_0: return launch_gemm<B200Q_Q4F16_0>(p, stream);
@@ -518,7 +849,8 @@ int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* 
   p.M = M; p.K = K; p.N = N;
   p.epilogue = epilogue;
   if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
-  if (int e = make_tmap_2d(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, T, K, N, kAK, kBN, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
+  const int bn = pick_pair_bn(M, N, device_sm_count() / 2);  // the pair kernel loads BN / 2 rows of T per CTA
+  if (int e = make_tmap_2d(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, T, K, N, kAK, bn ? bn / 2 : kBN, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
   return launch_gemm<kDense>(p, stream);
 }
 

@@ -146,14 +146,9 @@ inline size_t ws_partial_off(unsigned long long ll_elems, int ll_bytes) {
 // of the polls; a poll that is satisfied at once costs nothing.
 struct Wd {
   unsigned long long* status;  // may be NULL
-  unsigned long long ns;       // 0: no bound
+  unsigned max_spins;          // polls one wait may take before it expires; 0: no bound
 };
 enum WdSite { kWdActivation = 1, kWdPartial = 2, kWdEpOperand = 3, kWdTpPartial = 4, kWdProgId = 5 };
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
 __device__ __noinline__ void wd_expired(const Wd& wd, unsigned site, unsigned step) {
   if (wd.status) {
     *reinterpret_cast<volatile unsigned long long*>(wd.status) =
@@ -162,19 +157,26 @@ __device__ __noinline__ void wd_expired(const Wd& wd, unsigned site, unsigned st
   }
   asm volatile("trap;");
 }
+// The bound is a poll COUNT (one 32-bit register, live only inside the retry loop, two instructions per retry):
+// a time stamp per wait costs two more registers at the kernel's register cap and showed up as -3 % tokens/s.
+// One poll is an L2 (or NVLink) round trip of >= ~0.35 us, so the host converts the time-out into polls with that
+// figure: a wait expires no earlier than the configured time and at most a few times later.
 struct WdSpin {
   unsigned spins = 0;
-  unsigned long long t0 = 0;
 };
 __device__ __forceinline__ void wd_poll(WdSpin& w, const Wd& wd, unsigned site, unsigned step) {
 #ifdef B200Q_NO_WATCHDOG  // A/B builds only
   return;
 #endif
-  if ((++w.spins & 63u) == 0u) {
-    const unsigned long long now = globaltimer_ns();
-    if (w.spins == 64u) w.t0 = now;
-    else if (wd.ns != 0ull && now - w.t0 > wd.ns) wd_expired(wd, site, step);
-  }
+#ifndef B200Q_WD_ACTIVATION
+  // The activation polls sit on the critical path of every dependent step (the activation warps of the tcgen05
+  // program); counting there costs 1.5 % tokens/s.  They are left unbounded by default: a wait that can never be
+  // satisfied (dead peer, foreign workspace) is always ALSO seen by the epilogue warps' bounded polls of the same
+  // step (peer partial sums, K-split partial sums, epilogue operand) or by the workspace id check, and their trap
+  // ends the whole launch.  -DB200Q_WD_ACTIVATION bounds these polls as well.
+  if (site == kWdActivation) return;
+#endif
+  if (++w.spins == wd.max_spins) wd_expired(wd, site, step);
 }
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
@@ -655,7 +657,7 @@ int stage_bytes_for(int fmt) {
 }
 int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
   if (use_tc) {
-    int s = (kSmemPerSm - tc::kHeaderTc - tc::kBSlots * tc::kBSlotBytes - 1024) / tc::kStageBytesTc;  // no activation staging
+    int s = (kSmemPerSm - tc::kHeaderTc - tc::kBSlots * tc::kBSlotBytes - tc::kMiscBytes) / tc::kStageBytesTc;  // no activation staging
     return s > tc::kMaxStagesTc ? tc::kMaxStagesTc : s;
   }
   int s = (kSmemPerSm - kHeader - 2 * xs_bytes - 1024) / stage_bytes_for(fmt);
@@ -834,7 +836,7 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   if (G != device_sm_count()) return set_error(B200Q_ERR_BAD_SHAPE, "gemv_program_run: program was built for %d SMs", G);
   const bool use_tc = h->tc != 0;
   int stages = stages_for(h->fmt, h->xs_bytes, use_tc);
-  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kBSlots * tc::kBSlotBytes + 1024 + (size_t)stages * tc::kStageBytesTc
+  const size_t smem = use_tc ? (size_t)tc::kHeaderTc + tc::kBSlots * tc::kBSlotBytes + tc::kMiscBytes + (size_t)stages * tc::kStageBytesTc
                              : (size_t)kHeader + 2 * (size_t)h->xs_bytes + 1024 + (size_t)stages * stage_bytes_for(h->fmt);
 
   const ProgStep* prog = reinterpret_cast<const ProgStep*>(reinterpret_cast<const unsigned char*>(dev_blob) + sizeof(ProgHeader));
@@ -883,8 +885,10 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   unsigned prog_id = h->prog_id;
   Wd wd{};
   wd.status = g_wd_status.load(std::memory_order_relaxed);
-  const long long wd_ns = g_wd_ns.load(std::memory_order_relaxed);
-  wd.ns = wd_ns >= 0 ? (unsigned long long)wd_ns : (unsigned long long)env_config().watchdog_ms * 1000000ull;
+  const long long wd_ns0 = g_wd_ns.load(std::memory_order_relaxed);
+  const unsigned long long wd_ns = wd_ns0 >= 0 ? (unsigned long long)wd_ns0 : (unsigned long long)env_config().watchdog_ms * 1000000ull;
+  const unsigned long long spins = wd_ns / 350ull;  // one poll >= ~0.35 us (an L2 round trip)
+  wd.max_spins = wd_ns == 0 ? 0u : (spins >= 0xFFFFFFFFull ? 0xFFFFFFFFu : (spins < 16 ? 16u : (unsigned)spins));
   void* args_tc[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages,
                      (void*)&xs_bytes, (void*)&dbg, (void*)&prog_id, (void*)&wd, (void*)&tp};
   void* args_gen[] = {(void*)&prog, (void*)&n_steps, (void*)&ws_ctrl, (void*)&ws_ll, (void*)&ws_partial, (void*)&stages,

@@ -31,6 +31,27 @@
 
 namespace tc {
 
+// suspend-time hints (ns) of the mbarrier waits per role; 0 = spin.  Waiting dequant warps share their issue ports
+// with working ones (a spinning waiter costs the workers issue slots: 35 % of all executed instructions in the
+// round-1 profile), the single-lane MMA / producer loops and the epilogue warps do not have that problem to the
+// same degree, and a suspended warp wakes up later than a spinning one (scripts: B200Q_TC_HINT_* experiments).
+#ifndef B200Q_TC_HINT_DQ
+#define B200Q_TC_HINT_DQ 10000000
+#endif
+#ifndef B200Q_TC_HINT_MMA
+#define B200Q_TC_HINT_MMA 10000000
+#endif
+#ifndef B200Q_TC_HINT_HELP
+#define B200Q_TC_HINT_HELP 10000000
+#endif
+#ifndef B200Q_TC_HINT_X
+#define B200Q_TC_HINT_X 10000000
+#endif
+#ifdef B200Q_TC_NOUNROLL
+#define TC_UNROLL1 _Pragma("unroll 1")
+#else
+#define TC_UNROLL1
+#endif
 constexpr int kDqWarps = 16;                 // 4 slices (group of a stage) x 4 TMEM lane quadrants
 constexpr int kHelperWarp0 = 16;             // warps 16..19: epilogue + staging + cross-CTA traffic
 constexpr int kProducerWarpTc = 20;
@@ -41,7 +62,15 @@ constexpr int kThreadsTc = 27 * 32;          // 864
 constexpr int kASets = 4;                    // stages of operand buffers in flight
 constexpr int kABufs = 4 * kASets;           // TMEM operand buffers (16 columns each)
 constexpr int kBSlots = 2 * kABufs;          // B operand slots: two per (slice, group), so the next block's is written early
-constexpr int kNAcc = 8;                     // accumulators in flight (one per block, 16 columns each)
+#ifndef B200Q_TC_NACC
+#define B200Q_TC_NACC 8
+#endif
+constexpr int kNAcc = B200Q_TC_NACC;         // accumulators in flight (one per block, 16 columns each): 8 or 16
+// ring of per-block group corrections: the activation warps run up to 8 blocks ahead of the MMAs, the MMAs up to
+// kNAcc blocks ahead of the epilogue warps
+constexpr int kCorrRing = (kNAcc == 8) ? 16 : 32;  // >= 8 + kNAcc, a power of two
+static_assert(kNAcc == 8 || kNAcc == 16, "accumulators: D columns [256, 256 + 16 * kNAcc)");
+constexpr int kMiscBytes = kCorrRing * 16 + 2 * 80 * 4 + 128;  // corrections + two step tails + ring alignment
 constexpr int kTmemCols = 512;               // A: columns [0,256), D: [256,384)
 constexpr int kDCol0 = 256;
 constexpr int kStageWordBytes = kRows * kPanelCols * 4;             // 8192: [16 rows][128 cols] u32, no swizzle
@@ -56,6 +85,7 @@ constexpr int kBarFull = 0, kBarEmpty = kMaxStagesTc, kBarAReady = 2 * kMaxStage
 // the scalar tail of a ProgStep (everything behind the tensor maps) is mirrored in shared memory by the epilogue warps
 constexpr int kTailOff = (int)offsetof(ProgStep, op);
 constexpr int kTailWords = ((int)sizeof(ProgStep) - kTailOff) / 4;  // 80
+static_assert(kTailWords == 80, "kMiscBytes assumes 80 tail words");
 static_assert(kTailWords <= kHelperThreads, "the step tail is mirrored one word per helper thread");
 constexpr int kTmemPtrOff = 8 * kNumBars;    // 768
 constexpr int kHeaderTc = 1024;
@@ -202,7 +232,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + kTmemPtrOff);
   unsigned char* bslots = smem + kHeaderTc;
   float* corr_s = reinterpret_cast<float*>(bslots + kBSlots * kBSlotBytes);  // [16 blocks][4 groups]: 1136 * sum of the group's x
-  uint32_t* stepc = reinterpret_cast<uint32_t*>(corr_s + 64);  // [2][kTailWords]: step tails, see the epilogue warps
+  uint32_t* stepc = reinterpret_cast<uint32_t*>(corr_s + kCorrRing * 4);  // [2][kTailWords]: step tails, see the epilogue warps
   const uint32_t stage_base = (smem_u32(stepc + 2 * kTailWords) + 127u) & ~127u;
   (void)xs_bytes;
 
@@ -289,8 +319,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     TC_T0();
     int s = sl;        // ring stage of block m = m % stages, phase = (m / stages) & 1 (kept incrementally: a division
     uint32_t ph = 0;   // by a run-time number costs ~20 of the ~120 instructions of a block)
+    TC_UNROLL1
     for (int m = sl; m < n_total; m += 4, ++use) {
-      mbar_wait(full0 + 8 * s, ph);
+      mbar_wait_hint<B200Q_TC_HINT_DQ>(full0 + 8 * s, ph);
       TC_ACC(tq_full);
       if (q == 0 && lane == 0) TC_BEV(m, 0);
       const uint32_t sw = stage_base + s * kStageBytesTc + (uint32_t)n * 4;
@@ -310,7 +341,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           unpack_q4_direct(w3, a + 16 * gg + 12);
         }
         TC_ACC(tq_unp);
-        mbar_wait(afree0 + 8 * (2 * sl + h), (use & 1u) ^ 1u);  // the MMAs of this half set's previous block are done
+        mbar_wait_hint<B200Q_TC_HINT_DQ>(afree0 + 8 * (2 * sl + h), (use & 1u) ^ 1u);  // the MMAs of this half set's previous block are done
         TC_ACC(tq_afree);
         if (q == 0 && lane == 0 && h == 0) TC_BEV(m, 1);
         tc_fence_after();
@@ -438,7 +469,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         float sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
         sm += __shfl_xor_sync(0x0000ffffu, sm, 1);
         sm += __shfl_xor_sync(0x0000ffffu, sm, 2);
-        if (c == 0) corr_s[(p_m & 15) * 4 + g] = sm;
+        if (c == 0) corr_s[(p_m & (kCorrRing - 1)) * 4 + g] = sm;
       }
       fence_proxy_async_smem();
       __syncwarp();
@@ -446,10 +477,11 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     settle();
     if (it_valid) {
       preload();  // p_*: the block to serve; the iterator is already one block further
+      TC_UNROLL1
       for (uint32_t use = 0;; ++use) {
         const uint32_t par = use & 1u;
         // the MMAs of the block that used this slot set two uses ago are done (first two uses: passes at once)
-        mbar_wait(bfree0 + 8 * (2 * sl + par), ((use >> 1) & 1u) ^ 1u);
+        mbar_wait_hint<B200Q_TC_HINT_X>(bfree0 + 8 * (2 * sl + par), ((use >> 1) & 1u) ^ 1u);
         if (p_first && lane == 0) TC_EV(p_j, 5);
         bpart(par);
         if (lane == 0) mbar_arrive(bready0 + 8 * (2 * sl + par));
@@ -469,19 +501,20 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       TC_DECL(tm_accfree = 0, tm_bready = 0, tm_a0 = 0, tm_a1 = 0, tm_issue = 0);
       TC_T0();
       int cnt = 0;
+      TC_UNROLL1
       for (int m = (warp == kMmaWarp) ? 0 : 1; m < n_total; m += 2, ++cnt) {
         const int set = m & (kASets - 1), ai = m & (kNAcc - 1);
         const uint32_t use = (uint32_t)m / kASets, par = use & 1u;
         const uint32_t d_taddr = tmem_base + kDCol0 + ai * 16;
         const uint32_t a_taddr = tmem_base + set * 64;
         const uint64_t bd = bdesc0 + (uint64_t)((par * kABufs + set * 4) * (kBSlotBytes / 16));
-        mbar_wait(accfree0 + 8 * ai, ((m / kNAcc) & 1) ^ 1);  // the epilogue has read this accumulator
+        mbar_wait_hint<B200Q_TC_HINT_MMA>(accfree0 + 8 * ai, ((m / kNAcc) & 1) ^ 1);  // the epilogue has read this accumulator
         TC_ACC(tm_accfree);
-        mbar_wait(bready0 + 8 * (2 * set + par), (use >> 1) & 1u);
+        mbar_wait_hint<B200Q_TC_HINT_MMA>(bready0 + 8 * (2 * set + par), (use >> 1) & 1u);
         TC_ACC(tm_bready);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          mbar_wait(aready0 + 8 * (2 * set + h), use & 1u);
+          mbar_wait_hint<B200Q_TC_HINT_MMA>(aready0 + 8 * (2 * set + h), use & 1u);
           if (h == 0) TC_ACC(tm_a0); else TC_ACC(tm_a1);
           if (h == 1) TC_BEV(m, 4);
           tc_fence_after();
@@ -558,10 +591,11 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           else if (op_ep0) e0w |= (uint32_t)__half_as_ushort(__ldcg(reinterpret_cast<const __half*>(op_ep0) + n));
         }
         float sum = 0.f;
+        TC_UNROLL1
         for (int bb = 0; bb < n_blk; ++bb, ++m) {
           const int ai = m & (kNAcc - 1);
           TC_ACC(th_fin);
-          mbar_wait(accfull0 + 8 * ai, (m / kNAcc) & 1);
+          mbar_wait_hint<B200Q_TC_HINT_HELP>(accfull0 + 8 * ai, (m / kNAcc) & 1);
           TC_ACC(th_accfull);
           if (ht == 0 && t == t0 && bb == 0) TC_EV(j, 2);
           tc_fence_after();
@@ -569,7 +603,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           tmem_ld_32x4(d_taddr0 + ai * 16, d);
           // scales and corrections of the block while the TMEM load is in flight
           const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
-          const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & 15) * 4) * 4;
+          const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & (kCorrRing - 1)) * 4) * 4;
           float sc[4];
 #pragma unroll
           for (int g = 0; g < 4; ++g) sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
@@ -703,13 +737,14 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   tc_fence_before();
   __syncthreads();
 #ifdef B200Q_TC_TRACE
-  if (threadIdx.x < kTrSteps && n_steps > kTrStep0 + kTrSteps)
+  if (threadIdx.x < kTrSteps && n_steps > kTrStep0 + kTrSteps) {
     if (b == 5 || b == 77)
       for (int i = threadIdx.x; i < kTrBlks; i += kTrSteps)
         printf("BT %d %d %u %u %u %u %u %u %u %u\n", b, kTrBlk0 + i, tc_btrace[i][0], tc_btrace[i][1], tc_btrace[i][2], tc_btrace[i][3],
                tc_btrace[i][4], tc_btrace[i][5], tc_btrace[i][6], tc_btrace[i][7]);
     printf("TR %d %d %llu %llu %llu %llu %llu %llu\n", b, kTrStep0 + (int)threadIdx.x, tc_trace[threadIdx.x][0], tc_trace[threadIdx.x][1],
            tc_trace[threadIdx.x][2], tc_trace[threadIdx.x][3], tc_trace[threadIdx.x][4], tc_trace[threadIdx.x][5]);
+  }
 #endif
   if (warp == kMmaWarp) {
     tc_fence_after();

@@ -13,7 +13,8 @@ Attention, norms and rotary embedding are NOT part of this path (SURVEY.md 2.1 r
 activation that would come out of attention is taken from the q projection so that the
 dependency chain between launches is the real one.
 
-Weights are synthetic: W ~ N(0, 0.02^2) (HF initializer_range, llama.py:24) drawn on the device
+Weights are synthetic: W ~ N(0, 0.02^2) (HF initializer_range, llama.py:24; residual-branch output
+projections 0.02 / sqrt(2 L), see _build_weights) drawn on the device
 and packed by the library's own encoder (b200q_encode, bit-exact against the reference's
 te_encode_sym - tests/test_gpu_parity.py).
 """
@@ -112,15 +113,16 @@ def shard_packed(packed, scale, spec: QuantSpec, K: int, N: int, col_slice=None,
     return packed, scale, K, N
 
 
-def synth_weight(spec: QuantSpec, K: int, N: int, seed: int, device, col_slice=None, row_slice=None) -> QuantWeight:
-    """Draw W[N, K] ~ N(0, 0.02^2) on the device, pack it with the library encoder, slice for TP.
+def synth_weight(spec: QuantSpec, K: int, N: int, seed: int, device, col_slice=None, row_slice=None,
+                 std: float = 0.02) -> QuantWeight:
+    """Draw W[N, K] ~ N(0, std^2) on the device, pack it with the library encoder, slice for TP.
 
     col_slice=(r, tp): keep output columns [r*N/tp, (r+1)*N/tp)     (column parallel)
     row_slice=(r, tp): keep input rows    [r*K/tp, (r+1)*K/tp)      (row parallel; K/tp % group == 0)"""
     g = torch.Generator(device=device)
     g.manual_seed(seed)
     W = torch.empty((N, K), dtype=torch.float32, device=device)
-    W.normal_(0.0, 0.02, generator=g)
+    W.normal_(0.0, std, generator=g)
     W = W.to(spec.torch_dtype)
     packed, scale = ops.encode(W, spec, transpose=True)
     del W
@@ -190,16 +192,21 @@ class DecodeStack:
         self.layers: List[Dict[str, QuantWeight]] = []
         self.biases: List[Dict[str, torch.Tensor]] = []
         row_parallel = ("o", "down", "dense", "4h_to_h")
+        # HF initializer_range 0.02 (llama.py:24); the projections that write into the residual stream get the usual
+        # depth scaling 0.02 / sqrt(2 L) (GPT-2 / GPT-NeoX output-layer init): this stack has no norm layers (they are
+        # not on the path), and without it the un-normalized residual stream overflows f16 after a few layers
+        std_out = 0.02 / (2.0 * sh.layers) ** 0.5
         for li in range(self.n_layers):
             ws, bs = {}, {}
             for j, (name, K, N, ep) in enumerate(linear_list(sh)):
                 s = seed * 1000003 + li * 16 + j
+                std = std_out if name in row_parallel else 0.02
                 if tp > 1 and name in row_parallel:
-                    ws[name] = synth_weight(sp, K, N, s, self.device, row_slice=(r, tp))
+                    ws[name] = synth_weight(sp, K, N, s, self.device, row_slice=(r, tp), std=std)
                 elif tp > 1:
-                    ws[name] = synth_weight(sp, K, N, s, self.device, col_slice=(r, tp))
+                    ws[name] = synth_weight(sp, K, N, s, self.device, col_slice=(r, tp), std=std)
                 else:
-                    ws[name] = synth_weight(sp, K, N, s, self.device)
+                    ws[name] = synth_weight(sp, K, N, s, self.device, std=std)
                 if ep.startswith("bias"):
                     g = torch.Generator(device=self.device)
                     g.manual_seed(s + 7)

@@ -217,7 +217,10 @@ def encode(W: torch.Tensor, spec, transpose: bool = True):
     return packed, scale
 
 
-def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, pdl: bool = False):
+GEMM_TILES = {None: 0, "single": 2, "pair128": 4, "pair256": 8}  # B200Q_FLAG_GEMM_*
+
+
+def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, pdl: bool = False, tile=None):
     """fused_decode*_NT_matmul* / decode + NT_matmul: Y[m, n] = sum_k X[m, k] * w[k, n] (+ epilogue)
     on the tcgen05 tensor cores.  X dtype[..., M, K] -> Y dtype[..., M, N]."""
     spec = _spec(spec)
@@ -236,7 +239,7 @@ def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, 
         raise ValueError(f"out must be {odt}[{M}, {N}]")
     L = _lib.lib()
     _lib.check(L.b200q_gemm(packed.data_ptr(), scale.data_ptr(), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
-                            out.data_ptr(), M, K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, _stream()))
+                            out.data_ptr(), M, K, N, spec.fmt_id, ep, (FLAG_PDL if pdl else 0) | GEMM_TILES[tile], _stream()))
     return out
 
 

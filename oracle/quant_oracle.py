@@ -27,7 +27,7 @@ import numpy as np
 
 @dataclasses.dataclass(frozen=True)
 class Fmt:
-    """One symmetric ("_0") group-quantization scheme.
+    """One group-quantization scheme ("_0" = symmetric; "_asym" = the asymmetric scheme of te_encode_asym).
 
     name          BASELINE name
     nbit          bits per value                       (quantization.py:313  nbit = int(mode[-1]))
@@ -41,6 +41,7 @@ class Fmt:
     group: int
     dtype: str
     storage_nbit: int = 32
+    sym: bool = True  # --quantization-sym; False = the reference CLI's default (asymmetric: scale + min per group)
 
     @property
     def npu(self) -> int:  # values per storage word  (quantization.py:144)
@@ -67,6 +68,13 @@ FORMATS = {
     "q4f32_0": Fmt("q4f32_0", 4, 32, "float32"),
     "q8f16_0": Fmt("q8f16_0", 8, 32, "float16"),
 }
+# asymmetric int4 (build.py:19: --quantization-sym defaults to False): f16 = separate scale / min tensors,
+# f32 = scale and min rounded to bf16 and packed into one uint32 (quantization.py:15-37,105-140,183-211)
+ASYM_FORMATS = {
+    "q4f16_asym": Fmt("q4f16_asym", 4, 32, "float16", sym=False),
+    "q4f32_asym": Fmt("q4f32_asym", 4, 32, "float32", sym=False),
+}
+ALL_FORMATS = {**FORMATS, **ASYM_FORMATS}
 
 # epilogue ids shared with include/b200q.h
 EP_NONE, EP_ADD, EP_MULTIPLY, EP_SILU, EP_CAST_F32, EP_BIAS, EP_BIAS_GELU, EP_BIAS_ADD2 = range(8)
@@ -166,6 +174,107 @@ def take_decode_sym(packed_rm: np.ndarray, scale_rm: np.ndarray, ids: np.ndarray
     q = (word >> shift) & np.uint32((1 << fmt.nbit) - 1)
     w = (q.astype(dt) - dt(fmt.maxint)).astype(dt)
     return (w * scale_rm[ids][:, j // fmt.group]).astype(dt)
+
+
+# --------------------------------------------------------------------------------------
+# asymmetric scheme  (quantization.py:105-140 te_encode_asym, :183-211 te_decode_asym, :235-255 take)
+# --------------------------------------------------------------------------------------
+
+
+def f32x2_to_bf16x2(v0: np.ndarray, v1: np.ndarray) -> np.ndarray:
+    """_tir_f32x2_to_bf16x2_to_u32 (quantization.py:15-25), round_to_even=True: v0 in the low half."""
+    res = []
+    for v in (v0, v1):
+        u = np.ascontiguousarray(v, dtype=np.float32).view(np.uint32).astype(np.uint64)
+        bias = ((u >> np.uint64(16)) & np.uint64(1)) + np.uint64(0x7FFF)
+        u = (u + bias) & np.uint64(0xFFFFFFFF)  # uint32 arithmetic wraps
+        res.append(((u >> np.uint64(16)) & np.uint64(0xFFFF)).astype(np.uint32))
+    return res[0] | (res[1] << np.uint32(16))
+
+
+def bf16x2_to_f32x2(x: np.ndarray):
+    """_tir_u32_to_bf16x2_to_f32x2 (quantization.py:28-32)."""
+    lo = ((x & np.uint32(0xFFFF)) << np.uint32(16)).view(np.float32)
+    hi = (((x >> np.uint32(16)) & np.uint32(0xFFFF)) << np.uint32(16)).view(np.float32)
+    return lo, hi
+
+
+def encode_asym(W: np.ndarray, fmt: Fmt, transpose: bool = True):
+    """te_encode_asym: W[N, K] -> packed uint32[K/8, N] and
+        float16: scale f16[G, N], min f16[G, N]            (three tensors, quantization.py:134-138)
+        float32: scale_min uint32[G, N] = bf16(scale) | bf16(min) << 16   (:126-131; the weights are quantized
+                 with the UNROUNDED f32 scale / min, the decoder only ever sees the bf16 values)
+    K must be a multiple of the group size (:107 assert).  transpose=False: [N, K/8] / [N, G] (embedding)."""
+    dt = fmt.np_dtype
+    assert not fmt.sym and W.dtype == dt and W.ndim == 2
+    N, K = W.shape
+    g, npu = fmt.group, fmt.npu
+    assert K % g == 0
+    G = K // g
+    qmax = (1 << fmt.nbit) - 1
+    Wg = W.reshape(N, G, g)
+    mn, mx = Wg.min(axis=2), Wg.max(axis=2)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        scale = ((mx - mn).astype(dt) / dt(qmax)).astype(dt)
+        t = ((Wg - mn[:, :, None]).astype(dt) / scale[:, :, None]).astype(dt)
+    q = _round_half_away(t)
+    q = np.nan_to_num(q, nan=0.0, posinf=float(qmax), neginf=0.0)  # a constant group divides by zero: UB in the reference
+    q = np.minimum(np.maximum(q, 0.0), float(qmax)).astype(np.uint32).reshape(N, K // npu, npu)
+    packed = np.zeros((N, K // npu), dtype=np.uint32)
+    for tpos in range(npu):
+        packed |= q[:, :, tpos] << np.uint32(tpos * fmt.nbit)
+    if fmt.dtype == "float32":
+        sm = f32x2_to_bf16x2(scale, mn)
+        return (np.ascontiguousarray(packed.T), np.ascontiguousarray(sm.T)) if transpose else (packed, sm)
+    if transpose:
+        return np.ascontiguousarray(packed.T), np.ascontiguousarray(scale.T), np.ascontiguousarray(mn.T)
+    return packed, scale, mn
+
+
+def _asym_scale_min(fmt: Fmt, scale, mn):
+    if fmt.dtype == "float32":
+        return bf16x2_to_f32x2(scale)
+    return scale, mn
+
+
+def decode_asym(packed: np.ndarray, scale: np.ndarray, mn, K: int, fmt: Fmt, transpose_output: bool = False):
+    """te_decode_asym: w[k, n] = dtype(q) * scale + min, the product and the sum each rounded to dtype (the TVM C
+    and LLVM CPU builds of the reference do not contract them into an fma; quantization.py:196)."""
+    dt = fmt.np_dtype
+    k = np.arange(K)
+    q = (packed[k // fmt.npu, :] >> ((k % fmt.npu) * fmt.nbit).astype(np.uint32)[:, None]) & np.uint32((1 << fmt.nbit) - 1)
+    s, m = _asym_scale_min(fmt, scale, mn)
+    w = (q.astype(dt) * s[k // fmt.group, :]).astype(dt)
+    w = (w + m[k // fmt.group, :]).astype(dt)
+    return np.ascontiguousarray(w.T) if transpose_output else w
+
+
+def take_decode_asym(packed_rm, scale_rm, mn_rm, ids, K: int, fmt: Fmt):
+    """te_take_decode_asym (quantization.py:235-255): row-major (V, K/8) table."""
+    dt = fmt.np_dtype
+    j = np.arange(K)
+    q = (packed_rm[ids][:, j // fmt.npu] >> ((j % fmt.npu) * fmt.nbit).astype(np.uint32)[None, :]) & np.uint32((1 << fmt.nbit) - 1)
+    s, m = _asym_scale_min(fmt, scale_rm, mn_rm)
+    w = (q.astype(dt) * s[ids][:, j // fmt.group]).astype(dt)
+    return (w + m[ids][:, j // fmt.group]).astype(dt)
+
+
+def gemv_ref_asym(packed, scale, mn, x, fmt: Fmt, epilogue=EP_NONE, ep0=None):
+    """fused_decode4_matmul5_before / _fp16_before (dispatch/llama/main.py:4397-4415, 4979-4997): dtype accumulate."""
+    dt = fmt.np_dtype
+    K = x.size
+    x = x.reshape(-1).astype(dt)
+    w = decode_asym(packed, scale, mn, K, fmt)
+    acc = np.zeros(packed.shape[1], dtype=dt)
+    for k in range(K):
+        acc = (acc + (x[k] * w[k]).astype(dt)).astype(dt)
+    return apply_epilogue(acc, epilogue, ep0)
+
+
+def gemv_f64_asym(packed, scale, mn, x, fmt: Fmt):
+    w = decode_asym(packed, scale, mn, x.size, fmt).astype(np.float64)
+    xv = x.reshape(-1).astype(np.float64)
+    return xv @ w, np.abs(xv) @ np.abs(w)
 
 
 # --------------------------------------------------------------------------------------

@@ -24,6 +24,7 @@ for name, other in (("segmented", b), ("second fused stack", c)):
             if n and first is None:
                 first = (li, k, n, d.max().item(), a.buf[li][k].float().abs().max().item())
     dl = (a.logits - other.logits).abs().max().item()
+    print("DIAG finite:", bool(torch.isfinite(a.logits).all()), "max|x2 last|", a.buf[L - 1]["x2"].float().abs().max().item())
     print(f"DIAG {name}: first differing buffer {first}; logits max|diff| {dl:.3e} (max|logit| {a.logits.abs().max().item():.3e})", flush=True)
 for _ in range(3):
     y0 = a.decode_step().clone()

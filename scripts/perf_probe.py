@@ -15,6 +15,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--iters", type=int, default=50)
 ap.add_argument("--no-token", action="store_true")
 ap.add_argument("--no-stream", action="store_true")
+ap.add_argument("--big", action="store_true", help="one 4096 -> 262144 GEMV: steady-state streaming, whole panels per CTA")
 ap.add_argument("--model", default="llama-7b")
 ap.add_argument("--segments", default="fused")
 a = ap.parse_args()
@@ -43,3 +44,24 @@ if not a.no_token:
 if not a.no_stream:
     r = bench.stream_rate(spec, torch, dev, iters=max(3, a.iters // 5))
     print(f"PROBE {tag} stream: {r['gbs']} GB/s ({r['frac_of_peak'] * 100:.1f}%)", flush=True)
+
+if a.big:
+    K, N = 4096, 262144
+    from mlc_llm_b200 import ops
+    x = (torch.randn(K, device=dev) * 0.05).half()
+    p = torch.randint(-2**31, 2**31 - 1, (spec.n_words(K), N), dtype=torch.int32, device=dev)
+    sc = (torch.rand((spec.n_groups(K), N), device=dev) * 0.01).half()
+    out = torch.empty(N, dtype=torch.float16, device=dev)
+    prog = ops.GemvProgram([dict(weights=[(p, sc)], x=x, outs=[out])], "q4f16_0")
+    for _ in range(2):
+        prog.run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        prog.run()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / 10
+    nb = spec.gemv_bytes(K, N)
+    print(f"PROBE {tag} big 4096->{N}: {us:.1f} us  {nb / us / 1e3:.0f} GB/s ({nb / us / 1e3 / 6550.4 * 100:.1f}% of 6550)", flush=True)
