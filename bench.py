@@ -447,6 +447,28 @@ def decode_extra(args, torch, dist, dev, rank, world, model, fmt, barrier, max_o
     return rec
 
 
+def prefill_extra(args, torch, dist, dev, rank, world, model, fmt, barrier, max_over_ranks, M=2048, steps=3):
+    """Tensor-parallel prefill (BASELINE config 5): column-sharded q/k/v/gate/up GEMMs, row-sharded o/down GEMMs whose
+    per-rank partial sums are summed by one NCCL all-reduce per sharded block."""
+    from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack
+    from mlc_llm_b200.prefill_stack import PrefillStack
+
+    st = DecodeStack(MODEL_SHAPES[model], fmt, device=dev, tp_rank=rank, tp_size=world, use_program=False)
+    pf = PrefillStack(st, M)
+    pf.x_in.copy_((torch.randn(M, st.shape.hidden, device=dev) * 0.05).half())
+    ms = time_steps(torch, pf.run, steps, 3, barrier, max_over_ranks)
+    flops = pf.flops() * world
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak = float(peaks.get("bf16_tflops_sustained", 1379.4)) * world
+    rec = {"metric": f"{model}_{fmt}_prefill{M}_linear_tflops", "value": flops / ms / 1e9, "unit": "TFLOP/s (aggregate)", "n_gpus": world,
+           "ms_per_pass": ms, "config": {"workload": f"{model} {fmt} prefill M={M}, tp{world}: sharded tcgen05 dequant-GEMMs + one NCCL all-reduce of "
+                                                     f"[{M}, {st.shape.hidden}] f16 per sharded block", "flop": flops},
+           "frac_of_tensor_peak": flops / ms / 1e9 / peak, "gemms_per_pass": pf.gemms_per_pass, "collectives_per_pass": pf.collectives_per_pass}
+    del pf, st
+    torch.cuda.empty_cache()
+    return rec
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse_args()
@@ -612,6 +634,7 @@ def main():
             extra.append(decode_extra(args, torch, dist, dev, rank, world, "llama-13b", "q8f16_0", barrier, max_over_ranks))
         if world == 8:
             extra.append(decode_extra(args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks, steps=20))
+            extra.append(prefill_extra(args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks))
     if rank == 0:
         sampler.stop()
 

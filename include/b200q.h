@@ -182,14 +182,14 @@ B200Q_API int b200q_gemv_program_run(const void* host_blob, const void* dev_blob
 /* Tensor-parallel program (q4f16_0): the reference has no tensor parallelism; the sharding is SURVEY.md 8e
  * (q/k/v/gate/up column-sharded, o/down row-sharded, one reduction per sharded block).  reduce_mask[j] bit i
  * marks op i of step j as ROW-PARALLEL: its matmul result is this rank's partial sum.  The reduction over the
- * ranks happens inside the launch: every rank pushes its f32 partial over NVLink into the slots of the panel's
- * owner rank, the owner adds them in rank order, applies the epilogue once and pushes the finished value into
- * every rank's activation array, where the dependent steps pick it up - the all-reduce of the sharded block
- * without a collective kernel or a launch boundary.  Requirements: every rank builds the same step list
- * (its own shards), zero-fills its workspace once, launches the same number of times, and passes the
+ * ranks happens inside the launch, in ONE NVLink hop: every rank pushes its f32 partial into the slot
+ * [panel][its rank] of EVERY peer's workspace (peer-mapped symmetric memory), then adds the slots of its own
+ * workspace in rank order - the same order everywhere, so every rank holds the same bits -, applies the epilogue
+ * and publishes the finished activation locally, where the dependent steps pick it up: the all-reduce of the
+ * sharded block without a collective kernel or a launch boundary.  Requirements: every rank builds the same step
+ * list (its own shards), zero-fills its workspace once, launches the same number of times, and passes the
  * peer-mapped workspace pointers of ALL ranks (peer_workspaces[tp_rank] == workspace).  The plain `out` of a
- * row-parallel op is only written on the panel's owner rank; dependent steps inside the program see the
- * reduced value everywhere. */
+ * row-parallel op is complete on every rank.  A peer that never launches is caught by the watchdog below. */
 B200Q_API int b200q_gemv_program_build_tp(const b200q_gemv_step* steps, int n_steps, int fmt,
                                 const unsigned char* reduce_mask, int tp_rank, int tp_size, void* host_blob,
                                 size_t blob_bytes);

@@ -657,33 +657,42 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         }
         if (finalize && n < op_N) {
           if (op_reduce && tp.size > 1) {
-            // row-parallel op: `sum` is this rank's partial.  The ranks take turns owning panels: the others push
-            // their f32 partial to the owner's slots over NVLink; the owner adds them in rank order, applies the
-            // epilogue ONCE and pushes the finished {f16 | tag} word into every rank's activation array - the
-            // all-reduce of the sharded block, inside the launch (no collective kernel, no launch boundary).
-            const int owner = (panel - op.panel_begin) % tp.size;
+            // row-parallel op: `sum` is this rank's partial.  One-hop all-reduce inside the launch: every rank pushes
+            // its {f32, tag} partial over NVLink into the slot [panel][its rank] of EVERY peer's workspace and then
+            // adds the slots of its own workspace in rank order - the same order on every rank, so all ranks hold the
+            // same bits, apply the epilogue redundantly and publish the finished activation LOCALLY: no owner, no
+            // second hop for a broadcast, and the plain `out` is complete on every rank.
             const size_t slot = st.tp_partial_off + ((size_t)panel * tp.size) * kPanelCols + ht;
-            if (tp.rank != owner) {
-              uint2* dst = reinterpret_cast<uint2*>(tp.ws[owner] + tp.partial_off) + slot + (size_t)tp.rank * kPanelCols;
-              st_vol_v2(dst, __float_as_uint(sum), tag);
-              finalize = false;
-            } else {
-              const uint2* src = ws_partial + slot;
-              float tot = 0.f;
-              for (int r = 0; r < tp.size; ++r) {
+            const uint32_t sum_bits = __float_as_uint(sum);
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+              if (r < tp.size && r != tp.rank)
+                st_vol_v2(reinterpret_cast<uint2*>(tp.ws[r] + tp.partial_off) + slot + (size_t)tp.rank * kPanelCols, sum_bits, tag);
+            const uint2* src = ws_partial + slot;
+            float tot = 0.f;
+#pragma unroll
+            for (int r0 = 0; r0 < 8; r0 += 4) {  // four polls in flight together (register budget), added in rank order
+              if (r0 >= tp.size) break;
+              uint2 rv[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                if (r0 + q < tp.size && r0 + q != tp.rank) rv[q] = ld_vol_v2(src + (size_t)(r0 + q) * kPanelCols);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const int r = r0 + q;
+                if (r >= tp.size) break;
                 if (r == tp.rank) { tot += sum; continue; }
-                uint2 rv = ld_vol_v2(src + (size_t)r * kPanelCols);
-                if (rv.y != tag) {
+                if (rv[q].y != tag) {
                   WdSpin sp;
                   do {
                     wd_poll(sp, wd, kWdTpPartial, (unsigned)j);
-                    rv = ld_vol_v2(src + (size_t)r * kPanelCols);
-                  } while (rv.y != tag);
+                    rv[q] = ld_vol_v2(src + (size_t)r * kPanelCols);
+                  } while (rv[q].y != tag);
                 }
-                tot += __uint_as_float(rv.x);
+                tot += __uint_as_float(rv[q].x);
               }
-              sum = tot;
             }
+            sum = tot;
           }
           if (finalize) {
             if (op_ep == B200Q_EP_CAST_F32) {
@@ -700,12 +709,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
               const __half y = ep_f16(sum, op_ep, &e0, 0);
               if (op_out_ll >= 0) {
                 const uint32_t word = (tag << 16) | (uint32_t)__half_as_ushort(y);
-                if (op_reduce && tp.size > 1) {
-                  for (int r = 0; r < tp.size; ++r)
-                    st_vol_u32(reinterpret_cast<uint32_t*>(tp.ws[r] + tp.ll_off) + op_out_ll + n, word);
-                } else {
-                  st_vol_u32(reinterpret_cast<uint32_t*>(ws_ll) + op_out_ll + n, word);
-                }
+                st_vol_u32(reinterpret_cast<uint32_t*>(ws_ll) + op_out_ll + n, word);
               }
               reinterpret_cast<__half*>(op_out)[n] = y;
             }

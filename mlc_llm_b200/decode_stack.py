@@ -250,7 +250,7 @@ class DecodeStack:
                                     ops=[dict(w=w, epilogue=ep, ep0=e0, out=o) for w, ep, e0, o in items]))
             for _, _, _, o in items:
                 if self.tp_size > 1:
-                    self._layout[o.data_ptr()] = ("row_fused" if reduce else "rep") if row else "col"
+                    self._layout[o.data_ptr()] = "rep" if row else "col"  # (reduced outputs are complete on every rank)
             if self._trace_only:
                 return
         if self._steps is not None:  # recording a program
@@ -421,7 +421,7 @@ class DecodeStack:
 
     def _full_host(self, t: Optional[torch.Tensor]):
         """The complete (unsharded) tensor as a host array: column-parallel outputs are concatenated over the
-        ranks, outputs of an in-program row-parallel reduction are taken panel by panel from their owner rank."""
+        ranks; reduced (row-parallel) outputs and the input are complete on every rank."""
         if t is None:
             return None
         kind = self._layout.get(t.data_ptr(), "rep") if self.tp_size > 1 else "rep"
@@ -431,12 +431,7 @@ class DecodeStack:
 
         parts = [torch.empty_like(t) for _ in range(self.tp_size)]
         dist.all_gather(parts, t.contiguous(), group=self.pg)
-        if kind == "col":
-            return torch.cat([p.reshape(-1) for p in parts]).cpu().numpy()
-        full = parts[0].reshape(-1).clone()  # row_fused: 128-column panel p was finished by rank p % tp
-        for p in range((full.numel() + 127) // 128):
-            full[p * 128:(p + 1) * 128] = parts[p % self.tp_size].reshape(-1)[p * 128:(p + 1) * 128]
-        return full.cpu().numpy()
+        return torch.cat([p.reshape(-1) for p in parts]).cpu().numpy()  # "col"
 
     def snapshot(self):
         """After a decode_step(): for every launch of the step, the host copies of the FULL activation it read
