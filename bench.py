@@ -622,19 +622,35 @@ def main():
     torch.cuda.empty_cache()
     parity = None
     if not args.no_parity and not args.headline_only:
-        parity = parity_record(args, torch, dist, dev, rank, world, use_program)
+        try:
+            parity = parity_record(args, torch, dist, dev, rank, world, use_program)
+        except Exception as e:  # noqa: BLE001
+            parity = {"ok": False, "error": f"{type(e).__name__}: {str(e)[:300]}"}
     prefill = None
     if full_run and world == 1 and not args.no_prefill:
-        prefill = prefill_record(args, torch, dev, clocks_between)
+        try:
+            prefill = prefill_record(args, torch, dev, clocks_between)
+        except Exception as e:  # noqa: BLE001
+            prefill = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
     extra = []
+
+    def guarded(fn, *a, **kw):
+        # a failure in one of the side records must never cost the headline line (every rank takes the same path: the
+        # records are collective-free except where every rank calls them in the same order)
+        try:
+            extra.append(fn(*a, **kw))
+        except Exception as e:  # noqa: BLE001
+            extra.append({"error": f"{fn.__name__}{a[7:9]}: {type(e).__name__}: {str(e)[:300]}"})
+            torch.cuda.empty_cache()
+
     if full_run and not args.no_extra:
         if world == 1 and (args.model, args.fmt) != ("redpajama-3b", "q4f32_0"):
-            extra.append(decode_extra(args, torch, dist, dev, rank, world, "redpajama-3b", "q4f32_0", barrier, max_over_ranks, cpu=True))
+            guarded(decode_extra, args, torch, dist, dev, rank, world, "redpajama-3b", "q4f32_0", barrier, max_over_ranks, cpu=True)
         if (args.model, args.fmt) != ("llama-13b", "q8f16_0"):
-            extra.append(decode_extra(args, torch, dist, dev, rank, world, "llama-13b", "q8f16_0", barrier, max_over_ranks))
+            guarded(decode_extra, args, torch, dist, dev, rank, world, "llama-13b", "q8f16_0", barrier, max_over_ranks)
         if world == 8:
-            extra.append(decode_extra(args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks, steps=20))
-            extra.append(prefill_extra(args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks))
+            guarded(decode_extra, args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks, steps=20)
+            guarded(prefill_extra, args, torch, dist, dev, rank, world, "llama-65b", "q4f16_0", barrier, max_over_ranks)
     if rank == 0:
         sampler.stop()
 

@@ -853,8 +853,8 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
     case B200Q_Q8F16_0: kern = (const void*)gemv_program_kernel<B200Q_Q8F16_0>; break;
     default: kern = (const void*)gemv_program_kernel<B200Q_Q4F32_0>; break;
   }
-  if (use_tc) kern = (const void*)tc::gemv_program_tc_kernel;
-  if (int e2 = set_max_smem(kern, use_tc ? 4 : h->fmt, smem)) return e2;
+  if (use_tc) kern = h->tp_size > 1 ? (const void*)tc::gemv_program_tc_kernel<true> : (const void*)tc::gemv_program_tc_kernel<false>;
+  if (int e2 = set_max_smem(kern, use_tc ? (h->tp_size > 1 ? 5 : 4) : h->fmt, smem)) return e2;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(G, 1, 1);
   cfg.blockDim = dim3(use_tc ? tc::kThreadsTc : kProgThreads, 1, 1);

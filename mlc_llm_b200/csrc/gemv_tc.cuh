@@ -211,6 +211,10 @@ constexpr int kTrBlk0 = 870, kTrBlks = 64;
 //   activation warp m % 4 (B slot set (m / 4) % 2 of the slice),  MMA lane m % 2,  accumulator m % 8 (group g in column g),
 // so the four warps that share an SM sub-partition (same lane quadrant, different slice) work on different
 // blocks and are never in the same phase of their loop.
+// kTp: the tensor-parallel instantiation (row-parallel ops are reduced over the ranks inside the launch); the
+// single-GPU instantiation carries none of that code (the epilogue warps' finalize path is on the critical path of
+// every dependent step: 4 % tokens/s between the two)
+template <bool kTp>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
                        int stages, int xs_bytes, int dbg, unsigned prog_id, const __grid_constant__ Wd wd,
@@ -656,7 +660,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           }
         }
         if (finalize && n < op_N) {
-          if (op_reduce && tp.size > 1) {
+          if (kTp && op_reduce && tp.size > 1) {
             // row-parallel op: `sum` is this rank's partial.  One-hop all-reduce inside the launch: every rank pushes
             // its {f32, tag} partial over NVLink into the slot [panel][its rank] of EVERY peer's workspace and then
             // adds the slots of its own workspace in rank order - the same order on every rank, so all ranks hold the
