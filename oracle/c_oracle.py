@@ -97,6 +97,38 @@ def gemv_f64_unrounded(packed, scale, x, fmt: qo.Fmt, K=None):
     return y, a, c
 
 
+def decode_asym(packed, scale, mn, K, fmt: qo.Fmt, transpose_output=False):
+    """C version of quant_oracle.decode_asym (mn is None for the f32 scheme: scale holds bf16 scale | bf16 min)."""
+    N = packed.shape[1]
+    out = np.empty((N, K) if transpose_output else (K, N), fmt.np_dtype)
+    getattr(lib(), "orc_decode_asym_" + _suf(fmt))(_p(np.ascontiguousarray(packed)), _p(np.ascontiguousarray(scale)),
+                                                  _p(None if mn is None else np.ascontiguousarray(mn)), _p(out), K, N,
+                                                  int(transpose_output))
+    return out
+
+
+def gemv_ref_asym(packed, scale, mn, x, fmt: qo.Fmt, epilogue=qo.EP_NONE, ep0=None):
+    N = packed.shape[1]
+    x = np.ascontiguousarray(x.reshape(-1))
+    if ep0 is not None:
+        ep0 = np.ascontiguousarray(ep0.reshape(-1).astype(fmt.np_dtype))
+    out = np.empty(N, np.float32 if epilogue == qo.EP_CAST_F32 else fmt.np_dtype)
+    getattr(lib(), "orc_gemv_ref_asym_" + _suf(fmt))(_p(np.ascontiguousarray(packed)), _p(np.ascontiguousarray(scale)),
+                                                    _p(None if mn is None else np.ascontiguousarray(mn)), _p(x), _p(ep0),
+                                                    _p(out), x.size, N, int(epilogue))
+    return out
+
+
+def gemv_f64_asym(packed, scale, mn, x, fmt: qo.Fmt):
+    N = packed.shape[1]
+    x = np.ascontiguousarray(x.reshape(-1))
+    y, a = np.empty(N, np.float64), np.empty(N, np.float64)
+    getattr(lib(), "orc_gemv_f64_asym_" + _suf(fmt))(_p(np.ascontiguousarray(packed)), _p(np.ascontiguousarray(scale)),
+                                                    _p(None if mn is None else np.ascontiguousarray(mn)), _p(x), _p(y), _p(a),
+                                                    x.size, N)
+    return y, a
+
+
 def nt_matmul_ref_f16(X, T):
     M, K = X.shape
     N = T.shape[0]

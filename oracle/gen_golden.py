@@ -238,14 +238,111 @@ def gen_fused(tvm):
     np.savez_compressed(os.path.join(GOLDEN, "fused_gemv.npz"), **out)
 
 
+def gen_asym(tvm, refq):
+    """The reference CLI's DEFAULT scheme (asymmetric int4; quantization.py:105-140 encode, :183-211 decode,
+    :235-255 take_decode) and its fused GEMVs (dispatch/llama/main.py:4397-4415 f32, :4979-4997 f16)."""
+    from tvm import te
+
+    out = {}
+    for ci, (name, N, K) in enumerate([("q4f16_asym", 24, 256), ("q4f16_asym", 16, 4096), ("q4f32_asym", 24, 256),
+                                       ("q4f32_asym", 8, 2560)]):
+        fmt = qo.ASYM_FORMATS[name]
+        f32 = fmt.dtype == "float32"
+        rng = np.random.default_rng(2000 + ci)
+        W = (rng.standard_normal((N, K), dtype=np.float32) * 0.02).astype(fmt.np_dtype)
+        W[1, 0] = fmt.np_dtype(0.5)
+        W[2, 1] = fmt.np_dtype(-0.25)
+        R, G = K // 8, K // 32
+        aux_dt = np.uint32 if f32 else fmt.np_dtype
+        res = {"W": W}
+        for tr in (True, False):
+            enc = refq.encoding_func(False, 32, 4, "int4", 32, transpose=tr, dtype=fmt.dtype)
+            Wt = te.placeholder((N, K), fmt.dtype, name="W")
+            outs = list(enc(Wt))
+            f = te.create_prim_func([Wt] + outs)
+            pshape, ashape = ((R, N), (G, N)) if tr else ((N, R), (N, G))
+            bufs = [W, np.zeros(pshape, np.uint32)] + [np.zeros(ashape, aux_dt) for _ in outs[1:]]
+            r, _ = build_run(tvm, f, bufs)
+            sfx = "" if tr else "_rm"
+            res["packed" + sfx] = r[1]
+            res["scale" + sfx] = r[2]
+            if not f32:
+                res["min" + sfx] = r[3]
+        aux = [res["scale"]] + ([] if f32 else [res["min"]])
+        for tr in (False, True):
+            dec = refq.decoding_func(False, 32, 4, "int4", 32, K, data_transposed=True, transpose_output=tr, dtype=fmt.dtype)
+            D = te.placeholder((R, N), "uint32", name="D")
+            A = [te.placeholder((G, N), "uint32" if f32 else fmt.dtype, name=f"A{i}") for i in range(len(aux))]
+            f = te.create_prim_func([D] + A + [dec(D, *A)])
+            r, _ = build_run(tvm, f, [res["packed"]] + aux + [np.zeros((N, K) if tr else (K, N), fmt.np_dtype)])
+            res["w_t" if tr else "w"] = r[-1]
+        # arbitrary words / aux values
+        rw = rng.integers(0, 2**32, size=(R, N), dtype=np.uint64).astype(np.uint32)
+        if f32:
+            raux = [qo.f32x2_to_bf16x2((rng.random((G, N), dtype=np.float32) * 0.01), (-rng.random((G, N), dtype=np.float32) * 0.08))]
+        else:
+            raux = [(rng.random((G, N), dtype=np.float32) * 0.01).astype(np.float16), (-rng.random((G, N), dtype=np.float32) * 0.08).astype(np.float16)]
+        dec = refq.decoding_func(False, 32, 4, "int4", 32, K, data_transposed=True, transpose_output=False, dtype=fmt.dtype)
+        D = te.placeholder((R, N), "uint32", name="D")
+        A = [te.placeholder((G, N), "uint32" if f32 else fmt.dtype, name=f"A{i}") for i in range(len(raux))]
+        f = te.create_prim_func([D] + A + [dec(D, *A)])
+        r, _ = build_run(tvm, f, [rw] + raux + [np.zeros((K, N), fmt.np_dtype)])
+        res.update(rand_packed=rw, rand_scale=raux[0], rand_w=r[-1])
+        if not f32:
+            res["rand_min"] = raux[1]
+        # embedding gather
+        ids = np.array([3, 0, N - 1, 3, 7], dtype=np.int32)
+        tk = refq.decoding_after_taking_func(False, 32, 4, "int4", 32, K, dtype=fmt.dtype)
+        D = te.placeholder((N, R), "uint32", name="D")
+        A = [te.placeholder((N, G), "uint32" if f32 else fmt.dtype, name=f"A{i}") for i in range(len(aux))]
+        I = te.placeholder((len(ids),), "int32", name="I")
+        f = te.create_prim_func([D] + A + [I, tk(D, *A, I)])
+        aux_rm = [res["scale_rm"]] + ([] if f32 else [res["min_rm"]])
+        r, _ = build_run(tvm, f, [res["packed_rm"]] + aux_rm + [ids, np.zeros((len(ids), K), fmt.np_dtype)])
+        res.update(take_ids=ids, take_out=r[-1])
+        for k_, v_ in res.items():
+            out[f"{name}_N{N}_K{K}/{k_}"] = v_
+        print(f"asym encode/decode {name} N={N} K={K}: ok")
+    # fused GEMVs, the reference's unscheduled PrimFuncs at 4096 x 4096
+    try:
+        sys.path.insert(0, REF)
+        import mlc_llm  # noqa: F401
+        from mlc_llm.dispatch.llama import main as lm
+
+        for ci, (fname, name) in enumerate([("fused_decode4_matmul5_before", "q4f32_asym"), ("fused_decode4_matmul5_fp16_before", "q4f16_asym")]):
+            fmt = qo.ASYM_FORMATS[name]
+            f32 = fmt.dtype == "float32"
+            K = N = 4096
+            rng = np.random.default_rng(7300 + ci)
+            packed = rng.integers(0, 2**32, size=(K // 8, N), dtype=np.uint64).astype(np.uint32)
+            sc = rng.random((K // 32, N), dtype=np.float32) * 0.01
+            mn = -rng.random((K // 32, N), dtype=np.float32) * 0.08
+            aux = [qo.f32x2_to_bf16x2(sc, mn)] if f32 else [sc.astype(np.float16), mn.astype(np.float16)]
+            x = rng.standard_normal(K, dtype=np.float32).astype(fmt.np_dtype)
+            res, dt = build_run(tvm, getattr(lm, fname), [packed] + aux + [x.reshape(1, 1, K), np.zeros((1, 1, N), fmt.np_dtype)])
+            key = f"{name}/{fname}"
+            out[key + "/y"] = res[-1].reshape(N)
+            out[key + "/seed"] = np.array([7300 + ci], dtype=np.int64)
+            out[key + "/sha"] = np.frombuffer(sha(packed, *aux, x).encode(), dtype=np.uint8)
+            print(f"asym fused {fname}: {dt:.2f}s")
+    except Exception as e:  # pragma: no cover
+        print("asym fused skipped:", repr(e))
+    np.savez_compressed(os.path.join(GOLDEN, "asym.npz"), **out)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-fused", action="store_true")
     ap.add_argument("--skip-encdec", action="store_true")
+    ap.add_argument("--only-asym", action="store_true")
     a = ap.parse_args()
     os.makedirs(GOLDEN, exist_ok=True)
     tvm = _load_tvm()
     refq = _load_ref_quant()
+    if a.only_asym:
+        gen_asym(tvm, refq)
+        return
+    gen_asym(tvm, refq)
     if not a.skip_encdec:
         gen_encode_decode(tvm, refq)
     if not a.skip_fused:

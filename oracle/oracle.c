@@ -166,6 +166,91 @@ DEF_GEMV(f32, float)
 DEF_GEMV64(f16, half)
 DEF_GEMV64(f32, float)
 
+/* ---- asymmetric int4 (te_decode_asym, quantization.py:183-211; fused_decode4_matmul5*_before, ------------------
+ * dispatch/llama/main.py:4397-4415 f32 / 4979-4997 f16):  w = T(q) * scale + min, product and sum each rounded to T
+ * (the C / LLVM CPU builds of the reference do not contract them).  f32: scale_min is ONE uint32 per group and
+ * column, bf16(scale) in the low half, bf16(min) in the high half (quantization.py:28-32). */
+static inline float bf16lo(uint32_t u) { uint32_t v = u << 16; float f; memcpy(&f, &v, 4); return f; }
+static inline float bf16hi(uint32_t u) { uint32_t v = u & 0xFFFF0000u; float f; memcpy(&f, &v, 4); return f; }
+
+#define ASYM_SM_f16(G, N0, J) half s_ = scale[(size_t)(G) * N + (N0) + (J)], m_ = mn[(size_t)(G) * N + (N0) + (J)]
+#define ASYM_SM_f32(G, N0, J) uint32_t u_ = ((const uint32_t*)scale)[(size_t)(G) * N + (N0) + (J)]; float s_ = bf16lo(u_), m_ = bf16hi(u_)
+
+#define DEF_ASYM(SUF, T)                                                                             \
+  void orc_decode_asym_##SUF(const uint32_t* packed, const void* scale_, const void* mn_, T* out, int K, int N,  \
+                             int transpose_output) {                                                 \
+    const T* scale = (const T*)scale_; const T* mn = (const T*)mn_; (void)mn;                         \
+    _Pragma("omp parallel for schedule(static)") for (int k = 0; k < K; ++k) {                        \
+      const uint32_t* prow = packed + (size_t)(k / 8) * N;                                            \
+      uint32_t sh = (uint32_t)(k % 8) * 4;                                                            \
+      for (int n = 0; n < N; ++n) {                                                                   \
+        ASYM_SM_##SUF(k / 32, 0, n);                                                                  \
+        T q = (T)((prow[n] >> sh) & 15u);                                                             \
+        T w = q * s_;                                                                                 \
+        w = w + m_;                                                                                   \
+        if (transpose_output) out[(size_t)n * K + k] = w; else out[(size_t)k * N + n] = w;            \
+      }                                                                                               \
+    }                                                                                                 \
+  }                                                                                                   \
+  void orc_gemv_ref_asym_##SUF(const uint32_t* packed, const void* scale_, const void* mn_, const T* x, const T* ep0, \
+                               void* out, int K, int N, int epilogue) {                               \
+    const T* scale = (const T*)scale_; const T* mn = (const T*)mn_; (void)mn;                         \
+    const int BN = 512;                                                                               \
+    _Pragma("omp parallel for schedule(dynamic, 1)") for (int n0 = 0; n0 < N; n0 += BN) {             \
+      int nn = N - n0 < BN ? N - n0 : BN;                                                             \
+      T acc[512];                                                                                     \
+      for (int j = 0; j < nn; ++j) acc[j] = (T)0;                                                     \
+      for (int k = 0; k < K; ++k) {                                                                   \
+        const uint32_t* prow = packed + (size_t)(k / 8) * N + n0;                                     \
+        uint32_t sh = (uint32_t)(k % 8) * 4;                                                          \
+        T xk = x[k];                                                                                  \
+        for (int j = 0; j < nn; ++j) {                                                                \
+          ASYM_SM_##SUF(k / 32, n0, j);                                                               \
+          T q = (T)((prow[j] >> sh) & 15u);                                                           \
+          T w = q * s_;                                                                               \
+          w = w + m_;                                                                                 \
+          T t = xk * w;                                                                               \
+          acc[j] = acc[j] + t;                                                                        \
+        }                                                                                             \
+      }                                                                                               \
+      for (int j = 0; j < nn; ++j) {                                                                  \
+        T y = acc[j]; int n = n0 + j;                                                                 \
+        switch (epilogue) {                                                                           \
+          case 1: ((T*)out)[n] = ep0[n] + y; break;                                                   \
+          case 2: ((T*)out)[n] = ep0[n] * y; break;                                                   \
+          case 3: { T ny = (T)0 - y; T e = (T)expf((float)ny); T d = (T)1 + e; T sg = (T)1 / d; ((T*)out)[n] = y * sg; } break; \
+          case 4: ((float*)out)[n] = (float)y; break;                                                 \
+          default: ((T*)out)[n] = y;                                                                  \
+        }                                                                                             \
+      }                                                                                               \
+    }                                                                                                 \
+  }                                                                                                   \
+  void orc_gemv_f64_asym_##SUF(const uint32_t* packed, const void* scale_, const void* mn_, const T* x, double* y, \
+                               double* abs_sum, int K, int N) {                                       \
+    const T* scale = (const T*)scale_; const T* mn = (const T*)mn_; (void)mn;                         \
+    _Pragma("omp parallel for schedule(static)") for (int n0 = 0; n0 < N; n0 += 256) {                \
+      int nn = N - n0 < 256 ? N - n0 : 256;                                                           \
+      double a[256], b[256];                                                                          \
+      for (int j = 0; j < nn; ++j) a[j] = b[j] = 0.0;                                                 \
+      for (int k = 0; k < K; ++k) {                                                                   \
+        const uint32_t* prow = packed + (size_t)(k / 8) * N + n0;                                     \
+        uint32_t sh = (uint32_t)(k % 8) * 4;                                                          \
+        double xk = (double)x[k];                                                                     \
+        for (int j = 0; j < nn; ++j) {                                                                \
+          ASYM_SM_##SUF(k / 32, n0, j);                                                               \
+          T q = (T)((prow[j] >> sh) & 15u);                                                           \
+          T w = q * s_;                                                                               \
+          w = w + m_;                                                                                 \
+          double t = xk * (double)w;                                                                  \
+          a[j] += t; b[j] += fabs(t);                                                                 \
+        }                                                                                             \
+      }                                                                                               \
+      for (int j = 0; j < nn; ++j) { y[n0 + j] = a[j]; abs_sum[n0 + j] = b[j]; }                      \
+    }                                                                                                 \
+  }
+DEF_ASYM(f16, half)
+DEF_ASYM(f32, float)
+
 /* ---- f64 truth of the UNROUNDED weights (q - maxint) * s  (f16 formats) ----------------------
  * y, sum |x w| and the cancellation magnitude sum_k off_k |x_k| s of the tcgen05 decode program
  * (off_k = 1024 + maxint for even positions of a word, 64 + maxint for odd ones); see
