@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 101 /* major*100 + minor */
+#define B200Q_VERSION 102 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -52,7 +52,12 @@ typedef enum {
   B200Q_Q3F16_0 = 1, /* int3, group 40, 10 values per word (2 dead bits), f16  (offset 3)   */
   B200Q_Q4F32_0 = 2, /* int4, group 32, f32 scale/activation/output            (offset 7)   */
   B200Q_Q8F16_0 = 3, /* int8, group 32, 4 values per word, f16                 (offset 127) */
-  B200Q_NUM_FMT = 4
+  /* Asymmetric int4 - the reference CLI's default (--quantization-sym off, build.py:19; quantization.py:105-140,
+   * 183-211):  w = dtype(q) * scale + min, product and sum each rounded to dtype.  Only the *_asym entry points
+   * take these (they carry the extra `zmin` tensor). */
+  B200Q_Q4F16_ASYM = 4, /* f16: scale f16[G, N] and min f16[G, N] are separate tensors                      */
+  B200Q_Q4F32_ASYM = 5, /* f32: `scale` is uint32[G, N] = bf16(scale) | bf16(min) << 16, zmin is NULL        */
+  B200Q_NUM_FMT = 6
 } b200q_fmt;
 
 /* Epilogues fused by FuseDecodeMatmulEwise (mlc_llm/transform/decode_matmul_ewise.py:49-75) and by
@@ -244,6 +249,27 @@ B200Q_API int b200q_take_decode(const void* packed_rm, const void* scale_rm, con
  *   transpose == 0: packed uint32[N, n_words(K)], scale dtype[N, n_groups(K)]   (embedding table) */
 B200Q_API int b200q_encode(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
                  void* stream);
+
+/* ---- asymmetric scheme: the same operators with the group minimum as an extra tensor --------------------------
+ * Replace fused_decode4_matmul5* / fused_decode{3,4,5,6}_*matmul* of the asymmetric builds
+ * (dispatch/llama/main.py:4235-5313), decode6/7/8 + decode4/5/6_fp16 (:3985-4094), te_take_decode_asym and
+ * te_encode_asym.  Argument order = the PrimFuncs' (packed, scale, min, x[, operand], out) (main.py:4979).
+ * fmt: B200Q_Q4F16_ASYM (zmin = f16 tensor shaped like scale) or B200Q_Q4F32_ASYM (zmin = NULL, scale = the packed
+ * bf16 pair).  K must be a multiple of the group size (quantization.py:107).  Dequantized weights are bit-exact
+ * against the reference's CPU builds (two roundings, no fma contraction); matmuls accumulate in f32. */
+B200Q_API int b200q_gemv_asym(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0,
+                    void* out, int K, int N, int fmt, int epilogue, unsigned flags, void* workspace,
+                    size_t workspace_bytes, void* stream);
+B200Q_API int b200q_dequant_asym(const void* packed, const void* scale, const void* zmin, void* out, int K, int N,
+                       int fmt, int transposed, void* stream);
+B200Q_API int b200q_take_decode_asym(const void* packed_rm, const void* scale_rm, const void* zmin_rm, const int32_t* ids,
+                           void* out, int n_ids, int V, int K, int fmt, void* stream);
+B200Q_API int b200q_encode_asym(const void* W, void* packed, void* scale, void* zmin, int N, int K, int fmt, int transpose,
+                      void* stream);
+/* prefill: f16 scheme only (dequantize inside the tcgen05 GEMM) */
+B200Q_API int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0,
+                    const void* ep1, const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue,
+                    unsigned flags, void* stream);
 
 /* ---- a7 / a8: prefill GEMM -------------------------------------------------------------------
  * Y[m, n] = sum_k X[m, k] * w[k, n]  (+ epilogue), X dtype[M, K] row-major, Y dtype[M, N].

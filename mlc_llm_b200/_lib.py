@@ -68,6 +68,11 @@ PROTOTYPES = {
     "b200q_dequant": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
     "b200q_take_decode": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
     "b200q_encode": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
+    "b200q_gemv_asym": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
+    "b200q_dequant_asym": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
+    "b200q_take_decode_asym": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
+    "b200q_encode_asym": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
+    "b200q_gemm_asym": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p]),
     "b200q_gemm": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_uint, c_void_p]),
     "b200q_nt_matmul": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
 }

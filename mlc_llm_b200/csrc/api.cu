@@ -36,10 +36,16 @@ size_t gemv_program_workspace_bytes(const void* host_blob);
 void gemv_program_set_watchdog(unsigned long long* status, long long timeout_ns);
 int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspace, size_t workspace_bytes,
                      void* const* peer_workspaces, cudaStream_t stream);
-int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed,
+int dequant_launch(const void* packed, const void* scale, const void* zmin, void* out, int K, int N, int fmt, int transposed,
                    cudaStream_t stream);
-int take_decode_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
-                       int V, int K, int fmt, cudaStream_t stream);
+int take_decode_launch(const void* packed_rm, const void* scale_rm, const void* zmin_rm, const int32_t* ids, void* out,
+                       int n_ids, int V, int K, int fmt, cudaStream_t stream);
+int encode_asym_launch(const void* W, void* packed, void* scale, void* zmin, int N, int K, int fmt, int transpose,
+                       cudaStream_t stream);
+int gemv_asym_launch(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0, void* out, int K,
+                     int N, int fmt, int epilogue, unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
+                     const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream);
 int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
                   cudaStream_t stream);
 int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
@@ -50,8 +56,19 @@ int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* 
 
 static bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
-static int check_fmt(int fmt, const char* who) {
+static int check_fmt(int fmt, const char* who, bool asym_entry = false) {
   if (fmt < 0 || fmt >= B200Q_NUM_FMT) return set_error(B200Q_ERR_UNSUPPORTED, "%s: unknown fmt %d", who, fmt);
+  if (fmt_is_asym(fmt) != (asym_entry ? 1 : 0))
+    return set_error(B200Q_ERR_UNSUPPORTED, asym_entry ? "%s: fmt %d is a symmetric scheme (use the entry point without _asym)"
+                                                       : "%s: fmt %d is an asymmetric scheme (use the *_asym entry point)", who, fmt);
+  return B200Q_OK;
+}
+// asymmetric schemes: the f16 one carries a min tensor shaped like scale, the f32 one packs it into `scale`
+static int check_asym(int fmt, const void* zmin, int K, const char* who) {
+  if (fmt == B200Q_Q4F16_ASYM && !zmin) return set_error(B200Q_ERR_NULL, "%s: the f16 asymmetric scheme needs the min tensor", who);
+  if (fmt == B200Q_Q4F32_ASYM && zmin) return set_error(B200Q_ERR_UNSUPPORTED, "%s: the f32 asymmetric scheme packs min into scale (zmin must be NULL)", who);
+  if (zmin && !aligned(zmin, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "%s: zmin must be 16-byte aligned", who);
+  if (K <= 0 || K % 32 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "%s: K=%d must be a multiple of the group size 32 (quantization.py:107)", who, K);
   return B200Q_OK;
 }
 
@@ -107,18 +124,19 @@ const char* b200q_last_error(void) { return g_err; }
 unsigned long long b200q_launch_count(void) { return g_launches.load(); }
 
 int b200q_n_groups(int fmt, int K) {
-  if (check_fmt(fmt, "b200q_n_groups")) return B200Q_ERR_UNSUPPORTED;
+  if (fmt < 0 || fmt >= B200Q_NUM_FMT) return B200Q_ERR_UNSUPPORTED;
   return n_groups(fmt, K);
 }
 int b200q_n_words(int fmt, int K) {
-  if (check_fmt(fmt, "b200q_n_words")) return B200Q_ERR_UNSUPPORTED;
+  if (fmt < 0 || fmt >= B200Q_NUM_FMT) return B200Q_ERR_UNSUPPORTED;
   return n_words(fmt, K);
 }
 long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue) {
-  if (check_fmt(fmt, "b200q_gemv_bytes")) return B200Q_ERR_UNSUPPORTED;
+  if (fmt < 0 || fmt >= B200Q_NUM_FMT) return B200Q_ERR_UNSUPPORTED;
   const long long sb = fmt_is_f32(fmt) ? 4 : 2;
   const long long ob = (epilogue == B200Q_EP_CAST_F32 || fmt_is_f32(fmt)) ? 4 : 2;
   long long b = 4LL * n_words(fmt, K) * N + sb * n_groups(fmt, K) * N + sb * K + ob * N;
+  if (fmt == B200Q_Q4F16_ASYM) b += sb * n_groups(fmt, K) * N;  // the min tensor
   if (epilogue == B200Q_EP_ADD || epilogue == B200Q_EP_MULTIPLY) b += ob * N;
   if (epilogue == B200Q_EP_BIAS || epilogue == B200Q_EP_BIAS_GELU) b += sb * N;
   return b;
@@ -158,7 +176,7 @@ int b200q_gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt,
 
 int b200q_gemv_program_build_tp(const b200q_gemv_step* steps, int n_steps, int fmt, const unsigned char* reduce_mask,
                                 int tp_rank, int tp_size, void* host_blob, size_t blob_bytes) {
-  if (int e = check_fmt(fmt, "b200q_gemv_program_build")) return e;
+  if (int e = check_fmt(fmt, "b200q_gemv_program_build")) return e;  // (asymmetric schemes: per-operator launches only)
   if (!steps || !host_blob) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_build: NULL steps/blob");
   if (n_steps < 1 || n_steps > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_program_build: n_steps=%d", n_steps);
   const size_t el = fmt_is_f32(fmt) ? 4 : 2;
@@ -213,7 +231,7 @@ int b200q_dequant(const void* packed, const void* scale, void* out, int K, int N
   if (K <= 0 || N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_dequant: K=%d N=%d (N %% 8 == 0 required)", K, N);
   if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(out, 16))
     return set_error(B200Q_ERR_BAD_ALIGN, "b200q_dequant: pointers must be 16-byte aligned");
-  return dequant_launch(packed, scale, out, K, N, fmt, transposed, reinterpret_cast<cudaStream_t>(stream));
+  return dequant_launch(packed, scale, nullptr, out, K, N, fmt, transposed, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200q_take_decode(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
@@ -223,7 +241,7 @@ int b200q_take_decode(const void* packed_rm, const void* scale_rm, const int32_t
   if (K <= 0 || V <= 0 || n_ids < 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode: K=%d V=%d n_ids=%d", K, V, n_ids);
   if (n_ids == 0) return B200Q_OK;
   if (n_ids > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode: n_ids=%d > 65535", n_ids);
-  return take_decode_launch(packed_rm, scale_rm, ids, out, n_ids, V, K, fmt, reinterpret_cast<cudaStream_t>(stream));
+  return take_decode_launch(packed_rm, scale_rm, nullptr, ids, out, n_ids, V, K, fmt, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200q_encode(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose, void* stream) {
@@ -246,6 +264,65 @@ int b200q_gemm(const void* packed, const void* scale, const void* X, const void*
     return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm: pointers must be 16-byte aligned");
   return gemm_launch(packed, scale, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags,
                      reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_gemv_asym(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0, void* out, int K,
+                    int N, int fmt, int epilogue, unsigned flags, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_gemv_asym", true)) return e;
+  if (!x) return set_error(B200Q_ERR_NULL, "b200q_gemv_asym: NULL x");
+  if (int e = check_asym(fmt, zmin, K, "b200q_gemv_asym")) return e;
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  if (!aligned(x, el)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv_asym: x misaligned");
+  if (workspace && !aligned(workspace, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv_asym: workspace must be 16-byte aligned");
+  b200q_gemv_op op{packed, scale, ep0, out, N, epilogue};
+  if (int e = check_gemv_op(op, fmt, "b200q_gemv_asym")) return e;
+  if (int e = check_gemv_alias(&op, 1, x, nullptr, K, fmt, "b200q_gemv_asym")) return e;
+  return gemv_asym_launch(packed, scale, zmin, x, ep0, out, K, N, fmt, epilogue, flags, workspace, workspace ? workspace_bytes : 0,
+                          reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_dequant_asym(const void* packed, const void* scale, const void* zmin, void* out, int K, int N, int fmt,
+                       int transposed, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_dequant_asym", true)) return e;
+  if (!packed || !scale || !out) return set_error(B200Q_ERR_NULL, "b200q_dequant_asym: NULL pointer");
+  if (int e = check_asym(fmt, zmin, K, "b200q_dequant_asym")) return e;
+  if (N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_dequant_asym: N=%d (N %% 8 == 0 required)", N);
+  if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(out, 16))
+    return set_error(B200Q_ERR_BAD_ALIGN, "b200q_dequant_asym: pointers must be 16-byte aligned");
+  return dequant_launch(packed, scale, zmin, out, K, N, fmt, transposed, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_take_decode_asym(const void* packed_rm, const void* scale_rm, const void* zmin_rm, const int32_t* ids, void* out,
+                           int n_ids, int V, int K, int fmt, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_take_decode_asym", true)) return e;
+  if (!packed_rm || !scale_rm || !ids || !out) return set_error(B200Q_ERR_NULL, "b200q_take_decode_asym: NULL pointer");
+  if (fmt == B200Q_Q4F16_ASYM && !zmin_rm) return set_error(B200Q_ERR_NULL, "b200q_take_decode_asym: the f16 scheme needs the min table");
+  if (K <= 0 || K % 32 != 0 || V <= 0 || n_ids < 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode_asym: K=%d V=%d n_ids=%d", K, V, n_ids);
+  if (n_ids == 0) return B200Q_OK;
+  if (n_ids > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode_asym: n_ids=%d > 65535", n_ids);
+  return take_decode_launch(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, fmt, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_encode_asym(const void* W, void* packed, void* scale, void* zmin, int N, int K, int fmt, int transpose, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_encode_asym", true)) return e;
+  if (!W || !packed || !scale) return set_error(B200Q_ERR_NULL, "b200q_encode_asym: NULL pointer");
+  if (fmt == B200Q_Q4F16_ASYM && !zmin) return set_error(B200Q_ERR_NULL, "b200q_encode_asym: the f16 scheme writes a min tensor");
+  if (N <= 0 || K <= 0 || K % 32 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_encode_asym: N=%d K=%d (K %% 32 == 0 required)", N, K);
+  return encode_asym_launch(W, packed, scale, zmin, N, K, fmt, transpose, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
+                    const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_gemm_asym", true)) return e;
+  if (fmt != B200Q_Q4F16_ASYM) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_asym: f16 scheme only (f32 prefill is the reference's miss too)");
+  if (!packed || !scale || !X || !Y) return set_error(B200Q_ERR_NULL, "b200q_gemm_asym: NULL pointer");
+  if (int e = check_asym(fmt, zmin, K, "b200q_gemm_asym")) return e;
+  if (M < 0 || N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_asym: M=%d N=%d", M, N);
+  if (M == 0) return B200Q_OK;
+  if (epilogue < 0 || epilogue >= B200Q_NUM_EP) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_asym: epilogue %d", epilogue);
+  if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(X, 16) || !aligned(Y, 16))
+    return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_asym: pointers must be 16-byte aligned");
+  return gemm_asym_launch(packed, scale, zmin, X, ep0, ep1, ep2, Y, M, K, N, epilogue, flags, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200q_nt_matmul(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,

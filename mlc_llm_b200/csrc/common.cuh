@@ -51,6 +51,26 @@ struct Fmt<B200Q_Q4F32_0> {
   using scale_t = float;
 };
 
+template <>
+struct Fmt<B200Q_Q4F16_ASYM> {
+  static constexpr int kBits = 4, kGroup = 32, kNpu = 8, kMaxInt = 0;
+  static constexpr int kRowsPerGroup = 4;
+  static constexpr int kQuads = 2;
+  using scale_t = __half;
+};
+template <>
+struct Fmt<B200Q_Q4F32_ASYM> {
+  static constexpr int kBits = 4, kGroup = 32, kNpu = 8, kMaxInt = 0;
+  static constexpr int kRowsPerGroup = 4;
+  static constexpr int kQuads = 2;
+  using scale_t = float;  // bit pattern: bf16(scale) | bf16(min) << 16
+};
+__host__ __device__ constexpr bool fmt_is_asym_c(int fmt) { return fmt == B200Q_Q4F16_ASYM || fmt == B200Q_Q4F32_ASYM; }
+__host__ __device__ constexpr bool fmt_is_f32_c(int fmt) { return fmt == B200Q_Q4F32_0 || fmt == B200Q_Q4F32_ASYM; }
+// the f16 asymmetric scheme is the only one with a separate min tensor
+__host__ __device__ constexpr bool fmt_has_min_c(int fmt) { return fmt == B200Q_Q4F16_ASYM; }
+__host__ __device__ inline int fmt_is_asym(int fmt) { return fmt == B200Q_Q4F16_ASYM || fmt == B200Q_Q4F32_ASYM; }
+
 __host__ __device__ inline int fmt_group(int fmt) { return fmt == B200Q_Q3F16_0 ? 40 : 32; }
 __host__ __device__ inline int fmt_npu(int fmt) {
   return fmt == B200Q_Q3F16_0 ? 10 : (fmt == B200Q_Q8F16_0 ? 4 : 8);
@@ -58,7 +78,7 @@ __host__ __device__ inline int fmt_npu(int fmt) {
 __host__ __device__ inline int fmt_bits(int fmt) {
   return fmt == B200Q_Q3F16_0 ? 3 : (fmt == B200Q_Q8F16_0 ? 8 : 4);
 }
-__host__ __device__ inline int fmt_is_f32(int fmt) { return fmt == B200Q_Q4F32_0; }
+__host__ __device__ inline int fmt_is_f32(int fmt) { return fmt == B200Q_Q4F32_0 || fmt == B200Q_Q4F32_ASYM; }
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ inline int n_groups(int fmt, int K) { return ceil_div(K, fmt_group(fmt)); }
 __host__ __device__ inline int n_words(int fmt, int K) {
@@ -134,6 +154,29 @@ __device__ __forceinline__ void unpack_q4(uint32_t w, __half2 s2, __half2 (&out)
   out[1] = __hmul2(__hfma2(b, kMul16, kSubHi), s2);
   out[2] = __hmul2(__hadd2(c, kSubLo), s2);
   out[3] = __hmul2(__hfma2(d, kMul16, kSubHi), s2);
+}
+
+// asymmetric int4: out[i] = half(half(q * s) + m), the reference's two roundings (no fma contraction:
+// __hmul2_rn / __hadd2_rn are never fused).  q itself is exact: (1024 + q) - 1024, (1024 + 16 q) / 16 - 64.
+__device__ __forceinline__ void unpack_q4_asym(uint32_t w, __half2 s2, __half2 m2, __half2 (&out)[4]) {
+  const uint32_t kMagic = 0x64006400u;
+  const __half2 kSubLo = u32_as_h2(0xE400E400u);   // -1024
+  const __half2 kMul16 = u32_as_h2(0x2C002C00u);   // 1/16
+  const __half2 kSubHi = u32_as_h2(0xD400D400u);   // -64
+  uint32_t w8 = w >> 8;
+  __half2 a = __hadd2(u32_as_h2(lop3_and_or(w, 0x000F000Fu, kMagic)), kSubLo);
+  __half2 b = __hfma2(u32_as_h2(lop3_and_or(w, 0x00F000F0u, kMagic)), kMul16, kSubHi);
+  __half2 c = __hadd2(u32_as_h2(lop3_and_or(w8, 0x000F000Fu, kMagic)), kSubLo);
+  __half2 d = __hfma2(u32_as_h2(lop3_and_or(w8, 0x00F000F0u, kMagic)), kMul16, kSubHi);
+  out[0] = __hadd2_rn(__hmul2_rn(a, s2), m2);
+  out[1] = __hadd2_rn(__hmul2_rn(b, s2), m2);
+  out[2] = __hadd2_rn(__hmul2_rn(c, s2), m2);
+  out[3] = __hadd2_rn(__hmul2_rn(d, s2), m2);
+}
+// f32 asymmetric: scale / min from the packed bf16 pair; w = fl(fl(q * s) + m)
+__device__ __forceinline__ float asym_f32_weight(uint32_t w, int t, uint32_t sm) {
+  const float q = (float)((w >> (4 * t)) & 0xFu);
+  return __fadd_rn(__fmul_rn(q, __uint_as_float(sm << 16)), __uint_as_float(sm & 0xFFFF0000u));
 }
 
 // int3, 10 values in bits [0,30): out[i] = (v_i, v_{i+5}), i = 0..4

@@ -22,7 +22,7 @@ template <>
 struct Dec<B200Q_Q4F16_0> {
   using T = __half;
   static constexpr int kNpu = 8;
-  __device__ static void run(uint32_t w, __half s, __half (&o)[8]) {
+  __device__ static void run(uint32_t w, __half s, __half, __half (&o)[8]) {
     __half2 h[4];
     unpack_q4(w, __half2half2(s), h);
 #pragma unroll
@@ -36,7 +36,7 @@ template <>
 struct Dec<B200Q_Q3F16_0> {
   using T = __half;
   static constexpr int kNpu = 10;
-  __device__ static void run(uint32_t w, __half s, __half (&o)[10]) {
+  __device__ static void run(uint32_t w, __half s, __half, __half (&o)[10]) {
     __half2 h[5];
     unpack_q3(w, __half2half2(s), h);
 #pragma unroll
@@ -50,7 +50,7 @@ template <>
 struct Dec<B200Q_Q8F16_0> {
   using T = __half;
   static constexpr int kNpu = 4;
-  __device__ static void run(uint32_t w, __half s, __half (&o)[4]) {
+  __device__ static void run(uint32_t w, __half s, __half, __half (&o)[4]) {
     __half2 h[2];
     unpack_q8(w, __half2half2(s), h);
     o[0] = __low2half(h[0]);
@@ -63,7 +63,7 @@ template <>
 struct Dec<B200Q_Q4F32_0> {
   using T = float;
   static constexpr int kNpu = 8;
-  __device__ static void run(uint32_t w, float s, float (&o)[8]) {
+  __device__ static void run(uint32_t w, float s, float, float (&o)[8]) {
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
       uint32_t q = (w >> (4 * t)) & 0xFu;
@@ -72,10 +72,36 @@ struct Dec<B200Q_Q4F32_0> {
   }
 };
 
+template <>
+struct Dec<B200Q_Q4F16_ASYM> {  // w = half(half(q * s) + m)   (quantization.py:196)
+  using T = __half;
+  static constexpr int kNpu = 8;
+  __device__ static void run(uint32_t w, __half s, __half m, __half (&o)[8]) {
+    __half2 h[4];
+    unpack_q4_asym(w, __half2half2(s), __half2half2(m), h);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      o[t] = __low2half(h[t]);
+      o[t + 4] = __high2half(h[t]);
+    }
+  }
+};
+template <>
+struct Dec<B200Q_Q4F32_ASYM> {  // s carries the bit pattern bf16(scale) | bf16(min) << 16
+  using T = float;
+  static constexpr int kNpu = 8;
+  __device__ static void run(uint32_t w, float s, float, float (&o)[8]) {
+    const uint32_t sm = __float_as_uint(s);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) o[t] = asym_f32_weight(w, t, sm);
+  }
+};
+
 // out[K, N]: a thread owns 4 consecutive columns of one word row -> writes kNpu rows of 4 values.
 template <int FMT>
 __global__ void __launch_bounds__(256) dequant_kn_kernel(const uint32_t* __restrict__ packed,
                                                          const typename Dec<FMT>::T* __restrict__ scale,
+                                                         const typename Dec<FMT>::T* __restrict__ zmin,
                                                          typename Dec<FMT>::T* __restrict__ out, int K,
                                                          int N, int n_rows) {
   using D = Dec<FMT>;
@@ -89,13 +115,15 @@ __global__ void __launch_bounds__(256) dequant_kn_kernel(const uint32_t* __restr
     const int col = (int)(idx % n4) * 4;
     const uint4 w = ldg_stream_v4(packed + (size_t)row * N + col);
     const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
-    T s[4];
+    T s[4], m[4];
     const T* sp = scale + (size_t)(row / kRowsPerGroup) * N + col;
 #pragma unroll
     for (int j = 0; j < 4; ++j) s[j] = sp[j];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) m[j] = fmt_has_min_c(FMT) ? zmin[(size_t)(row / kRowsPerGroup) * N + col + j] : T(0.0f);
     T o[4][D::kNpu];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) D::run(wv[j], s[j], o[j]);
+    for (int j = 0; j < 4; ++j) D::run(wv[j], s[j], m[j], o[j]);
 #pragma unroll
     for (int t = 0; t < D::kNpu; ++t) {
       const int k = row * D::kNpu + t;
@@ -118,6 +146,7 @@ __global__ void __launch_bounds__(256) dequant_kn_kernel(const uint32_t* __restr
 template <int FMT>
 __global__ void __launch_bounds__(256) dequant_nk_kernel(const uint32_t* __restrict__ packed,
                                                          const typename Dec<FMT>::T* __restrict__ scale,
+                                                         const typename Dec<FMT>::T* __restrict__ zmin,
                                                          typename Dec<FMT>::T* __restrict__ out, int K,
                                                          int N, int n_rows) {
   using D = Dec<FMT>;
@@ -126,6 +155,7 @@ __global__ void __launch_bounds__(256) dequant_nk_kernel(const uint32_t* __restr
   constexpr int kGroupsPerTile = 32 / kRowsPerGroup;
   __shared__ uint32_t tw[32][33];
   __shared__ T ts[kGroupsPerTile][33];
+  __shared__ T tm[kGroupsPerTile][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 8 warps
   const int row0 = blockIdx.y * 32, col0 = blockIdx.x * 32;
 #pragma unroll
@@ -135,7 +165,9 @@ __global__ void __launch_bounds__(256) dequant_nk_kernel(const uint32_t* __restr
   }
   if (ty < kGroupsPerTile) {
     int g = row0 / kRowsPerGroup + ty, col = col0 + tx;
-    ts[ty][tx] = (g * kRowsPerGroup < n_rows && col < N) ? scale[(size_t)g * N + col] : T(0);
+    const bool in = (g * kRowsPerGroup < n_rows && col < N);
+    ts[ty][tx] = in ? scale[(size_t)g * N + col] : T(0);
+    tm[ty][tx] = (in && fmt_has_min_c(FMT)) ? zmin[(size_t)g * N + col] : T(0);
   }
   __syncthreads();
   // now lane <-> word row (contiguous k), warp <-> column
@@ -144,7 +176,7 @@ __global__ void __launch_bounds__(256) dequant_nk_kernel(const uint32_t* __restr
     const int col = col0 + cc, row = row0 + tx;
     if (col >= N || row >= n_rows) continue;
     T o[D::kNpu];
-    D::run(tw[tx][cc], ts[tx / kRowsPerGroup][cc], o);
+    D::run(tw[tx][cc], ts[tx / kRowsPerGroup][cc], tm[tx / kRowsPerGroup][cc], o);
     const int k0 = row * D::kNpu;
     T* dst = out + (size_t)col * K + k0;
     if (k0 + D::kNpu <= K && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) && (sizeof(T) * D::kNpu) % 16 == 0) {
@@ -163,6 +195,7 @@ __global__ void __launch_bounds__(256) dequant_nk_kernel(const uint32_t* __restr
 template <int FMT>
 __global__ void __launch_bounds__(256) take_decode_kernel(const uint32_t* __restrict__ packed_rm,
                                                           const typename Dec<FMT>::T* __restrict__ scale_rm,
+                                                          const typename Dec<FMT>::T* __restrict__ zmin_rm,
                                                           const int32_t* __restrict__ ids,
                                                           typename Dec<FMT>::T* __restrict__ out, int V,
                                                           int K, int n_rows, int n_grp) {
@@ -180,7 +213,8 @@ __global__ void __launch_bounds__(256) take_decode_kernel(const uint32_t* __rest
 #pragma unroll
       for (int t = 0; t < D::kNpu; ++t) o[t] = T(0.0f);
     } else {
-      D::run(packed_rm[(size_t)id * n_rows + r], scale_rm[(size_t)id * n_grp + r / kRowsPerGroup], o);
+      const size_t gi = (size_t)id * n_grp + r / kRowsPerGroup;
+      D::run(packed_rm[(size_t)id * n_rows + r], scale_rm[gi], fmt_has_min_c(FMT) ? zmin_rm[gi] : T(0.0f), o);
     }
     const int k0 = r * D::kNpu;
 #pragma unroll
@@ -190,7 +224,7 @@ __global__ void __launch_bounds__(256) take_decode_kernel(const uint32_t* __rest
 }
 
 template <int FMT>
-int launch_dequant(const void* packed, const void* scale, void* out, int K, int N, int transposed,
+int launch_dequant(const void* packed, const void* scale, const void* zmin, void* out, int K, int N, int transposed,
                    cudaStream_t stream) {
   using T = typename Dec<FMT>::T;
   const int rows = n_words(FMT, K);
@@ -200,12 +234,12 @@ int launch_dequant(const void* packed, const void* scale, void* out, int K, int 
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (blocks < 1) blocks = 1;
     dequant_kn_kernel<FMT><<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(packed),
-                                                       reinterpret_cast<const T*>(scale),
+                                                       reinterpret_cast<const T*>(scale), reinterpret_cast<const T*>(zmin),
                                                        reinterpret_cast<T*>(out), K, N, rows);
   } else {
     dim3 grid(ceil_div(N, 32), ceil_div(rows, 32));
     dequant_nk_kernel<FMT><<<grid, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(packed),
-                                                     reinterpret_cast<const T*>(scale),
+                                                     reinterpret_cast<const T*>(scale), reinterpret_cast<const T*>(zmin),
                                                      reinterpret_cast<T*>(out), K, N, rows);
   }
   count_launch();
@@ -213,37 +247,41 @@ int launch_dequant(const void* packed, const void* scale, void* out, int K, int 
 }
 
 template <int FMT>
-int launch_take(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids,
+int launch_take(const void* packed_rm, const void* scale_rm, const void* zmin_rm, const int32_t* ids, void* out, int n_ids,
                 int V, int K, cudaStream_t stream) {
   using T = typename Dec<FMT>::T;
   const int rows = n_words(FMT, K), grp = n_groups(FMT, K);
   dim3 grid(ceil_div(rows, 256), n_ids);
   take_decode_kernel<FMT><<<grid, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(packed_rm),
-                                                    reinterpret_cast<const T*>(scale_rm), ids,
+                                                    reinterpret_cast<const T*>(scale_rm), reinterpret_cast<const T*>(zmin_rm), ids,
                                                     reinterpret_cast<T*>(out), V, K, rows, grp);
   count_launch();
   return check_cuda(cudaGetLastError(), "take_decode launch");
 }
 }  // namespace
 
-int dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt,
+int dequant_launch(const void* packed, const void* scale, const void* zmin, void* out, int K, int N, int fmt,
                    int transposed, cudaStream_t stream) {
   switch (fmt) {
-    case B200Q_Q4F16_0: return launch_dequant<B200Q_Q4F16_0>(packed, scale, out, K, N, transposed, stream);
-    case B200Q_Q3F16_0: return launch_dequant<B200Q_Q3F16_0>(packed, scale, out, K, N, transposed, stream);
-    case B200Q_Q4F32_0: return launch_dequant<B200Q_Q4F32_0>(packed, scale, out, K, N, transposed, stream);
-    case B200Q_Q8F16_0: return launch_dequant<B200Q_Q8F16_0>(packed, scale, out, K, N, transposed, stream);
+    case B200Q_Q4F16_0: return launch_dequant<B200Q_Q4F16_0>(packed, scale, zmin, out, K, N, transposed, stream);
+    case B200Q_Q3F16_0: return launch_dequant<B200Q_Q3F16_0>(packed, scale, zmin, out, K, N, transposed, stream);
+    case B200Q_Q4F32_0: return launch_dequant<B200Q_Q4F32_0>(packed, scale, zmin, out, K, N, transposed, stream);
+    case B200Q_Q8F16_0: return launch_dequant<B200Q_Q8F16_0>(packed, scale, zmin, out, K, N, transposed, stream);
+    case B200Q_Q4F16_ASYM: return launch_dequant<B200Q_Q4F16_ASYM>(packed, scale, zmin, out, K, N, transposed, stream);
+    case B200Q_Q4F32_ASYM: return launch_dequant<B200Q_Q4F32_ASYM>(packed, scale, zmin, out, K, N, transposed, stream);
     default: return set_error(B200Q_ERR_UNSUPPORTED, "dequant: fmt %d", fmt);
   }
 }
 
-int take_decode_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out,
+int take_decode_launch(const void* packed_rm, const void* scale_rm, const void* zmin_rm, const int32_t* ids, void* out,
                        int n_ids, int V, int K, int fmt, cudaStream_t stream) {
   switch (fmt) {
-    case B200Q_Q4F16_0: return launch_take<B200Q_Q4F16_0>(packed_rm, scale_rm, ids, out, n_ids, V, K, stream);
-    case B200Q_Q3F16_0: return launch_take<B200Q_Q3F16_0>(packed_rm, scale_rm, ids, out, n_ids, V, K, stream);
-    case B200Q_Q4F32_0: return launch_take<B200Q_Q4F32_0>(packed_rm, scale_rm, ids, out, n_ids, V, K, stream);
-    case B200Q_Q8F16_0: return launch_take<B200Q_Q8F16_0>(packed_rm, scale_rm, ids, out, n_ids, V, K, stream);
+    case B200Q_Q4F16_0: return launch_take<B200Q_Q4F16_0>(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, stream);
+    case B200Q_Q3F16_0: return launch_take<B200Q_Q3F16_0>(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, stream);
+    case B200Q_Q4F32_0: return launch_take<B200Q_Q4F32_0>(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, stream);
+    case B200Q_Q8F16_0: return launch_take<B200Q_Q8F16_0>(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, stream);
+    case B200Q_Q4F16_ASYM: return launch_take<B200Q_Q4F16_ASYM>(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, stream);
+    case B200Q_Q4F32_ASYM: return launch_take<B200Q_Q4F32_ASYM>(packed_rm, scale_rm, zmin_rm, ids, out, n_ids, V, K, stream);
     default: return set_error(B200Q_ERR_UNSUPPORTED, "take_decode: fmt %d", fmt);
   }
 }

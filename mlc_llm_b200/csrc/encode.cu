@@ -75,7 +75,74 @@ __global__ void __launch_bounds__(256) encode_kernel(const T* __restrict__ W, ui
     }
   }
 }
+// asymmetric int4 (te_encode_asym, quantization.py:105-140): one thread per (n, group)
+//   scale = dtype(max - min) / dtype(15);  q = clamp(int(round(dtype(dtype(W - min) / scale))), 0, 15)
+//   f16: scale and min stored as they are; f32: bf16(scale) | bf16(min) << 16 with round-to-nearest-even by the
+//   integer bias trick of _tir_f32x2_to_bf16x2_to_u32 (:15-25) - the weights are quantized with the f32 values
+template <typename T>
+__global__ void __launch_bounds__(256) encode_asym_kernel(const T* __restrict__ W, uint32_t* __restrict__ packed,
+                                                          void* __restrict__ scale_out, T* __restrict__ min_out, int N, int K,
+                                                          int transpose) {
+  constexpr bool kF32 = sizeof(T) == 4;
+  const int G = K / 32, R = K / 8;
+  const long long total = (long long)N * G;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(idx % N), g = (int)(idx / N);
+    const T* w = W + (size_t)n * K + (size_t)g * 32;
+    float mn = Num<T>::load(w), mx = mn;
+    for (int k = 1; k < 32; ++k) {
+      const float v = Num<T>::load(w + k);
+      mn = fminf(mn, v);
+      mx = fmaxf(mx, v);
+    }
+    const float s = Num<T>::rnd(__fdiv_rn(Num<T>::rnd(__fsub_rn(mx, mn)), 15.0f));
+    const size_t ai = transpose ? (size_t)g * N + n : (size_t)n * G + g;
+    if constexpr (kF32) {
+      auto bf = [](float v) {
+        uint32_t u = __float_as_uint(v);
+        u += ((u >> 16) & 1u) + 0x7FFFu;
+        return (u >> 16) & 0xFFFFu;
+      };
+      reinterpret_cast<uint32_t*>(scale_out)[ai] = bf(s) | (bf(mn) << 16);
+    } else {
+      Num<T>::store(reinterpret_cast<T*>(scale_out) + ai, s);
+      Num<T>::store(min_out + ai, mn);
+    }
+    for (int r = 0; r < 4; ++r) {
+      uint32_t word = 0;
+      for (int t = 0; t < 8; ++t) {
+        float q = Num<T>::rnd(__fdiv_rn(Num<T>::rnd(__fsub_rn(Num<T>::load(w + r * 8 + t), mn)), s));
+        q = roundf(q);
+        // a constant group divides by zero (undefined in the reference): NaN -> 0, +inf -> 15
+        q = (q != q) ? 0.f : fminf(fmaxf(q, 0.f), 15.f);
+        word |= ((uint32_t)q) << (t * 4);
+      }
+      const int row = g * 4 + r;
+      if (transpose)
+        packed[(size_t)row * N + n] = word;
+      else
+        packed[(size_t)n * R + row] = word;
+    }
+  }
+}
 }  // namespace
+
+int encode_asym_launch(const void* W, void* packed, void* scale, void* zmin, int N, int K, int fmt, int transpose,
+                       cudaStream_t stream) {
+  const long long total = (long long)N * (K / 32);
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  if (blocks < 1) blocks = 1;
+  if (fmt == B200Q_Q4F32_ASYM)
+    encode_asym_kernel<float><<<blocks, 256, 0, stream>>>(reinterpret_cast<const float*>(W), reinterpret_cast<uint32_t*>(packed),
+                                                         scale, nullptr, N, K, transpose);
+  else
+    encode_asym_kernel<__half><<<blocks, 256, 0, stream>>>(reinterpret_cast<const __half*>(W), reinterpret_cast<uint32_t*>(packed),
+                                                          scale, reinterpret_cast<__half*>(zmin), N, K, transpose);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "encode_asym launch");
+}
 
 int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
                   cudaStream_t stream) {

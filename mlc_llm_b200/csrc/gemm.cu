@@ -76,6 +76,7 @@ struct GemmParams {
   CUtensorMap tm_b;  // dense mode: T f16 [N, K], box 256 x 64, 128B swizzle
   const uint32_t* packed;
   const __half* scale;
+  const __half* zmin;  // f16 asymmetric scheme: group minima, shaped like scale
   const __half* ep0;
   const __half* ep1;
   const __half* ep2;
@@ -101,10 +102,36 @@ __device__ __forceinline__ void sts128(uint32_t a, uint32_t x, uint32_t y, uint3
 }
 
 template <int FMT, int KATOM = kKAtomBytes>
-__device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint32_t (&s)[4], uint32_t stage, int kl0,
-                                              int chunk) {
+__device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint32_t (&s)[4], const uint32_t (&mn)[4],
+                                              uint32_t stage, int kl0, int chunk) {
   const uint32_t kMagic = 0x64006400u;
-  if constexpr (FMT == B200Q_Q4F16_0) {
+  (void)mn;
+  if constexpr (FMT == B200Q_Q4F16_ASYM) {
+    // w = half(half(q * s) + m): q exact from the magic numbers, then the reference's two roundings (never fused)
+    const __half2 kSubLo = u32_as_h2(0xE400E400u);  // -1024
+    const __half2 kMul16 = u32_as_h2(0x2C002C00u);  // 1/16
+    const __half2 kSubHi = u32_as_h2(0xD400D400u);  // -64
+    uint32_t o[8][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2 s2 = u32_as_h2(s[j]), m2 = u32_as_h2(mn[j]);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t p = __byte_perm(w[2 * j], w[2 * j + 1], h ? 0x7632 : 0x5410);
+        const uint32_t p8 = p >> 8;
+        const __half2 q0 = __hadd2(u32_as_h2(lop3_and_or(p, 0x000F000Fu, kMagic)), kSubLo);
+        const __half2 q1 = __hfma2(u32_as_h2(lop3_and_or(p, 0x00F000F0u, kMagic)), kMul16, kSubHi);
+        const __half2 q2 = __hadd2(u32_as_h2(lop3_and_or(p8, 0x000F000Fu, kMagic)), kSubLo);
+        const __half2 q3 = __hfma2(u32_as_h2(lop3_and_or(p8, 0x00F000F0u, kMagic)), kMul16, kSubHi);
+        o[4 * h + 0][j] = h2_as_u32(__hadd2_rn(__hmul2_rn(q0, s2), m2));
+        o[4 * h + 1][j] = h2_as_u32(__hadd2_rn(__hmul2_rn(q1, s2), m2));
+        o[4 * h + 2][j] = h2_as_u32(__hadd2_rn(__hmul2_rn(q2, s2), m2));
+        o[4 * h + 3][j] = h2_as_u32(__hadd2_rn(__hmul2_rn(q3, s2), m2));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sts128(b_chunk_addr<KATOM>(stage, kl0 + i, chunk), o[i][0], o[i][1], o[i][2], o[i][3]);
+  } else if constexpr (FMT == B200Q_Q4F16_0) {
     const __half2 kSubLo = u32_as_h2(0xE407E407u);  // -(1024 + 7)
     const __half2 kMul16 = u32_as_h2(0x2C002C00u);  // 1/16
     const __half2 kSubHi = u32_as_h2(0xD470D470u);  // -(64 + 7)
@@ -377,7 +404,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       const int chunk = lane;  // 8 columns each: 32 chunks = 256 columns
       int sb = 0;
       uint32_t pb = 0;
-      uint32_t w[B::kItems][8], s[B::kItems][4];
+      uint32_t w[B::kItems][8], s[B::kItems][4], mn[B::kItems][4];
       auto load_stage = [&](int n0, int i) {
 #pragma unroll
         for (int t = 0; t < B::kItems; ++t) {
@@ -390,11 +417,17 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             w[t][4] = hi.x; w[t][5] = hi.y; w[t][6] = hi.z; w[t][7] = hi.w;
             const uint4 sv = __ldg(reinterpret_cast<const uint4*>(p.scale + (size_t)(r / F::kRowsPerGroup) * p.N + n));
             s[t][0] = sv.x; s[t][1] = sv.y; s[t][2] = sv.z; s[t][3] = sv.w;
+            if constexpr (fmt_has_min_c(MODE)) {
+              const uint4 mv = __ldg(reinterpret_cast<const uint4*>(p.zmin + (size_t)(r / F::kRowsPerGroup) * p.N + n));
+              mn[t][0] = mv.x; mn[t][1] = mv.y; mn[t][2] = mv.z; mn[t][3] = mv.w;
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) w[t][j] = 0u;
 #pragma unroll
             for (int j = 0; j < 4; ++j) s[t][j] = 0u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mn[t][j] = 0u;
           }
         }
       };
@@ -402,13 +435,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         const int n0 = (tile / p.tiles_m) * kBN;
         load_stage(n0, 0);
         for (int i = 0; i < n_b_stages; ++i) {
-          uint32_t wc[B::kItems][8], sc[B::kItems][4];
+          uint32_t wc[B::kItems][8], sc[B::kItems][4], mc[B::kItems][4];
 #pragma unroll
           for (int t = 0; t < B::kItems; ++t) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) wc[t][j] = w[t][j];
 #pragma unroll
             for (int j = 0; j < 4; ++j) sc[t][j] = s[t][j];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mc[t][j] = fmt_has_min_c(MODE) ? mn[t][j] : 0u;
           }
           if (i + 1 < n_b_stages) load_stage(n0, i + 1);  // in flight while this stage is unpacked
           mbar_wait(b_empty + 8 * sb, pb ^ 1);
@@ -416,7 +451,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
           if (!(p.debug & 1)) {
 #pragma unroll
             for (int t = 0; t < B::kItems; ++t)
-              dequant_chunk<MODE>(wc[t], sc[t], stage, (dw + t * kDqWarps) * F::kNpu, chunk);
+              dequant_chunk<MODE>(wc[t], sc[t], mc[t], stage, (dw + t * kDqWarps) * F::kNpu, chunk);
           }
           fence_proxy_async_smem();
           __syncwarp();
@@ -623,7 +658,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
       const int dwa = warp - kFirstDqWarp;
       const int grp = dwa / C::kDq, dw = dwa % C::kDq;
       const int sub = lane / C::kChunks, chunk = lane % C::kChunks;  // word row of the pass, 8-column chunk
-      uint32_t w[C::kItems][8], s[C::kItems][4];
+      uint32_t w[C::kItems][8], s[C::kItems][4], mn[C::kItems][4];
       auto row_of = [&](int t) { return dw * C::kRowsPerPass + sub + 8 * t; };  // stage-local word row
       auto load_stage = [&](int n0, int i) {
 #pragma unroll
@@ -637,11 +672,17 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
             w[t][4] = hi.x; w[t][5] = hi.y; w[t][6] = hi.z; w[t][7] = hi.w;
             const uint4 sv = __ldg(reinterpret_cast<const uint4*>(p.scale + (size_t)(r / F::kRowsPerGroup) * p.N + n));
             s[t][0] = sv.x; s[t][1] = sv.y; s[t][2] = sv.z; s[t][3] = sv.w;
+            if constexpr (fmt_has_min_c(MODE)) {
+              const uint4 mv = __ldg(reinterpret_cast<const uint4*>(p.zmin + (size_t)(r / F::kRowsPerGroup) * p.N + n));
+              mn[t][0] = mv.x; mn[t][1] = mv.y; mn[t][2] = mv.z; mn[t][3] = mv.w;
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) w[t][j] = 0u;
 #pragma unroll
             for (int j = 0; j < 4; ++j) s[t][j] = 0u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mn[t][j] = 0u;
           }
         }
       };
@@ -664,13 +705,15 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
         const long long c = c0 + i;
         const int sb = (int)(c % C::kBStages);
         const uint32_t pb = (uint32_t)((c / C::kBStages) & 1);
-        uint32_t wc[C::kItems][8], sc[C::kItems][4];
+        uint32_t wc[C::kItems][8], sc[C::kItems][4], mc[C::kItems][4];
 #pragma unroll
         for (int t = 0; t < C::kItems; ++t) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) wc[t][j] = w[t][j];
 #pragma unroll
           for (int j = 0; j < 4; ++j) sc[t][j] = s[t][j];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mc[t][j] = fmt_has_min_c(MODE) ? mn[t][j] : 0u;
         }
         // this group's next stage (possibly in the next tile): its loads are in flight during this stage's unpack
         i += C::kDqGroups;
@@ -679,7 +722,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
         mbar_wait(b_empty + 8 * sb, pb ^ 1);
         const uint32_t stage = b_ring + sb * C::kBStage;
 #pragma unroll
-        for (int t = 0; t < C::kItems; ++t) dequant_chunk<MODE, C::kKAtom>(wc[t], sc[t], stage, row_of(t) * F::kNpu, chunk);
+        for (int t = 0; t < C::kItems; ++t) dequant_chunk<MODE, C::kKAtom>(wc[t], sc[t], mc[t], stage, row_of(t) * F::kNpu, chunk);
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
@@ -835,6 +878,25 @@ int gemm_launch(const void* packed, const void* scale, const void* X, const void
     case B200Q_Q8F16_0: return launch_gemm<B200Q_Q8F16_0>(p, stream);
     default: return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: fmt %d", fmt);
   }
+}
+
+int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
+                     const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream) {
+  if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_gemm_asym")) return e;
+  GemmParams p{};
+  p.packed = reinterpret_cast<const uint32_t*>(packed);
+  p.scale = reinterpret_cast<const __half*>(scale);
+  p.zmin = reinterpret_cast<const __half*>(zmin);
+  p.ep0 = reinterpret_cast<const __half*>(ep0);
+  p.ep1 = reinterpret_cast<const __half*>(ep1);
+  p.ep2 = reinterpret_cast<const __half*>(ep2);
+  p.Y = Y;
+  p.M = M; p.K = K; p.N = N;
+  p.n_rows = n_words(B200Q_Q4F16_ASYM, K);
+  p.epilogue = epilogue;
+  p.flags = flags;
+  if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
+  return launch_gemm<B200Q_Q4F16_ASYM>(p, stream);
 }
 
 int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y, int M,

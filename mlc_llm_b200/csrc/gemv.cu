@@ -68,10 +68,12 @@ template <int FMT>
 struct Stream {
   using F = Fmt<FMT>;
   using scale_t = typename F::scale_t;
-  static constexpr bool kF32 = (FMT == B200Q_Q4F32_0);
+  static constexpr bool kF32 = fmt_is_f32_c(FMT);
+  static constexpr bool kHasMin = fmt_has_min_c(FMT);  // f16 asymmetric: a second box (the group minima) behind the scales
   static constexpr int kGroupsPerBlock = kBlockRows / F::kRowsPerGroup;
   static constexpr int kScalePitch = kPanelCols * (int)sizeof(scale_t);
-  static constexpr int kScaleStageBytes = kGroupsPerBlock * kScalePitch;
+  static constexpr int kMinOff = kGroupsPerBlock * kScalePitch;
+  static constexpr int kScaleStageBytes = kMinOff * (kHasMin ? 2 : 1);
   static constexpr int kStageTx = kWordStageBytes + kScaleStageBytes;       // bytes TMA delivers per stage
   static constexpr int kStageBytes = (kStageTx + 1023) / 1024 * 1024;       // swizzled boxes need 1024B alignment
   static constexpr int kXRowBytes = XLayout<FMT>::kXRowBytes;
@@ -80,6 +82,7 @@ struct Stream {
 struct StreamOp {
   const uint32_t* packed;
   const void* scale;
+  const void* zmin;  // f16 asymmetric scheme only
   const void* ep0;
   void* out;
   int N;
@@ -90,6 +93,7 @@ struct StreamOp {
 struct StreamParams {
   CUtensorMap tm_w[kMaxOps];  // packed  uint32[n_rows, N], box 32 x 32, 128B swizzle
   CUtensorMap tm_s[kMaxOps];  // scale   dtype[n_groups, N], box kGroupsPerBlock x 128
+  CUtensorMap tm_m[kMaxOps];  // min     dtype[n_groups, N] (f16 asymmetric scheme), same box
   StreamOp op[kMaxOps];
   int n_ops;
   const void* x;
@@ -185,6 +189,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
         for (int q = 0; q < kPanelCols / kBoxCols; ++q)
           tma_2d(sw + q * kBoxBytes, &p.tm_w[oi], col0 + q * kBoxCols, rb * kBlockRows, bar, pol);
         tma_2d(sw + kWordStageBytes, &p.tm_s[oi], col0, rb * S::kGroupsPerBlock, bar, pol);
+        if constexpr (S::kHasMin) tma_2d(sw + kWordStageBytes + S::kMinOff, &p.tm_m[oi], col0, rb * S::kGroupsPerBlock, bar, pol);
         if (++s == stages) { s = 0; ph ^= 1; }
         if (++rb == p.RB) { rb = 0; ++panel; }
       }
@@ -231,12 +236,28 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_stream_kernel(const __grid_c
         const uint4 w00 = lds128(sw + w_off0), w01 = lds128(sw + w_off1);
         const uint4 w10 = lds128(sw + w_off0 + 8 * 128), w11 = lds128(sw + w_off1 + 8 * 128);
         const uint32_t xr = xs_base + rb * kBlockRows * S::kXRowBytes;
-        if constexpr (S::kF32) {
+        if constexpr (FMT == B200Q_Q4F32_ASYM) {
+          const uint4 sc0 = lds128(sw + s_off0), sc1 = lds128(sw + s_off1);
+          compute_row_f32_asym(w00, sc0, xr, acc[0]);
+          compute_row_f32_asym(w01, sc0, xr + S::kXRowBytes, acc[0]);
+          compute_row_f32_asym(w10, sc1, xr + 8 * S::kXRowBytes, acc[0]);
+          compute_row_f32_asym(w11, sc1, xr + 9 * S::kXRowBytes, acc[0]);
+        } else if constexpr (S::kF32) {
           const uint4 sc0 = lds128(sw + s_off0), sc1 = lds128(sw + s_off1);
           compute_row_f32(w00, sc0, xr, acc[0]);
           compute_row_f32(w01, sc0, xr + S::kXRowBytes, acc[0]);
           compute_row_f32(w10, sc1, xr + 8 * S::kXRowBytes, acc[0]);
           compute_row_f32(w11, sc1, xr + 9 * S::kXRowBytes, acc[0]);
+        } else if constexpr (S::kHasMin) {
+          __half2 s2[4], m2[4];
+          split_scales(lds64(sw + s_off0), s2);
+          split_scales(lds64(sw + s_off0 + S::kMinOff), m2);
+          compute_row_f16_asym(w00, s2, m2, xr, acc);
+          compute_row_f16_asym(w01, s2, m2, xr + S::kXRowBytes, acc);
+          split_scales(lds64(sw + s_off1), s2);
+          split_scales(lds64(sw + s_off1 + S::kMinOff), m2);
+          compute_row_f16_asym(w10, s2, m2, xr + 8 * S::kXRowBytes, acc);
+          compute_row_f16_asym(w11, s2, m2, xr + 9 * S::kXRowBytes, acc);
         } else {
           __half2 s2[4];
           split_scales(lds64(sw + s_off0), s2);
@@ -389,6 +410,11 @@ int launch_stream(StreamParams& p, unsigned flags, void* workspace, size_t works
                           (int)sizeof(typename S::scale_t), p.op[i].scale, p.op[i].N, n_grp, kPanelCols,
                           S::kGroupsPerBlock, CU_TENSOR_MAP_SWIZZLE_NONE))
       return e;
+    if constexpr (S::kHasMin) {
+      if (int e = make_tmap(&p.tm_m[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, p.op[i].zmin, p.op[i].N, n_grp, kPanelCols,
+                            S::kGroupsPerBlock, CU_TENSOR_MAP_SWIZZLE_NONE))
+        return e;
+    }
   }
   const int per_sm = (g_tune_ctas_per_sm == 2) ? 2 : 1;
   int G = sm_count() * per_sm;
@@ -468,6 +494,26 @@ void gemv_tune(int ctas_per_sm, int stages, int flags) {
   g_tune_ctas_per_sm = ctas_per_sm;
   g_tune_stages = stages;
   g_tune_flags = flags;
+}
+
+int gemv_asym_launch(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0, void* out, int K,
+                     int N, int fmt, int epilogue, unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  StreamParams p{};
+  p.n_ops = 1;
+  p.x = x;
+  p.K = K;
+  p.n_rows = n_words(fmt, K);
+  p.op[0].packed = reinterpret_cast<const uint32_t*>(packed);
+  p.op[0].scale = scale;
+  p.op[0].zmin = zmin;
+  p.op[0].ep0 = ep0;
+  p.op[0].out = out;
+  p.op[0].N = N;
+  p.op[0].epilogue = epilogue;
+  p.op[0].panel_begin = 0;
+  p.n_panels = ceil_div(N, kPanelCols);
+  if (fmt == B200Q_Q4F16_ASYM) return launch_stream<B200Q_Q4F16_ASYM>(p, flags, workspace, workspace_bytes, stream);
+  return launch_stream<B200Q_Q4F32_ASYM>(p, flags, workspace, workspace_bytes, stream);
 }
 
 size_t gemv_workspace_bytes() { return (size_t)kCounterBytes + (size_t)4 * 1024 * 1024; }

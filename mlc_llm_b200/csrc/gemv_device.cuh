@@ -14,7 +14,7 @@ constexpr int kBoxCols = 32;     // one TMA word box: 32 words = 128-byte rows
 template <int FMT>
 struct XLayout {
   using F = Fmt<FMT>;
-  static constexpr bool kF32 = (FMT == B200Q_Q4F32_0);
+  static constexpr bool kF32 = fmt_is_f32_c(FMT);
   // permuted activation bytes per packed word row
   static constexpr int kXRowBytes = kF32 ? 32 : F::kQuads * 8;
 };
@@ -53,6 +53,23 @@ __device__ __forceinline__ void split_scales(uint2 sc, __half2 (&s2)[4]) {
   s2[2] = u32_as_h2(__byte_perm(sc.y, 0, 0x1010));
   s2[3] = u32_as_h2(__byte_perm(sc.y, 0, 0x3232));
 }
+// asymmetric f16: the same contraction on the weights half(half(q * s) + m)
+__device__ __forceinline__ void compute_row_f16_asym(uint4 w, const __half2 (&s2)[4], const __half2 (&m2)[4], uint32_t xr,
+                                                     float (&acc)[2][4]) {
+  const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
+  uint4 xv = lds128(xr);  // (x0,x4)(x1,x5)(x2,x6)(x3,x7)
+  __half2 h[4][4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) unpack_q4_asym(wv[j], s2[j], m2[j], h[j]);
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    mma16816(acc[m], h2_as_u32(h[2 * m][0]), h2_as_u32(h[2 * m + 1][0]), h2_as_u32(h[2 * m][1]), h2_as_u32(h[2 * m + 1][1]),
+             xv.x, xv.y);
+    mma16816(acc[m], h2_as_u32(h[2 * m][2]), h2_as_u32(h[2 * m + 1][2]), h2_as_u32(h[2 * m][3]), h2_as_u32(h[2 * m + 1][3]),
+             xv.z, xv.w);
+  }
+}
+
 template <int FMT>
 __device__ __forceinline__ void compute_row_f16(uint4 w, const __half2 (&s2)[4], uint32_t xr, float (&acc)[2][4]) {
   const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
@@ -117,12 +134,26 @@ __device__ __forceinline__ void compute_row_f32(uint4 w, uint4 sc, uint32_t xr, 
   }
 }
 
+// asymmetric f32: sc carries bf16(scale) | bf16(min) << 16 of the four columns
+__device__ __forceinline__ void compute_row_f32_asym(uint4 w, uint4 sc, uint32_t xr, float (&acc)[4]) {
+  const uint32_t sm[4] = {sc.x, sc.y, sc.z, sc.w};
+  const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
+  uint4 xa = lds128(xr), xb = lds128(xr + 16);
+  const float xv[8] = {__uint_as_float(xa.x), __uint_as_float(xa.y), __uint_as_float(xa.z), __uint_as_float(xa.w),
+                       __uint_as_float(xb.x), __uint_as_float(xb.y), __uint_as_float(xb.z), __uint_as_float(xb.w)};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+#pragma unroll
+    for (int t = 0; t < 8; ++t) acc[j] = fmaf(xv[t], asym_f32_weight(wv[j], t, sm[j]), acc[j]);
+  }
+}
+
 // ---- activation staging: the whole x (optionally x * x_mul) into shared memory ---------------------
 // f16 formats: word row r -> xs[r][kXRowBytes] in the pair order the unpack produces.
 // one packed word row of activations (kNpu values, zero padded to 12) -> the pair order the unpack produces
 template <int FMT>
 __device__ __forceinline__ void permute_x_row(const __half (&v)[12], __half (&o)[12]) {
-  if constexpr (FMT == B200Q_Q4F16_0) {
+  if constexpr (FMT == B200Q_Q4F16_0 || FMT == B200Q_Q4F16_ASYM) {
     o[0] = v[0]; o[1] = v[4]; o[2] = v[1]; o[3] = v[5];
     o[4] = v[2]; o[5] = v[6]; o[6] = v[3]; o[7] = v[7];
   } else if constexpr (FMT == B200Q_Q3F16_0) {

@@ -42,11 +42,15 @@ def lookup(spec, K: int, N: int, epilogue: str = "none", m_is_one: bool = True) 
         if epilogue not in GEMV_EPILOGUES:
             return None
 
-        def gemv_op(packed, scale, x, *rest):
+        def gemv_op(packed, scale, *rest):
+            zmin = None
+            if spec.has_min:  # (packed, scale, min, x[, operand], out): dispatch/llama/main.py:4979
+                zmin, *rest = rest
+            x, *rest = rest
             *eps, out = rest
             if len(eps) != N_OPERANDS[epilogue]:
                 raise TypeError(f"{reference_name(spec, K, N, epilogue, True)} takes {N_OPERANDS[epilogue]} epilogue operand(s)")
-            return ops.gemv(packed, scale, x, spec, epilogue, eps[0] if eps else None, out=out, pdl=False)
+            return ops.gemv(packed, scale, x, spec, epilogue, eps[0] if eps else None, out=out, pdl=False, zmin=zmin)
 
         gemv_op.__name__ = reference_name(spec, K, N, epilogue, True)
         return gemv_op
@@ -54,12 +58,16 @@ def lookup(spec, K: int, N: int, epilogue: str = "none", m_is_one: bool = True) 
     if spec.dtype != "float16" or epilogue not in GEMM_EPILOGUES:
         return None
 
-    def gemm_op(packed, scale, x, *rest):
+    def gemm_op(packed, scale, *rest):
+        zmin = None
+        if spec.has_min:
+            zmin, *rest = rest
+        x, *rest = rest
         *eps, out = rest
         if len(eps) != N_OPERANDS[epilogue]:
             raise TypeError(f"{reference_name(spec, K, N, epilogue, False)} takes {N_OPERANDS[epilogue]} epilogue operand(s)")
         eps = list(eps) + [None] * (3 - len(eps))
-        return ops.gemm(packed, scale, x, spec, epilogue, eps[0], eps[1], eps[2], out=out)
+        return ops.gemm(packed, scale, x, spec, epilogue, eps[0], eps[1], eps[2], out=out, zmin=zmin)
 
     gemm_op.__name__ = reference_name(spec, K, N, epilogue, False)
     return gemm_op
@@ -72,8 +80,12 @@ def lookup_decode(spec, K: int, N: int, transpose_output: bool) -> Optional[Call
     if spec is None or N % 8 != 0:
         return None
 
-    def decode_op(packed, scale, out):
-        return ops.dequantize(packed, scale, K, spec, transpose_output, out=out)
+    def decode_op(packed, scale, *rest):
+        zmin = None
+        if spec.has_min:  # decode4_fp16(data, scale, min, out): dispatch/llama/main.py:4042
+            zmin, *rest = rest
+        (out,) = rest
+        return ops.dequantize(packed, scale, K, spec, transpose_output, out=out, zmin=zmin)
 
     decode_op.__name__ = f"decode_{spec.name}_k{K}_n{N}" + ("_T" if transpose_output else "")
     return decode_op

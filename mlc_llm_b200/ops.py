@@ -73,9 +73,18 @@ def _check_weight(spec: QuantSpec, packed: torch.Tensor, scale: torch.Tensor, K:
     N = packed.shape[1]
     if packed.shape[0] != spec.n_words(K):
         raise ValueError(f"packed has {packed.shape[0]} word rows, {spec.name} with K={K} needs {spec.n_words(K)}")
-    if scale.dtype != spec.torch_dtype or tuple(scale.shape) != (spec.n_groups(K), N):
-        raise ValueError(f"scale must be {spec.dtype}[{spec.n_groups(K)}, {N}]")
+    if scale.dtype != spec.scale_torch_dtype or tuple(scale.shape) != (spec.n_groups(K), N):
+        raise ValueError(f"scale must be {spec.scale_torch_dtype}[{spec.n_groups(K)}, {N}]")
     return N
+
+
+def _check_min(spec: QuantSpec, scale: torch.Tensor, zmin: Optional[torch.Tensor]):
+    """The group-minimum tensor of the f16 asymmetric scheme (None for every other scheme)."""
+    if spec.has_min:
+        if zmin is None or zmin.dtype != scale.dtype or zmin.shape != scale.shape:
+            raise ValueError(f"{spec.name}: zmin must be a tensor shaped like scale")
+    elif zmin is not None:
+        raise ValueError(f"{spec.name} has no separate min tensor")
 
 
 def gemv(
@@ -88,6 +97,7 @@ def gemv(
     out: Optional[torch.Tensor] = None,
     pdl: bool = False,
     ws=None,
+    zmin: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """fused_decode*_matmul*: y[..., n] = sum_k x[..., k] * decode(packed, scale)[k, n] (+ epilogue).
 
@@ -111,6 +121,12 @@ def gemv(
         raise ValueError(f"ep0 must be {spec.dtype}[{N}]")
     L = _lib.lib()
     wp, wb = _ws_args(ws)
+    _need_cuda(zmin)
+    _check_min(spec, scale, zmin)
+    if not spec.sym:  # (packed, scale, min, x[, operand], out): dispatch/llama/main.py:4979
+        _lib.check(L.b200q_gemv_asym(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), x.data_ptr(), _ptr(ep0), out.data_ptr(),
+                                     K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, wp, wb, _stream()))
+        return out
     _lib.check(
         L.b200q_gemv(
             packed.data_ptr(), scale.data_ptr(), x.data_ptr(), _ptr(ep0), out.data_ptr(),
@@ -166,7 +182,7 @@ def gemv_tune(ctas_per_sm: int = 0, stages: int = 0, dbg_flags: int = 0) -> None
     _lib.lib().b200q_gemv_tune(ctas_per_sm, stages, dbg_flags)
 
 
-def dequantize(packed, scale, K: int, spec, transpose_output: bool = False, out=None) -> torch.Tensor:
+def dequantize(packed, scale, K: int, spec, transpose_output: bool = False, out=None, zmin=None) -> torch.Tensor:
     """decode*: packed/scale -> dtype[K, N] (or [N, K]); bit-exact against the reference decode."""
     spec = _spec(spec)
     _need_cuda(packed, scale, out)
@@ -177,12 +193,18 @@ def dequantize(packed, scale, K: int, spec, transpose_output: bool = False, out=
     elif tuple(out.shape) != shape or out.dtype != spec.torch_dtype:
         raise ValueError(f"out must be {spec.dtype}{list(shape)}")
     L = _lib.lib()
+    _need_cuda(zmin)
+    _check_min(spec, scale, zmin)
+    if not spec.sym:
+        _lib.check(L.b200q_dequant_asym(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), out.data_ptr(), K, N, spec.fmt_id,
+                                        int(transpose_output), _stream()))
+        return out
     _lib.check(L.b200q_dequant(packed.data_ptr(), scale.data_ptr(), out.data_ptr(), K, N, spec.fmt_id,
                                int(transpose_output), _stream()))
     return out
 
 
-def take_decode(packed_rm, scale_rm, ids, K: int, spec, out=None) -> torch.Tensor:
+def take_decode(packed_rm, scale_rm, ids, K: int, spec, out=None, zmin_rm=None) -> torch.Tensor:
     """take_decode: quantized embedding gather from the row-major (V, n_words) layout."""
     spec = _spec(spec)
     _need_cuda(packed_rm, scale_rm, ids, out)
@@ -195,6 +217,12 @@ def take_decode(packed_rm, scale_rm, ids, K: int, spec, out=None) -> torch.Tenso
     if out is None:
         out = torch.empty((n, K), dtype=spec.torch_dtype, device=packed_rm.device)
     L = _lib.lib()
+    _need_cuda(zmin_rm)
+    _check_min(spec, scale_rm, zmin_rm)
+    if not spec.sym:
+        _lib.check(L.b200q_take_decode_asym(packed_rm.data_ptr(), scale_rm.data_ptr(), _ptr(zmin_rm), ids.data_ptr(),
+                                            out.data_ptr(), n, V, K, spec.fmt_id, _stream()))
+        return out
     _lib.check(L.b200q_take_decode(packed_rm.data_ptr(), scale_rm.data_ptr(), ids.data_ptr(), out.data_ptr(),
                                    n, V, K, spec.fmt_id, _stream()))
     return out
@@ -210,8 +238,15 @@ def encode(W: torch.Tensor, spec, transpose: bool = True):
     R, G = spec.n_words(K), spec.n_groups(K)
     pshape, sshape = ((R, N), (G, N)) if transpose else ((N, R), (N, G))
     packed = torch.empty(pshape, dtype=torch.int32, device=W.device)
-    scale = torch.empty(sshape, dtype=spec.torch_dtype, device=W.device)
+    scale = torch.empty(sshape, dtype=spec.scale_torch_dtype, device=W.device)
     L = _lib.lib()
+    if not spec.sym:  # te_encode_asym: (packed, scale, min) for f16, (packed, scale_min) for f32
+        if K % spec.group_size:
+            raise ValueError("asymmetric encode: K must be a multiple of the group size (quantization.py:107)")
+        zmin = torch.empty(sshape, dtype=spec.torch_dtype, device=W.device) if spec.has_min else None
+        _lib.check(L.b200q_encode_asym(W.data_ptr(), packed.data_ptr(), scale.data_ptr(), _ptr(zmin), N, K, spec.fmt_id,
+                                       int(transpose), _stream()))
+        return (packed, scale, zmin) if spec.has_min else (packed, scale)
     _lib.check(L.b200q_encode(W.data_ptr(), packed.data_ptr(), scale.data_ptr(), N, K, spec.fmt_id,
                               int(transpose), _stream()))
     return packed, scale
@@ -220,7 +255,8 @@ def encode(W: torch.Tensor, spec, transpose: bool = True):
 GEMM_TILES = {None: 0, "single": 2, "pair128": 4, "pair256": 8}  # B200Q_FLAG_GEMM_*
 
 
-def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, pdl: bool = False, tile=None):
+def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, pdl: bool = False, tile=None,
+         zmin=None):
     """fused_decode*_NT_matmul* / decode + NT_matmul: Y[m, n] = sum_k X[m, k] * w[k, n] (+ epilogue)
     on the tcgen05 tensor cores.  X dtype[..., M, K] -> Y dtype[..., M, N]."""
     spec = _spec(spec)
@@ -238,6 +274,12 @@ def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, 
     elif out.numel() != M * N or out.dtype != odt:
         raise ValueError(f"out must be {odt}[{M}, {N}]")
     L = _lib.lib()
+    _need_cuda(zmin)
+    _check_min(spec, scale, zmin)
+    if not spec.sym:
+        _lib.check(L.b200q_gemm_asym(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
+                                     out.data_ptr(), M, K, N, spec.fmt_id, ep, (FLAG_PDL if pdl else 0) | GEMM_TILES[tile], _stream()))
+        return out
     _lib.check(L.b200q_gemm(packed.data_ptr(), scale.data_ptr(), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
                             out.data_ptr(), M, K, N, spec.fmt_id, ep, (FLAG_PDL if pdl else 0) | GEMM_TILES[tile], _stream()))
     return out

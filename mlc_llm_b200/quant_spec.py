@@ -8,7 +8,7 @@ import dataclasses
 import torch
 
 # ids shared with include/b200q.h
-FMT_IDS = {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3}
+FMT_IDS = {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5}
 EPILOGUES = {
     "none": 0,
     "add": 1,
@@ -57,11 +57,20 @@ class QuantSpec:
     def n_words(self, K: int) -> int:
         return -(-self.group_size // self.npu) * self.n_groups(K)
 
+    @property
+    def has_min(self) -> bool:
+        """A separate group-minimum tensor (the f16 asymmetric scheme; the f32 one packs bf16 scale | bf16 min)."""
+        return (not self.sym) and self.dtype == "float16"
+
+    @property
+    def scale_torch_dtype(self) -> torch.dtype:
+        return torch.int32 if (not self.sym and self.dtype == "float32") else self.torch_dtype
+
     def gemv_bytes(self, K: int, N: int, epilogue: str = "none") -> int:
         """Algorithmic HBM bytes of one GEMV."""
         sb = 2 if self.dtype == "float16" else 4
         ob = 4 if (epilogue == "cast_f32" or self.dtype == "float32") else 2
-        b = 4 * self.n_words(K) * N + sb * self.n_groups(K) * N + sb * K + ob * N
+        b = 4 * self.n_words(K) * N + sb * self.n_groups(K) * N * (2 if self.has_min else 1) + sb * K + ob * N
         if epilogue in ("add", "multiply"):
             b += ob * N
         if epilogue in ("bias", "bias_gelu"):
@@ -74,20 +83,23 @@ SPECS = {
     "q3f16_0": QuantSpec("q3f16_0", "int3", "float16", 40),
     "q4f32_0": QuantSpec("q4f32_0", "int4", "float32", 32),
     "q8f16_0": QuantSpec("q8f16_0", "int8", "float16", 32),
+    # the reference CLI's default: asymmetric int4 (build.py:19 --quantization-sym off; quantization.py:105-140,183-211)
+    "q4f16_asym": QuantSpec("q4f16_asym", "int4", "float16", 32, sym=False),
+    "q4f32_asym": QuantSpec("q4f32_asym", "int4", "float32", 32, sym=False),
 }
 
 
 def spec_from_flags(dtype: str, mode: str, sym: bool, storage_nbit: int, group_size: int | None = None) -> QuantSpec:
-    """The reference's CLI flags -> QuantSpec.  Raises for combinations outside the `_0` contract
-    (asymmetric, uint16/uint8 storage, fp4): those are SURVEY.md 8(f) 'next' rows."""
-    if not sym:
-        raise NotImplementedError("asymmetric group quantization is not on this path yet (SURVEY.md 8f rank 1)")
+    """The reference's CLI flags -> QuantSpec (sym=False is the reference's default: the asymmetric int4 schemes).
+    Raises for the combinations that are not on this path (uint16/uint8 storage, fp4: SURVEY.md 8(f) rank 4)."""
     if storage_nbit != 32:
         raise NotImplementedError("only uint32 storage is on this path (SURVEY.md 8f rank 4)")
     if not mode.startswith("int"):
         raise NotImplementedError("fp4 is not on this path (SURVEY.md 8f rank 4)")
+    if not sym and mode != "int4":
+        raise NotImplementedError("asymmetric quantization exists for int4 only (quantization.py:283-284 asserts sym for int3 / fp4)")
     for s in SPECS.values():
-        if s.mode == mode and s.dtype == dtype:
+        if s.mode == mode and s.dtype == dtype and s.sym == sym:
             if group_size is not None and group_size != s.group_size:
                 raise NotImplementedError(f"group size {group_size} (the reference hard-wires {s.group_size})")
             return s

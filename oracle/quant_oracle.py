@@ -451,6 +451,8 @@ def gemv_bytes(K: int, N: int, fmt: Fmt, epilogue=EP_NONE) -> int:
     sb = 2 if fmt.dtype == "float16" else 4
     ob = 4 if (epilogue == EP_CAST_F32 or fmt.dtype == "float32") else 2
     b = 4 * fmt.n_words(K) * N + sb * fmt.n_groups(K) * N + sb * K + ob * N
+    if not fmt.sym and fmt.dtype == "float16":
+        b += sb * fmt.n_groups(K) * N  # the min tensor
     if epilogue in (EP_ADD, EP_MULTIPLY):
         b += ob * N
     if epilogue in (EP_BIAS, EP_BIAS_GELU):

@@ -31,10 +31,10 @@ def test_header_symbols_exported_and_bound():
 
 def test_version_and_layout_helpers_match_oracle():
     L = _lib.lib()
-    assert L.b200q_version() == 101
+    assert L.b200q_version() == 102
     for name, spec in SPECS.items():
-        f = qo.FORMATS[name]
-        assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3}[name]
+        f = qo.ALL_FORMATS[name]
+        assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5}[name]
         for K in (32, 40, 100, 2560, 4096, 5120, 11008, 13824, 22016):
             assert L.b200q_n_groups(spec.fmt_id, K) == f.n_groups(K) == spec.n_groups(K)
             assert L.b200q_n_words(spec.fmt_id, K) == f.n_words(K) == spec.n_words(K)
@@ -79,6 +79,13 @@ def test_argument_validation_codes():
     assert L.b200q_dequant(a, a, a, 4096, 4100, 0, 0, st) == -1
     assert L.b200q_gemm(a, a, a, None, None, None, a, 16, 4096, 4096, 2, 0, 0, st) == -3  # f32 GEMM
     assert L.b200q_take_decode(a, a, a, a, 0, 10, 64, 0, st) == 0  # empty gather is a no-op
+    # asymmetric schemes go through the *_asym entry points (and only they)
+    assert L.b200q_gemv(a, a, b, None, c, 4096, 4096, 4, 0, 0, None, 0, st) == -3
+    assert L.b200q_gemv_asym(a, a, a, b, None, c, 4096, 4096, 0, 0, 0, None, 0, st) == -3
+    assert L.b200q_gemv_asym(a, a, None, b, None, c, 4096, 4096, 4, 0, 0, None, 0, st) == -5  # f16 scheme needs min
+    assert L.b200q_gemv_asym(a, a, a, b, None, c, 4096, 4096, 5, 0, 0, None, 0, st) == -3     # f32 scheme packs it
+    assert L.b200q_gemv_asym(a, a, a, b, None, c, 4100, 4096, 4, 0, 0, None, 0, st) == -1     # K % 32
+    assert L.b200q_gemm_asym(a, a, None, a, None, None, None, c, 16, 4096, 4096, 5, 0, 0, st) == -3  # f32 prefill
 
 
 def test_spec_from_flags():
@@ -86,8 +93,11 @@ def test_spec_from_flags():
     assert spec_from_flags("float16", "int3", True, 32).name == "q3f16_0"
     assert spec_from_flags("float32", "int4", True, 32).name == "q4f32_0"
     assert spec_from_flags("float16", "int8", True, 32).name == "q8f16_0"
+    # the reference CLI's default (build.py:19: --quantization-sym off) is the asymmetric scheme
+    assert spec_from_flags("float16", "int4", False, 32).name == "q4f16_asym"
+    assert spec_from_flags("float32", "int4", False, 32).name == "q4f32_asym"
     with pytest.raises(NotImplementedError):
-        spec_from_flags("float16", "int4", False, 32)
+        spec_from_flags("float16", "int3", False, 32)  # quantization.py:283-284: int3 asserts sym
     with pytest.raises(NotImplementedError):
         spec_from_flags("float16", "int3", True, 16)
 
