@@ -421,6 +421,71 @@ def prefill_record(args, torch, dev, clocks_fn):
     return rec
 
 
+def reference_gpu_record(torch, dev):
+    """The reference's OWN hand-scheduled kernels (TVM-generated CUDA of mlc_llm/dispatch PrimFuncs, built for sm_100a
+    by oracle/build_ref_cuda.py) on this GPU, beside this library's kernel for the same operator, same protocol:
+    32 distinct weight sets per sweep (>= 300 MB: every byte from HBM), CUDA events, back-to-back launches."""
+    from mlc_llm_b200 import ops
+    from mlc_llm_b200.quant_spec import SPECS
+    from oracle import ref_cuda
+
+    if not ref_cuda.available():
+        return {"unavailable": "oracle/_ref/cuda not built (oracle/build_ref_cuda.py needs /root/reference + the TVM bundled with tilelang)"}
+    man = ref_cuda.manifest()
+    ident = lambda v: v
+    rows = []
+    R = 32
+    h = lambda *s: (torch.randn(*s, device=dev) * 0.05).half()
+    rnd_w = lambda r, n: torch.randint(-2**31, 2**31 - 1, (r, n), dtype=torch.int32, device=dev)
+    rnd_s = lambda g, n: (torch.rand((g, n), device=dev) * 0.01).half()
+    # (kernel, K, N, our spec, epilogue, which operands the reference kernel takes)
+    gemvs = [("gemv_q4f16_0_4096x4096", 4096, 4096, "q4f16_0", "none", False),
+             ("gemv_q4f16_0_4096x11008_silu", 4096, 11008, "q4f16_0", "silu", False),
+             ("gemv_q4f16_asym_4096x4096", 4096, 4096, "q4f16_asym", "none", True)]
+    for name, K, N, fmt, ep, has_min in gemvs:
+        if name not in man:
+            continue
+        spec = SPECS[fmt]
+        k = ref_cuda.RefKernel(name)
+        ws = [(rnd_w(K // 8, N), rnd_s(K // 32, N), rnd_s(K // 32, N) if has_min else None) for _ in range(R)]
+        x, out = h(1, 1, K), torch.zeros((1, 1, N), dtype=torch.float16, device=dev)
+
+        def ref_sweep():
+            for p, sc, mn in ws:
+                k(*([p, sc] + ([mn] if has_min else []) + [x, out]))
+
+        def our_sweep():
+            for p, sc, mn in ws:
+                ops.gemv(p, sc, x, fmt, ep, out=out, pdl=True, zmin=mn)
+
+        t_ref = time_steps(torch, ref_sweep, 5, 3, torch.cuda.synchronize, ident) * 1e3 / R
+        t_our = time_steps(torch, our_sweep, 5, 3, torch.cuda.synchronize, ident) * 1e3 / R
+        nb = spec.gemv_bytes(K, N, ep)
+        rows.append({"op": f"{fmt} GEMV {K}->{N} {ep}", "reference_kernel": name, "grid": man[name]["grid"], "block": man[name]["block"],
+                     "reference_us": round(t_ref, 2), "reference_gbs": round(nb / t_ref / 1e3, 1), "b200q_us": round(t_our, 2),
+                     "b200q_gbs": round(nb / t_our / 1e3, 1), "speedup": round(t_ref / t_our, 2)})
+    if "decode_q4f16_asym_4096x4096" in man and "nt_matmul_f16_4096x4096" in man:
+        K = N = 4096
+        M = 2048
+        kd, km = ref_cuda.RefKernel("decode_q4f16_asym_4096x4096"), ref_cuda.RefKernel("nt_matmul_f16_4096x4096")
+        p, sc, mn = rnd_w(K // 8, N), rnd_s(K // 32, N), rnd_s(K // 32, N)
+        X, Wt = h(1, M, K), torch.zeros((N, K), dtype=torch.float16, device=dev)
+        Y = torch.zeros((1, M, N), dtype=torch.float16, device=dev)
+
+        def ref_prefill():  # the reference's CUDA route: decode to [N, K] in HBM, then the SIMT NT_matmul
+            kd(p, sc, mn, Wt)
+            km(X, Wt, Y)
+
+        t_ref = time_steps(torch, ref_prefill, 5, 3, torch.cuda.synchronize, ident) * 1e3
+        t_our = time_steps(torch, lambda: ops.gemm(p, sc, X[0], "q4f16_asym", out=Y[0], zmin=mn), 10, 3, torch.cuda.synchronize, ident) * 1e3
+        fl = 2.0 * M * K * N
+        rows.append({"op": f"q4f16_asym prefill Linear {M}x{K}->{N} (decode4_fp16 + NT_matmul1_fp16 vs one tcgen05 dequant-GEMM)",
+                     "reference_us": round(t_ref, 1), "reference_tflops": round(fl / t_ref / 1e6, 2), "b200q_us": round(t_our, 1),
+                     "b200q_tflops": round(fl / t_our / 1e6, 1), "speedup": round(t_ref / t_our, 1)})
+    return {"what": "the reference's hand-scheduled PrimFuncs lowered to CUDA by TVM 0.23 and compiled with nvcc for sm_100a "
+                    "(oracle/build_ref_cuda.py); launch geometry is the schedule's own", "rows": rows}
+
+
 def decode_extra(args, torch, dist, dev, rank, world, model, fmt, barrier, max_over_ranks, steps=30, cpu=False):
     """One more decode configuration of BASELINE.json on the ranks of this run (same protocol, fewer steps)."""
     from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack, token_bytes
@@ -632,6 +697,12 @@ def main():
             prefill = prefill_record(args, torch, dev, clocks_between)
         except Exception as e:  # noqa: BLE001
             prefill = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+    reference_gpu = None
+    if full_run and world == 1:
+        try:
+            reference_gpu = reference_gpu_record(torch, dev)
+        except Exception as e:  # noqa: BLE001
+            reference_gpu = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
     extra = []
 
     def guarded(fn, *a, **kw):
@@ -673,6 +744,7 @@ def main():
             "segmented": segmented,
             "per_shape": per_shape,
             "prefill": prefill,
+            "reference_gpu": reference_gpu,
             "extra": extra,
         }
         if args.layers is not None:
