@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 102 /* major*100 + minor */
+#define B200Q_VERSION 103 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -57,7 +57,13 @@ typedef enum {
    * take these (they carry the extra `zmin` tensor). */
   B200Q_Q4F16_ASYM = 4, /* f16: scale f16[G, N] and min f16[G, N] are separate tensors                      */
   B200Q_Q4F32_ASYM = 5, /* f32: `scale` is uint32[G, N] = bf16(scale) | bf16(min) << 16, zmin is NULL        */
-  B200Q_NUM_FMT = 6
+  /* The remaining --quantization-* combinations (symmetric; encode / dequant / take_decode / gemv entry points only;
+   * streaming kernels, not the headline path): */
+  B200Q_Q3F16_U16 = 6, /* int3 in uint16 words: packed uint16[8 * n_groups, N], 5 values per word, group 40
+                          (--quantization-storage-nbit 16, the iOS build; dispatch/llama/main.py:4151-4203, 5815-6363) */
+  B200Q_FP4F16_0 = 7,  /* fp4 = sign + 3-bit exponent code (quantization.py:51-101), uint32 words, group 32, f16   */
+  B200Q_FP4F32_0 = 8,  /* the same with f32 scale / activations                                                   */
+  B200Q_NUM_FMT = 9
 } b200q_fmt;
 
 /* Epilogues fused by FuseDecodeMatmulEwise (mlc_llm/transform/decode_matmul_ewise.py:49-75) and by

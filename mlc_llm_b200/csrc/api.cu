@@ -40,6 +40,13 @@ int dequant_launch(const void* packed, const void* scale, const void* zmin, void
                    cudaStream_t stream);
 int take_decode_launch(const void* packed_rm, const void* scale_rm, const void* zmin_rm, const int32_t* ids, void* out,
                        int n_ids, int V, int K, int fmt, cudaStream_t stream);
+bool fmt_is_variant(int fmt);
+int variant_encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose, cudaStream_t stream);
+int variant_dequant_launch(const void* packed, const void* scale, void* out, int K, int N, int fmt, int transposed, cudaStream_t stream);
+int variant_take_launch(const void* packed_rm, const void* scale_rm, const int32_t* ids, void* out, int n_ids, int V, int K, int fmt,
+                        cudaStream_t stream);
+int variant_gemv_launch(const void* packed, const void* scale, const void* x, const void* ep0, void* out, int K, int N, int fmt,
+                        int epilogue, cudaStream_t stream);
 int encode_asym_launch(const void* W, void* packed, void* scale, void* zmin, int N, int K, int fmt, int transpose,
                        cudaStream_t stream);
 int gemv_asym_launch(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0, void* out, int K,
@@ -135,7 +142,7 @@ long long b200q_gemv_bytes(int fmt, int K, int N, int epilogue) {
   if (fmt < 0 || fmt >= B200Q_NUM_FMT) return B200Q_ERR_UNSUPPORTED;
   const long long sb = fmt_is_f32(fmt) ? 4 : 2;
   const long long ob = (epilogue == B200Q_EP_CAST_F32 || fmt_is_f32(fmt)) ? 4 : 2;
-  long long b = 4LL * n_words(fmt, K) * N + sb * n_groups(fmt, K) * N + sb * K + ob * N;
+  long long b = (long long)fmt_word_bytes(fmt) * n_words(fmt, K) * N + sb * n_groups(fmt, K) * N + sb * K + ob * N;
   if (fmt == B200Q_Q4F16_ASYM) b += sb * n_groups(fmt, K) * N;  // the min tensor
   if (epilogue == B200Q_EP_ADD || epilogue == B200Q_EP_MULTIPLY) b += ob * N;
   if (epilogue == B200Q_EP_BIAS || epilogue == B200Q_EP_BIAS_GELU) b += sb * N;
@@ -157,6 +164,11 @@ int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* x, const v
   for (int i = 0; i < n_ops; ++i)
     if (int e = check_gemv_op(ops[i], fmt, "b200q_gemv")) return e;
   if (int e = check_gemv_alias(ops, n_ops, x, x_mul, K, fmt, "b200q_gemv")) return e;
+  if (fmt_is_variant(fmt)) {  // uint16-storage int3 / fp4: the streaming kernel of variants.cu, one Linear per launch
+    if (n_ops != 1 || x_mul) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemv_multi: fmt %d takes one op and no x_mul", fmt);
+    return variant_gemv_launch(ops[0].packed, ops[0].scale, x, ops[0].ep0, ops[0].out, K, ops[0].N, fmt, ops[0].epilogue,
+                               reinterpret_cast<cudaStream_t>(stream));
+  }
   return gemv_launch(ops, n_ops, x, x_mul, K, fmt, flags, workspace, workspace ? workspace_bytes : 0,
                      reinterpret_cast<cudaStream_t>(stream));
 }
@@ -177,6 +189,7 @@ int b200q_gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt,
 int b200q_gemv_program_build_tp(const b200q_gemv_step* steps, int n_steps, int fmt, const unsigned char* reduce_mask,
                                 int tp_rank, int tp_size, void* host_blob, size_t blob_bytes) {
   if (int e = check_fmt(fmt, "b200q_gemv_program_build")) return e;  // (asymmetric schemes: per-operator launches only)
+  if (fmt_is_variant(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemv_program_build: fmt %d has per-operator kernels only", fmt);
   if (!steps || !host_blob) return set_error(B200Q_ERR_NULL, "b200q_gemv_program_build: NULL steps/blob");
   if (n_steps < 1 || n_steps > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_program_build: n_steps=%d", n_steps);
   const size_t el = fmt_is_f32(fmt) ? 4 : 2;
@@ -231,6 +244,7 @@ int b200q_dequant(const void* packed, const void* scale, void* out, int K, int N
   if (K <= 0 || N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_dequant: K=%d N=%d (N %% 8 == 0 required)", K, N);
   if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(out, 16))
     return set_error(B200Q_ERR_BAD_ALIGN, "b200q_dequant: pointers must be 16-byte aligned");
+  if (fmt_is_variant(fmt)) return variant_dequant_launch(packed, scale, out, K, N, fmt, transposed, reinterpret_cast<cudaStream_t>(stream));
   return dequant_launch(packed, scale, nullptr, out, K, N, fmt, transposed, reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -241,6 +255,7 @@ int b200q_take_decode(const void* packed_rm, const void* scale_rm, const int32_t
   if (K <= 0 || V <= 0 || n_ids < 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode: K=%d V=%d n_ids=%d", K, V, n_ids);
   if (n_ids == 0) return B200Q_OK;
   if (n_ids > 65535) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_take_decode: n_ids=%d > 65535", n_ids);
+  if (fmt_is_variant(fmt)) return variant_take_launch(packed_rm, scale_rm, ids, out, n_ids, V, K, fmt, reinterpret_cast<cudaStream_t>(stream));
   return take_decode_launch(packed_rm, scale_rm, nullptr, ids, out, n_ids, V, K, fmt, reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -248,6 +263,7 @@ int b200q_encode(const void* W, void* packed, void* scale, int N, int K, int fmt
   if (int e = check_fmt(fmt, "b200q_encode")) return e;
   if (!W || !packed || !scale) return set_error(B200Q_ERR_NULL, "b200q_encode: NULL pointer");
   if (N <= 0 || K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_encode: N=%d K=%d", N, K);
+  if (fmt_is_variant(fmt)) return variant_encode_launch(W, packed, scale, N, K, fmt, transpose, reinterpret_cast<cudaStream_t>(stream));
   return encode_launch(W, packed, scale, N, K, fmt, transpose, reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -255,6 +271,7 @@ int b200q_gemm(const void* packed, const void* scale, const void* X, const void*
                const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
                void* stream) {
   if (int e = check_fmt(fmt, "b200q_gemm")) return e;
+  if (fmt_is_variant(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: fmt %d has decode / GEMV kernels only (prefill: b200q_dequant + b200q_nt_matmul)", fmt);
   if (fmt_is_f32(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: f16 formats only (q4f32_0 prefill: dequant + f32 GEMM is out of scope)");
   if (!packed || !scale || !X || !Y) return set_error(B200Q_ERR_NULL, "b200q_gemm: NULL pointer");
   if (M < 0 || K <= 0 || N <= 0 || N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm: M=%d K=%d N=%d", M, K, N);

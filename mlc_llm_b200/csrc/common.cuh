@@ -71,14 +71,15 @@ __host__ __device__ constexpr bool fmt_is_f32_c(int fmt) { return fmt == B200Q_Q
 __host__ __device__ constexpr bool fmt_has_min_c(int fmt) { return fmt == B200Q_Q4F16_ASYM; }
 __host__ __device__ inline int fmt_is_asym(int fmt) { return fmt == B200Q_Q4F16_ASYM || fmt == B200Q_Q4F32_ASYM; }
 
-__host__ __device__ inline int fmt_group(int fmt) { return fmt == B200Q_Q3F16_0 ? 40 : 32; }
-__host__ __device__ inline int fmt_npu(int fmt) {
-  return fmt == B200Q_Q3F16_0 ? 10 : (fmt == B200Q_Q8F16_0 ? 4 : 8);
+__host__ __device__ inline int fmt_group(int fmt) { return (fmt == B200Q_Q3F16_0 || fmt == B200Q_Q3F16_U16) ? 40 : 32; }
+__host__ __device__ inline int fmt_npu(int fmt) {  // values per storage word
+  return fmt == B200Q_Q3F16_0 ? 10 : (fmt == B200Q_Q3F16_U16 ? 5 : (fmt == B200Q_Q8F16_0 ? 4 : 8));
 }
 __host__ __device__ inline int fmt_bits(int fmt) {
-  return fmt == B200Q_Q3F16_0 ? 3 : (fmt == B200Q_Q8F16_0 ? 8 : 4);
+  return (fmt == B200Q_Q3F16_0 || fmt == B200Q_Q3F16_U16) ? 3 : (fmt == B200Q_Q8F16_0 ? 8 : 4);
 }
-__host__ __device__ inline int fmt_is_f32(int fmt) { return fmt == B200Q_Q4F32_0 || fmt == B200Q_Q4F32_ASYM; }
+__host__ __device__ inline int fmt_word_bytes(int fmt) { return fmt == B200Q_Q3F16_U16 ? 2 : 4; }
+__host__ __device__ inline int fmt_is_f32(int fmt) { return fmt == B200Q_Q4F32_0 || fmt == B200Q_Q4F32_ASYM || fmt == B200Q_FP4F32_0; }
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ inline int n_groups(int fmt, int K) { return ceil_div(K, fmt_group(fmt)); }
 __host__ __device__ inline int n_words(int fmt, int K) {

@@ -54,8 +54,9 @@ def lookup(spec, K: int, N: int, epilogue: str = "none", m_is_one: bool = True) 
 
         gemv_op.__name__ = reference_name(spec, K, N, epilogue, True)
         return gemv_op
-    # prefill: dequantize inside the tensor-core GEMM (f16 schemes only)
-    if spec.dtype != "float16" or epilogue not in GEMM_EPILOGUES:
+    # prefill: dequantize inside the tensor-core GEMM (f16 schemes with uint32 integer storage only; the others take
+    # the reference's own route, lookup_decode + a dense NT matmul)
+    if spec.dtype != "float16" or spec.is_variant or epilogue not in GEMM_EPILOGUES:
         return None
 
     def gemm_op(packed, scale, *rest):

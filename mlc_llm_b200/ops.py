@@ -68,8 +68,9 @@ def _ep_id(epilogue) -> int:
 
 
 def _check_weight(spec: QuantSpec, packed: torch.Tensor, scale: torch.Tensor, K: int):
-    if packed.dtype not in (torch.int32, torch.uint32) or packed.dim() != 2:
-        raise ValueError("packed must be a 2-D uint32/int32 tensor [n_words, N]")
+    ok = (torch.int16, torch.uint16) if spec.storage_nbit == 16 else (torch.int32, torch.uint32)
+    if packed.dtype not in ok or packed.dim() != 2:
+        raise ValueError(f"packed must be a 2-D uint{spec.storage_nbit} (or int{spec.storage_nbit} view) tensor [n_words, N]")
     N = packed.shape[1]
     if packed.shape[0] != spec.n_words(K):
         raise ValueError(f"packed has {packed.shape[0]} word rows, {spec.name} with K={K} needs {spec.n_words(K)}")
@@ -237,7 +238,7 @@ def encode(W: torch.Tensor, spec, transpose: bool = True):
     N, K = W.shape
     R, G = spec.n_words(K), spec.n_groups(K)
     pshape, sshape = ((R, N), (G, N)) if transpose else ((N, R), (N, G))
-    packed = torch.empty(pshape, dtype=torch.int32, device=W.device)
+    packed = torch.empty(pshape, dtype=spec.packed_torch_dtype, device=W.device)
     scale = torch.empty(sshape, dtype=spec.scale_torch_dtype, device=W.device)
     L = _lib.lib()
     if not spec.sym:  # te_encode_asym: (packed, scale, min) for f16, (packed, scale_min) for f32

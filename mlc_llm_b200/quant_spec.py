@@ -8,7 +8,8 @@ import dataclasses
 import torch
 
 # ids shared with include/b200q.h
-FMT_IDS = {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5}
+FMT_IDS = {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5,
+           "q3f16_u16": 6, "fp4f16_0": 7, "fp4f32_0": 8}
 EPILOGUES = {
     "none": 0,
     "add": 1,
@@ -58,6 +59,16 @@ class QuantSpec:
         return -(-self.group_size // self.npu) * self.n_groups(K)
 
     @property
+    def packed_torch_dtype(self) -> torch.dtype:
+        """Storage words as torch sees them (torch has no unsigned 16 / 32-bit arithmetic types: same bits)."""
+        return torch.int16 if self.storage_nbit == 16 else torch.int32
+
+    @property
+    def is_variant(self) -> bool:
+        """uint16-storage int3 / fp4: encode, dequantize, take_decode and single-op GEMV only."""
+        return self.storage_nbit != 32 or self.mode == "fp4"
+
+    @property
     def has_min(self) -> bool:
         """A separate group-minimum tensor (the f16 asymmetric scheme; the f32 one packs bf16 scale | bf16 min)."""
         return (not self.sym) and self.dtype == "float16"
@@ -70,7 +81,7 @@ class QuantSpec:
         """Algorithmic HBM bytes of one GEMV."""
         sb = 2 if self.dtype == "float16" else 4
         ob = 4 if (epilogue == "cast_f32" or self.dtype == "float32") else 2
-        b = 4 * self.n_words(K) * N + sb * self.n_groups(K) * N * (2 if self.has_min else 1) + sb * K + ob * N
+        b = (self.storage_nbit // 8) * self.n_words(K) * N + sb * self.n_groups(K) * N * (2 if self.has_min else 1) + sb * K + ob * N
         if epilogue in ("add", "multiply"):
             b += ob * N
         if epilogue in ("bias", "bias_gelu"):
@@ -86,20 +97,22 @@ SPECS = {
     # the reference CLI's default: asymmetric int4 (build.py:19 --quantization-sym off; quantization.py:105-140,183-211)
     "q4f16_asym": QuantSpec("q4f16_asym", "int4", "float16", 32, sym=False),
     "q4f32_asym": QuantSpec("q4f32_asym", "int4", "float32", 32, sym=False),
+    # the remaining flag combinations: int3 in uint16 words (ios/README.md:39), fp4
+    "q3f16_u16": QuantSpec("q3f16_u16", "int3", "float16", 40, storage_nbit=16),
+    "fp4f16_0": QuantSpec("fp4f16_0", "fp4", "float16", 32),
+    "fp4f32_0": QuantSpec("fp4f32_0", "fp4", "float32", 32),
 }
 
 
 def spec_from_flags(dtype: str, mode: str, sym: bool, storage_nbit: int, group_size: int | None = None) -> QuantSpec:
     """The reference's CLI flags -> QuantSpec (sym=False is the reference's default: the asymmetric int4 schemes).
     Raises for the combinations that are not on this path (uint16/uint8 storage, fp4: SURVEY.md 8(f) rank 4)."""
-    if storage_nbit != 32:
-        raise NotImplementedError("only uint32 storage is on this path (SURVEY.md 8f rank 4)")
-    if not mode.startswith("int"):
-        raise NotImplementedError("fp4 is not on this path (SURVEY.md 8f rank 4)")
+    if storage_nbit == 8:
+        raise NotImplementedError("uint8 storage: no kernel of the reference uses it (build.py:22-25 lists it, dispatch/ has none)")
     if not sym and mode != "int4":
         raise NotImplementedError("asymmetric quantization exists for int4 only (quantization.py:283-284 asserts sym for int3 / fp4)")
     for s in SPECS.values():
-        if s.mode == mode and s.dtype == dtype and s.sym == sym:
+        if s.mode == mode and s.dtype == dtype and s.sym == sym and s.storage_nbit == (32 if mode == "fp4" else storage_nbit):
             if group_size is not None and group_size != s.group_size:
                 raise NotImplementedError(f"group size {group_size} (the reference hard-wires {s.group_size})")
             return s

@@ -330,11 +330,77 @@ def gen_asym(tvm, refq):
     np.savez_compressed(os.path.join(GOLDEN, "asym.npz"), **out)
 
 
+def gen_variants(tvm, refq):
+    """uint16-storage int3 and fp4 (quantization.py:51-101, 142-177, 213-270 with storage_nbit=16 / mode="fp4")."""
+    from tvm import te
+
+    out = {}
+    for ci, (name, N, K) in enumerate([("q3f16_u16", 24, 320), ("q3f16_u16", 8, 4096), ("q3f16_u16", 24, 100),
+                                       ("fp4f16_0", 24, 256), ("fp4f32_0", 24, 256), ("fp4f16_0", 8, 4096)]):
+        fmt = qo.VARIANT_FORMATS[name]
+        mode = "fp4" if qo.is_fp4(fmt) else "int3"
+        sdt = "uint16" if fmt.storage_nbit == 16 else "uint32"
+        rng = np.random.default_rng(3000 + ci)
+        W = (rng.standard_normal((N, K), dtype=np.float32) * 0.02).astype(fmt.np_dtype)
+        W[0, : fmt.group] = 0
+        W[1, 0] = fmt.np_dtype(0.5)
+        R, G = fmt.n_words(K), fmt.n_groups(K)
+        res = {"W": W}
+        for tr in (True, False):
+            enc = refq.encoding_func(True, fmt.group, fmt.nbit, mode, fmt.storage_nbit, transpose=tr, dtype=fmt.dtype)
+            Wt = te.placeholder((N, K), fmt.dtype, name="W")
+            pt, st = enc(Wt)
+            f = te.create_prim_func([Wt, pt, st])
+            pshape, sshape = ((R, N), (G, N)) if tr else ((N, R), (N, G))
+            (_, p_, s_), _ = build_run(tvm, f, [W, np.zeros(pshape, sdt), np.zeros(sshape, fmt.np_dtype)])
+            res["packed" + ("" if tr else "_rm")] = p_
+            res["scale" + ("" if tr else "_rm")] = s_
+        if name == "fp4f16_0":
+            # the reference's own fp4 -> f16 decoder (_tir_u32_to_f4_to_f16, quantization.py:88-101) reinterprets a
+            # uint32 expression as float16; TVM rejects the size mismatch, so that PrimFunc cannot be built: only the
+            # encoder is pinned for this scheme (the decode restatement takes the evident intent, the low 16 bits)
+            for k_, v_ in res.items():
+                out[f"{name}_N{N}_K{K}/{k_}"] = v_
+            print(f"variant {name} N={N} K={K}: encode only (reference decoder does not build)")
+            continue
+        for tr in (False, True):
+            dec = refq.decoding_func(True, fmt.group, fmt.nbit, mode, fmt.storage_nbit, K, data_transposed=True,
+                                     transpose_output=tr, dtype=fmt.dtype)
+            D = te.placeholder((R, N), sdt, name="D")
+            S = te.placeholder((G, N), fmt.dtype, name="S")
+            f = te.create_prim_func([D, S, dec(D, S)])
+            (_, _, w), _ = build_run(tvm, f, [res["packed"], res["scale"], np.zeros((N, K) if tr else (K, N), fmt.np_dtype)])
+            res["w_t" if tr else "w"] = w
+        rw = rng.integers(0, 2**fmt.storage_nbit, size=(R, N), dtype=np.uint64).astype(sdt)
+        rs = (rng.random((G, N), dtype=np.float32) * 0.01).astype(fmt.np_dtype)
+        dec = refq.decoding_func(True, fmt.group, fmt.nbit, mode, fmt.storage_nbit, K, data_transposed=True,
+                                 transpose_output=False, dtype=fmt.dtype)
+        D = te.placeholder((R, N), sdt, name="D")
+        S = te.placeholder((G, N), fmt.dtype, name="S")
+        f = te.create_prim_func([D, S, dec(D, S)])
+        (_, _, w), _ = build_run(tvm, f, [rw, rs, np.zeros((K, N), fmt.np_dtype)])
+        res.update(rand_packed=rw, rand_scale=rs, rand_w=w)
+        if K % fmt.group == 0:
+            ids = np.array([3, 0, N - 1, 3, 7], dtype=np.int32)
+            tk = refq.decoding_after_taking_func(True, fmt.group, fmt.nbit, mode, fmt.storage_nbit, K, dtype=fmt.dtype)
+            D = te.placeholder((N, R), sdt, name="D")
+            S = te.placeholder((N, G), fmt.dtype, name="S")
+            I = te.placeholder((len(ids),), "int32", name="I")
+            f = te.create_prim_func([D, S, I, tk(D, S, I)])
+            (_, _, _, emb), _ = build_run(tvm, f, [res["packed_rm"], res["scale_rm"], ids, np.zeros((len(ids), K), fmt.np_dtype)])
+            res.update(take_ids=ids, take_out=emb)
+        for k_, v_ in res.items():
+            out[f"{name}_N{N}_K{K}/{k_}"] = v_
+        print(f"variant {name} N={N} K={K}: ok")
+    np.savez_compressed(os.path.join(GOLDEN, "variants.npz"), **out)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-fused", action="store_true")
     ap.add_argument("--skip-encdec", action="store_true")
     ap.add_argument("--only-asym", action="store_true")
+    ap.add_argument("--only-variants", action="store_true")
     a = ap.parse_args()
     os.makedirs(GOLDEN, exist_ok=True)
     tvm = _load_tvm()
@@ -342,7 +408,11 @@ def main():
     if a.only_asym:
         gen_asym(tvm, refq)
         return
+    if a.only_variants:
+        gen_variants(tvm, refq)
+        return
     gen_asym(tvm, refq)
+    gen_variants(tvm, refq)
     if not a.skip_encdec:
         gen_encode_decode(tvm, refq)
     if not a.skip_fused:

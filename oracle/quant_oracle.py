@@ -74,7 +74,23 @@ ASYM_FORMATS = {
     "q4f16_asym": Fmt("q4f16_asym", 4, 32, "float16", sym=False),
     "q4f32_asym": Fmt("q4f32_asym", 4, 32, "float32", sym=False),
 }
-ALL_FORMATS = {**FORMATS, **ASYM_FORMATS}
+# the remaining --quantization-* combinations: int3 in uint16 words (5 values per word, the iOS
+# build: ios/README.md:39; kernels dispatch/llama/main.py:4151-4203, 5815-6363) and fp4, an exponent-only 4-bit float
+# (quantization.py:51-101), symmetric, uint32 words
+VARIANT_FORMATS = {
+    "q3f16_u16": Fmt("q3f16_u16", 3, 40, "float16", storage_nbit=16),
+    "fp4f16_0": Fmt("fp4f16_0", 4, 32, "float16"),
+    "fp4f32_0": Fmt("fp4f32_0", 4, 32, "float32"),
+}
+ALL_FORMATS = {**FORMATS, **ASYM_FORMATS, **VARIANT_FORMATS}
+
+
+def is_fp4(fmt: "Fmt") -> bool:
+    return fmt.name.startswith("fp4")
+
+
+def storage_dtype(fmt: "Fmt"):
+    return np.uint16 if fmt.storage_nbit == 16 else np.uint32
 
 # epilogue ids shared with include/b200q.h
 EP_NONE, EP_ADD, EP_MULTIPLY, EP_SILU, EP_CAST_F32, EP_BIAS, EP_BIAS_GELU, EP_BIAS_ADD2 = range(8)
@@ -174,6 +190,85 @@ def take_decode_sym(packed_rm: np.ndarray, scale_rm: np.ndarray, ids: np.ndarray
     q = (word >> shift) & np.uint32((1 << fmt.nbit) - 1)
     w = (q.astype(dt) - dt(fmt.maxint)).astype(dt)
     return (w * scale_rm[ids][:, j // fmt.group]).astype(dt)
+
+
+# --------------------------------------------------------------------------------------
+# variant schemes: uint16-storage int3 and fp4  (same te_encode_sym / te_decode_sym, other branches)
+# --------------------------------------------------------------------------------------
+
+
+def f_to_f4(v: np.ndarray, dt) -> np.ndarray:
+    """_tir_f32_to_uint_to_f4 / _tir_f16_to_uint_to_f4 (quantization.py:51-75): sign | 3-bit exponent code.
+    e > bias: min(e - bias + M_h, 7) with M_h the top mantissa bit (round half up on the exponent); e == bias: 1;
+    below: 0.  bias = 120 (f32) / 8 (f16)."""
+    if dt == np.float32:
+        u = np.ascontiguousarray(v, np.float32).view(np.uint32).astype(np.int64)
+        m_h, e, sg, bias = (u >> 22) & 1, (u >> 23) & 255, u >> 31, 120
+    else:
+        u = np.ascontiguousarray(v, np.float16).view(np.uint16).astype(np.int64)
+        m_h, e, sg, bias = (u >> 9) & 1, (u >> 10) & 31, u >> 15, 8
+    e4 = np.where(e > bias, np.minimum(e - bias + m_h, 7), np.where(e == bias, 1, 0))
+    return ((sg << 3) | e4).astype(np.uint32)
+
+
+def f4_to_f(code: np.ndarray, dt) -> np.ndarray:
+    """_tir_u32_to_f4_to_f32 / _f16 (quantization.py:78-101): 0 for exponent code 0, else sign * 2^(code - 7)."""
+    sg, e4 = (code >> 3) & 1, code & 7
+    if dt == np.float32:
+        bits = (((e4 | 120) | (sg << 8)).astype(np.uint32) << np.uint32(23)).view(np.float32)
+    else:
+        bits = (((e4 | 8) | (sg << 5)).astype(np.uint16) << np.uint16(10)).view(np.float16)
+    return np.where(e4 == 0, dt(0), bits).astype(dt)
+
+
+def encode_variant(W: np.ndarray, fmt: Fmt, transpose: bool = True):
+    """te_encode_sym (quantization.py:142-177) for the variant schemes: storage words of fmt.storage_nbit bits;
+    fp4: scale = max(max_abs, 1e-4) (not divided), code = f4(W / scale)."""
+    dt, sdt = fmt.np_dtype, storage_dtype(fmt)
+    N, K = W.shape
+    g, npu, maxint = fmt.group, fmt.npu, fmt.maxint
+    G, R = fmt.n_groups(K), fmt.n_words(K)
+    Wp = np.full((N, G * g), np.finfo(dt).min, dtype=dt)
+    Wp[:, :K] = np.abs(W)
+    mx = np.maximum(Wp.reshape(N, G, g).max(axis=2), dt(1e-4))
+    scale = mx.astype(dt) if is_fp4(fmt) else (mx / dt(maxint)).astype(dt)
+    t = (W / np.repeat(scale, g, axis=1)[:, :K]).astype(dt)
+    if is_fp4(fmt):
+        q = f_to_f4(t, dt)
+    else:
+        q = np.minimum(np.maximum(_round_half_away((t + dt(maxint)).astype(dt)), 0.0), float(2 * maxint)).astype(np.uint32)
+    qp = np.zeros((N, R * npu), dtype=np.uint32)
+    qp[:, :K] = q
+    qp = qp.reshape(N, R, npu)
+    packed = np.zeros((N, R), dtype=np.uint32)
+    for tpos in range(npu):
+        packed |= qp[:, :, tpos] << np.uint32(tpos * fmt.nbit)
+    packed = packed.astype(sdt)
+    return (np.ascontiguousarray(packed.T), np.ascontiguousarray(scale.T)) if transpose else (packed, scale)
+
+
+def decode_variant(packed: np.ndarray, scale: np.ndarray, K: int, fmt: Fmt, transpose_output: bool = False):
+    dt = fmt.np_dtype
+    k = np.arange(K)
+    q = (packed[k // fmt.npu, :].astype(np.uint32) >> ((k % fmt.npu) * fmt.nbit).astype(np.uint32)[:, None]) & np.uint32((1 << fmt.nbit) - 1)
+    v = f4_to_f(q, dt) if is_fp4(fmt) else (q.astype(dt) - dt(fmt.maxint)).astype(dt)
+    w = (v * scale[k // fmt.group, :]).astype(dt)
+    return np.ascontiguousarray(w.T) if transpose_output else w
+
+
+def take_decode_variant(packed_rm, scale_rm, ids, K: int, fmt: Fmt):
+    dt = fmt.np_dtype
+    j = np.arange(K)
+    q = (packed_rm[ids][:, j // fmt.npu].astype(np.uint32) >> ((j % fmt.npu) * fmt.nbit).astype(np.uint32)[None, :]) & np.uint32((1 << fmt.nbit) - 1)
+    v = f4_to_f(q, dt) if is_fp4(fmt) else (q.astype(dt) - dt(fmt.maxint)).astype(dt)
+    return (v * scale_rm[ids][:, j // fmt.group]).astype(dt)
+
+
+def gemv_f64_variant(packed, scale, x, fmt: Fmt, K=None):
+    K = x.size if K is None else K
+    w = decode_variant(packed, scale, K, fmt).astype(np.float64)
+    xv = x.reshape(-1).astype(np.float64)[:K]
+    return xv @ w, np.abs(xv) @ np.abs(w)
 
 
 # --------------------------------------------------------------------------------------
@@ -450,7 +545,7 @@ def tolerance(y64: np.ndarray, abs_sum: np.ndarray, out_f32: bool, group_scaled:
 def gemv_bytes(K: int, N: int, fmt: Fmt, epilogue=EP_NONE) -> int:
     sb = 2 if fmt.dtype == "float16" else 4
     ob = 4 if (epilogue == EP_CAST_F32 or fmt.dtype == "float32") else 2
-    b = 4 * fmt.n_words(K) * N + sb * fmt.n_groups(K) * N + sb * K + ob * N
+    b = (fmt.storage_nbit // 8) * fmt.n_words(K) * N + sb * fmt.n_groups(K) * N + sb * K + ob * N
     if not fmt.sym and fmt.dtype == "float16":
         b += sb * fmt.n_groups(K) * N  # the min tensor
     if epilogue in (EP_ADD, EP_MULTIPLY):

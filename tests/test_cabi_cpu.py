@@ -31,10 +31,11 @@ def test_header_symbols_exported_and_bound():
 
 def test_version_and_layout_helpers_match_oracle():
     L = _lib.lib()
-    assert L.b200q_version() == 102
+    assert L.b200q_version() == 103
     for name, spec in SPECS.items():
         f = qo.ALL_FORMATS[name]
-        assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5}[name]
+        assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5,
+                               "q3f16_u16": 6, "fp4f16_0": 7, "fp4f32_0": 8}[name]
         for K in (32, 40, 100, 2560, 4096, 5120, 11008, 13824, 22016):
             assert L.b200q_n_groups(spec.fmt_id, K) == f.n_groups(K) == spec.n_groups(K)
             assert L.b200q_n_words(spec.fmt_id, K) == f.n_words(K) == spec.n_words(K)
@@ -98,8 +99,11 @@ def test_spec_from_flags():
     assert spec_from_flags("float32", "int4", False, 32).name == "q4f32_asym"
     with pytest.raises(NotImplementedError):
         spec_from_flags("float16", "int3", False, 32)  # quantization.py:283-284: int3 asserts sym
+    assert spec_from_flags("float16", "int3", True, 16).name == "q3f16_u16"  # the iOS build (ios/README.md:39)
+    assert spec_from_flags("float16", "fp4", True, 32).name == "fp4f16_0"
+    assert spec_from_flags("float32", "fp4", True, 32).name == "fp4f32_0"
     with pytest.raises(NotImplementedError):
-        spec_from_flags("float16", "int3", True, 16)
+        spec_from_flags("float16", "int4", True, 8)
 
 
 def test_ops_refuse_cpu_tensors():
