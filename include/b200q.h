@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 103 /* major*100 + minor */
+#define B200Q_VERSION 104 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -131,6 +131,24 @@ B200Q_API size_t b200q_gemv_workspace_bytes(void);
 B200Q_API int b200q_gemv(const void* packed, const void* scale, const void* x, const void* ep0, void* out,
                int K, int N, int fmt, int epilogue, unsigned flags, void* workspace,
                size_t workspace_bytes, void* stream);
+
+/* b200q_gemv for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Same kernel, arithmetic and results as b200q_gemv called with a zero-filled
+ * workspace of b200q_gemv_workspace_bytes() bytes, but the split-K scratch (panel counters + partial sums) is a
+ * static device array inside the library: B200Q_GEMV_STATIC_SCRATCH_BYTES per GPU that loads the library, held until
+ * the process exits.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); the
+ * caller still passes inputs and outputs.
+ * Limits: symmetric formats (q4f16_0, q3f16_0, q4f32_0, q8f16_0); N <= B200Q_GEMV_STATIC_MAX_N; a shape whose split
+ * needs more scratch than the array holds is refused with B200Q_ERR_BAD_SHAPE (never a silent fall-back).
+ * Sharing: every call on a GPU uses the same array, which keeps the last call's contents; the entry point clears
+ * the counters it needs zeroed (a cudaMemsetAsync on `stream`) before the kernel.  Calls that may overlap on the
+ * GPU (two streams, two host threads) RACE on the array: serialize them on one stream, or use b200q_gemv with a
+ * workspace per stream. */
+#define B200Q_GEMV_STATIC_SCRATCH_BYTES (4096u * 4u + 4u * 1024u * 1024u)
+#define B200Q_GEMV_STATIC_MAX_N (4096 * 128)
+B200Q_API int b200q_gemv_static(const void* packed, const void* scale, const void* x, const void* ep0, void* out,
+                      int K, int N, int fmt, int epilogue, unsigned flags, void* stream);
 
 /* Several GEMVs that read the SAME activation vector in ONE launch (q|k|v, gate|up: the reference
  * launches them back to back on the same x, relax_model/llama.py:233-236,147-152).  Tensors stay

@@ -53,6 +53,7 @@ PROTOTYPES = {
     "b200q_gemv_bytes": (c_ll, [c_int, c_int, c_int, c_int]),
     "b200q_gemv_workspace_bytes": (ctypes.c_size_t, []),
     "b200q_gemv": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
+    "b200q_gemv_static": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_uint, c_void_p]),
     "b200q_gemv_multi": (c_int, [ctypes.POINTER(GemvOp), c_int, c_void_p, c_void_p, c_int, c_int, c_uint, c_void_p,
                                  ctypes.c_size_t, c_void_p]),
     "b200q_gemv_program_bytes": (ctypes.c_size_t, [c_int]),

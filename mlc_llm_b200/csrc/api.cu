@@ -29,6 +29,8 @@ int gemv_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* 
                 unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 void gemv_tune(int ctas_per_sm, int stages, int flags);
 size_t gemv_workspace_bytes();
+int gemv_static_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K, int fmt, unsigned flags,
+                       cudaStream_t stream);
 size_t gemv_program_bytes(int n_steps);
 int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void* host_blob, size_t blob_bytes,
                        const unsigned char* reduce_mask, int tp_rank, int tp_size);
@@ -178,6 +180,20 @@ int b200q_gemv(const void* packed, const void* scale, const void* x, const void*
                void* stream) {
   b200q_gemv_op op{packed, scale, ep0, out, N, epilogue};
   return b200q_gemv_multi(&op, 1, x, nullptr, K, fmt, flags, workspace, workspace_bytes, stream);
+}
+
+int b200q_gemv_static(const void* packed, const void* scale, const void* x, const void* ep0, void* out, int K, int N,
+                      int fmt, int epilogue, unsigned flags, void* stream) {
+  if (int e = check_fmt(fmt, "b200q_gemv_static")) return e;
+  if (fmt_is_variant(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemv_static: fmt %d has no split-K kernel (no scratch to replace)", fmt);
+  if (!x) return set_error(B200Q_ERR_NULL, "b200q_gemv_static: NULL x");
+  if (K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_static: K=%d", K);
+  const size_t el = fmt_is_f32(fmt) ? 4 : 2;
+  if (!aligned(x, el)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemv_static: x misaligned");
+  b200q_gemv_op op{packed, scale, ep0, out, N, epilogue};
+  if (int e = check_gemv_op(op, fmt, "b200q_gemv_static")) return e;
+  if (int e = check_gemv_alias(&op, 1, x, nullptr, K, fmt, "b200q_gemv_static")) return e;
+  return gemv_static_launch(&op, 1, x, nullptr, K, fmt, flags, reinterpret_cast<cudaStream_t>(stream));
 }
 
 size_t b200q_gemv_program_bytes(int n_steps) { return n_steps > 0 ? gemv_program_bytes(n_steps) : 0; }

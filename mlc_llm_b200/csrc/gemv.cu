@@ -547,4 +547,58 @@ int gemv_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* 
   }
 }
 
+// ---- b200q_gemv_static: the split-K GEMV for callers that cannot allocate device memory -------------------------
+// The scratch of gemv_launch (panel counters + partial sums, gemv_workspace_bytes() bytes) lives in this file-scope
+// device array instead of a caller-provided buffer.  Every GPU context that loads the library holds the array until
+// the process exits.  All calls share it: two calls that overlap on the GPU (different streams, or two host threads)
+// race on it.  In host code `g_static_ws` is only a stand-in for the symbol, not a device address: the address is
+// looked up once per device with cudaGetSymbolAddress, with that device current.
+constexpr size_t kStaticWsBytes = (size_t)kCounterBytes + (size_t)4 * 1024 * 1024;  // == gemv_workspace_bytes()
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+
+int static_ws_ptr(void** out) {
+  static std::atomic<void*> cache[kMaxDevices];
+  const int dev = current_device();
+  if (dev < 0) return set_error(B200Q_ERR_CUDA, "b200q_gemv_static: no current CUDA device (or device id >= %d)", kMaxDevices);
+  void* ptr = cache[dev].load(std::memory_order_acquire);
+  if (!ptr) {
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_ws);
+    if (e != cudaSuccess) return check_cuda(e, "cudaGetSymbolAddress(static GEMV scratch)");
+    if (!ptr) return set_error(B200Q_ERR_CUDA, "b200q_gemv_static: cudaGetSymbolAddress returned NULL");
+    cache[dev].store(ptr, std::memory_order_release);
+  }
+  *out = ptr;
+  return B200Q_OK;
+}
+
+int gemv_static_launch(const b200q_gemv_op* ops, int n_ops, const void* x, const void* x_mul, int K, int fmt, unsigned flags,
+                       cudaStream_t stream) {
+  // the scratch the split needs, as launch_stream sizes it; beyond the array the call is refused (no silent
+  // fall-back to the unsplit kernel, no allocation)
+  int panels = 0;
+  for (int i = 0; i < n_ops; ++i) panels += ceil_div(ops[i].N, kPanelCols);
+  if (panels > kMaxPanels)
+    return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_static: %d column panels (N = %lld) exceed the static scratch: at most %d panels (N <= %d)",
+                     panels, (long long)panels * kPanelCols, kMaxPanels, kMaxPanels * kPanelCols);
+  const int RB = ceil_div(n_words(fmt, K), kBlockRows);
+  const long long T = (long long)panels * RB;
+  long long G = (long long)sm_count() * ((g_tune_ctas_per_sm == 2) ? 2 : 1);
+  if (G > T) G = T;
+  if (G > 1) {
+    const long long per_cta = T / G;
+    const long long c_max = (RB + per_cta - 1) / per_cta + 1;
+    const size_t need = (size_t)kCounterBytes + (size_t)panels * (size_t)c_max * kPanelCols * sizeof(float);
+    if (need > kStaticWsBytes)
+      return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemv_static: K=%d, %d panels need %zu bytes of scratch, the static array holds %zu",
+                       K, panels, need, (size_t)kStaticWsBytes);
+  }
+  void* ws = nullptr;
+  if (int e = static_ws_ptr(&ws)) return e;
+  // the array keeps the previous call's contents; the panel counters must start at zero (the partial sums are
+  // written before they are read).  A memset node, not an allocation: legal under stream capture.
+  cudaError_t ce = cudaMemsetAsync(ws, 0, kCounterBytes, stream);
+  if (ce != cudaSuccess) return check_cuda(ce, "cudaMemsetAsync(static GEMV scratch)");
+  return gemv_launch(ops, n_ops, x, x_mul, K, fmt, flags, ws, kStaticWsBytes, stream);
+}
+
 }  // namespace b200q

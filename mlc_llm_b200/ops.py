@@ -137,6 +137,31 @@ def gemv(
     return out
 
 
+def gemv_static(packed, scale, x, spec, epilogue="none", ep0=None, out=None, pdl: bool = False) -> torch.Tensor:
+    """b200q_gemv_static: `gemv` with the split-K scratch in the library's static device array - the entry point itself
+    allocates nothing (pass `out` to keep the whole call allocation-free).  Calls that overlap on the GPU race on the
+    shared array; N <= 524288.  No counterpart in the reference."""
+    spec = _spec(spec)
+    ep = _ep_id(epilogue)
+    _need_cuda(packed, scale, x, ep0, out)
+    K = x.shape[-1]
+    if x.numel() != K:
+        raise ValueError("gemv is the batch-1 decode path: x must have exactly K elements")
+    if x.dtype != spec.torch_dtype:
+        raise ValueError(f"x must be {spec.dtype}")
+    N = _check_weight(spec, packed, scale, K)
+    odt = torch.float32 if (ep == EPILOGUES["cast_f32"] or spec.dtype == "float32") else torch.float16
+    if out is None:
+        out = torch.empty((1, 1, N), dtype=odt, device=x.device)
+    elif out.numel() != N or out.dtype != odt:
+        raise ValueError(f"out must be {odt}[{N}]")
+    if ep0 is not None and (ep0.numel() != N or ep0.dtype != spec.torch_dtype):
+        raise ValueError(f"ep0 must be {spec.dtype}[{N}]")
+    _lib.check(_lib.lib().b200q_gemv_static(packed.data_ptr(), scale.data_ptr(), x.data_ptr(), _ptr(ep0), out.data_ptr(),
+                                            K, N, spec.fmt_id, ep, FLAG_PDL if pdl else 0, _stream()))
+    return out
+
+
 def gemv_multi(
     weights: Sequence[tuple],
     x: torch.Tensor,
