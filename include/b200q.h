@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 104 /* major*100 + minor */
+#define B200Q_VERSION 105 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -306,6 +306,22 @@ B200Q_API int b200q_gemm_asym(const void* packed, const void* scale, const void*
 B200Q_API int b200q_gemm(const void* packed, const void* scale, const void* X, const void* ep0,
                const void* ep1, const void* ep2, void* Y, int M, int K, int N, int fmt,
                int epilogue, unsigned flags, void* stream);
+
+/* b200q_gemm / b200q_gemm_asym with a device workspace (b200q_gemm_workspace_bytes() bytes, 16-byte aligned, zero-filled
+ * ONCE by the caller; every launch leaves its flag area zeroed again; not shared by launches that may overlap on
+ * the GPU: one per stream).  With it the CTA-pair kernel may cut the (tile, k) space into equal ranges per pair
+ * ("stream-K") when whole 256 x 256 tiles would leave most pairs idle in the last round (80 tiles on 74 pairs: M =
+ * 2048, N = 2560): pairs that do not finish a tile park their f32 partial tile in the workspace, the tile's
+ * finisher adds the partials in pair order - deterministic, same tolerance as b200q_gemm, not bit-identical to
+ * it.  The schedule is chosen from the shape (a measured cost model in csrc/gemm.cu; B200Q_GEMM_STREAMK=0/1 in the
+ * environment overrides it).  zmin: NULL for the symmetric formats.  workspace NULL, B200Q_FLAG_GEMM_NO_STREAMK,
+ * or a shape that fills its last round of tiles: exactly b200q_gemm. */
+#define B200Q_FLAG_GEMM_NO_STREAMK 16u
+#define B200Q_FLAG_GEMM_STREAMK 32u /* stream-K whenever the workspace allows it, whatever the shape (tests, experiments) */
+B200Q_API size_t b200q_gemm_workspace_bytes(void);
+B200Q_API int b200q_gemm_ws(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0,
+                  const void* ep1, const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue,
+                  unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Dense NT GEMM on an already dequantized weight  T dtype[N, K]  (replaces NT_matmul*,
  * transform/transpose_matmul.py:34-101, dispatch/llama/main.py:3884-3981). f16 only. */

@@ -75,6 +75,8 @@ PROTOTYPES = {
     "b200q_encode_asym": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
     "b200q_gemm_asym": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p]),
     "b200q_gemm": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_uint, c_void_p]),
+    "b200q_gemm_workspace_bytes": (ctypes.c_size_t, []),
+    "b200q_gemm_ws": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_nt_matmul": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
 }
 

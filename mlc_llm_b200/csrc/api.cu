@@ -54,12 +54,14 @@ int encode_asym_launch(const void* W, void* packed, void* scale, void* zmin, int
 int gemv_asym_launch(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0, void* out, int K,
                      int N, int fmt, int epilogue, unsigned flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
-                     const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream);
+                     const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream,
+                     void* workspace, size_t workspace_bytes);
+size_t gemm_workspace_bytes();
 int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
                   cudaStream_t stream);
 int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
                 const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
-                cudaStream_t stream);
+                cudaStream_t stream, void* workspace, size_t workspace_bytes);
 int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,
                      int M, int K, int N, int epilogue, cudaStream_t stream);
 
@@ -283,9 +285,9 @@ int b200q_encode(const void* W, void* packed, void* scale, int N, int K, int fmt
   return encode_launch(W, packed, scale, N, K, fmt, transpose, reinterpret_cast<cudaStream_t>(stream));
 }
 
-int b200q_gemm(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
-               const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
-               void* stream) {
+static int gemm_sym(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
+                    const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
+                    void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_fmt(fmt, "b200q_gemm")) return e;
   if (fmt_is_variant(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: fmt %d has decode / GEMV kernels only (prefill: b200q_dequant + b200q_nt_matmul)", fmt);
   if (fmt_is_f32(fmt)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: f16 formats only (q4f32_0 prefill: dequant + f32 GEMM is out of scope)");
@@ -296,7 +298,13 @@ int b200q_gemm(const void* packed, const void* scale, const void* X, const void*
   if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(X, 16) || !aligned(Y, 16))
     return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm: pointers must be 16-byte aligned");
   return gemm_launch(packed, scale, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags,
-                     reinterpret_cast<cudaStream_t>(stream));
+                     reinterpret_cast<cudaStream_t>(stream), workspace, workspace_bytes);
+}
+
+int b200q_gemm(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
+               const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
+               void* stream) {
+  return gemm_sym(packed, scale, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags, nullptr, 0, stream);
 }
 
 int b200q_gemv_asym(const void* packed, const void* scale, const void* zmin, const void* x, const void* ep0, void* out, int K,
@@ -344,8 +352,9 @@ int b200q_encode_asym(const void* W, void* packed, void* scale, void* zmin, int 
   return encode_asym_launch(W, packed, scale, zmin, N, K, fmt, transpose, reinterpret_cast<cudaStream_t>(stream));
 }
 
-int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
-                    const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags, void* stream) {
+static int gemm_asym(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
+                     const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags, void* workspace,
+                     size_t workspace_bytes, void* stream) {
   if (int e = check_fmt(fmt, "b200q_gemm_asym", true)) return e;
   if (fmt != B200Q_Q4F16_ASYM) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_asym: f16 scheme only (f32 prefill is the reference's miss too)");
   if (!packed || !scale || !X || !Y) return set_error(B200Q_ERR_NULL, "b200q_gemm_asym: NULL pointer");
@@ -355,7 +364,24 @@ int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, con
   if (epilogue < 0 || epilogue >= B200Q_NUM_EP) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_asym: epilogue %d", epilogue);
   if (!aligned(packed, 16) || !aligned(scale, 16) || !aligned(X, 16) || !aligned(Y, 16))
     return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_asym: pointers must be 16-byte aligned");
-  return gemm_asym_launch(packed, scale, zmin, X, ep0, ep1, ep2, Y, M, K, N, epilogue, flags, reinterpret_cast<cudaStream_t>(stream));
+  return gemm_asym_launch(packed, scale, zmin, X, ep0, ep1, ep2, Y, M, K, N, epilogue, flags, reinterpret_cast<cudaStream_t>(stream),
+                          workspace, workspace_bytes);
+}
+
+int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
+                    const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags, void* stream) {
+  return gemm_asym(packed, scale, zmin, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags, nullptr, 0, stream);
+}
+
+size_t b200q_gemm_workspace_bytes(void) { return gemm_workspace_bytes(); }
+
+int b200q_gemm_ws(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
+                  const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags, void* workspace,
+                  size_t workspace_bytes, void* stream) {
+  if (workspace && !aligned(workspace, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_ws: workspace must be 16-byte aligned");
+  if (!workspace) workspace_bytes = 0;
+  if (fmt_is_asym(fmt)) return gemm_asym(packed, scale, zmin, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags, workspace, workspace_bytes, stream);
+  return gemm_sym(packed, scale, X, ep0, ep1, ep2, Y, M, K, N, fmt, epilogue, flags, workspace, workspace_bytes, stream);
 }
 
 int b200q_nt_matmul(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,

@@ -86,6 +86,10 @@ struct GemmParams {
   int epilogue;
   int tiles_m, tiles_n;
   unsigned flags;  // B200Q_FLAG_GEMM_*: tile selection override
+  // stream-K schedule of the pair kernel (see TileSched): 0 = whole tiles dealt round-robin
+  int streamk;
+  unsigned* ws_flags;  // [pair][CTA rank][epilogue warp]: 1 = that warp's rows of the pair's partial tile are in ws_partial
+  float* ws_partial;   // [pair][CTA rank][128 rows][BN] f32
   int debug;  // experiments (B200Q_GEMM_DEBUG): 1 = operands are not loaded / unpacked (protocol intact, data garbage), 2 = epilogue does not store
 };
 
@@ -483,6 +487,80 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 //     there through the pair form of cp.async.bulk.tensor, the peer's dequant / epilogue warps arrive remotely);
 //     "empty" barriers and accumulator-full barriers exist in both CTAs and are signalled by multicast commits.
 // Warp roles per CTA: 0 TMA producer, 1 MMA issue (leader) + TMEM alloc (both), 2-5 epilogue, 6.. dequant.
+// ---- work distribution of the pair kernel ------------------------------------------------------------------------
+// classic: pair p computes the whole tiles p, p + P, p + 2P, ..  With 80 tiles on 74 pairs (M = 2048, N = 2560) the
+// second round is 8 % full and the kernel takes two tile times for 1.08 tile times of work.
+// stream-K: the (tile, k chunk) space - tiles in order, `C` chunks of `chunk` 16-k steps each - is cut into P equal
+// ranges.  A range is: the tail of a tile (chunks [c0, C), c0 > 0), whole tiles, the head of a tile ([0, c1), c1 < C).
+// The head's owner finishes that tile: the pairs behind it write their f32 partial tile (at most ONE per pair: its
+// first segment) into the workspace slot [pair][rank] and raise a flag per epilogue warp; the finisher adds the slots
+// in pair order (deterministic) and applies the epilogue.  A writer never waits, so there is no deadlock whatever the
+// residency; a finisher processes its head FIRST (right after its own tail), so the partials it waits for - the
+// tails the following pairs start with - are on their way, and its fix-up overlaps the whole tiles that follow.
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* q) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(q) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned* q, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(q), "r"(v) : "memory");
+}
+struct Seg {
+  int tile, ks0, ks1;  // 16-k steps [ks0, ks1) of the tile
+  int kind;            // 0 whole tile, 1 partial writer, 2 finisher
+};
+struct TileSched {
+  int streamk, pair, n_pairs, n_ksteps, chunk, C;
+  long long W;
+  int n_seg, first_tile, a_off, b_off;
+  bool has_tail, has_head;
+  __device__ void init(int streamk_, int pair_, int n_pairs_, int n_tiles, int n_ksteps_, int chunk_) {
+    streamk = streamk_; pair = pair_; n_pairs = n_pairs_; n_ksteps = n_ksteps_; chunk = chunk_;
+    C = (n_ksteps + chunk - 1) / chunk;
+    W = (long long)n_tiles * C;
+    has_tail = has_head = false;
+    first_tile = a_off = b_off = 0;
+    if (!streamk) {
+      n_seg = pair < n_tiles ? (n_tiles - pair + n_pairs - 1) / n_pairs : 0;
+      return;
+    }
+    const long long a = W * pair / n_pairs, b = W * (pair + 1) / n_pairs;
+    if (a == b) { n_seg = 0; return; }
+    first_tile = (int)(a / C);
+    a_off = (int)(a - (long long)first_tile * C);
+    const int last_tile = (int)((b - 1) / C);
+    b_off = (int)(b - (long long)last_tile * C);
+    n_seg = last_tile - first_tile + 1;
+    has_tail = a_off > 0;
+    has_head = b_off < C && (n_seg > 1 || !has_tail);
+  }
+  __device__ long long range_begin(int q) const { return W * q / n_pairs; }
+  // i-th segment in PROCESSING order: the tail, the head, then the whole tiles
+  __device__ Seg get(int i) const {
+    Seg sg;
+    if (!streamk) {
+      sg.tile = pair + i * n_pairs; sg.ks0 = 0; sg.ks1 = n_ksteps; sg.kind = 0;
+      return sg;
+    }
+    int j = i;
+    if (has_tail) { if (has_head && i >= 1) j = (i == 1) ? n_seg - 1 : i - 1; }
+    else if (has_head) j = (i == 0) ? n_seg - 1 : i - 1;
+    const int c0 = (j == 0) ? a_off : 0, c1 = (j == n_seg - 1) ? b_off : C;
+    sg.tile = first_tile + j;
+    sg.ks0 = c0 * chunk;
+    sg.ks1 = min(c1 * chunk, n_ksteps);
+    sg.kind = (c0 > 0) ? 1 : (c1 < C ? 2 : 0);
+    return sg;
+  }
+  // pairs behind this one that hold a partial of `tile` (the finisher's contributors): (pair, end)
+  __device__ int contributors_end(int tile) const {
+    int q = pair + 1;
+    while (q < n_pairs && range_begin(q) < (long long)(tile + 1) * C) ++q;
+    return q;
+  }
+};
+constexpr int kWsFlagBytes = 16384;  // flags of up to 512 pairs
+
 template <int MODE, int BN>
 struct Pair {
   using B = BCfg<MODE>;
@@ -510,6 +588,8 @@ struct Pair {
   static constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 4;
   static constexpr int kBytes = kBarOff + kNumBars * 8 + 16;
   static constexpr int kTmemCols = 2 * BN;              // two accumulators: 512 or 256 columns
+  // stream-K cuts a tile's k range where an X stage (4 steps of 16 k) and a weight stage (kKSteps) both begin
+  static constexpr int kChunk = (B::kKSteps % 4 == 0) ? B::kKSteps : 4 * B::kKSteps;
 };
 
 template <int MODE, int BN>
@@ -534,8 +614,8 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
   const int tiles_n = (p.N + BN - 1) / BN;
   const int n_tiles = tiles_m * tiles_n;
   const int n_ksteps = (p.K + 15) >> 4;
-  const int n_a_stages = (n_ksteps + 3) >> 2;
-  const int n_b_stages = (n_ksteps + B::kKSteps - 1) / B::kKSteps;
+  TileSched sched;
+  sched.init(p.streamk, pair, n_pairs, n_tiles, n_ksteps, C::kChunk);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tm_a);
@@ -567,9 +647,11 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
     // ================= TMA producer: this CTA's 128 rows of X (and, dense mode, its BN/2 rows of T) ==============
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
-    for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+    for (int si = 0; si < sched.n_seg; ++si) {
+      const Seg sg = sched.get(si);
+      const int tile = sg.tile;
       const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tile / tiles_m) * BN + (int)rank * C::kHalfN;
-      for (int i = 0; i < n_a_stages; ++i) {
+      for (int i = sg.ks0 >> 2; i < (sg.ks1 + 3) >> 2; ++i) {
         mbar_wait(a_empty + 8 * sa, pa ^ 1);
         if (elect_one()) {
           if (rank == 0) mbar_expect_tx(a_full + 8 * sa, 2 * kAStageBytes);
@@ -599,13 +681,14 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
       if (elect_one()) {  // (the whole loop in one lane, see the single-CTA kernel)
         int sa = 0, sb = 0, it = 0;
         uint32_t pa = 0, pb = 0;
-        for (int tile = pair; tile < n_tiles; tile += n_pairs, ++it) {
+        for (; it < sched.n_seg; ++it) {
+          const Seg sg = sched.get(it);
           const int acc = it & 1;
           mbar_wait(t_empty + 8 * acc, ((it >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t d = tmem_base + acc * BN;
           int ka = 0, kb = 0;
-          for (int ks = 0; ks < n_ksteps; ++ks) {
+          for (int ks = sg.ks0; ks < sg.ks1; ++ks) {
             if (ka == 0) mbar_wait(a_full + 8 * sa, pa);
             if (kb == 0) mbar_wait(b_full + 8 * sb, pb);
             if (ka == 0 || kb == 0) tc_fence_after();
@@ -613,9 +696,9 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
             const uint32_t b_addr = b_ring + sb * C::kBStage + kb * kBStep;
             const uint64_t da = da_hi | (uint64_t)(da_lo0 | ((a_addr & 0x3FFFFu) >> 4));
             const uint64_t db = db_hi | (uint64_t)(db_lo0 | ((b_addr & 0x3FFFFu) >> 4));
-            const bool last = (ks == n_ksteps - 1);
+            const bool last = (ks == sg.ks1 - 1);
             const bool rel_a = (ka == 3) || last, rel_b = (kb == B::kKSteps - 1) || last;
-            umma_f16_pair(d, da, db, idesc, ks > 0 ? 1u : 0u);
+            umma_f16_pair(d, da, db, idesc, ks > sg.ks0 ? 1u : 0u);
             if (rel_a) umma_commit_pair(a_empty + 8 * sa);
             if (rel_b) umma_commit_pair(b_empty + 8 * sb);
             if (last) umma_commit_pair(t_full + 8 * acc);
@@ -629,19 +712,105 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
   } else if (warp < kFirstDqWarp) {
     // ================= epilogue: this CTA's 128 rows of the pair's tile ============================================
     const int quarter = warp & 3;
-    int it = 0;
-    for (int tile = pair; tile < n_tiles; tile += n_pairs, ++it) {
+    const int row_local = quarter * 32 + lane;
+    // workspace slot / flags of (pair q, this rank): the slot is [BN / 4 column quads][128 rows] float4, so that a warp
+    // (32 consecutive rows) moves 512 contiguous bytes per instruction
+    auto slot_of = [&](int q) {
+      return reinterpret_cast<uint4*>(p.ws_partial + (size_t)(q * 2 + (int)rank) * kBM * BN) + row_local;
+    };
+    auto flag_of = [&](int q) { return p.ws_flags + (q * 2 + (int)rank) * 4 + quarter; };
+    auto wait_flag = [&](int q) {
+      if (lane == 0) {
+        unsigned spins = 0;
+        while (ld_acquire_u32(flag_of(q)) == 0u) {
+          __nanosleep(64);
+          if (++spins == (1u << 27)) asm volatile("trap;");  // ~10 s: a writer never waits, this cannot happen
+        }
+      }
+      __syncwarp();
+    };
+    for (int it = 0; it < sched.n_seg; ++it) {
+      const Seg sg = sched.get(it);
+      const int tile = sg.tile;
       const int acc = it & 1;
       const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tile / tiles_m) * BN;
-      mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
-      tc_fence_after();
-      const int m = m0 + quarter * 32 + lane;
+      const int m = m0 + row_local;
+      const uint32_t t_acc = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
+      if (sg.kind == 1) {
+        // partial tile of a pair that does not finish it: f32 accumulators -> this pair's slot, then the flag
+        mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
+        tc_fence_after();
+        uint4* dst = slot_of(pair);
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c, v);
-        tmem_ld_wait();
-        if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_acc + c, v);
+          tmem_ld_wait();
+          if (!(p.debug & 4)) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              __stcg(dst + (size_t)(c / 4 + j) * kBM, make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+          }
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) st_release_u32(flag_of(pair), 1u);
+      } else if (sg.kind == 2) {
+        // finisher: the pairs behind this one hold the rest of the tile's k range.  Their partials are usually there
+        // long before this pair's own MMAs are done: the flags are awaited and the first columns fetched meanwhile,
+        // and the partial of the next 32 columns is in flight while the current ones are finished.
+        const int q_end = sched.contributors_end(tile);
+        wait_flag(pair + 1);
+        const uint4* src1 = slot_of(pair + 1);
+        uint4 nx[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) nx[j] = __ldcg(src1 + (size_t)j * kBM);
+        for (int q = pair + 2; q < q_end; ++q) wait_flag(q);
+        mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_acc + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(nx[j].x));
+            v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(nx[j].y));
+            v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(nx[j].z));
+            v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(nx[j].w));
+          }
+          if (c + 32 < BN && !(p.debug & 8)) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) nx[j] = __ldcg(src1 + (size_t)((c + 32) / 4 + j) * kBM);
+          }
+          for (int q = pair + 2; q < q_end; ++q) {  // (a tile cut over more than two pairs) added in pair order
+            const uint4* src = slot_of(q);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint4 pv = __ldcg(src + (size_t)(c / 4 + j) * kBM);
+              v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(pv.x));
+              v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(pv.y));
+              v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(pv.z));
+              v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(pv.w));
+            }
+          }
+          if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+        }
+        // the slots have been read: lower the flags for the next launch
+        __syncwarp();
+        if (lane == 0)
+          for (int q = pair + 1; q < q_end; ++q) *flag_of(q) = 0u;
+      } else {
+        mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_acc + c, v);
+          tmem_ld_wait();
+          if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -686,22 +855,31 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
           }
         }
       };
-      // c = running number of B stages of this CTA over all its tiles; this group takes those with c % groups == grp
-      long long c0 = 0;  // stages before the current tile
-      // first own stage: find it, load it
+      // c = running number of B stages of this CTA over all its segments; this group takes those with c % groups == grp
+      long long c0 = 0;  // stages before the current segment
       auto n0_of = [&](int tile) { return (tile / tiles_m) * BN + (int)rank * C::kHalfN; };
-      int tile = pair;
-      int i = (int)((grp - c0 % C::kDqGroups + C::kDqGroups) % C::kDqGroups);  // first own stage index inside the tile
-      auto settle = [&]() {  // move (tile, i) to the next tile while i runs past the tile's stages
-        while (tile < n_tiles && i >= n_b_stages) {
-          i -= n_b_stages;
-          c0 += n_b_stages;
-          tile += n_pairs;
+      int si = 0, seg_tile = 0, bs0 = 0, nb = 0;  // current segment: tile, first weight stage of its k range, stages
+      auto open = [&]() {
+        if (si < sched.n_seg) {
+          const Seg sg = sched.get(si);
+          seg_tile = sg.tile;
+          bs0 = sg.ks0 / B::kKSteps;
+          nb = (sg.ks1 + B::kKSteps - 1) / B::kKSteps - bs0;
+        }
+      };
+      open();
+      int i = grp;  // first own stage, counted from the segment's first
+      auto settle = [&]() {  // move (segment, i) on while i runs past the segment's stages
+        while (si < sched.n_seg && i >= nb) {
+          i -= nb;
+          c0 += nb;
+          ++si;
+          open();
         }
       };
       settle();
-      if (tile < n_tiles) load_stage(n0_of(tile), i);
-      while (tile < n_tiles) {
+      if (si < sched.n_seg) load_stage(n0_of(seg_tile), bs0 + i);
+      while (si < sched.n_seg) {
         const long long c = c0 + i;
         const int sb = (int)(c % C::kBStages);
         const uint32_t pb = (uint32_t)((c / C::kBStages) & 1);
@@ -715,10 +893,10 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
 #pragma unroll
           for (int j = 0; j < 4; ++j) mc[t][j] = fmt_has_min_c(MODE) ? mn[t][j] : 0u;
         }
-        // this group's next stage (possibly in the next tile): its loads are in flight during this stage's unpack
+        // this group's next stage (possibly in the next segment): its loads are in flight during this stage's unpack
         i += C::kDqGroups;
         settle();
-        if (tile < n_tiles) load_stage(n0_of(tile), i);
+        if (si < sched.n_seg) load_stage(n0_of(seg_tile), bs0 + i);
         mbar_wait(b_empty + 8 * sb, pb ^ 1);
         const uint32_t stage = b_ring + sb * C::kBStage;
 #pragma unroll
@@ -760,11 +938,47 @@ int gemm_pair_mode() {
   return mode;
 }
 
+// B200Q_GEMM_STREAMK = 0 (never) | 1 (whenever a workspace is given); default: when whole tiles fill the pairs badly
+int gemm_streamk_mode() {
+  static const int mode = [] {
+    const char* e = getenv("B200Q_GEMM_STREAMK");
+    return e ? atoi(e) : -1;
+  }();
+  return mode;
+}
+
 template <int MODE, int BN>
-int launch_gemm_pair(GemmParams& p, int n_pairs, cudaStream_t stream) {
+int launch_gemm_pair(GemmParams& p, int n_pairs, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   using C = Pair<MODE, BN>;
   const int n_tiles = ceil_div(p.M, 256) * ceil_div(p.N, BN);
-  if (n_pairs > n_tiles) n_pairs = n_tiles;
+  // stream-K when the caller gave a workspace and whole tiles would leave pairs idle in the last round
+  p.streamk = 0;
+  {
+    const int n_ksteps = ceil_div(p.K, 16);
+    const long long W = (long long)n_tiles * ceil_div(n_ksteps, C::kChunk);
+    // Measured on B200 (q4f16_0, M = 2048, scripts/gemm_sk_sweep.py): whole tiles take 12 us + 21.5 us x (K / 2560) per
+    // round of tiles; stream-K takes ~10 us more than the same with the FRACTIONAL number of rounds x = tiles / pairs
+    // (two accumulator hand-offs more per pair, the partial tiles' trip through L2, the finisher's longer epilogue),
+    // and much more when a tile is cut over more than two or three pairs (x < 0.45).  It is taken when the idle part
+    // of the last round is worth more than that.
+    const double x = (double)n_tiles / n_pairs;
+    const double idle_us = ((double)ceil_div(n_tiles, n_pairs) - x) * 21.5 * ((double)p.K / 2560.0);
+    const int pairs_sk = (int)(W < n_pairs ? W : n_pairs);
+    const size_t need = (size_t)kWsFlagBytes + (size_t)pairs_sk * 2 * kBM * BN * sizeof(float);
+    const int mode = gemm_streamk_mode();
+    const bool want = (mode == 1) || (p.flags & B200Q_FLAG_GEMM_STREAMK) || (mode != 0 && BN == 256 && x >= 0.45 && idle_us > 12.0);
+    if (want && !(p.flags & B200Q_FLAG_GEMM_NO_STREAMK) && workspace && workspace_bytes >= need && pairs_sk * 2 * 4 * 4 <= kWsFlagBytes) {
+      p.streamk = 1;
+      p.ws_flags = reinterpret_cast<unsigned*>(workspace);
+      p.ws_partial = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + kWsFlagBytes);
+      n_pairs = pairs_sk;
+    }
+  }
+  if (!p.streamk && n_pairs > n_tiles) n_pairs = n_tiles;
+  {
+    static const int dbg = getenv("B200Q_GEMM_DEBUG") ? atoi(getenv("B200Q_GEMM_DEBUG")) : 0;
+    p.debug = dbg;  // experiments: 4 = partial tiles are not stored, 8 = not loaded (results wrong, protocol intact)
+  }
   const size_t smem = (size_t)C::kBytes + 1024;
   auto kern = gemm_tc2_kernel<MODE, BN>;
   static std::atomic<bool> attr_set[64];
@@ -809,13 +1023,13 @@ int pick_pair_bn(int M, int N, int n_pairs, unsigned flags = 0) {
 }
 
 template <int MODE>
-int launch_gemm(GemmParams& p, cudaStream_t stream) {
+int launch_gemm(GemmParams& p, cudaStream_t stream, void* workspace = nullptr, size_t workspace_bytes = 0) {
   using S = Smem<MODE>;
   {
     const int n_pairs = device_sm_count() / 2;
     const int bn = pick_pair_bn(p.M, p.N, n_pairs, p.flags);
-    if (bn == 256) return launch_gemm_pair<MODE, 256>(p, n_pairs, stream);
-    if (bn == 128) return launch_gemm_pair<MODE, 128>(p, n_pairs, stream);
+    if (bn == 256) return launch_gemm_pair<MODE, 256>(p, n_pairs, workspace, workspace_bytes, stream);
+    if (bn == 128) return launch_gemm_pair<MODE, 128>(p, n_pairs, workspace, workspace_bytes, stream);
   }
   p.tiles_m = ceil_div(p.M, kBM);
   p.tiles_n = ceil_div(p.N, kBN);
@@ -855,9 +1069,13 @@ int check_epilogue_operands(int epilogue, const void* ep0, const void* ep1, cons
 
 }  // namespace
 
+size_t gemm_workspace_bytes() {  // flags + one 256 x 256 f32 partial tile per CTA pair
+  return (size_t)kWsFlagBytes + (size_t)(device_sm_count() / 2) * 2 * kBM * 256 * sizeof(float);
+}
+
 int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
                 const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
-                cudaStream_t stream) {
+                cudaStream_t stream, void* workspace, size_t workspace_bytes) {
   if (K % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm: K=%d must be a multiple of 8 (16-byte rows of X)", K);
   if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_gemm")) return e;
   GemmParams p{};
@@ -873,15 +1091,16 @@ int gemm_launch(const void* packed, const void* scale, const void* X, const void
   p.flags = flags;
   if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
   switch (fmt) {
-    case B200Q_Q4F16_0: return launch_gemm<B200Q_Q4F16_0>(p, stream);
-    case B200Q_Q3F16_0: return launch_gemm<B200Q_Q3F16_0>(p, stream);
-    case B200Q_Q8F16_0: return launch_gemm<B200Q_Q8F16_0>(p, stream);
+    case B200Q_Q4F16_0: return launch_gemm<B200Q_Q4F16_0>(p, stream, workspace, workspace_bytes);
+    case B200Q_Q3F16_0: return launch_gemm<B200Q_Q3F16_0>(p, stream, workspace, workspace_bytes);
+    case B200Q_Q8F16_0: return launch_gemm<B200Q_Q8F16_0>(p, stream, workspace, workspace_bytes);
     default: return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm: fmt %d", fmt);
   }
 }
 
 int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
-                     const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream) {
+                     const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream,
+                     void* workspace, size_t workspace_bytes) {
   if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_gemm_asym")) return e;
   GemmParams p{};
   p.packed = reinterpret_cast<const uint32_t*>(packed);
@@ -896,7 +1115,7 @@ int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, co
   p.epilogue = epilogue;
   p.flags = flags;
   if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
-  return launch_gemm<B200Q_Q4F16_ASYM>(p, stream);
+  return launch_gemm<B200Q_Q4F16_ASYM>(p, stream, workspace, workspace_bytes);
 }
 
 int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y, int M,

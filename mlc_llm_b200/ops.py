@@ -281,10 +281,32 @@ def encode(W: torch.Tensor, spec, transpose: bool = True):
 GEMM_TILES = {None: 0, "single": 2, "pair128": 4, "pair256": 8}  # B200Q_FLAG_GEMM_*
 
 
+_GEMM_WORKSPACES: dict = {}
+FLAG_GEMM_NO_STREAMK = 16
+FLAG_GEMM_STREAMK = 32
+
+
+def gemm_workspace(device=None) -> torch.Tensor:
+    """The prefill GEMM's stream-K scratch of (device, current stream): allocated and zero-filled once, left clean by
+    every launch (include/b200q.h, b200q_gemm_ws).  One per stream: overlapping launches must not share it."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), _stream())
+    ws = _GEMM_WORKSPACES.get(key)
+    if ws is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("allocate the b200q GEMM workspace before graph capture: call ops.gemm_workspace() first")
+        with torch.cuda.device(dev):
+            ws = torch.zeros(int(_lib.lib().b200q_gemm_workspace_bytes()), dtype=torch.uint8, device=dev)
+        _GEMM_WORKSPACES[key] = ws
+    return ws
+
+
 def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, pdl: bool = False, tile=None,
-         zmin=None):
+         zmin=None, ws=None, streamk: bool = True):
     """fused_decode*_NT_matmul* / decode + NT_matmul: Y[m, n] = sum_k X[m, k] * w[k, n] (+ epilogue)
-    on the tcgen05 tensor cores.  X dtype[..., M, K] -> Y dtype[..., M, N]."""
+    on the tcgen05 tensor cores.  X dtype[..., M, K] -> Y dtype[..., M, N].
+    ws: stream-K workspace (None: the stream's gemm_workspace(); False: b200q_gemm without one); streamk=False keeps
+    the whole-tile schedule even with a workspace, streamk="force" cuts the k range whatever the shape."""
     spec = _spec(spec)
     ep = _ep_id(epilogue)
     _need_cuda(packed, scale, X, ep0, ep1, ep2, out)
@@ -302,12 +324,19 @@ def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, 
     L = _lib.lib()
     _need_cuda(zmin)
     _check_min(spec, scale, zmin)
+    flags = (FLAG_PDL if pdl else 0) | GEMM_TILES[tile]
+    flags |= FLAG_GEMM_STREAMK if streamk == "force" else (0 if streamk else FLAG_GEMM_NO_STREAMK)
+    if ws is not False:
+        w = gemm_workspace(X.device) if ws is None else ws
+        _lib.check(L.b200q_gemm_ws(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
+                                   out.data_ptr(), M, K, N, spec.fmt_id, ep, flags, w.data_ptr(), w.numel() * w.element_size(), _stream()))
+        return out
     if not spec.sym:
         _lib.check(L.b200q_gemm_asym(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
-                                     out.data_ptr(), M, K, N, spec.fmt_id, ep, (FLAG_PDL if pdl else 0) | GEMM_TILES[tile], _stream()))
+                                     out.data_ptr(), M, K, N, spec.fmt_id, ep, flags, _stream()))
         return out
     _lib.check(L.b200q_gemm(packed.data_ptr(), scale.data_ptr(), X.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2),
-                            out.data_ptr(), M, K, N, spec.fmt_id, ep, (FLAG_PDL if pdl else 0) | GEMM_TILES[tile], _stream()))
+                            out.data_ptr(), M, K, N, spec.fmt_id, ep, flags, _stream()))
     return out
 
 

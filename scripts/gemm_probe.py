@@ -26,10 +26,13 @@ for fmt in ("q3f16_0", "q4f16_0", "q8f16_0"):
         Y = torch.empty(M, N, dtype=torch.float16, device=dev)
         fl = 2.0 * M * K * N
         res = []
-        for tile in ("single", "pair128", "pair256", None):
+        for tile in ("single", "pair128", "pair256", "whole", None):
             try:
-                ms = t(lambda: ops.gemm(p, sc, X, fmt, out=Y, tile=tile))
-                res.append(f"{tile or 'auto'} {fl / ms / 1e9:7.1f}")
+                if tile == "whole":  # the pair kernel's whole-tile schedule (no stream-K)
+                    ms = t(lambda: ops.gemm(p, sc, X, fmt, out=Y, ws=False))
+                else:
+                    ms = t(lambda: ops.gemm(p, sc, X, fmt, out=Y, tile=tile, ws=(None if tile is None else False)))
+                res.append(f"{tile or 'auto(stream-K)'} {fl / ms / 1e9:7.1f}")
             except Exception as e:
                 res.append(f"{tile} ERR {str(e)[:60]}")
         Wt = ops.dequantize(p, sc, K, fmt, True)

@@ -142,8 +142,11 @@ def test_two_kernel_prefill_equals_fused():
     p, s, xd = dev(packed), dev(scale), dev(X)
     T = ops.dequantize(p, s, K, name, transpose_output=True)
     y2 = host(ops.nt_matmul(xd, T))
-    y1 = host(ops.gemm(p, s, xd, name))
-    assert beq(y1, y2)  # same weights, same tile shape, same k order: identical f32 sums
+    y1 = host(ops.gemm(p, s, xd, name, streamk=False))
+    assert beq(y1, y2)  # same weights, same tile shape, same k order (whole-tile schedule): identical f32 sums
+    y3 = host(ops.gemm(p, s, xd, name, streamk="force"))  # stream-K cuts the k range of a tile: f32 rounding of the partial sums only
+    d = np.abs(y3.astype(np.float64) - y2.astype(np.float64))
+    assert (d <= 2.0 ** -9 * np.abs(y2.astype(np.float64)) + 2.0 ** -14).all()
 
 
 def test_gemm_dispatch_lookup_and_errors():
@@ -183,3 +186,52 @@ def test_gemm_every_tile_kernel(name, tile):
         assert beq(Y, qo.apply_epilogue(Y0, qo.EP_BIAS, np.broadcast_to(bias, (M, N)))), (tile, M, K, N)
         rows = np.random.default_rng(0).choice(M, min(M, 48), replace=False)
         _check(Y0[rows], packed, scale, X[rows], fmt, f"{name} {tile} {M}x{K}x{N}")
+
+
+@pytest.mark.parametrize("name", F16 + ["q4f16_asym"])
+@pytest.mark.parametrize("M,K,N", [(2048, 2560, 2560), (2048, 10240, 2560), (300, 640, 1000), (512, 1280, 256), (256, 320, 264),
+                                   (1030, 2560, 520)])
+def test_gemm_streamk_schedule(name, M, K, N):
+    """b200q_gemm_ws: the stream-K schedule of the CTA-pair kernel (a tile's k range cut over several pairs, f32
+    partial tiles parked in the workspace, the finisher adds them in pair order) against the oracle, against the
+    whole-tile schedule, and launch after launch on the same workspace (flags lowered by the finisher)."""
+    from mlc_llm_b200.quant_spec import SPECS
+    spec = SPECS[name]
+    if spec.nbit == 3 and K % 40:
+        K = K // 40 * 40
+    rng = np.random.default_rng(M + K + N)
+    if spec.sym:
+        fmt = qo.FORMATS[name]
+        packed, scale = rand_weight(fmt, K, N, seed=M + N + 1)
+        zmin = None
+    else:
+        packed = rng.integers(0, 2**32, size=(spec.n_words(K), N), dtype=np.uint64).astype(np.uint32)
+        scale = (rng.random((spec.n_groups(K), N), dtype=np.float32) * 0.01).astype(np.float16)
+        zmin = (-(rng.random((spec.n_groups(K), N), dtype=np.float32)) * 0.07).astype(np.float16)
+    X = (rng.standard_normal((M, K)) * 0.5).astype(np.float16)
+    p, s, x = dev(packed), dev(scale), dev(X)
+    z = dev(zmin) if zmin is not None else None
+    ws = torch.zeros(int(ops._lib.lib().b200q_gemm_workspace_bytes()), dtype=torch.uint8, device="cuda")
+    whole = host(ops.gemm(p, s, x, name, zmin=z, ws=ws, streamk=False, tile="pair256"))
+    assert beq(whole, host(ops.gemm(p, s, x, name, zmin=z, ws=False, tile="pair256")))  # NO_STREAMK == no workspace
+    outs = [host(ops.gemm(p, s, x, name, zmin=z, ws=ws, tile="pair256", streamk="force")) for _ in range(3)]
+    torch.cuda.synchronize()
+    assert int(ws[:16384].max()) == 0, "the finisher lowers every flag it consumed"
+    assert beq(outs[0], outs[1]) and beq(outs[0], outs[2]), "deterministic, launch after launch"
+    # both schedules within the oracle's tolerance of the f64 result; they differ from one another by f32 rounding only
+    rows = rng.choice(M, min(M, 40), replace=False)
+    if spec.sym:
+        _check(outs[0][rows], packed, scale, X[rows], qo.FORMATS[name], f"stream-K {name} {M}x{K}x{N}")
+    else:
+        w = qo.decode_asym(packed, scale, zmin, K, qo.ASYM_FORMATS[name]).astype(np.float64)
+        y64 = X[rows].astype(np.float64) @ w
+        ab = np.abs(X[rows].astype(np.float64)) @ np.abs(w)
+        assert (np.abs(outs[0][rows].astype(np.float64) - y64) <= qo.tolerance(y64, ab, False)).all()
+    if spec.sym:
+        y64, ab = qo.gemm_f64(packed, scale, X[rows], qo.FORMATS[name])
+    d = np.abs(outs[0][rows].astype(np.float64) - whole[rows].astype(np.float64))
+    assert (d <= 2 * qo.tolerance(y64, ab, False)).all(), float(d.max())
+    # epilogue through the finisher
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float16)
+    yb = host(ops.gemm(p, s, x, name, "bias", dev(bias), zmin=z, ws=ws, tile="pair256", streamk="force"))
+    assert beq(yb, qo.apply_epilogue(outs[0], qo.EP_BIAS, np.broadcast_to(bias, (M, N))))
