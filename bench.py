@@ -313,7 +313,7 @@ def parity_record(args, torch, dist, dev, rank, world, use_program: bool):
     st.decode_step()
     st.decode_step()
     snap = st.snapshot()
-    group_scaled = bool(use_program and args.fmt == "q4f16_0" and os.environ.get("B200Q_PROG_TC", "1") != "0")
+    group_scaled = bool(use_program and ops.program_uses_tensor_cores(args.fmt))
     rec = None
     if rank == 0:
         from oracle import quant_oracle as qo
@@ -560,7 +560,7 @@ def main():
     n_gpus = world
     spec = SPECS[args.fmt]
     shape = MODEL_SHAPES[args.model]
-    use_program = (args.fmt == "q4f16_0") if args.program < 0 else bool(args.program)
+    use_program = ops.program_uses_tensor_cores(args.fmt) if args.program < 0 else bool(args.program)
 
     stack = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, layers=args.layers,
                         pdl=not args.no_pdl, fuse_qkv=not args.no_fuse_qkv, fuse_gate_up=not args.no_fuse_gate_up,
@@ -664,7 +664,7 @@ def main():
     roofline = None
     if step_bytes is not None:
         achieved = step_bytes / (ms_per_step * 1e-3) / 1e9
-        tc = use_program and args.fmt == "q4f16_0"
+        tc = use_program and ops.program_uses_tensor_cores(args.fmt)
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": ncu_traffic("gemv_program_tc_llama7b_token_dram_bytes") if (tc and world == 1 and args.model == "llama-7b" and args.segments == "fused") else None,

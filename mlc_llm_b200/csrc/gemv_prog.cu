@@ -666,6 +666,7 @@ int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
 // environment switches are read ONCE per process (never on the launch path)
 struct EnvConfig {
   bool prog_tc = true;          // B200Q_PROG_TC=0: q4f16_0 programs use the exact per-weight mma.sync kernel
+  bool prog_tc8 = true;         // B200Q_PROG_TC8=0: the same for q8f16_0 programs
   int tc_dbg = 0;               // B200Q_TC_DBG (only honoured by -DB200Q_TC_DBGFLAGS builds)
   long long watchdog_ms = 10000;  // B200Q_WATCHDOG_MS: bound of one cross-CTA / cross-GPU wait; 0 = unbounded
 };
@@ -673,13 +674,16 @@ const EnvConfig& env_config() {
   static const EnvConfig cfg = [] {
     EnvConfig c;
     if (const char* e = std::getenv("B200Q_PROG_TC")) c.prog_tc = !(e[0] == '0');
+    if (const char* e = std::getenv("B200Q_PROG_TC8")) c.prog_tc8 = !(e[0] == '0');
     if (const char* e = std::getenv("B200Q_TC_DBG")) c.tc_dbg = std::atoi(e);
     if (const char* e = std::getenv("B200Q_WATCHDOG_MS")) c.watchdog_ms = std::atoll(e);
     return c;
   }();
   return cfg;
 }
-bool want_tc(int fmt) { return fmt == B200Q_Q4F16_0 && env_config().prog_tc; }
+bool want_tc(int fmt) {
+  return (fmt == B200Q_Q4F16_0 && env_config().prog_tc) || (fmt == B200Q_Q8F16_0 && env_config().prog_tc && env_config().prog_tc8);
+}
 
 // watchdog settings of the process (b200q_gemv_program_set_watchdog); a launch captures them by value
 std::atomic<unsigned long long*> g_wd_status{nullptr};
@@ -755,7 +759,7 @@ int gemv_program_build(const b200q_gemv_step* steps, int n_steps, int fmt, void*
     switch (fmt) {
       case B200Q_Q4F16_0: e = build_step<B200Q_Q4F16_0>(st, steps[j], G, use_tc); break;
       case B200Q_Q3F16_0: e = build_step<B200Q_Q3F16_0>(st, steps[j], G, false); break;
-      case B200Q_Q8F16_0: e = build_step<B200Q_Q8F16_0>(st, steps[j], G, false); break;
+      case B200Q_Q8F16_0: e = build_step<B200Q_Q8F16_0>(st, steps[j], G, use_tc); break;
       case B200Q_Q4F32_0: e = build_step<B200Q_Q4F32_0>(st, steps[j], G, false); break;
       default: return set_error(B200Q_ERR_UNSUPPORTED, "gemv_program_build: fmt %d", fmt);
     }
@@ -853,8 +857,14 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
     case B200Q_Q8F16_0: kern = (const void*)gemv_program_kernel<B200Q_Q8F16_0>; break;
     default: kern = (const void*)gemv_program_kernel<B200Q_Q4F32_0>; break;
   }
-  if (use_tc) kern = h->tp_size > 1 ? (const void*)tc::gemv_program_tc_kernel<true> : (const void*)tc::gemv_program_tc_kernel<false>;
-  if (int e2 = set_max_smem(kern, use_tc ? (h->tp_size > 1 ? 5 : 4) : h->fmt, smem)) return e2;
+  int kern_id = h->fmt;
+  if (use_tc) {
+    const bool tpk = h->tp_size > 1, q8 = (h->fmt == B200Q_Q8F16_0);
+    kern = q8 ? (tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q8F16_0, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q8F16_0, false>)
+              : (tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, false>);
+    kern_id = 4 + (tpk ? 1 : 0) + (q8 ? 2 : 0);
+  }
+  if (int e2 = set_max_smem(kern, kern_id, smem)) return e2;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(G, 1, 1);
   cfg.blockDim = dim3(use_tc ? tc::kThreadsTc : kProgThreads, 1, 1);

@@ -168,6 +168,7 @@ __device__ __forceinline__ void unpack_q4_direct(uint32_t w, uint32_t* out) {
   out[3] = lop3_and_or(t, 0x00F000F0u, 0x54005400u);  // (64 + v3, 64 + v7)
 }
 constexpr float kOffEven = 1024.0f + 7.0f, kOffOdd = 64.0f + 7.0f;
+constexpr float kOffQ8 = 1024.0f + 127.0f;
 
 // event trace of a few steps (scripts/trace_steps.py reads the printed lines): build with EXTRA=-DB200Q_TC_TRACE
 #ifdef B200Q_TC_TRACE
@@ -214,7 +215,10 @@ constexpr int kTrBlk0 = 870, kTrBlks = 64;
 // kTp: the tensor-parallel instantiation (row-parallel ops are reduced over the ranks inside the launch); the
 // single-GPU instantiation carries none of that code (the epilogue warps' finalize path is on the critical path of
 // every dependent step: 4 % tokens/s between the two)
-template <bool kTp>
+// FMT: B200Q_Q4F16_0 (a block = 16 word rows = 128 k = four groups, two per half block) or B200Q_Q8F16_0 (16 word
+// rows = 64 k = two groups, one per half block; a byte under the exponent of 1024 is the f16 number 1024 + q, two
+// LOP3 and one shift per word, offset 1024 + 127 for every k).
+template <int FMT, bool kTp>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
                        int stages, int xs_bytes, int dbg, unsigned prog_id, const __grid_constant__ Wd wd,
@@ -224,6 +228,12 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   __shared__ unsigned long long tc_trace[kTrSteps][6];
   __shared__ unsigned tc_btrace[kTrBlks][8];
 #endif
+  static_assert(FMT == B200Q_Q4F16_0 || FMT == B200Q_Q8F16_0, "tcgen05 decode program: q4f16_0 and q8f16_0");
+  constexpr bool kQ8 = (FMT == B200Q_Q8F16_0);
+  constexpr int kG = kQ8 ? 2 : 4;            // groups per block
+  constexpr int kGH = kG / 2;                // groups per half block
+  constexpr int kKBlk = kQ8 ? 64 : 128;      // k per block
+  constexpr uint32_t kStageTx = kStageWordBytes + kG * kPanelCols * 2;  // bytes TMA delivers per stage
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
   (void)dbg;
@@ -299,10 +309,10 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           for (; rb < rb_end; ++rb) {
             mbar_wait(empty0 + 8 * s, ph ^ 1);
             const uint32_t bar = full0 + 8 * s;
-            mbar_expect_tx(bar, (uint32_t)kStageBytesTc);
+            mbar_expect_tx(bar, kStageTx);
             const uint32_t sw = stage_base + s * kStageBytesTc;
             tma_load_2d_hint(sw, tmw, col0, rb * kRows, bar, pol);
-            tma_load_2d_hint(sw + kStageWordBytes, tms, col0, rb * 4, bar, pol);
+            tma_load_2d_hint(sw + kStageWordBytes, tms, col0, rb * kG, bar, pol);
             if (++s == stages) { s = 0; ph ^= 1; }
           }
           if (rb == RB) { rb = 0; ++panel; }
@@ -334,22 +344,35 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         // half a block = two groups = one x32 tcgen05.st (a store costs its warp ~150 cycles whatever its width).
         // The halves are handed to the MMA warp separately: the tensor core works on one while the slice
         // unpacks the other.
-        uint32_t a[32];
+        uint32_t a[16 * kGH];
+        if constexpr (kQ8) {
+          const uint32_t sg = sw + h * (8 * kPanelCols * 4);  // group h: word rows 8 h .. 8 h + 7
 #pragma unroll
-        for (int gg = 0; gg < 2; ++gg) {
-          const uint32_t sg = sw + (2 * h + gg) * (4 * kPanelCols * 4);
-          const uint32_t w0 = lds32(sg), w1 = lds32(sg + 512), w2 = lds32(sg + 1024), w3 = lds32(sg + 1536);
-          unpack_q4_direct(w0, a + 16 * gg);
-          unpack_q4_direct(w1, a + 16 * gg + 4);
-          unpack_q4_direct(w2, a + 16 * gg + 8);
-          unpack_q4_direct(w3, a + 16 * gg + 12);
+          for (int r = 0; r < 8; ++r) {
+            const uint32_t w = lds32(sg + r * (kPanelCols * 4));
+            a[2 * r] = lop3_and_or(w, 0x00FF00FFu, 0x64006400u);           // (1024 + b0, 1024 + b2)
+            a[2 * r + 1] = lop3_and_or(w >> 8, 0x00FF00FFu, 0x64006400u);  // (1024 + b1, 1024 + b3)
+          }
+        } else {
+#pragma unroll
+          for (int gg = 0; gg < 2; ++gg) {
+            const uint32_t sg = sw + (2 * h + gg) * (4 * kPanelCols * 4);
+            const uint32_t w0 = lds32(sg), w1 = lds32(sg + 512), w2 = lds32(sg + 1024), w3 = lds32(sg + 1536);
+            unpack_q4_direct(w0, a + 16 * gg);
+            unpack_q4_direct(w1, a + 16 * gg + 4);
+            unpack_q4_direct(w2, a + 16 * gg + 8);
+            unpack_q4_direct(w3, a + 16 * gg + 12);
+          }
         }
         TC_ACC(tq_unp);
         mbar_wait_hint<B200Q_TC_HINT_DQ>(afree0 + 8 * (2 * sl + h), (use & 1u) ^ 1u);  // the MMAs of this half set's previous block are done
         TC_ACC(tq_afree);
         if (q == 0 && lane == 0 && h == 0) TC_BEV(m, 1);
         tc_fence_after();
-        if (!TC_DBG(2)) tmem_st_32x32(a_taddr0 + h * 32, a);
+        if (!TC_DBG(2)) {
+          if constexpr (kQ8) tmem_st_32x16(a_taddr0 + h * 16, a);
+          else tmem_st_32x32(a_taddr0 + h * 32, a);
+        }
         tmem_st_wait();  // (.sync.aligned: the whole warp's stores are done - no __syncwarp needed before lane 0 signals)
         tc_fence_before();
         if (lane == 0) {
@@ -415,8 +438,8 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
       p_j = it_j;
       p_m = it_m;
       p_ll = it_ll; p_ptr = it_ptr; p_hasm = it_hasm;
-      p_k0 = (it_rb * kRows + 4 * g + c) * 8;
-      p_nvalid = (upper == 0 || it_hasm) ? min(8, max(0, it_K - p_k0)) : 0;
+      p_k0 = it_rb * kKBlk + 32 * g + 8 * c;  // (q8: the lane's two word rows 2 c, 2 c + 1 of group g)
+      p_nvalid = (g < kG && (upper == 0 || it_hasm)) ? min(8, max(0, it_K - p_k0)) : 0;
       row.lo = row.hi = make_uint4(0, 0, 0, 0);
       if (p_nvalid == 8) {
         if (p_ll >= 0) {
@@ -462,15 +485,24 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         v.z = h2_as_u32(__hmul2(u32_as_h2(v.z), u32_as_h2(mv.z)));
         v.w = h2_as_u32(__hmul2(u32_as_h2(v.w), u32_as_h2(mv.w)));
       }
-      // v = (x0,x1)(x2,x3)(x4,x5)(x6,x7); even k carry the offset 1024 + 7, odd k 64 + 7
+      // v = (x0,x1)(x2,x3)(x4,x5)(x6,x7); q4: even k carry the offset 1024 + 7, odd k 64 + 7; q8: every k 1024 + 127
       if (lane < 16) {  // (the upper half warp only supplies x_mul rows: it takes no part in the reduction below)
-        // the unpack's pair order: (x0,x4)(x1,x5)(x2,x6)(x3,x7)
-        sts128(slot_lane + par * (kABufs * kBSlotBytes),
-               make_uint4(__byte_perm(v.x, v.z, 0x5410), __byte_perm(v.x, v.z, 0x7632), __byte_perm(v.y, v.w, 0x5410),
-                          __byte_perm(v.y, v.w, 0x7632)));
         const float2 f0 = __half22float2(u32_as_h2(v.x)), f1 = __half22float2(u32_as_h2(v.y));
         const float2 f2 = __half22float2(u32_as_h2(v.z)), f3 = __half22float2(u32_as_h2(v.w));
-        float sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
+        float sm;
+        if constexpr (kQ8) {
+          // the unpack's pair order, two words of four bytes: (x0,x2)(x1,x3)(x4,x6)(x5,x7)
+          sts128(slot_lane + par * (kABufs * kBSlotBytes),
+                 make_uint4(__byte_perm(v.x, v.y, 0x5410), __byte_perm(v.x, v.y, 0x7632), __byte_perm(v.z, v.w, 0x5410),
+                            __byte_perm(v.z, v.w, 0x7632)));
+          sm = kOffQ8 * (((f0.x + f1.x) + (f2.x + f3.x)) + ((f0.y + f1.y) + (f2.y + f3.y)));
+        } else {
+          // the unpack's pair order: (x0,x4)(x1,x5)(x2,x6)(x3,x7)
+          sts128(slot_lane + par * (kABufs * kBSlotBytes),
+                 make_uint4(__byte_perm(v.x, v.z, 0x5410), __byte_perm(v.x, v.z, 0x7632), __byte_perm(v.y, v.w, 0x5410),
+                            __byte_perm(v.y, v.w, 0x7632)));
+          sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
+        }
         sm += __shfl_xor_sync(0x0000ffffu, sm, 1);
         sm += __shfl_xor_sync(0x0000ffffu, sm, 2);
         if (c == 0) corr_s[(p_m & (kCorrRing - 1)) * 4 + g] = sm;
@@ -524,7 +556,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           tc_fence_after();
           if (!TC_DBG(1)) {
 #pragma unroll
-            for (int g = 2 * h; g < 2 * h + 2; ++g) {
+            for (int g = kGH * h; g < kGH * h + kGH; ++g) {
               umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
               umma_f16_ts(d_taddr, a_taddr + g * 16 + 8, bd + (uint64_t)(g * (kBSlotBytes / 16) + 512 / 16), idesc, 1u);
             }
@@ -608,9 +640,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           // scales and corrections of the block while the TMEM load is in flight
           const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
           const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & (kCorrRing - 1)) * 4) * 4;
-          float sc[4];
+          float sc[kG];
 #pragma unroll
-          for (int g = 0; g < 4; ++g) sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
+          for (int g = 0; g < kG; ++g) sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
           const uint4 cg4 = gemvdev::lds128(c_addr);
           const float cg[4] = {__uint_as_float(cg4.x), __uint_as_float(cg4.y), __uint_as_float(cg4.z), __uint_as_float(cg4.w)};
           tmem_ld_wait();  // (.sync.aligned, like the shared-memory loads above: warp-wide)
@@ -621,7 +653,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           }
           if (!TC_DBG(8)) {
 #pragma unroll
-            for (int g = 0; g < 4; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
+            for (int g = 0; g < kG; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
           }
           if (++s == stages) s = 0;
           TC_ACC(th_blk);

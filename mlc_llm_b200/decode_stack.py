@@ -174,7 +174,7 @@ class DecodeStack:
         self.use_program = use_program
         # tensor parallel + program + q4f16_0: the per-block all-reduce is fused into the program (one launch per
         # token and rank; only the final logits all-gather is an NCCL call)
-        self.fused_tp = bool(use_program and tp_size > 1 and self.spec.name == "q4f16_0" and
+        self.fused_tp = bool(use_program and tp_size > 1 and ops.program_uses_tensor_cores(self.spec) and
                              os.environ.get("B200Q_FUSED_TP", "1") != "0")
         self._plan = None
         self._steps = None

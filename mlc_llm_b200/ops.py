@@ -281,6 +281,16 @@ def encode(W: torch.Tensor, spec, transpose: bool = True):
 GEMM_TILES = {None: 0, "single": 2, "pair128": 4, "pair256": 8}  # B200Q_FLAG_GEMM_*
 
 
+def program_uses_tensor_cores(spec) -> bool:
+    """True when b200q_gemv_program_* runs this format on the tcgen05 kernel (group scale applied to the f32 group
+    sum: include/b200q.h "arithmetic"): q4f16_0 and q8f16_0, unless B200Q_PROG_TC / B200Q_PROG_TC8 = 0."""
+    import os
+    name = _spec(spec).name
+    if os.environ.get("B200Q_PROG_TC", "1") == "0":
+        return False
+    return name == "q4f16_0" or (name == "q8f16_0" and os.environ.get("B200Q_PROG_TC8", "1") != "0")
+
+
 _GEMM_WORKSPACES: dict = {}
 FLAG_GEMM_NO_STREAMK = 16
 FLAG_GEMM_STREAMK = 32

@@ -253,7 +253,7 @@ DEF_ASYM(f32, float)
 
 /* ---- f64 truth of the UNROUNDED weights (q - maxint) * s  (f16 formats) ----------------------
  * y, sum |x w| and the cancellation magnitude sum_k off_k |x_k| s of the tcgen05 decode program
- * (off_k = 1024 + maxint for even positions of a word, 64 + maxint for odd ones); see
+ * (4-bit: off_k = 1024 + maxint for even positions of a word, 64 + maxint for odd ones; 8-bit: 1024 + maxint); see
  * quant_oracle.gemv_f64_unrounded / tolerance_group_scaled. */
 void orc_gemv_f64u_f16(const uint32_t* packed, const half* scale, const half* x, double* y, double* abs_sum,
                        double* cancel_sum, int K, int N, int nbit, int group) {
@@ -269,7 +269,7 @@ void orc_gemv_f64u_f16(const uint32_t* packed, const half* scale, const half* x,
       const half* srow = scale + (size_t)(k / group) * N + n0;
       uint32_t sh = (uint32_t)(k % f.npu) * nbit;
       double xk = (double)x[k];
-      double off = ((k % f.npu) % 2 == 0 ? 1024.0 : 64.0) + (double)f.maxint;
+      double off = ((nbit == 8 || (k % f.npu) % 2 == 0) ? 1024.0 : 64.0) + (double)f.maxint;
       for (int j = 0; j < nn; ++j) {
         double w = ((double)((prow[j] >> sh) & mask) - (double)f.maxint) * (double)srow[j];
         double t = xk * w;

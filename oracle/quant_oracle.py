@@ -462,14 +462,16 @@ def gemv_f64_unrounded(packed, scale, x, fmt: Fmt, K=None, chunk: int = 2048):
     """f64 evaluation with the UNROUNDED weights (q - maxint) * s (s = the stored scale, exact in f64): what the
     format means in real arithmetic, before the reference rounds every weight to dtype (quantization.py:222-224).
     Returns (y, sum_k |x_k w_kn|, sum_k off_k |x_k| s_kn) where off_k is the integer offset the tcgen05 decode
-    program carries through its tensor-core sum for element k (1024 + maxint for even nibbles of a word, 64 + maxint
-    for odd ones; csrc/gemv_tc.cuh) - the magnitude that cancels in  T - C  and bounds that kernel's extra error."""
+    program carries through its tensor-core sum for element k (4-bit: 1024 + maxint for even nibbles of a word,
+    64 + maxint for odd ones; 8-bit: 1024 + maxint; csrc/gemv_tc.cuh) - the magnitude that cancels in  T - C  and bounds that kernel's extra error."""
     K = x.size if K is None else K
     xv = x.reshape(-1).astype(np.float64)[:K]
     N = packed.shape[1]
     k = np.arange(K)
     shift = ((k % fmt.npu) * fmt.nbit).astype(np.uint32)[:, None]
     off = np.where((k % fmt.npu) % 2 == 0, 1024.0 + fmt.maxint, 64.0 + fmt.maxint)
+    if fmt.nbit == 8:  # q8f16_0 on the tcgen05 program: every byte sits under the exponent of 1024
+        off = np.full(K, 1024.0 + fmt.maxint)
     y = np.empty(N, np.float64)
     ab = np.empty(N, np.float64)
     cc = np.empty(N, np.float64)

@@ -18,9 +18,10 @@ ap.add_argument("--no-stream", action="store_true")
 ap.add_argument("--big", action="store_true", help="one 4096 -> 262144 GEMV: steady-state streaming, whole panels per CTA")
 ap.add_argument("--model", default="llama-7b")
 ap.add_argument("--segments", default="fused")
+ap.add_argument("--fmt", default="q4f16_0")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
-spec = SPECS["q4f16_0"]
+spec = SPECS[a.fmt]
 tag = os.path.basename(os.environ.get("B200Q_LIB", "libb200q.so"))
 if not a.no_token:
     st = DecodeStack(a.model, spec, device=dev, use_program=True, segments=a.segments)
@@ -37,7 +38,7 @@ if not a.no_token:
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / a.iters
     nb = token_bytes(st.shape, spec, 1)
-    print(f"PROBE {tag} token {a.model} segments={a.segments}: {1000 / ms:.1f} tok/s  {ms * 1e3:.1f} us  {nb / ms / 1e6:.0f} GB/s "
+    print(f"PROBE {tag} {a.fmt} token {a.model} segments={a.segments}: {1000 / ms:.1f} tok/s  {ms * 1e3:.1f} us  {nb / ms / 1e6:.0f} GB/s "
           f"({nb / ms / 1e6 / 6550.4 * 100:.1f}% of 6550)", flush=True)
     del st
     torch.cuda.empty_cache()
@@ -52,7 +53,7 @@ if a.big:
     p = torch.randint(-2**31, 2**31 - 1, (spec.n_words(K), N), dtype=torch.int32, device=dev)
     sc = (torch.rand((spec.n_groups(K), N), device=dev) * 0.01).half()
     out = torch.empty(N, dtype=torch.float16, device=dev)
-    prog = ops.GemvProgram([dict(weights=[(p, sc)], x=x, outs=[out])], "q4f16_0")
+    prog = ops.GemvProgram([dict(weights=[(p, sc)], x=x, outs=[out])], a.fmt)
     for _ in range(2):
         prog.run()
     torch.cuda.synchronize()

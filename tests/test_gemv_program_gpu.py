@@ -30,7 +30,7 @@ def test_single_step_matches_gemv_and_oracle(name):
         prog = ops.GemvProgram([dict(weights=[(pd, sd)], x=xd, outs=[out])], name)
         prog.run()
         y = host(out)
-        tc = name == "q4f16_0"  # tcgen05 program: group scale applied to the f32 group sum
+        tc = ops.program_uses_tensor_cores(name)  # tcgen05 program: group scale applied to the f32 group sum
         check_gemv_tolerance(y, p, s, x, fmt, out_f32=f32, what=f"{name} {K}x{N}", group_scaled=tc)
         y1 = host(ops.gemv(pd, sd, xd, name)).reshape(-1)
         if tc:

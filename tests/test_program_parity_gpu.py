@@ -48,7 +48,7 @@ def run_program(name, packed, scale, x, ep="none", epv=None):
 def matmul_bound(name, packed, scale, x, out_f32, K=None):
     """(truth, tolerance) of the matmul for the program kernel of this format."""
     fmt = qo.FORMATS[name]
-    if name == "q4f16_0":
+    if ops.program_uses_tensor_cores(name):
         y64, ab, cc = co.gemv_f64_unrounded(packed, scale, x, fmt, K)
         return y64, qo.tolerance_group_scaled(y64, ab, cc, out_f32), qo.tolerance(y64, ab, out_f32)
     y64, ab = co.gemv_f64(packed, scale, x, fmt, K)
@@ -78,7 +78,7 @@ def test_program_against_reference_goldens(fused):
         y = run_program(fname, packed, scale, x, EP_NAME[ep], epv if need else None).reshape(-1)
         y_ref = fused[n + "/y"]
         assert y.dtype == y_ref.dtype and y.shape == y_ref.shape
-        truth, tol = stack_check.op_truth_and_tol(packed, scale, x, fmt, ep, epv if need else None, K, fname == "q4f16_0")
+        truth, tol = stack_check.op_truth_and_tol(packed, scale, x, fmt, ep, epv if need else None, K, ops.program_uses_tensor_cores(fname))
         err = np.abs(y.astype(np.float64) - truth)
         assert (err <= tol).all(), (n, float((err / tol).max()))
         # closer to the truth of the reference's own (rounded) weights than the reference is
@@ -250,7 +250,7 @@ def test_stack_operator_by_operator(name, use_program):
         w = st.lm_head if nm == "lm_head" else st.layers[li][nm]
         return host(w.packed), host(w.scale)
 
-    rec = stack_check.check_launches(snap, weights, fmt, group_scaled=(use_program and name == "q4f16_0"))
+    rec = stack_check.check_launches(snap, weights, fmt, group_scaled=(use_program and ops.program_uses_tensor_cores(name)))
     assert rec["ops_checked"] == 2 * 7 + 1
     assert rec["ok"], rec
 
