@@ -667,6 +667,7 @@ int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
 struct EnvConfig {
   bool prog_tc = true;          // B200Q_PROG_TC=0: q4f16_0 programs use the exact per-weight mma.sync kernel
   bool prog_tc8 = true;         // B200Q_PROG_TC8=0: the same for q8f16_0 programs
+  bool prog_i8 = true;          // B200Q_PROG_I8=0: q4f16_0 programs use the f16 formulation of the tcgen05 kernel
   int tc_dbg = 0;               // B200Q_TC_DBG (only honoured by -DB200Q_TC_DBGFLAGS builds)
   long long watchdog_ms = 10000;  // B200Q_WATCHDOG_MS: bound of one cross-CTA / cross-GPU wait; 0 = unbounded
 };
@@ -675,6 +676,7 @@ const EnvConfig& env_config() {
     EnvConfig c;
     if (const char* e = std::getenv("B200Q_PROG_TC")) c.prog_tc = !(e[0] == '0');
     if (const char* e = std::getenv("B200Q_PROG_TC8")) c.prog_tc8 = !(e[0] == '0');
+    if (const char* e = std::getenv("B200Q_PROG_I8")) c.prog_i8 = !(e[0] == '0');
     if (const char* e = std::getenv("B200Q_TC_DBG")) c.tc_dbg = std::atoi(e);
     if (const char* e = std::getenv("B200Q_WATCHDOG_MS")) c.watchdog_ms = std::atoll(e);
     return c;
@@ -692,7 +694,7 @@ std::atomic<long long> g_wd_ns{-1};  // -1: the B200Q_WATCHDOG_MS default
 // cudaFuncSetAttribute is a per-device setting: remember the largest opt-in per (device, kernel)
 constexpr int kMaxDevices = 64;
 int set_max_smem(const void* kern, int kern_id, size_t smem) {
-  static std::atomic<size_t> done[kMaxDevices][8];
+  static std::atomic<size_t> done[kMaxDevices][10];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) dev = -1;
   if (dev >= 0 && done[dev][kern_id].load(std::memory_order_relaxed) >= smem) return B200Q_OK;
@@ -860,9 +862,11 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   int kern_id = h->fmt;
   if (use_tc) {
     const bool tpk = h->tp_size > 1, q8 = (h->fmt == B200Q_Q8F16_0);
-    kern = q8 ? (tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q8F16_0, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q8F16_0, false>)
-              : (tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, false>);
-    kern_id = 4 + (tpk ? 1 : 0) + (q8 ? 2 : 0);
+    const bool i8 = !q8 && env_config().prog_i8;
+    if (q8) kern = tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q8F16_0, false, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q8F16_0, false, false>;
+    else if (i8) kern = tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, true, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, true, false>;
+    else kern = tpk ? (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, false, true> : (const void*)tc::gemv_program_tc_kernel<B200Q_Q4F16_0, false, false>;
+    kern_id = 4 + (tpk ? 1 : 0) + (q8 ? 2 : (i8 ? 4 : 0));
   }
   if (int e2 = set_max_smem(kern, kern_id, smem)) return e2;
   cudaLaunchConfig_t cfg{};

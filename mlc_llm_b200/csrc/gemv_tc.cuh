@@ -70,7 +70,7 @@ constexpr int kNAcc = B200Q_TC_NACC;         // accumulators in flight (one per 
 // kNAcc blocks ahead of the epilogue warps
 constexpr int kCorrRing = (kNAcc == 8) ? 16 : 32;  // >= 8 + kNAcc, a power of two
 static_assert(kNAcc == 8 || kNAcc == 16, "accumulators: D columns [256, 256 + 16 * kNAcc)");
-constexpr int kMiscBytes = kCorrRing * 16 + 2 * 80 * 4 + 128;  // corrections + two step tails + ring alignment
+constexpr int kMiscBytes = kCorrRing * 32 + 2 * 80 * 4 + 128;  // corrections (8 words per block) + two step tails + ring alignment
 constexpr int kTmemCols = 512;               // A: columns [0,256), D: [256,384)
 constexpr int kDCol0 = 256;
 constexpr int kStageWordBytes = kRows * kPanelCols * 4;             // 8192: [16 rows][128 cols] u32, no swizzle
@@ -109,6 +109,9 @@ __device__ __forceinline__ float lds_f32(uint32_t a) {
   float r;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(a));
   return r;
+}
+__device__ __forceinline__ void sts64(uint32_t a, uint32_t x, uint32_t y) {
+  asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a), "r"(x), "r"(y) : "memory");
 }
 __device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
@@ -218,7 +221,15 @@ constexpr int kTrBlk0 = 870, kTrBlks = 64;
 // FMT: B200Q_Q4F16_0 (a block = 16 word rows = 128 k = four groups, two per half block) or B200Q_Q8F16_0 (16 word
 // rows = 64 k = two groups, one per half block; a byte under the exponent of 1024 is the f16 number 1024 + q, two
 // LOP3 and one shift per word, offset 1024 + 127 for every k).
-template <int FMT, bool kTp>
+// kI8 (q4f16_0 only): the integer formulation.  The weights go to tensor memory as the bytes 0 .. 15 themselves (two
+// LOP3 and one shift per word, a group = 8 columns = ONE tcgen05.mma.kind::i8 of K = 32: a block costs what a q8
+// block costs for the same 8 KB).  The activations of a group are scaled by a power of two (from the group's
+// largest magnitude) to integers |X| < 2^21 and split into three signed base-256 digits - three s8 rows of the B
+// operand, three s32 accumulator columns per group; T = D0 + 256 D1 + 65536 D2 - 7 sum X is EXACT, and
+// y += s * 2^-shift * T.  An activation more than 2^10 below its group's largest loses low bits (error <=
+// 2^-21 of the group's largest per element: quant_oracle.tolerance_group_scaled); a non-finite activation makes
+// the group's factor NaN.
+template <int FMT, bool kI8, bool kTp>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned* ws_ctrl, void* ws_ll, uint2* ws_partial,
                        int stages, int xs_bytes, int dbg, unsigned prog_id, const __grid_constant__ Wd wd,
@@ -229,6 +240,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   __shared__ unsigned tc_btrace[kTrBlks][8];
 #endif
   static_assert(FMT == B200Q_Q4F16_0 || FMT == B200Q_Q8F16_0, "tcgen05 decode program: q4f16_0 and q8f16_0");
+  static_assert(!kI8 || FMT == B200Q_Q4F16_0, "the integer formulation is the q4f16_0 one");
   constexpr bool kQ8 = (FMT == B200Q_Q8F16_0);
   constexpr int kG = kQ8 ? 2 : 4;            // groups per block
   constexpr int kGH = kG / 2;                // groups per half block
@@ -245,8 +257,10 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   const uint32_t bready0 = bar0 + 8 * kBarBReady, bfree0 = bar0 + 8 * kBarBFree;  // [slice][slot set of the slice]
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + kTmemPtrOff);
   unsigned char* bslots = smem + kHeaderTc;
-  float* corr_s = reinterpret_cast<float*>(bslots + kBSlots * kBSlotBytes);  // [16 blocks][4 groups]: 1136 * sum of the group's x
-  uint32_t* stepc = reinterpret_cast<uint32_t*>(corr_s + kCorrRing * 4);  // [2][kTailWords]: step tails, see the epilogue warps
+  // [16 blocks][8 words]: f16 modes: words 0..3 = offset * sum of the group's x; int8 mode: words 0..3 = 7 * sum of the
+  // group's integer activations, words 4..7 = the group's 2^-shift
+  float* corr_s = reinterpret_cast<float*>(bslots + kBSlots * kBSlotBytes);
+  uint32_t* stepc = reinterpret_cast<uint32_t*>(corr_s + kCorrRing * 8);  // [2][kTailWords]: step tails, see the epilogue warps
   const uint32_t stage_base = (smem_u32(stepc + 2 * kTailWords) + 127u) & ~127u;
   (void)xs_bytes;
 
@@ -344,8 +358,19 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         // half a block = two groups = one x32 tcgen05.st (a store costs its warp ~150 cycles whatever its width).
         // The halves are handed to the MMA warp separately: the tensor core works on one while the slice
         // unpacks the other.
-        uint32_t a[16 * kGH];
-        if constexpr (kQ8) {
+        uint32_t a[kI8 ? 16 : 16 * kGH];
+        if constexpr (kI8) {
+#pragma unroll
+          for (int gg = 0; gg < 2; ++gg) {
+            const uint32_t sg = sw + (2 * h + gg) * (4 * kPanelCols * 4);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const uint32_t w = lds32(sg + r * (kPanelCols * 4));
+              a[8 * gg + 2 * r] = w & 0x0F0F0F0Fu;             // nibbles 0, 2, 4, 6 of the word
+              a[8 * gg + 2 * r + 1] = (w >> 4) & 0x0F0F0F0Fu;  // nibbles 1, 3, 5, 7
+            }
+          }
+        } else if constexpr (kQ8) {
           const uint32_t sg = sw + h * (8 * kPanelCols * 4);  // group h: word rows 8 h .. 8 h + 7
 #pragma unroll
           for (int r = 0; r < 8; ++r) {
@@ -370,7 +395,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         if (q == 0 && lane == 0 && h == 0) TC_BEV(m, 1);
         tc_fence_after();
         if (!TC_DBG(2)) {
-          if constexpr (kQ8) tmem_st_32x16(a_taddr0 + h * 16, a);
+          if constexpr (kI8 || kQ8) tmem_st_32x16(a_taddr0 + h * 16, a);
           else tmem_st_32x32(a_taddr0 + h * 32, a);
         }
         tmem_st_wait();  // (.sync.aligned: the whole warp's stores are done - no __syncwarp needed before lane 0 signals)
@@ -401,6 +426,9 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const int sl = warp - kXWarp0;
     const int upper = lane >> 4, g = (lane >> 2) & 3, c = lane & 3;
     const uint32_t slot_lane = smem_u32(bslots) + (4 * sl + g) * kBSlotBytes + (c >> 1) * 512 + (c & 1) * 256 + g * 16;
+    // int8 mode: rows 3 g + d (digit d) of the group's K = 32 operand, this lane's 8 bytes at K positions 8 c .. 8 c + 7
+    const uint32_t slot_lane_i8 = smem_u32(bslots) + (4 * sl + g) * kBSlotBytes + (c >> 1) * 256 + (3 * g) * 16 + (c & 1) * 8;
+    (void)slot_lane_i8;
     const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
     const uint32_t tag = (ld_acquire_u32(ws_ctrl) % 65535u) + 1u;
     // iterator: the slice's next block (CTA-local number it_m, it_m % 4 == sl) = block it_t of step it_j.
@@ -490,7 +518,41 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
         const float2 f0 = __half22float2(u32_as_h2(v.x)), f1 = __half22float2(u32_as_h2(v.y));
         const float2 f2 = __half22float2(u32_as_h2(v.z)), f3 = __half22float2(u32_as_h2(v.w));
         float sm;
-        if constexpr (kQ8) {
+        if constexpr (kI8) {
+          // the group's scale: 2^shift with  largest |x| * 2^shift < 2^21  (from the f16 exponent of the largest)
+          const uint32_t m2 = __vmaxu2(__vmaxu2(v.x & 0x7FFF7FFFu, v.y & 0x7FFF7FFFu), __vmaxu2(v.z & 0x7FFF7FFFu, v.w & 0x7FFF7FFFu));
+          uint32_t am = max(m2 & 0xFFFFu, m2 >> 16);
+          am = max(am, __shfl_xor_sync(0x0000ffffu, am, 1));
+          am = max(am, __shfl_xor_sync(0x0000ffffu, am, 2));
+          const uint32_t e16 = max(am >> 10, 1u);
+          const bool finite = e16 < 31u;
+          const float up = finite ? __uint_as_float((162u - e16) << 23) : 0.f;                   // 2^(35 - e16)
+          const float fg = finite ? __uint_as_float((92u + e16) << 23) : __uint_as_float(0x7FC00000u);  // its inverse | NaN
+          const int X0 = __float2int_rn(f0.x * up), X1 = __float2int_rn(f0.y * up), X2 = __float2int_rn(f1.x * up),
+                    X3 = __float2int_rn(f1.y * up), X4 = __float2int_rn(f2.x * up), X5 = __float2int_rn(f2.y * up),
+                    X6 = __float2int_rn(f3.x * up), X7 = __float2int_rn(f3.y * up);
+          int sx = ((X0 + X1) + (X2 + X3)) + ((X4 + X5) + (X6 + X7));
+          sx += __shfl_xor_sync(0x0000ffffu, sx, 1);
+          sx += __shfl_xor_sync(0x0000ffffu, sx, 2);
+          // three signed base-256 digits of X: the bytes of X + 0x808080 with their top bits flipped.  Byte order of
+          // the operand row = the unpack's: nibbles 0, 2, 4, 6 | 1, 3, 5, 7 of the word
+          const uint32_t kB = 0x00808080u;
+          const uint32_t U0 = (uint32_t)X0 + kB, U1 = (uint32_t)X1 + kB, U2 = (uint32_t)X2 + kB, U3 = (uint32_t)X3 + kB,
+                         U4 = (uint32_t)X4 + kB, U5 = (uint32_t)X5 + kB, U6 = (uint32_t)X6 + kB, U7 = (uint32_t)X7 + kB;
+          const uint32_t te0 = __byte_perm(U0, U2, 0x5140), te1 = __byte_perm(U4, U6, 0x5140);  // (a0 b0 a1 b1)
+          const uint32_t to0 = __byte_perm(U1, U3, 0x5140), to1 = __byte_perm(U5, U7, 0x5140);
+          const uint32_t he0 = __byte_perm(U0, U2, 0x0062), he1 = __byte_perm(U4, U6, 0x0062);  // (a2 b2 . .)
+          const uint32_t ho0 = __byte_perm(U1, U3, 0x0062), ho1 = __byte_perm(U5, U7, 0x0062);
+          const uint32_t dst = slot_lane_i8 + par * (kABufs * kBSlotBytes);
+          sts64(dst, __byte_perm(te0, te1, 0x5410) ^ 0x80808080u, __byte_perm(to0, to1, 0x5410) ^ 0x80808080u);
+          sts64(dst + 16, __byte_perm(te0, te1, 0x7632) ^ 0x80808080u, __byte_perm(to0, to1, 0x7632) ^ 0x80808080u);
+          sts64(dst + 32, __byte_perm(he0, he1, 0x5410) ^ 0x80808080u, __byte_perm(ho0, ho1, 0x5410) ^ 0x80808080u);
+          if (c == 0) {
+            corr_s[(p_m & (kCorrRing - 1)) * 8 + g] = __int_as_float(7 * sx);
+            corr_s[(p_m & (kCorrRing - 1)) * 8 + 4 + g] = fg;
+          }
+          sm = 0.f;
+        } else if constexpr (kQ8) {
           // the unpack's pair order, two words of four bytes: (x0,x2)(x1,x3)(x4,x6)(x5,x7)
           sts128(slot_lane + par * (kABufs * kBSlotBytes),
                  make_uint4(__byte_perm(v.x, v.y, 0x5410), __byte_perm(v.x, v.y, 0x7632), __byte_perm(v.z, v.w, 0x5410),
@@ -503,9 +565,11 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
                             __byte_perm(v.y, v.w, 0x7632)));
           sm = fmaf(kOffEven, (f0.x + f1.x) + (f2.x + f3.x), kOffOdd * ((f0.y + f1.y) + (f2.y + f3.y)));
         }
-        sm += __shfl_xor_sync(0x0000ffffu, sm, 1);
-        sm += __shfl_xor_sync(0x0000ffffu, sm, 2);
-        if (c == 0) corr_s[(p_m & (kCorrRing - 1)) * 4 + g] = sm;
+        if constexpr (!kI8) {
+          sm += __shfl_xor_sync(0x0000ffffu, sm, 1);
+          sm += __shfl_xor_sync(0x0000ffffu, sm, 2);
+          if (c == 0) corr_s[(p_m & (kCorrRing - 1)) * 8 + g] = sm;
+        }
       }
       fence_proxy_async_smem();
       __syncwarp();
@@ -529,7 +593,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     }
   } else if (warp == kMmaWarp || warp == kMmaWarp2) {
     // ================= MMA warps: eight tcgen05.mma per block (two per group), whole loop in one lane ========
-    const uint32_t idesc = make_idesc_f16(128, 16, 0, 0);
+    const uint32_t idesc = kI8 ? make_idesc_i8_u8s8(128, 16) : make_idesc_f16(128, 16, 0, 0);
     const uint64_t bdesc0 = make_smem_desc_nosw(smem_u32(bslots), 256, 128);
     if (elect_one()) {
       int n_total = 0;
@@ -557,8 +621,12 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           if (!TC_DBG(1)) {
 #pragma unroll
             for (int g = kGH * h; g < kGH * h + kGH; ++g) {
-              umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
-              umma_f16_ts(d_taddr, a_taddr + g * 16 + 8, bd + (uint64_t)(g * (kBSlotBytes / 16) + 512 / 16), idesc, 1u);
+              if constexpr (kI8) {  // one K = 32 MMA per group: 8 columns of weight bytes x three digit rows
+                umma_i8_ts(d_taddr, a_taddr + g * 8, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
+              } else {
+                umma_f16_ts(d_taddr, a_taddr + g * 16, bd + (uint64_t)(g * (kBSlotBytes / 16)), idesc, g == 0 ? 0u : 1u);
+                umma_f16_ts(d_taddr, a_taddr + g * 16 + 8, bd + (uint64_t)(g * (kBSlotBytes / 16) + 512 / 16), idesc, 1u);
+              }
             }
           }
           umma_commit(afree0 + 8 * (2 * set + h));
@@ -635,16 +703,19 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           TC_ACC(th_accfull);
           if (ht == 0 && t == t0 && bb == 0) TC_EV(j, 2);
           tc_fence_after();
-          uint32_t d[4];
-          tmem_ld_32x4(d_taddr0 + ai * 16, d);
+          uint32_t d[kI8 ? 16 : 4];
+          if constexpr (kI8) tmem_ld_32x16(d_taddr0 + ai * 16, d);  // three digit columns per group
+          else tmem_ld_32x4(d_taddr0 + ai * 16, d);
           // scales and corrections of the block while the TMEM load is in flight
           const uint32_t sc_addr = stage_base + s * kStageBytesTc + kStageWordBytes + ht * 2;
-          const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & (kCorrRing - 1)) * 4) * 4;
+          const uint32_t c_addr = smem_u32(corr_s) + (uint32_t)((m & (kCorrRing - 1)) * 8) * 4;
           float sc[kG];
 #pragma unroll
           for (int g = 0; g < kG; ++g) sc[g] = __half2float(__ushort_as_half((unsigned short)lds16(sc_addr + g * (kPanelCols * 2))));
           const uint4 cg4 = gemvdev::lds128(c_addr);
           const float cg[4] = {__uint_as_float(cg4.x), __uint_as_float(cg4.y), __uint_as_float(cg4.z), __uint_as_float(cg4.w)};
+          uint4 cf4 = make_uint4(0, 0, 0, 0);
+          if constexpr (kI8) cf4 = gemvdev::lds128(c_addr + 16);  // the groups' 2^-shift
           tmem_ld_wait();  // (.sync.aligned, like the shared-memory loads above: warp-wide)
           tc_fence_before();
           if (lane == 0) {
@@ -652,8 +723,18 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             mbar_arrive(empty0 + 8 * s);
           }
           if (!TC_DBG(8)) {
+            if constexpr (kI8) {
+              const int ci[4] = {(int)cg4.x, (int)cg4.y, (int)cg4.z, (int)cg4.w};
+              const float cf[4] = {__uint_as_float(cf4.x), __uint_as_float(cf4.y), __uint_as_float(cf4.z), __uint_as_float(cf4.w)};
 #pragma unroll
-            for (int g = 0; g < kG; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
+              for (int g = 0; g < 4; ++g) {  // exact: |T| < 2^31
+                const int T = (int)d[3 * g] + ((int)d[3 * g + 1] << 8) + ((int)d[3 * g + 2] << 16) - ci[g];
+                sum = fmaf(sc[g] * cf[g], (float)T, sum);
+              }
+            } else {
+#pragma unroll
+              for (int g = 0; g < kG; ++g) sum = fmaf(sc[g], __uint_as_float(d[g]) - cg[g], sum);
+            }
           }
           if (++s == stages) s = 0;
           TC_ACC(th_blk);

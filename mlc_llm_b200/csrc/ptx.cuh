@@ -176,6 +176,17 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
       "r"(tmem_a), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// D[tmem, s32] (+)= A[tmem, u8: M lanes x K/4 32-bit columns of four K-adjacent bytes] * B[smem desc, s8], K = 32
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // 16 registers per thread -> this warp's 32 TMEM lanes x 16 consecutive 32-bit columns
 __device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v)[16]) {
   asm volatile(
@@ -285,6 +296,12 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t addr, uint32_t
 __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) |
          ((uint32_t)(M >> 4) << 24);
+}
+
+// instruction descriptor, kind::i8: u8 A, s8 B, s32 accumulator (checked against the host on B200: scripts/ubench/umma_i8.cu)
+// bits [4,6) D format (2 = s32) | [7,10) A format (0 = u8) | [10,13) B format (1 = s8) | [17,23) N >> 3 | [24,29) M >> 4
+__host__ __device__ constexpr uint32_t make_idesc_i8_u8s8(int M, int N) {
+  return (2u << 4) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 }  // namespace ptx

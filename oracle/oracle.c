@@ -278,6 +278,22 @@ void orc_gemv_f64u_f16(const uint32_t* packed, const half* scale, const half* x,
         c[j] += fabs(xk) * off * fabs((double)srow[j]);
       }
     }
+    /* int8 formulation of the 4-bit program (csrc/gemv_tc.cuh, kI8): a group's activations become integers at
+     * 2^-21 of the group's largest magnitude -> error <= 2^-21 amax_g sum_{k in g} |w_k| = 2^-22 (2 amax_g sum |w|) */
+    if (nbit == 4) {
+      for (int k0 = 0; k0 < K; k0 += group) {
+        int k1 = k0 + group < K ? k0 + group : K;
+        double amax = 0.0;
+        for (int k = k0; k < k1; ++k) { double v = fabs((double)x[k]); if (v > amax) amax = v; }
+        for (int k = k0; k < k1; ++k) {
+          const uint32_t* prow = packed + (size_t)(k / f.npu) * N + n0;
+          const half* srow = scale + (size_t)(k / group) * N + n0;
+          uint32_t sh = (uint32_t)(k % f.npu) * nbit;
+          for (int j = 0; j < nn; ++j)
+            c[j] += 2.0 * amax * fabs(((double)((prow[j] >> sh) & mask) - (double)f.maxint) * (double)srow[j]);
+        }
+      }
+    }
     for (int j = 0; j < nn; ++j) { y[n0 + j] = a[j]; abs_sum[n0 + j] = b[j]; cancel_sum[n0 + j] = c[j]; }
   }
 }

@@ -483,12 +483,20 @@ def gemv_f64_unrounded(packed, scale, x, fmt: Fmt, K=None, chunk: int = 2048):
         y[sl] = xv @ w
         ab[sl] = np.abs(xv) @ np.abs(w)
         cc[sl] = (np.abs(xv) * off) @ np.abs(sc)
+        if fmt.nbit == 4:
+            # int8 formulation of the 4-bit program (csrc/gemv_tc.cuh, kI8): a group's activations become integers at
+            # 2^-21 of the group's largest magnitude -> error <= 2^-21 amax_g sum_{k in g} |w_k|
+            ng = -(-K // fmt.group)
+            xa = np.zeros(ng * fmt.group)
+            xa[:K] = np.abs(xv)
+            amax = np.repeat(xa.reshape(ng, fmt.group).max(axis=1), fmt.group)[:K]
+            cc[sl] += 2.0 * (amax @ np.abs(w))
     return y, ab, cc
 
 
 def tolerance_group_scaled(y64u, abs_sum_u, cancel_sum, out_f32: bool) -> np.ndarray:
     """Bound of the tcgen05 decode program against the UNROUNDED truth (gemv_f64_unrounded):
-        |y - y64u| <= rel*|y64u| + 2^-14 * sum|x w| + 2^-22 * sum_k off_k |x_k| s + 2^-24
+        |y - y64u| <= rel*|y64u| + 2^-14 * sum|x w| + 2^-22 * (sum_k off_k |x_k| s + 2 sum_g amax_g sum_{k in g} |w_k|) + 2^-24
     the SURVEY 8c(ii) bound plus the cancellation term: T = sum (off + q) x and C = sum (off + maxint) x are each
     rounded to f32 (relative 2^-24 per accumulation step of a magnitude <= sum off |x|) before they are
     subtracted.  For zero-mean activations the third term is about as large as the second; it dominates when a
