@@ -301,6 +301,7 @@ def parity_record(args, torch, dist, dev, rank, world, use_program: bool):
     fused dequant-GEMV it launched is re-evaluated by the CPU oracle (oracle/stack_check.py) from the bits it
     read.  At N > 1 the shards are gathered and checked against the full (unsharded) weights regenerated on
     rank 0 from the same seeds - the only way a tensor-parallel line can carry correctness."""
+    from mlc_llm_b200 import ops
     from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack
 
     shape = MODEL_SHAPES[args.model]

@@ -667,7 +667,7 @@ int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
 struct EnvConfig {
   bool prog_tc = true;          // B200Q_PROG_TC=0: q4f16_0 programs use the exact per-weight mma.sync kernel
   bool prog_tc8 = true;         // B200Q_PROG_TC8=0: the same for q8f16_0 programs
-  bool prog_i8 = true;          // B200Q_PROG_I8=0: q4f16_0 programs use the f16 formulation of the tcgen05 kernel
+  bool prog_i8 = false;         // B200Q_PROG_I8=1: q4f16_0 programs use the integer formulation of the tcgen05 kernel (slower: kept for study)
   int tc_dbg = 0;               // B200Q_TC_DBG (only honoured by -DB200Q_TC_DBGFLAGS builds)
   long long watchdog_ms = 10000;  // B200Q_WATCHDOG_MS: bound of one cross-CTA / cross-GPU wait; 0 = unbounded
 };
@@ -676,7 +676,7 @@ const EnvConfig& env_config() {
     EnvConfig c;
     if (const char* e = std::getenv("B200Q_PROG_TC")) c.prog_tc = !(e[0] == '0');
     if (const char* e = std::getenv("B200Q_PROG_TC8")) c.prog_tc8 = !(e[0] == '0');
-    if (const char* e = std::getenv("B200Q_PROG_I8")) c.prog_i8 = !(e[0] == '0');
+    if (const char* e = std::getenv("B200Q_PROG_I8")) c.prog_i8 = (e[0] == '1');
     if (const char* e = std::getenv("B200Q_TC_DBG")) c.tc_dbg = std::atoi(e);
     if (const char* e = std::getenv("B200Q_WATCHDOG_MS")) c.watchdog_ms = std::atoll(e);
     return c;

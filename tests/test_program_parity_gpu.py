@@ -231,6 +231,54 @@ print("EXACT-OK")
     assert r.returncode == 0 and "EXACT-OK" in r.stdout, (r.stdout + r.stderr)[-2000:]
 
 
+def test_integer_formulation_documented_env():
+    """B200Q_PROG_I8=1 selects the integer (tcgen05.mma.kind::i8) formulation of the q4f16_0 program: exact s32 group
+    sums over three signed base-256 digits of the activations.  Bound: tolerance_group_scaled (its activation
+    quantization term); an all-q=7 column is EXACTLY zero whatever the activations (no T - C cancellation), and a
+    non-finite activation poisons the outputs that depend on it."""
+    code = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r + "/tests")
+from mlc_llm_b200 import ops
+from oracle import c_oracle as co, quant_oracle as qo
+from util import dev, host, rand_weight
+fmt = qo.FORMATS["q4f16_0"]
+rng = np.random.default_rng(1)
+for K, N, kind in ((4096, 512, "mean80"), (11008, 256, "normal"), (4096, 4096, "outlier"), (224, 136, "ragged")):
+    packed, scale = rand_weight(fmt, K, N, seed=K + N)
+    packed[:, :64] = np.uint32(0x77777777)
+    x = rng.standard_normal(K)
+    if kind == "mean80": x = 80.0 + x
+    if kind == "outlier": x[::97] *= 300.0
+    x = x.astype(np.float16)
+    out = torch.zeros(N, dtype=torch.float16, device="cuda")
+    ops.GemvProgram([dict(weights=[(dev(packed), dev(scale))], x=dev(x), outs=[out])], "q4f16_0").run()
+    y = host(out)
+    y64, ab, cc = co.gemv_f64_unrounded(packed, scale, x, fmt, K)
+    err = np.abs(y.astype(np.float64) - y64)
+    assert (err <= qo.tolerance_group_scaled(y64, ab, cc, False)).all(), (kind, float((err / qo.tolerance_group_scaled(y64, ab, cc, False)).max()))
+    assert (y[:64] == 0).all(), kind
+# a chain of two steps (LL-linked) and a non-finite activation
+K, N = 512, 512
+p1, s1 = rand_weight(fmt, K, N, seed=1); p2, s2 = rand_weight(fmt, N, 256, seed=2)
+x = rng.standard_normal(K).astype(np.float16)
+mid = torch.zeros(N, dtype=torch.float16, device="cuda"); out = torch.zeros(256, dtype=torch.float16, device="cuda")
+prog = ops.GemvProgram([dict(weights=[(dev(p1), dev(s1))], x=dev(x), outs=[mid]), dict(weights=[(dev(p2), dev(s2))], x=mid, outs=[out])], "q4f16_0")
+prog.run(); torch.cuda.synchronize()
+m = host(mid)
+y64, ab, cc = co.gemv_f64_unrounded(p2, s2, m, fmt, N)
+assert (np.abs(host(out).astype(np.float64) - y64) <= qo.tolerance_group_scaled(y64, ab, cc, False)).all()
+xn = x.copy(); xn[5] = np.inf
+out2 = torch.zeros(N, dtype=torch.float16, device="cuda")
+ops.GemvProgram([dict(weights=[(dev(p1), dev(s1))], x=dev(xn), outs=[out2])], "q4f16_0").run()
+assert not np.isfinite(host(out2)).any()
+print("I8-OK")
+""" % (ROOT, ROOT)
+    env = dict(os.environ, B200Q_PROG_I8="1")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0 and "I8-OK" in r.stdout, (r.stdout + r.stderr)[-2000:]
+
+
 @pytest.mark.parametrize("use_program", [True, False])
 @pytest.mark.parametrize("name", ["q4f16_0", "q8f16_0", "q3f16_0"])
 def test_stack_operator_by_operator(name, use_program):
