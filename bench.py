@@ -368,7 +368,7 @@ def prefill_record(args, torch, dev, clocks_fn):
                                "(bias, bias+GELU, bias+2 residual adds); attention / norms excluded", "flop": flops,
                    "l2": "192 GEMMs over 1.1 GB of distinct packed weights per pass"},
         "roofline": {"bound": "tensor", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
-                     "frac_of_burst": tf / burst, "kernel": "b200q::gemm_tc_kernel<q3f16_0> (tcgen05.mma, dequant in the B-operand warps)",
+                     "frac_of_burst": tf / burst, "kernel": "b200q::gemm_tc2_kernel<q3f16_0, 256> (CTA pair, tcgen05.mma.cta_group::2 M = 256, dequant in the B-operand warps, stream-K schedule when whole tiles fill the pairs badly)",
                      "flop_per_launch": flops / max(1, launches), "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (burst beside it)"},
         "gpu_launches_per_pass": launches, "clocks": clocks,
     }

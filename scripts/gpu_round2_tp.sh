@@ -10,7 +10,7 @@ import json
 try:
     d=json.loads([l for l in open('gpurun_out/tp${N}_bench.json') if l.startswith('{')][-1])
     print('TP${N}', round(d['value'],1), 'tok/s e2e', round(d['e2e']['value'],1), 'parity', d['parity'] and (d['parity']['ok'], d['parity']['max_err_over_tol']), 'launches', d['roofline']['launches_per_step'])
-    for e in d['extra']: print('  extra', e['metric'], round(e['value'],1), e['config'].get('reduction'), round(e['frac_of_hbm_peak'],3))
+    for e in d['extra']: print('  extra', e['metric'], round(e['value'],1), e['config'].get('reduction'), round(e.get('frac_of_hbm_peak', e.get('frac_of_tensor_peak', 0)),3))
 except Exception as e:
     print('bench parse failed', e); print(open('gpurun_out/tp${N}_bench.err').read()[-1500:])
 PY
