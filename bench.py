@@ -366,7 +366,7 @@ def prefill_record(args, torch, dev, clocks_fn):
         "metric": "dolly_v2_3b_q3f16_0_prefill2048_linear_tflops", "value": tf, "unit": "TFLOP/s", "ms_per_pass": ms,
         "config": {"workload": f"{model} {fmt} prefill, M={M}: 6 quantized Linears x {st.n_layers} layers with fused epilogues "
                                "(bias, bias+GELU, bias+2 residual adds); attention / norms excluded", "flop": flops,
-                   "l2": "192 GEMMs over 1.1 GB of distinct packed weights per pass"},
+                   "l2": "192 Linears (q|k|v of a layer in one launch: 128 launches) over 1.1 GB of distinct packed weights per pass"},
         "roofline": {"bound": "tensor", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
                      "frac_of_burst": tf / burst, "kernel": "b200q::gemm_tc2_kernel<q3f16_0, 256> (CTA pair, tcgen05.mma.cta_group::2 M = 256, dequant in the B-operand warps, stream-K schedule when whole tiles fill the pairs badly)",
                      "flop_per_launch": flops / max(1, launches), "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (burst beside it)"},
@@ -393,6 +393,27 @@ def prefill_record(args, torch, dev, clocks_fn):
         fl = 2.0 * M * w.K * w.N
         shapes.append({"shape": f"{M}x{label}", "us": round(t * 1e3, 2), "tflops": round(fl / t / 1e9, 1),
                        "dequant_plus_cublas_us": round(t_ref * 1e3, 2), "dequant_plus_cublas_tflops": round(fl / t_ref / 1e9, 1)})
+    # q | k | v of a layer as the stack runs them: ONE launch (b200q_gemm_multi) against three, and the plain GEMM
+    # (no epilogue) of the widest Linear - the GELU costs the epilogue warps ~25 us of a 2560 -> 10240 Linear
+    X = (torch.randn(M, w0["q"].K, device=dev, generator=g) * 0.05).half()
+    Ys = [torch.empty(M, w0[n].N, dtype=torch.float16, device=dev) for n in "qkv"]
+    bs = [torch.zeros(w0[n].N, dtype=torch.float16, device=dev) for n in "qkv"]
+    Ws = [(w0[n].packed, w0[n].scale) for n in "qkv"]
+    t_one = time_steps(torch, lambda: ops.gemm_multi(Ws, X, fmt, ["bias"] * 3, bs, outs=Ys), 20, 3, torch.cuda.synchronize, ident)
+
+    def three():
+        for i in range(3):
+            ops.gemm(Ws[i][0], Ws[i][1], X, fmt, "bias", bs[i], out=Ys[i])
+
+    t_three = time_steps(torch, three, 20, 3, torch.cuda.synchronize, ident)
+    fl = 2.0 * M * w0["q"].K * sum(w0[n].N for n in "qkv")
+    shapes.append({"shape": f"{M}x2560->3x2560 +bias (q|k|v, one launch)", "us": round(t_one * 1e3, 2), "tflops": round(fl / t_one / 1e9, 1),
+                   "three_launches_us": round(t_three * 1e3, 2), "three_launches_tflops": round(fl / t_three / 1e9, 1)})
+    w = w0["h_to_4h"]
+    X = (torch.randn(M, w.K, device=dev, generator=g) * 0.05).half()
+    Y = torch.empty(M, w.N, dtype=torch.float16, device=dev)
+    t = time_steps(torch, lambda: ops.gemm(w.packed, w.scale, X, fmt, out=Y), 20, 3, torch.cuda.synchronize, ident)
+    shapes.append({"shape": f"{M}x2560->10240 (no epilogue)", "us": round(t * 1e3, 2), "tflops": round(2.0 * M * w.K * w.N / t / 1e9, 1)})
     rec["per_shape"] = shapes
     # CPU port on a row sample: the reference's f16-accumulating NT matmul loop nest on the dequantized weight
     if not args.no_cpu_baseline:

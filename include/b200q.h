@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 105 /* major*100 + minor */
+#define B200Q_VERSION 106 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -322,6 +322,26 @@ B200Q_API size_t b200q_gemm_workspace_bytes(void);
 B200Q_API int b200q_gemm_ws(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0,
                   const void* ep1, const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue,
                   unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Up to three weights that read the SAME X in one launch (q | k | v: the reference launches them back to back on the
+ * same x, relax_model/llama.py:233-236; gpt_neox.py query/key/value).  Tensors stay the reference's separate
+ * per-Linear arrays, every weight has its own epilogue and output.  The column tiles of all weights form ONE tile
+ * space (and one stream-K split): three 2560-wide NeoX projections cost 3.24 rounds of tiles instead of 3 x 2.
+ * Results are those of b200q_gemm_ws weight by weight (bit-identical under the whole-tile schedule).  No output
+ * may alias X or another weight's epilogue operand.  zmin: NULL for the symmetric formats. */
+typedef struct {
+  const void* packed;
+  const void* scale;
+  const void* zmin;
+  const void* ep0;
+  const void* ep1;
+  const void* ep2;
+  void* Y;
+  int N;
+  int epilogue;
+} b200q_gemm_op;
+B200Q_API int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt,
+                     unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Dense NT GEMM on an already dequantized weight  T dtype[N, K]  (replaces NT_matmul*,
  * transform/transpose_matmul.py:34-101, dispatch/llama/main.py:3884-3981). f16 only. */

@@ -24,6 +24,22 @@ c_void_p, c_int, c_uint, c_ll, c_ull = (
 )
 
 
+class GemmOp(ctypes.Structure):
+    """b200q_gemm_op (include/b200q.h)."""
+
+    _fields_ = [
+        ("packed", c_void_p),
+        ("scale", c_void_p),
+        ("zmin", c_void_p),
+        ("ep0", c_void_p),
+        ("ep1", c_void_p),
+        ("ep2", c_void_p),
+        ("Y", c_void_p),
+        ("N", c_int),
+        ("epilogue", c_int),
+    ]
+
+
 class GemvOp(ctypes.Structure):
     """b200q_gemv_op (include/b200q.h)."""
 
@@ -76,6 +92,8 @@ PROTOTYPES = {
     "b200q_gemm_asym": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p]),
     "b200q_gemm": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_uint, c_void_p]),
     "b200q_gemm_workspace_bytes": (ctypes.c_size_t, []),
+    "b200q_gemm_multi": (c_int, [ctypes.POINTER(GemmOp), c_int, c_void_p, c_int, c_int, c_int, c_uint, c_void_p, ctypes.c_size_t,
+                                 c_void_p]),
     "b200q_gemm_ws": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_nt_matmul": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
 }

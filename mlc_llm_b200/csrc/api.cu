@@ -57,6 +57,8 @@ int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, co
                      const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream,
                      void* workspace, size_t workspace_bytes);
 size_t gemm_workspace_bytes();
+int gemm_multi_launch(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,
+                      cudaStream_t stream, void* workspace, size_t workspace_bytes);
 int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
                   cudaStream_t stream);
 int gemm_launch(const void* packed, const void* scale, const void* X, const void* ep0, const void* ep1,
@@ -374,6 +376,43 @@ int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, con
 }
 
 size_t b200q_gemm_workspace_bytes(void) { return gemm_workspace_bytes(); }
+
+int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,
+                     void* workspace, size_t workspace_bytes, void* stream) {
+  const bool asym = fmt_is_asym(fmt);
+  if (int e = check_fmt(fmt, "b200q_gemm_multi", asym)) return e;
+  if (fmt_is_variant(fmt) || fmt_is_f32(fmt) || (asym && fmt != B200Q_Q4F16_ASYM))
+    return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: fmt %d has no prefill GEMM", fmt);
+  if (!ops || !X) return set_error(B200Q_ERR_NULL, "b200q_gemm_multi: NULL ops / X");
+  if (n_ops < 1 || n_ops > 3) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: n_ops=%d not in [1,3]", n_ops);
+  if (M < 0 || K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: M=%d K=%d", M, K);
+  if (M == 0) return B200Q_OK;
+  if (!aligned(X, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_multi: X must be 16-byte aligned");
+  if (workspace && !aligned(workspace, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_multi: workspace must be 16-byte aligned");
+  if (!workspace) workspace_bytes = 0;
+  const size_t xb = (size_t)M * K * 2;
+  for (int i = 0; i < n_ops; ++i) {
+    const b200q_gemm_op& o = ops[i];
+    if (!o.packed || !o.scale || !o.Y) return set_error(B200Q_ERR_NULL, "b200q_gemm_multi: op %d: NULL packed / scale / Y", i);
+    if (o.N <= 0 || o.N % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: op %d: N=%d", i, o.N);
+    if (o.epilogue < 0 || o.epilogue >= B200Q_NUM_EP) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: op %d: epilogue %d", i, o.epilogue);
+    if (!aligned(o.packed, 16) || !aligned(o.scale, 16) || !aligned(o.Y, 16))
+      return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_multi: op %d: pointers must be 16-byte aligned", i);
+    if (asym) { if (int e = check_asym(fmt, o.zmin, K, "b200q_gemm_multi")) return e; }
+    const size_t yb = (size_t)M * o.N * (o.epilogue == B200Q_EP_CAST_F32 ? 4 : 2);
+    if (overlaps(o.Y, yb, X, xb)) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: output of op %d aliases X", i);
+    for (int j = 0; j < n_ops; ++j) {
+      if (j != i && overlaps(o.Y, yb, ops[j].Y, (size_t)M * ops[j].N * (ops[j].epilogue == B200Q_EP_CAST_F32 ? 4 : 2)))
+        return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: outputs of ops %d and %d overlap", i, j);
+      const int ej = ops[j].epilogue;
+      const bool bias_like = ej == B200Q_EP_BIAS || ej == B200Q_EP_BIAS_GELU || ej == B200Q_EP_BIAS_ADD2;
+      const size_t eb = (bias_like ? (size_t)1 : (size_t)M) * ops[j].N * 2;
+      if (overlaps(o.Y, yb, ops[j].ep0, eb) && j != i)
+        return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: output of op %d aliases an epilogue operand of op %d", i, j);
+    }
+  }
+  return gemm_multi_launch(ops, n_ops, X, M, K, fmt, flags, reinterpret_cast<cudaStream_t>(stream), workspace, workspace_bytes);
+}
 
 int b200q_gemm_ws(const void* packed, const void* scale, const void* zmin, const void* X, const void* ep0, const void* ep1,
                   const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags, void* workspace,

@@ -71,6 +71,20 @@ struct BCfg<kDense> {
   static constexpr int kBK = 64, kStages = 4, kStageBytes = kBN * kAK * 2, kKSteps = 4;
 };
 
+// one weight of a multi-weight launch of the pair kernel (q | k | v read the same X): b200q_gemm_multi
+struct GemmOp {
+  const uint32_t* packed;
+  const __half* scale;
+  const __half* zmin;
+  const __half* ep0;
+  const __half* ep1;
+  const __half* ep2;
+  void* Y;
+  int N;
+  int epilogue;
+};
+constexpr int kMaxGemmOps = 3;
+
 struct GemmParams {
   CUtensorMap tm_a;  // X f16 [M, K], box 128 x 64, 128B swizzle
   CUtensorMap tm_b;  // dense mode: T f16 [N, K], box 256 x 64, 128B swizzle
@@ -86,6 +100,10 @@ struct GemmParams {
   int epilogue;
   int tiles_m, tiles_n;
   unsigned flags;  // B200Q_FLAG_GEMM_*: tile selection override
+  // pair kernel: the weights of the launch (op[0] mirrors the fields above) and the first column tile of each
+  int n_ops;
+  GemmOp op[kMaxGemmOps];
+  int nt_begin[kMaxGemmOps + 1];  // column tiles [nt_begin[i], nt_begin[i + 1]) belong to op i; unused entries: INT_MAX
   // stream-K schedule of the pair kernel (see TileSched): 0 = whole tiles dealt round-robin
   int streamk;
   unsigned* ws_flags;  // [pair][CTA rank][epilogue warp]: 1 = that warp's rows of the pair's partial tile are in ws_partial
@@ -205,7 +223,8 @@ __device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint
 // ---- epilogue: 32 consecutive columns of one output row ------------------------------------------------
 // y = f16(acc) first (the reference's matmul result is an f16 tensor), then every epilogue op in f16,
 // op for op (ep_f16 in common.cuh).  bias operands are [N]; residual / multiply operands are [M, N].
-__device__ __forceinline__ void epilogue_row(const GemmParams& p, const uint32_t (&acc)[32], int m, int n0) {
+template <class P>  // GemmParams (single-CTA kernel) or GemmOp (pair kernel)
+__device__ __forceinline__ void epilogue_row(const P& p, const uint32_t (&acc)[32], int m, int n0) {
   const int ep = p.epilogue;
   const size_t row = (size_t)m * p.N;
   if (ep == B200Q_EP_CAST_F32) {
@@ -611,8 +630,12 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
   const uint32_t rank = cluster_ctarank();  // 0 = leader
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int tiles_m = (p.M + 255) >> 8;
-  const int tiles_n = (p.N + BN - 1) / BN;
+  const int tiles_n = p.nt_begin[p.n_ops];  // over all weights of the launch
   const int n_tiles = tiles_m * tiles_n;
+  // column tile -> (weight, first column inside it)
+  auto op_of = [&](int tn) { return (tn >= p.nt_begin[1] ? 1 : 0) + (tn >= p.nt_begin[2] ? 1 : 0); };
+  // (the weights are kernel parameters: they are only ever indexed with constants, so every field stays a
+  // constant-bank operand - a run-time index made ptxas copy the table to local memory, 2x slower kernels)
   const int n_ksteps = (p.K + 15) >> 4;
   TileSched sched;
   sched.init(p.streamk, pair, n_pairs, n_tiles, n_ksteps, C::kChunk);
@@ -733,7 +756,8 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
       const Seg sg = sched.get(it);
       const int tile = sg.tile;
       const int acc = it & 1;
-      const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tile / tiles_m) * BN;
+      const int tn = tile / tiles_m, oi = op_of(tn);
+      const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tn - (oi == 0 ? 0 : (oi == 1 ? p.nt_begin[1] : p.nt_begin[2]))) * BN;
       const int m = m0 + row_local;
       const uint32_t t_acc = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
       if (sg.kind == 1) {
@@ -755,17 +779,21 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
         __threadfence();
         __syncwarp();
         if (lane == 0) st_release_u32(flag_of(pair), 1u);
-      } else if (sg.kind == 2) {
-        // finisher: the pairs behind this one hold the rest of the tile's k range.  Their partials are usually there
-        // long before this pair's own MMAs are done: the flags are awaited and the first columns fetched meanwhile,
-        // and the partial of the next 32 columns is in flight while the current ones are finished.
-        const int q_end = sched.contributors_end(tile);
-        wait_flag(pair + 1);
+      } else {
+        // whole tile, or finisher (kind 2): the pairs behind this one hold the rest of the tile's k range.  Their
+        // partials are usually there long before this pair's own MMAs are done: the flags are awaited and the first
+        // columns fetched meanwhile, and the partial of the next 32 columns is in flight while the current ones
+        // are finished.
+        const bool fin = sg.kind == 2;
+        const int q_end = fin ? sched.contributors_end(tile) : pair + 1;
         const uint4* src1 = slot_of(pair + 1);
         uint4 nx[8];
+        if (fin) {
+          wait_flag(pair + 1);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) nx[j] = __ldcg(src1 + (size_t)j * kBM);
-        for (int q = pair + 2; q < q_end; ++q) wait_flag(q);
+          for (int j = 0; j < 8; ++j) nx[j] = __ldcg(src1 + (size_t)j * kBM);
+          for (int q = pair + 2; q < q_end; ++q) wait_flag(q);
+        }
         mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
         tc_fence_after();
 #pragma unroll 1
@@ -773,43 +801,40 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
           uint32_t v[32];
           tmem_ld_32x32(t_acc + c, v);
           tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(nx[j].x));
-            v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(nx[j].y));
-            v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(nx[j].z));
-            v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(nx[j].w));
-          }
-          if (c + 32 < BN && !(p.debug & 8)) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) nx[j] = __ldcg(src1 + (size_t)((c + 32) / 4 + j) * kBM);
-          }
-          for (int q = pair + 2; q < q_end; ++q) {  // (a tile cut over more than two pairs) added in pair order
-            const uint4* src = slot_of(q);
+          if (fin) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const uint4 pv = __ldcg(src + (size_t)(c / 4 + j) * kBM);
-              v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(pv.x));
-              v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(pv.y));
-              v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(pv.z));
-              v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(pv.w));
+              v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(nx[j].x));
+              v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(nx[j].y));
+              v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(nx[j].z));
+              v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(nx[j].w));
+            }
+            if (c + 32 < BN && !(p.debug & 8)) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) nx[j] = __ldcg(src1 + (size_t)((c + 32) / 4 + j) * kBM);
+            }
+            for (int q = pair + 2; q < q_end; ++q) {  // (a tile cut over more than two pairs) added in pair order
+              const uint4* src = slot_of(q);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const uint4 pv = __ldcg(src + (size_t)(c / 4 + j) * kBM);
+                v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(pv.x));
+                v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(pv.y));
+                v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(pv.z));
+                v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(pv.w));
+              }
             }
           }
-          if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+          if (m < p.M) {  // (weights indexed with constants only, see pick_op)
+            if (oi == 0) { if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c); }
+            else if (oi == 1) { if (n0 + c < p.op[1].N) epilogue_row(p.op[1], v, m, n0 + c); }
+            else { if (n0 + c < p.op[2].N) epilogue_row(p.op[2], v, m, n0 + c); }
+          }
         }
-        // the slots have been read: lower the flags for the next launch
-        __syncwarp();
-        if (lane == 0)
-          for (int q = pair + 1; q < q_end; ++q) *flag_of(q) = 0u;
-      } else {
-        mbar_wait(t_full + 8 * acc, (it >> 1) & 1);
-        tc_fence_after();
-#pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-          uint32_t v[32];
-          tmem_ld_32x32(t_acc + c, v);
-          tmem_ld_wait();
-          if (m < p.M && n0 + c < p.N) epilogue_row(p, v, m, n0 + c);
+        if (fin) {  // the slots have been read: lower the flags for the next launch
+          __syncwarp();
+          if (lane == 0)
+            for (int q = pair + 1; q < q_end; ++q) *flag_of(q) = 0u;
         }
       }
       tc_fence_before();
@@ -829,20 +854,20 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
       const int sub = lane / C::kChunks, chunk = lane % C::kChunks;  // word row of the pass, 8-column chunk
       uint32_t w[C::kItems][8], s[C::kItems][4], mn[C::kItems][4];
       auto row_of = [&](int t) { return dw * C::kRowsPerPass + sub + 8 * t; };  // stage-local word row
-      auto load_stage = [&](int n0, int i) {
+      auto load_stage_op = [&](const GemmOp& o, int n0, int i) {
 #pragma unroll
         for (int t = 0; t < C::kItems; ++t) {
           const int r = i * C::kRows + row_of(t);
           const int n = n0 + chunk * 8;
-          if (r < p.n_rows && n < p.N) {
-            const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)r * p.N + n);
+          if (r < p.n_rows && n < o.N) {
+            const uint4* src = reinterpret_cast<const uint4*>(o.packed + (size_t)r * o.N + n);
             const uint4 lo = __ldg(src), hi = __ldg(src + 1);
             w[t][0] = lo.x; w[t][1] = lo.y; w[t][2] = lo.z; w[t][3] = lo.w;
             w[t][4] = hi.x; w[t][5] = hi.y; w[t][6] = hi.z; w[t][7] = hi.w;
-            const uint4 sv = __ldg(reinterpret_cast<const uint4*>(p.scale + (size_t)(r / F::kRowsPerGroup) * p.N + n));
+            const uint4 sv = __ldg(reinterpret_cast<const uint4*>(o.scale + (size_t)(r / F::kRowsPerGroup) * o.N + n));
             s[t][0] = sv.x; s[t][1] = sv.y; s[t][2] = sv.z; s[t][3] = sv.w;
             if constexpr (fmt_has_min_c(MODE)) {
-              const uint4 mv = __ldg(reinterpret_cast<const uint4*>(p.zmin + (size_t)(r / F::kRowsPerGroup) * p.N + n));
+              const uint4 mv = __ldg(reinterpret_cast<const uint4*>(o.zmin + (size_t)(r / F::kRowsPerGroup) * o.N + n));
               mn[t][0] = mv.x; mn[t][1] = mv.y; mn[t][2] = mv.z; mn[t][3] = mv.w;
             }
           } else {
@@ -855,9 +880,15 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
           }
         }
       };
+      auto load_stage = [&](int tile, int i) {
+        const int tn = tile / tiles_m, oi = op_of(tn);
+        const int half0 = (int)rank * C::kHalfN;
+        if (oi == 0) load_stage_op(p.op[0], tn * BN + half0, i);
+        else if (oi == 1) load_stage_op(p.op[1], (tn - p.nt_begin[1]) * BN + half0, i);
+        else load_stage_op(p.op[2], (tn - p.nt_begin[2]) * BN + half0, i);
+      };
       // c = running number of B stages of this CTA over all its segments; this group takes those with c % groups == grp
       long long c0 = 0;  // stages before the current segment
-      auto n0_of = [&](int tile) { return (tile / tiles_m) * BN + (int)rank * C::kHalfN; };
       int si = 0, seg_tile = 0, bs0 = 0, nb = 0;  // current segment: tile, first weight stage of its k range, stages
       auto open = [&]() {
         if (si < sched.n_seg) {
@@ -878,7 +909,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
         }
       };
       settle();
-      if (si < sched.n_seg) load_stage(n0_of(seg_tile), bs0 + i);
+      if (si < sched.n_seg) load_stage(seg_tile, bs0 + i);
       while (si < sched.n_seg) {
         const long long c = c0 + i;
         const int sb = (int)(c % C::kBStages);
@@ -896,7 +927,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
         // this group's next stage (possibly in the next segment): its loads are in flight during this stage's unpack
         i += C::kDqGroups;
         settle();
-        if (si < sched.n_seg) load_stage(n0_of(seg_tile), bs0 + i);
+        if (si < sched.n_seg) load_stage(seg_tile, bs0 + i);
         mbar_wait(b_empty + 8 * sb, pb ^ 1);
         const uint32_t stage = b_ring + sb * C::kBStage;
 #pragma unroll
@@ -950,7 +981,18 @@ int gemm_streamk_mode() {
 template <int MODE, int BN>
 int launch_gemm_pair(GemmParams& p, int n_pairs, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   using C = Pair<MODE, BN>;
-  const int n_tiles = ceil_div(p.M, 256) * ceil_div(p.N, BN);
+  if (p.n_ops < 1) {  // a single weight: op[0] mirrors the plain fields
+    p.n_ops = 1;
+    p.op[0] = GemmOp{p.packed, p.scale, p.zmin, p.ep0, p.ep1, p.ep2, p.Y, p.N, p.epilogue};
+  }
+  int col_tiles = 0;
+  for (int i = 0; i <= kMaxGemmOps; ++i) p.nt_begin[i] = 0x7FFFFFFF;
+  for (int i = 0; i < p.n_ops; ++i) {
+    p.nt_begin[i] = col_tiles;
+    col_tiles += ceil_div(p.op[i].N, BN);
+  }
+  p.nt_begin[p.n_ops] = col_tiles;
+  const int n_tiles = ceil_div(p.M, 256) * col_tiles;
   // stream-K when the caller gave a workspace and whole tiles would leave pairs idle in the last round
   p.streamk = 0;
   {
@@ -1116,6 +1158,52 @@ int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, co
   p.flags = flags;
   if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
   return launch_gemm<B200Q_Q4F16_ASYM>(p, stream, workspace, workspace_bytes);
+}
+
+// Several weights that read the SAME X in one launch of the pair kernel: their column tiles form one tile space
+// (and one stream-K range split), so three 80-tile GEMMs on 74 pairs cost 3.24 rounds instead of three times two.
+int gemm_multi_launch(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,
+                      cudaStream_t stream, void* workspace, size_t workspace_bytes) {
+  const bool asym = fmt == B200Q_Q4F16_ASYM;
+  const int n_pairs = device_sm_count() / 2;
+  const int bn = pick_pair_bn(M, ops[0].N, n_pairs, flags);
+  if (n_ops == 1 || bn == 0) {  // the single-CTA kernel takes one weight per launch
+    for (int i = 0; i < n_ops; ++i) {
+      const b200q_gemm_op& o = ops[i];
+      const int e = asym ? gemm_asym_launch(o.packed, o.scale, o.zmin, X, o.ep0, o.ep1, o.ep2, o.Y, M, K, o.N, o.epilogue, flags, stream,
+                                            workspace, workspace_bytes)
+                         : gemm_launch(o.packed, o.scale, X, o.ep0, o.ep1, o.ep2, o.Y, M, K, o.N, fmt, o.epilogue, flags, stream, workspace,
+                                       workspace_bytes);
+      if (e) return e;
+    }
+    return B200Q_OK;
+  }
+  if (K % 8 != 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: K=%d must be a multiple of 8 (16-byte rows of X)", K);
+  GemmParams p{};
+  p.M = M; p.K = K;
+  p.n_rows = n_words(fmt, K);
+  p.flags = flags;
+  p.n_ops = n_ops;
+  for (int i = 0; i < n_ops; ++i) {
+    const b200q_gemm_op& o = ops[i];
+    if (int e = check_epilogue_operands(o.epilogue, o.ep0, o.ep1, o.ep2, "b200q_gemm_multi")) return e;
+    p.op[i] = GemmOp{reinterpret_cast<const uint32_t*>(o.packed), reinterpret_cast<const __half*>(o.scale),
+                     reinterpret_cast<const __half*>(o.zmin), reinterpret_cast<const __half*>(o.ep0),
+                     reinterpret_cast<const __half*>(o.ep1), reinterpret_cast<const __half*>(o.ep2), o.Y, o.N, o.epilogue};
+  }
+  p.N = ops[0].N;
+  if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
+  switch (fmt) {
+    case B200Q_Q4F16_0: return bn == 256 ? launch_gemm_pair<B200Q_Q4F16_0, 256>(p, n_pairs, workspace, workspace_bytes, stream)
+                                         : launch_gemm_pair<B200Q_Q4F16_0, 128>(p, n_pairs, workspace, workspace_bytes, stream);
+    case B200Q_Q3F16_0: return bn == 256 ? launch_gemm_pair<B200Q_Q3F16_0, 256>(p, n_pairs, workspace, workspace_bytes, stream)
+                                         : launch_gemm_pair<B200Q_Q3F16_0, 128>(p, n_pairs, workspace, workspace_bytes, stream);
+    case B200Q_Q8F16_0: return bn == 256 ? launch_gemm_pair<B200Q_Q8F16_0, 256>(p, n_pairs, workspace, workspace_bytes, stream)
+                                         : launch_gemm_pair<B200Q_Q8F16_0, 128>(p, n_pairs, workspace, workspace_bytes, stream);
+    case B200Q_Q4F16_ASYM: return bn == 256 ? launch_gemm_pair<B200Q_Q4F16_ASYM, 256>(p, n_pairs, workspace, workspace_bytes, stream)
+                                            : launch_gemm_pair<B200Q_Q4F16_ASYM, 128>(p, n_pairs, workspace, workspace_bytes, stream);
+    default: return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: fmt %d", fmt);
+  }
 }
 
 int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y, int M,

@@ -350,6 +350,46 @@ def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, 
     return out
 
 
+def gemm_multi(weights, X, spec, epilogues=None, ep0s=None, outs=None, ws=None, streamk=True, tile=None):
+    """b200q_gemm_multi: up to three weights that read the same X (q | k | v) in ONE launch of the CTA-pair kernel.
+    weights: [(packed, scale) | (packed, scale, zmin), ...]; epilogues / ep0s: per weight ("none" | "bias" | ..).
+    Returns the outputs [dtype[..., M, N_i]]."""
+    spec = _spec(spec)
+    n = len(weights)
+    epilogues = list(epilogues) if epilogues is not None else ["none"] * n
+    ep0s = list(ep0s) if ep0s is not None else [None] * n
+    K = X.shape[-1]
+    M = X.numel() // K
+    if X.dtype != spec.torch_dtype:
+        raise ValueError(f"X must be {spec.dtype}")
+    _need_cuda(X)
+    arr = (_lib.GemmOp * n)()
+    res, keep = [], []
+    for i, w in enumerate(weights):
+        packed, scale = w[0], w[1]
+        zmin = w[2] if len(w) > 2 else None
+        _need_cuda(packed, scale, zmin, ep0s[i])
+        _check_min(spec, scale, zmin)
+        N = _check_weight(spec, packed, scale, K)
+        ep = _ep_id(epilogues[i])
+        odt = torch.float32 if ep == EPILOGUES["cast_f32"] else spec.torch_dtype
+        out = outs[i] if outs is not None else torch.empty(tuple(X.shape[:-1]) + (N,), dtype=odt, device=X.device)
+        if out.numel() != M * N or out.dtype != odt:
+            raise ValueError(f"out {i} must be {odt}[{M}, {N}]")
+        arr[i] = _lib.GemmOp(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), _ptr(ep0s[i]), None, None, out.data_ptr(), N, ep)
+        res.append(out)
+        keep.append((packed, scale, zmin))
+    flags = GEMM_TILES[tile]
+    flags |= FLAG_GEMM_STREAMK if streamk == "force" else (0 if streamk else FLAG_GEMM_NO_STREAMK)
+    if ws is False:
+        wp, wb = None, 0
+    else:
+        w_ = gemm_workspace(X.device) if ws is None else ws
+        wp, wb = w_.data_ptr(), w_.numel() * w_.element_size()
+    _lib.check(_lib.lib().b200q_gemm_multi(arr, n, X.data_ptr(), M, K, spec.fmt_id, flags, wp, wb, _stream()))
+    return res
+
+
 def nt_matmul(X, T, epilogue="none", ep0=None, ep1=None, ep2=None, out=None):
     """NT_matmul: Y[m, n] = sum_k X[m, k] * T[n, k] (+ epilogue), f16, tcgen05."""
     ep = _ep_id(epilogue)

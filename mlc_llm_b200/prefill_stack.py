@@ -35,10 +35,11 @@ class PrefillStack:
     """Runs the prefill GEMM sequence on the weights of a DecodeStack (same packed tensors: decode and prefill
     share the weights exactly as in the reference, where both `decoding` and `encoding` read the same params)."""
 
-    def __init__(self, stack: DecodeStack, M: int):
+    def __init__(self, stack: DecodeStack, M: int, fuse_qkv: bool = True):
         if stack.spec.dtype != "float16":
             raise NotImplementedError("prefill GEMM: f16 schemes (b200q_gemm)")
         self.st, self.M = stack, M
+        self.fuse_qkv = fuse_qkv and stack.spec.sym
         sh, tp, dev = stack.shape, stack.tp_size, stack.device
         h, i = sh.hidden, sh.inter
         e = lambda *s: torch.zeros(*s, dtype=torch.float16, device=dev)
@@ -49,6 +50,7 @@ class PrefillStack:
         self.g, self.a = e(M, i // tp), e(M, i // tp)
         self.m_out = e(M, h)
         self.gemms_per_pass = 0
+        self.launches_per_pass = 0
         self.collectives_per_pass = 0
 
     def flops(self) -> int:
@@ -62,6 +64,18 @@ class PrefillStack:
     def _gemm(self, w, X, ep, out, ep0=None, ep1=None, ep2=None):
         ops.gemm(w.packed, w.scale, X, self.st.spec, ep, ep0, ep1, ep2, out=out)
         self.gemms_per_pass += 1
+        self.launches_per_pass += 1
+
+    def _qkv(self, w, x, ep, b):
+        """q | k | v read the same x: one launch (b200q_gemm_multi), three outputs with their own bias."""
+        if self.fuse_qkv:
+            ops.gemm_multi([(w[n].packed, w[n].scale) for n in "qkv"], x, self.st.spec, [ep] * 3,
+                           [b[n] if b is not None else None for n in "qkv"], outs=[self.q, self.k, self.v])
+            self.gemms_per_pass += 3  # Linears; one launch
+            self.launches_per_pass += 1
+        else:
+            for n, o in (("q", self.q), ("k", self.k), ("v", self.v)):
+                self._gemm(w[n], x, ep, o, b[n] if b is not None else None)
 
     def _row(self, w, X, out, ep, ep0=None, ep1=None, ep2=None):
         """Row-parallel GEMM: partial sums, then one all-reduce per sharded block."""
@@ -79,6 +93,7 @@ class PrefillStack:
     def run(self, x: Optional[torch.Tensor] = None) -> torch.Tensor:
         st = self.st
         self.gemms_per_pass = 0
+        self.launches_per_pass = 0
         self.collectives_per_pass = 0
         x = self.x_in if x is None else x
         llama = st.shape.family == "llama"
@@ -86,16 +101,14 @@ class PrefillStack:
             w = st.layers[li]
             out = self.x2 if (li % 2 == 0) else self.x3  # ping-pong the layer output (x_in is never written)
             if llama:
-                for n, o in (("q", self.q), ("k", self.k), ("v", self.v)):
-                    self._gemm(w[n], x, "none", o)
+                self._qkv(w, x, "none", None)
                 self._row(w["o"], self.q, self.x1, "add", x)
                 self._gemm(w["gate"], self.x1, "silu", self.g)
                 self._gemm(w["up"], self.x1, "multiply", self.a, self.g)
                 self._row(w["down"], self.a, out, "add", self.x1)
             else:
                 b = st.biases[li]
-                for n, o in (("q", self.q), ("k", self.k), ("v", self.v)):
-                    self._gemm(w[n], x, "bias", o, b[n])
+                self._qkv(w, x, "bias", b)
                 self._gemm(w["h_to_4h"], x, "bias_gelu", self.a, b["h_to_4h"])
                 self._row(w["4h_to_h"], self.a, self.m_out, "bias", b["4h_to_h"])
                 self._row(w["dense"], self.q, out, "bias_add2", b["dense"], self.m_out, x)

@@ -11,7 +11,7 @@ import json
 d=json.loads([l for l in open('gpurun_out/${T}_bench.json') if l.startswith('{')][-1])
 print('HEADLINE', round(d['value'],1), 'tok/s frac', round(d['roofline']['frac'],4), 'e2e', round(d['e2e']['value'],1), 'parity', d['parity'] and (d['parity'].get('ok'), d['parity'].get('max_err_over_tol')))
 print('segmented', d['segmented'] and (round(d['segmented']['value'],1), d['segmented']['logits_equal_to_headline']))
-p=d['prefill']; print('prefill', p and (round(p.get('value',0),1), [ (s['shape'], s['tflops'], s['dequant_plus_cublas_tflops']) for s in p.get('per_shape',[])]))
+p=d['prefill']; print('prefill', p and (round(p.get('value',0),1), [ (s['shape'], s['tflops'], s.get('dequant_plus_cublas_tflops', s.get('three_launches_tflops'))) for s in p.get('per_shape',[])]))
 for e in d['extra']: print('extra', json.dumps(e)[:300])
 print('cpu', d.get('cpu_baseline',{}).get('value'))
 PY

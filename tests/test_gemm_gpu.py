@@ -235,3 +235,38 @@ def test_gemm_streamk_schedule(name, M, K, N):
     bias = (rng.standard_normal(N) * 0.1).astype(np.float16)
     yb = host(ops.gemm(p, s, x, name, "bias", dev(bias), zmin=z, ws=ws, tile="pair256", streamk="force"))
     assert beq(yb, qo.apply_epilogue(outs[0], qo.EP_BIAS, np.broadcast_to(bias, (M, N))))
+
+
+@pytest.mark.parametrize("name", F16)
+@pytest.mark.parametrize("M,K,Ns", [(2048, 2560, (2560, 2560, 2560)), (300, 640, (264, 520, 136)), (512, 1280, (1280, 256)),
+                                    (100, 320, (264, 264, 264))])
+def test_gemm_multi_equals_single_launches(name, M, K, Ns):
+    """b200q_gemm_multi: q | k | v in one launch of the pair kernel (one tile space over the three weights) - the
+    whole-tile schedule reproduces the three single launches bit for bit, the stream-K schedule stays inside the
+    oracle's bound; per-weight bias epilogues; M <= 128 falls back to one launch per weight."""
+    fmt = qo.FORMATS[name]
+    if fmt.nbit == 3 and K % 40:
+        K = K // 40 * 40
+    rng = np.random.default_rng(M + K)
+    X = (rng.standard_normal((M, K)) * 0.5).astype(np.float16)
+    xd = dev(X)
+    ws, host_w, biases = [], [], []
+    for i, N in enumerate(Ns):
+        packed, scale = rand_weight(fmt, K, N, seed=10 * i + N)
+        host_w.append((packed, scale))
+        ws.append((dev(packed), dev(scale)))
+        biases.append(dev((rng.standard_normal(N) * 0.1).astype(np.float16)))
+    eps = ["bias"] * len(Ns)
+    single = [host(ops.gemm(w[0], w[1], xd, name, "bias", b, ws=False)) for w, b in zip(ws, biases)]
+    multi = [host(y) for y in ops.gemm_multi(ws, xd, name, eps, biases, streamk=False)]
+    for a, b in zip(single, multi):
+        assert beq(a, b)
+    sk = [host(y) for y in ops.gemm_multi(ws, xd, name, eps, biases, streamk="force")]
+    sk2 = [host(y) for y in ops.gemm_multi(ws, xd, name, eps, biases, streamk="force")]
+    rows = rng.choice(M, min(M, 24), replace=False)
+    for (packed, scale), y, y2, bias, ref in zip(host_w, sk, sk2, biases, single):
+        assert beq(y, y2)
+        y0 = host(ops.gemm(dev(packed), dev(scale), xd, name, streamk="force")) if M > 128 else None
+        y64, ab = qo.gemm_f64(packed, scale, X[rows], fmt)
+        d = np.abs(y[rows].astype(np.float64) - ref[rows].astype(np.float64))
+        assert (d <= 2 * qo.tolerance(y64, ab, False) + 2.0 ** -10 * np.abs(ref[rows].astype(np.float64))).all()
