@@ -510,11 +510,14 @@ def reference_gpu_record(torch, dev):
 
 def decode_extra(args, torch, dist, dev, rank, world, model, fmt, barrier, max_over_ranks, steps=30, cpu=False):
     """One more decode configuration of BASELINE.json on the ranks of this run (same protocol, fewer steps)."""
+    from mlc_llm_b200 import ops
     from mlc_llm_b200.decode_stack import MODEL_SHAPES, DecodeStack, token_bytes
     from mlc_llm_b200.quant_spec import SPECS
 
     shape, spec = MODEL_SHAPES[model], SPECS[fmt]
-    st = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, use_program=True)
+    # the one-launch program where it runs on the tensor cores (q4f16_0, q8f16_0); the per-operator PDL chain otherwise
+    # (q4f32_0: 696 against 277 tok/s through the register-level program kernel)
+    st = DecodeStack(shape, spec, device=dev, tp_rank=rank, tp_size=world, use_program=ops.program_uses_tensor_cores(spec))
     st.x_in.copy_((torch.randn(shape.hidden, device=dev) * 0.05).to(st.dt))
     st.capture()
     ms = time_steps(torch, st.decode_step, steps, 5, barrier, max_over_ranks)

@@ -19,6 +19,7 @@ ap.add_argument("--big", action="store_true", help="one 4096 -> 262144 GEMV: ste
 ap.add_argument("--model", default="llama-7b")
 ap.add_argument("--segments", default="fused")
 ap.add_argument("--fmt", default="q4f16_0")
+ap.add_argument("--big-n", type=int, default=262144, help="columns of the --big GEMV (16384: 37 MB of q4 weights, L2-resident: the consumer's ceiling)")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 spec = SPECS[a.fmt]
@@ -47,7 +48,7 @@ if not a.no_stream:
     print(f"PROBE {tag} stream: {r['gbs']} GB/s ({r['frac_of_peak'] * 100:.1f}%)", flush=True)
 
 if a.big:
-    K, N = 4096, 262144
+    K, N = 4096, a.big_n
     from mlc_llm_b200 import ops
     x = (torch.randn(K, device=dev) * 0.05).half()
     p = torch.randint(-2**31, 2**31 - 1, (spec.n_words(K), N), dtype=torch.int32, device=dev)
