@@ -264,23 +264,26 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   const uint32_t stage_base = (smem_u32(stepc + 2 * kTailWords) + 127u) & ~127u;
   (void)xs_bytes;
 
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < stages; ++s) {
+  // Start-up is on the critical path of every launch (a program cut at the reference's operator boundaries is ~97
+  // launches per token): the producer warp initialises the ring barriers ITSELF and starts streaming weights at
+  // once - it only ARRIVES at the start barrier below, it never waits for the TMEM allocation, the zeroing of the B
+  // slots or the other roles' step-table reads; the remaining barriers are initialised one per thread.
+  if (warp == kProducerWarpTc) {
+    for (int s = lane; s < stages; s += 32) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, 4 + kHelperWarps);  // the block's dequant slice + the epilogue warps
     }
-    for (int i = 0; i < 2 * kASets; ++i) {  // one pair per half block (two groups)
-      mbar_init(aready0 + 8 * i, 4);  // the four warps of the dequant slice
-      mbar_init(afree0 + 8 * i, 1);
-    }
-    for (int i = 0; i < kNAcc; ++i) {
-      mbar_init(accfull0 + 8 * i, 1);
-      mbar_init(accfree0 + 8 * i, kHelperWarps);
-    }
-    for (int i = 0; i < 2 * kASets; ++i) {
-      mbar_init(bready0 + 8 * i, 1);
-      mbar_init(bfree0 + 8 * i, 1);
-    }
+    fence_barrier_init();
+    __syncwarp();
+  } else if (threadIdx.x < 2 * kASets) {  // one pair per half block (two groups)
+    mbar_init(aready0 + 8 * threadIdx.x, 4);  // the four warps of the dequant slice
+    mbar_init(afree0 + 8 * threadIdx.x, 1);
+    mbar_init(bready0 + 8 * threadIdx.x, 1);
+    mbar_init(bfree0 + 8 * threadIdx.x, 1);
+    fence_barrier_init();
+  } else if (threadIdx.x >= 32 && threadIdx.x < 32 + kNAcc) {
+    mbar_init(accfull0 + 8 * (threadIdx.x - 32), 1);
+    mbar_init(accfree0 + 8 * (threadIdx.x - 32), kHelperWarps);
     fence_barrier_init();
   }
 #ifdef B200Q_TC_TRACE
@@ -295,9 +298,13 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   }
   fence_proxy_async_smem();
   tc_fence_before();
-  __syncthreads();
+  if (warp == kProducerWarpTc) {
+    asm volatile("bar.arrive 3, %0;" ::"n"(kThreadsTc) : "memory");  // (its barriers are initialised: the consumers may go)
+  } else {
+    asm volatile("bar.sync 3, %0;" ::"n"(kThreadsTc) : "memory");
+  }
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_base = (warp == kProducerWarpTc) ? 0u : *tmem_ptr;
 
   if (warp == kProducerWarpTc) {
     // ================= producer: never waits for a dependency (weights are constants) ==================
