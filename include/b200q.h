@@ -173,7 +173,7 @@ B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* 
  * A "program" is that chain as data: a list of steps, each step = 1..4 GEMVs reading the same
  * activation (x, optionally x * x_mul) exactly like b200q_gemv_multi.  The library derives the
  * dependencies between steps from pointer overlap (a step waits for the steps that write its x /
- * x_mul / ep0, or whose inputs / outputs it overwrites) and runs everything in one cooperative,
+ * x_mul / ep0, or whose inputs / outputs it overwrites) and runs everything in one grid-resident (one CTA per SM),
  * persistent kernel: weights of later steps stream into shared memory while earlier steps finish.
  * Arithmetic: q3f16_0 / q8f16_0 / q4f32_0 programs (and q4f16_0 with B200Q_PROG_TC=0 in the environment) use
  * the per-weight arithmetic of b200q_gemv_multi (every weight rounded to dtype exactly like the reference's

@@ -667,6 +667,15 @@ int stages_for(int fmt, int xs_bytes, bool use_tc = false) {
 struct EnvConfig {
   bool prog_tc = true;          // B200Q_PROG_TC=0: q4f16_0 programs use the exact per-weight mma.sync kernel
   bool prog_tc8 = true;         // B200Q_PROG_TC8=0: the same for q8f16_0 programs
+  // B200Q_PROG_PDL: how the tcgen05 program is launched.  2 (default): programmatic dependent launch WITHOUT the
+  // cooperative attribute - the CTAs of the next program launch take an SM as soon as this launch's CTA there has left,
+  // stream their first weights and wait (griddepcontrol.wait) only before they touch the workspace or an input.  The
+  // cooperative attribute makes the driver drain the whole grid first (measured, program cut at the reference's
+  // operator boundaries: 689 tok/s cooperative, 719 cooperative + PDL, 803 PDL alone).  Residency: the grid is one
+  // CTA per SM and a dependent launch starts only after EVERY CTA of its predecessor has started, so all CTAs of a
+  // launch become resident without waiting for one another; the watchdog bounds the wait if foreign work holds SMs.
+  // 1 = cooperative + PDL, 0 = cooperative only.
+  int prog_pdl = 2;
   bool prog_i8 = false;         // B200Q_PROG_I8=1: q4f16_0 programs use the integer formulation of the tcgen05 kernel (slower: kept for study)
   int tc_dbg = 0;               // B200Q_TC_DBG (only honoured by -DB200Q_TC_DBGFLAGS builds)
   long long watchdog_ms = 10000;  // B200Q_WATCHDOG_MS: bound of one cross-CTA / cross-GPU wait; 0 = unbounded
@@ -677,6 +686,7 @@ const EnvConfig& env_config() {
     if (const char* e = std::getenv("B200Q_PROG_TC")) c.prog_tc = !(e[0] == '0');
     if (const char* e = std::getenv("B200Q_PROG_TC8")) c.prog_tc8 = !(e[0] == '0');
     if (const char* e = std::getenv("B200Q_PROG_I8")) c.prog_i8 = (e[0] == '1');
+    if (const char* e = std::getenv("B200Q_PROG_PDL")) c.prog_pdl = std::atoi(e);
     if (const char* e = std::getenv("B200Q_TC_DBG")) c.tc_dbg = std::atoi(e);
     if (const char* e = std::getenv("B200Q_WATCHDOG_MS")) c.watchdog_ms = std::atoll(e);
     return c;
@@ -874,11 +884,23 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   cfg.blockDim = dim3(use_tc ? tc::kThreadsTc : kProgThreads, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attrs[1];
-  attrs[0].id = cudaLaunchAttributeCooperative;  // CTAs wait on one another: they must all be resident
-  attrs[0].val.cooperative = 1;
+  cudaLaunchAttribute attrs[2];
+  int na = 0;
+  const int pdl = use_tc ? env_config().prog_pdl : 0;
+  if (pdl != 2) {
+    attrs[na].id = cudaLaunchAttributeCooperative;  // CTAs wait on one another: they must all be resident
+    attrs[na].val.cooperative = 1;
+    ++na;
+  }
+  if (pdl) {
+    // programmatic dependent launch: the next program launch's CTAs take an SM as soon as this launch's CTA there is
+    // done, stream their first weights and wait (griddepcontrol.wait) only before they touch the workspace / inputs
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attrs;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = na;
   TpInfo tp{};
   tp.rank = h->tp_rank;
   tp.size = h->tp_size;

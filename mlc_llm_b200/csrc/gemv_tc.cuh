@@ -249,6 +249,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int G = gridDim.x, b = blockIdx.x;
   (void)dbg;
+  pdl_launch_dependents();  // (no-op unless launched with the programmatic attribute)
 
   const uint32_t bar0 = smem_u32(smem);
   const uint32_t full0 = bar0 + 8 * kBarFull, empty0 = bar0 + 8 * kBarEmpty;
@@ -437,6 +438,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const uint32_t slot_lane_i8 = smem_u32(bslots) + (4 * sl + g) * kBSlotBytes + (c >> 1) * 256 + (3 * g) * 16 + (c & 1) * 8;
     (void)slot_lane_i8;
     const uint32_t* ll = reinterpret_cast<const uint32_t*>(ws_ll);
+    pdl_wait();  // (programmatic dependent launch) the workspace and the plain inputs belong to the previous launch until here
     const uint32_t tag = (ld_acquire_u32(ws_ctrl) % 65535u) + 1u;
     // iterator: the slice's next block (CTA-local number it_m, it_m % 4 == sl) = block it_t of step it_j.
     // (The step table is in global memory and there is no L1 to speak of next to 227 KB of shared memory: every
@@ -651,6 +653,7 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
     const int hq = warp - kHelperWarp0;  // TMEM lane quadrant (warp 16 + hq, (16 + hq) % 4 == hq)
     const int ht = hq * 32 + lane;       // panel column
     const uint32_t d_taddr0 = tmem_base + ((uint32_t)(hq * 32) << 16) + kDCol0;
+    pdl_wait();  // (programmatic dependent launch) as the activation warps
     const uint32_t epoch = ld_acquire_u32(ws_ctrl);
     const uint32_t tag = (epoch % 65535u) + 1u;
     check_prog_id(ws_ctrl, prog_id, wd, b == 0 && ht == 0);
