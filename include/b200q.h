@@ -175,18 +175,24 @@ B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* 
  * dependencies between steps from pointer overlap (a step waits for the steps that write its x /
  * x_mul / ep0, or whose inputs / outputs it overwrites) and runs everything in one grid-resident (one CTA per SM),
  * persistent kernel: weights of later steps stream into shared memory while earlier steps finish.
- * Arithmetic: q3f16_0 / q8f16_0 / q4f32_0 programs (and q4f16_0 with B200Q_PROG_TC=0 in the environment) use
+ * Arithmetic: q3f16_0 / q4f32_0 programs (and q4f16_0 / q8f16_0 with B200Q_PROG_TC=0 / B200Q_PROG_TC8=0 in the environment) use
  * the per-weight arithmetic of b200q_gemv_multi (every weight rounded to dtype exactly like the reference's
  * decode, exact products, f32 accumulation; results differ from the step-by-step launches only by the f32
- * summation order of the K split).  The DEFAULT q4f16_0 program runs on tcgen05: it accumulates
- * T[g,n] = sum_k (off_k + q[k,n]) x[k] per quantization group in f32 and applies s[g,n] * (T - C[g]) once per
- * group (C[g] = sum_k (off_k + 7) x[k], rounded to f32 separately), i.e. the group scale multiplies an f32 group
+ * summation order of the K split).  The DEFAULT q4f16_0 and q8f16_0 programs run on tcgen05: they accumulate
+ * T[g,n] = sum_k (off_k + q[k,n]) x[k] per quantization group in f32 and apply s[g,n] * (T - C[g]) once per
+ * group (C[g] = sum_k (off_k + maxint) x[k], rounded to f32 separately), i.e. the group scale multiplies an f32 group
  * sum instead of every weight being rounded to f16 first.  It is therefore NOT bit-equal to b200q_gemv_multi or
  * to the reference; it is closer to real arithmetic than both (tests/test_program_parity_gpu.py: against the f64
  * sum of the UNROUNDED (q-7)*s it meets the 2^-14 bound that the per-weight kernels meet against the rounded
  * weights), and the T - C cancellation costs accuracy only when |sum_k x[k]| of a group is large against
- * |sum_k (q-7) x[k]| (bounded and tested with shifted / outlier activations).  Every program is deterministic:
+ * |sum_k (q-7) x[k]| (bounded and tested with shifted / outlier activations).  B200Q_PROG_I8=1 selects an integer
+ * formulation for q4f16_0 (tcgen05.mma.kind::i8 on three signed base-256 digits of the group-scaled activations:
+ * exact s32 group sums, no cancellation; an activation more than 2^10 below its group's largest loses low bits, a
+ * non-finite activation yields NaN for the outputs that depend on its group).  Every program is deterministic:
  * replays give identical bits for a given SM count.
+ * Launch: the tcgen05 programs use programmatic dependent launch (B200Q_PROG_PDL): consecutive program launches on
+ * a stream overlap their set-up with the predecessor's tail; kernels of other kinds before / after are ordered as
+ * usual.
  *
  *   1. b200q_gemv_program_build fills a HOST blob of b200q_gemv_program_bytes(n_steps) bytes
  *      (tensor-map descriptors + step table; needs a CUDA context but launches nothing);
