@@ -628,6 +628,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();  // 0 = leader
+  pdl_launch_dependents();  // (no-op unless launched with B200Q_FLAG_PDL)
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int tiles_m = (p.M + 255) >> 8;
   const int tiles_n = p.nt_begin[p.n_ops];  // over all weights of the launch
@@ -668,6 +669,8 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
 
   if (warp == 0) {
     // ================= TMA producer: this CTA's 128 rows of X (and, dense mode, its BN/2 rows of T) ==============
+    pdl_wait();  // (programmatic dependent launch) X / T may be the previous kernel's output; the weights are constants:
+                 // the dequant warps start at once
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
     for (int si = 0; si < sched.n_seg; ++si) {
@@ -736,6 +739,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
     // ================= epilogue: this CTA's 128 rows of the pair's tile ============================================
     const int quarter = warp & 3;
     const int row_local = quarter * 32 + lane;
+    pdl_wait();  // the workspace, the epilogue operands and Y belong to the previous kernel until here
     // workspace slot / flags of (pair q, this rank): the slot is [BN / 4 column quads][128 rows] float4, so that a warp
     // (32 consecutive rows) moves 512 contiguous bytes per instruction
     auto slot_of = [&](int q) {
@@ -1036,13 +1040,21 @@ int launch_gemm_pair(GemmParams& p, int n_pairs, void* workspace, size_t workspa
   cfg.blockDim = dim3(C::kThreads, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attrs[1];
+  cudaLaunchAttribute attrs[2];
   attrs[0].id = cudaLaunchAttributeClusterDimension;  // the two CTAs of a cluster run on the two SMs of one TPC
   attrs[0].val.clusterDim.x = 2;
   attrs[0].val.clusterDim.y = 1;
   attrs[0].val.clusterDim.z = 1;
+  int na = 1;
+  if (p.flags & B200Q_FLAG_PDL) {
+    // the next launch's CTAs take an SM as soon as this launch's pair there is done: set-up and the first weight
+    // stages (constants) overlap this launch's tail; X, the epilogue operands and the workspace wait (griddepcontrol.wait)
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attrs;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
   if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelEx(gemm pair)");
   count_launch();

@@ -350,7 +350,7 @@ def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, 
     return out
 
 
-def gemm_multi(weights, X, spec, epilogues=None, ep0s=None, outs=None, ws=None, streamk=True, tile=None):
+def gemm_multi(weights, X, spec, epilogues=None, ep0s=None, outs=None, ws=None, streamk=True, tile=None, pdl=False):
     """b200q_gemm_multi: up to three weights that read the same X (q | k | v) in ONE launch of the CTA-pair kernel.
     weights: [(packed, scale) | (packed, scale, zmin), ...]; epilogues / ep0s: per weight ("none" | "bias" | ..).
     Returns the outputs [dtype[..., M, N_i]]."""
@@ -379,7 +379,7 @@ def gemm_multi(weights, X, spec, epilogues=None, ep0s=None, outs=None, ws=None, 
         arr[i] = _lib.GemmOp(packed.data_ptr(), scale.data_ptr(), _ptr(zmin), _ptr(ep0s[i]), None, None, out.data_ptr(), N, ep)
         res.append(out)
         keep.append((packed, scale, zmin))
-    flags = GEMM_TILES[tile]
+    flags = GEMM_TILES[tile] | (FLAG_PDL if pdl else 0)
     flags |= FLAG_GEMM_STREAMK if streamk == "force" else (0 if streamk else FLAG_GEMM_NO_STREAMK)
     if ws is False:
         wp, wb = None, 0

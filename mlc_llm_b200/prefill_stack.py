@@ -35,11 +35,12 @@ class PrefillStack:
     """Runs the prefill GEMM sequence on the weights of a DecodeStack (same packed tensors: decode and prefill
     share the weights exactly as in the reference, where both `decoding` and `encoding` read the same params)."""
 
-    def __init__(self, stack: DecodeStack, M: int, fuse_qkv: bool = True):
+    def __init__(self, stack: DecodeStack, M: int, fuse_qkv: bool = True, pdl: bool = True):
         if stack.spec.dtype != "float16":
             raise NotImplementedError("prefill GEMM: f16 schemes (b200q_gemm)")
         self.st, self.M = stack, M
         self.fuse_qkv = fuse_qkv and stack.spec.sym
+        self.pdl = pdl  # programmatic dependent launch between the GEMMs of the pass (B200Q_FLAG_PDL)
         sh, tp, dev = stack.shape, stack.tp_size, stack.device
         h, i = sh.hidden, sh.inter
         e = lambda *s: torch.zeros(*s, dtype=torch.float16, device=dev)
@@ -62,7 +63,7 @@ class PrefillStack:
         return tot
 
     def _gemm(self, w, X, ep, out, ep0=None, ep1=None, ep2=None):
-        ops.gemm(w.packed, w.scale, X, self.st.spec, ep, ep0, ep1, ep2, out=out)
+        ops.gemm(w.packed, w.scale, X, self.st.spec, ep, ep0, ep1, ep2, out=out, pdl=self.pdl)
         self.gemms_per_pass += 1
         self.launches_per_pass += 1
 
@@ -70,7 +71,7 @@ class PrefillStack:
         """q | k | v read the same x: one launch (b200q_gemm_multi), three outputs with their own bias."""
         if self.fuse_qkv:
             ops.gemm_multi([(w[n].packed, w[n].scale) for n in "qkv"], x, self.st.spec, [ep] * 3,
-                           [b[n] if b is not None else None for n in "qkv"], outs=[self.q, self.k, self.v])
+                           [b[n] if b is not None else None for n in "qkv"], outs=[self.q, self.k, self.v], pdl=self.pdl)
             self.gemms_per_pass += 3  # Linears; one launch
             self.launches_per_pass += 1
         else:
