@@ -104,6 +104,7 @@ struct GemmParams {
   int n_ops;
   GemmOp op[kMaxGemmOps];
   int nt_begin[kMaxGemmOps + 1];  // column tiles [nt_begin[i], nt_begin[i + 1]) belong to op i; unused entries: INT_MAX
+  int gelu_lut;  // pair kernel: 1 = a weight of the launch has the bias + GELU epilogue: tabulate erf in shared memory
   // stream-K schedule of the pair kernel (see TileSched): 0 = whole tiles dealt round-robin
   int streamk;
   unsigned* ws_flags;  // [pair][CTA rank][epilogue warp]: 1 = that warp's rows of the pair's partial tile are in ws_partial
@@ -223,7 +224,46 @@ __device__ __forceinline__ void dequant_chunk(const uint32_t (&w)[8], const uint
 // ---- epilogue: 32 consecutive columns of one output row ------------------------------------------------
 // y = f16(acc) first (the reference's matmul result is an f16 tensor), then every epilogue op in f16,
 // op for op (ep_f16 in common.cuh).  bias operands are [N]; residual / multiply operands are [M, N].
+// GELU through a table: the reference's op sequence is  v = y + b; t = v * f16(0.7071..); e = f16(erf(f32(t))); out =
+// v * (f16(0.5) + e * f16(0.5)),  i.e. e is a function of the 16 bits of t.  The pair kernel's epilogue warps tabulate
+// e = f16(erff(t)) for every f16 t in [0, 4) (17408 entries, 34 KB of shared memory; erf is odd, |t| >= 4 gives 1)
+// while the first tile's main loop runs, and a lookup replaces the ~40 instructions of erff() - bit-identical by
+// construction.  2048 x 2560 -> 10240 + bias + GELU: 144 -> 1xx us.
+constexpr int kGeluLutEntries = 0x4400;  // f16 bit patterns of [0, 4)
+constexpr int kGeluLutBytes = kGeluLutEntries * 2;
+__device__ __forceinline__ __half gelu_lut_f16(float acc, __half bias, uint32_t lut) {
+  const __half v = __hadd(__float2half_rn(acc), bias);
+  const __half t = __hmul(v, __float2half_rn(0.70710678118654757f));
+  const uint32_t tb = __half_as_ushort(t), a = tb & 0x7FFFu;
+  uint32_t eb;
+  if (a < (uint32_t)kGeluLutEntries) {
+    unsigned short r;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(lut + 2u * a));
+    eb = r;
+  } else {
+    eb = (a > 0x7C00u) ? 0x7E00u : 0x3C00u;  // NaN stays NaN, |t| >= 4 (and inf): erf = 1
+  }
+  const __half e = __ushort_as_half((unsigned short)(eb | (tb & 0x8000u)));
+  const __half h = __hadd(__float2half_rn(0.5f), __hmul(e, __float2half_rn(0.5f)));
+  return __hmul(v, h);
+}
+
 template <class P>  // GemmParams (single-CTA kernel) or GemmOp (pair kernel)
+__device__ __forceinline__ void epilogue_row(const P& p, const uint32_t (&acc)[32], int m, int n0, uint32_t gelu_lut) {
+  // the table variant: bias + GELU only (the launcher picks it for exactly that epilogue)
+  const size_t row = (size_t)m * p.N;
+  __half* y = reinterpret_cast<__half*>(p.Y) + row + n0;
+#pragma unroll
+  for (int c = 0; c < 32; c += 8) {
+    if (n0 + c >= p.N) break;
+    __align__(16) __half o[8], a0[8];
+    *reinterpret_cast<uint4*>(a0) = *reinterpret_cast<const uint4*>(p.ep0 + n0 + c);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = gelu_lut_f16(__uint_as_float(acc[c + i]), a0[i], gelu_lut);
+    *reinterpret_cast<uint4*>(y + c) = *reinterpret_cast<const uint4*>(o);
+  }
+}
+template <class P>
 __device__ __forceinline__ void epilogue_row(const P& p, const uint32_t (&acc)[32], int m, int n0) {
   const int ep = p.epilogue;
   const size_t row = (size_t)m * p.N;
@@ -606,12 +646,13 @@ struct Pair {
   static constexpr int kBarOff = kBOff + kBStages * kBStage;
   static constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 4;
   static constexpr int kBytes = kBarOff + kNumBars * 8 + 16;
+  static constexpr int kLutOff = (kBytes + 15) / 16 * 16;  // GELU table (only allocated for launches with a GELU epilogue)
   static constexpr int kTmemCols = 2 * BN;              // two accumulators: 512 or 256 columns
   // stream-K cuts a tile's k range where an X stage (4 steps of 16 k) and a weight stage (kKSteps) both begin
   static constexpr int kChunk = (B::kKSteps % 4 == 0) ? B::kKSteps : 4 * B::kKSteps;
 };
 
-template <int MODE, int BN>
+template <int MODE, int BN, bool kGelu = false>
 __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(const __grid_constant__ GemmParams p) {
   using C = Pair<MODE, BN>;
   using B = BCfg<MODE>;
@@ -739,6 +780,17 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
     // ================= epilogue: this CTA's 128 rows of the pair's tile ============================================
     const int quarter = warp & 3;
     const int row_local = quarter * 32 + lane;
+    // (a separate instantiation: the table path in the common kernel pushed it over its register budget - a stack
+    // frame in this kernel halves its speed)
+    uint32_t gelu_lut = 0u;
+    if constexpr (kGelu) {  // (before the wait: nothing here depends on the previous kernel)
+      gelu_lut = base + C::kLutOff;
+      for (int i = row_local; i < kGeluLutEntries; i += kEpWarps * 32) {
+        const __half e = __float2half_rn(erff(__half2float(__ushort_as_half((unsigned short)i))));
+        asm volatile("st.shared.u16 [%0], %1;" ::"r"(gelu_lut + 2u * i), "h"(__half_as_ushort(e)) : "memory");
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpWarps * 32) : "memory");
+    }
     pdl_wait();  // the workspace, the epilogue operands and Y belong to the previous kernel until here
     // workspace slot / flags of (pair q, this rank): the slot is [BN / 4 column quads][128 rows] float4, so that a warp
     // (32 consecutive rows) moves 512 contiguous bytes per instruction
@@ -830,9 +882,13 @@ __global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(c
             }
           }
           if (m < p.M) {  // (weights indexed with constants only, see pick_op)
-            if (oi == 0) { if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c); }
-            else if (oi == 1) { if (n0 + c < p.op[1].N) epilogue_row(p.op[1], v, m, n0 + c); }
-            else { if (n0 + c < p.op[2].N) epilogue_row(p.op[2], v, m, n0 + c); }
+            if constexpr (kGelu) {  // (single-weight launches only)
+              if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c, gelu_lut);
+            } else {
+              if (oi == 0) { if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c); }
+              else if (oi == 1) { if (n0 + c < p.op[1].N) epilogue_row(p.op[1], v, m, n0 + c); }
+              else { if (n0 + c < p.op[2].N) epilogue_row(p.op[2], v, m, n0 + c); }
+            }
           }
         }
         if (fin) {  // the slots have been read: lower the flags for the next launch
@@ -1025,15 +1081,24 @@ int launch_gemm_pair(GemmParams& p, int n_pairs, void* workspace, size_t workspa
     static const int dbg = getenv("B200Q_GEMM_DEBUG") ? atoi(getenv("B200Q_GEMM_DEBUG")) : 0;
     p.debug = dbg;  // experiments: 4 = partial tiles are not stored, 8 = not loaded (results wrong, protocol intact)
   }
-  const size_t smem = (size_t)C::kBytes + 1024;
-  auto kern = gemm_tc2_kernel<MODE, BN>;
-  static std::atomic<bool> attr_set[64];
+  // bias + GELU on a single weight with 256-wide tiles: the instantiation that tabulates erf in shared memory
+  const bool gelu = (BN == 256) && p.n_ops == 1 && p.op[0].epilogue == B200Q_EP_BIAS_GELU;
+  p.gelu_lut = gelu ? 1 : 0;
+  const size_t smem_max = (size_t)C::kLutOff + kGeluLutBytes + 1024;
+  const size_t smem = gelu ? smem_max : (size_t)C::kBytes + 1024;
+  static_assert(C::kLutOff + kGeluLutBytes + 1024 <= 232448, "pair kernel + GELU table exceed 227 KB of shared memory");
+  using KernT = void (*)(GemmParams);
+  KernT kern = gemm_tc2_kernel<MODE, BN, false>;
+  if constexpr (BN == 256) {
+    if (gelu) kern = gemm_tc2_kernel<MODE, BN, true>;
+  }
+  static std::atomic<bool> attr_set[64][2];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
-  if (dev < 0 || !attr_set[dev].load(std::memory_order_relaxed)) {
+  if (dev < 0 || !attr_set[dev][gelu].load(std::memory_order_relaxed)) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gemm pair smem)");
-    if (dev >= 0) attr_set[dev].store(true, std::memory_order_relaxed);
+    if (dev >= 0) attr_set[dev][gelu].store(true, std::memory_order_relaxed);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * n_pairs, 1, 1);

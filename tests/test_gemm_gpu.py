@@ -270,3 +270,30 @@ def test_gemm_multi_equals_single_launches(name, M, K, Ns):
         y64, ab = qo.gemm_f64(packed, scale, X[rows], fmt)
         d = np.abs(y[rows].astype(np.float64) - ref[rows].astype(np.float64))
         assert (d <= 2 * qo.tolerance(y64, ab, False) + 2.0 ** -10 * np.abs(ref[rows].astype(np.float64))).all()
+
+
+@pytest.mark.parametrize("name", F16)
+def test_gemm_gelu_table_equals_erff(name):
+    """bias + GELU on 256-wide pair tiles reads erf from a shared-memory table of f16(erff(t)) for every f16 t in [0, 4)
+    (csrc/gemm.cu, kGelu instantiation); the other tile kernels call erff(): identical bits, also for |t| >= 4, tiny t
+    and both signs."""
+    fmt = qo.FORMATS[name]
+    M, K, N = 300, 640, 520
+    if fmt.nbit == 3:
+        K = 640 // 40 * 40
+    packed, scale = rand_weight(fmt, K, N, seed=5)
+    scale = (scale.astype(np.float32) * 40).astype(np.float16)  # |t| up to ~10
+    rng = np.random.default_rng(6)
+    X = rng.standard_normal((M, K)).astype(np.float16)
+    X[:40] *= np.float16(1e-3)  # rows with tiny pre-activations
+    bias = (rng.standard_normal(N) * 0.5).astype(np.float16)
+    p, s, xd, b = dev(packed), dev(scale), dev(X), dev(bias)
+    lut = host(ops.gemm(p, s, xd, name, "bias_gelu", b, tile="pair256", ws=False))
+    for other in ("pair128", "single"):
+        assert beq(lut, host(ops.gemm(p, s, xd, name, "bias_gelu", b, tile=other, ws=False))), other
+    y0 = host(ops.gemm(p, s, xd, name, ws=False))
+    e = qo.apply_epilogue(y0, qo.EP_BIAS_GELU, np.broadcast_to(bias, (M, N)))
+    ulp = np.abs(lut.view(np.int16).astype(np.int32) - e.view(np.int16).astype(np.int32))
+    assert ulp.max() <= 1
+    t = (y0.astype(np.float32) + bias) * 0.7071
+    assert (np.abs(t) >= 4).any() and (np.abs(t) < 1e-2).any()
