@@ -380,7 +380,7 @@ def prefill_record(args, torch, dev, clocks_fn):
         X = (torch.randn(M, w.K, device=dev, generator=g) * 0.05).half()
         bias = torch.zeros(w.N, dtype=torch.float16, device=dev)
         Y = torch.empty(M, w.N, dtype=torch.float16, device=dev)
-        f = lambda: ops.gemm(w.packed, w.scale, X, fmt, ep, bias, out=Y)
+        f = lambda: ops.gemm(w.packed, w.scale, X, fmt, ep, bias, out=Y, pdl=True)  # (as PrefillStack launches it)
         t = time_steps(torch, f, 20, 3, torch.cuda.synchronize, ident)
         # the reference's CUDA route from library parts: dequantize to [N, K] in HBM, then a dense NT matmul (cuBLAS)
         Wt = torch.empty(w.N, w.K, dtype=torch.float16, device=dev)
@@ -399,11 +399,11 @@ def prefill_record(args, torch, dev, clocks_fn):
     Ys = [torch.empty(M, w0[n].N, dtype=torch.float16, device=dev) for n in "qkv"]
     bs = [torch.zeros(w0[n].N, dtype=torch.float16, device=dev) for n in "qkv"]
     Ws = [(w0[n].packed, w0[n].scale) for n in "qkv"]
-    t_one = time_steps(torch, lambda: ops.gemm_multi(Ws, X, fmt, ["bias"] * 3, bs, outs=Ys), 20, 3, torch.cuda.synchronize, ident)
+    t_one = time_steps(torch, lambda: ops.gemm_multi(Ws, X, fmt, ["bias"] * 3, bs, outs=Ys, pdl=True), 20, 3, torch.cuda.synchronize, ident)
 
     def three():
         for i in range(3):
-            ops.gemm(Ws[i][0], Ws[i][1], X, fmt, "bias", bs[i], out=Ys[i])
+            ops.gemm(Ws[i][0], Ws[i][1], X, fmt, "bias", bs[i], out=Ys[i], pdl=True)
 
     t_three = time_steps(torch, three, 20, 3, torch.cuda.synchronize, ident)
     fl = 2.0 * M * w0["q"].K * sum(w0[n].N for n in "qkv")
@@ -412,7 +412,7 @@ def prefill_record(args, torch, dev, clocks_fn):
     w = w0["h_to_4h"]
     X = (torch.randn(M, w.K, device=dev, generator=g) * 0.05).half()
     Y = torch.empty(M, w.N, dtype=torch.float16, device=dev)
-    t = time_steps(torch, lambda: ops.gemm(w.packed, w.scale, X, fmt, out=Y), 20, 3, torch.cuda.synchronize, ident)
+    t = time_steps(torch, lambda: ops.gemm(w.packed, w.scale, X, fmt, out=Y, pdl=True), 20, 3, torch.cuda.synchronize, ident)
     shapes.append({"shape": f"{M}x2560->10240 (no epilogue)", "us": round(t * 1e3, 2), "tflops": round(2.0 * M * w.K * w.N / t / 1e9, 1)})
     rec["per_shape"] = shapes
     # CPU port on a row sample: the reference's f16-accumulating NT matmul loop nest on the dequantized weight

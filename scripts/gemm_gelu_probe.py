@@ -24,4 +24,6 @@ for K, N, ep in ((2560, 2560, "bias"), (2560, 10240, "bias_gelu"), (10240, 2560,
     fl = 2.0 * M * K * N
     a = t(lambda: ops.gemm(p, sc, X, fmt, out=Y))
     c = t(lambda: ops.gemm(p, sc, X, fmt, ep, b, out=Y))
-    print(f"EP {fmt} {M}x{K}x{N}: none {a * 1e3:6.1f} us {fl / a / 1e9:6.1f} TF | {ep} {c * 1e3:6.1f} us {fl / c / 1e9:6.1f} TF", flush=True)
+    d = t(lambda: ops.gemm(p, sc, X, fmt, ep, b, out=Y, pdl=True))
+    e = t(lambda: ops.gemm(p, sc, X, fmt, ep, b, out=Y, pdl=True, streamk=False))
+    print(f"EP {fmt} {M}x{K}x{N}: none {a * 1e3:6.1f} us {fl / a / 1e9:6.1f} TF | {ep} {c * 1e3:6.1f} us {fl / c / 1e9:6.1f} TF | +pdl {d * 1e3:6.1f} us {fl / d / 1e9:6.1f} TF | +pdl whole tiles {e * 1e3:6.1f} us {fl / e / 1e9:6.1f} TF", flush=True)
