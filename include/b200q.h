@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 106 /* major*100 + minor */
+#define B200Q_VERSION 107 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -353,6 +353,10 @@ B200Q_API int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* 
  * transform/transpose_matmul.py:34-101, dispatch/llama/main.py:3884-3981). f16 only. */
 B200Q_API int b200q_nt_matmul(const void* X, const void* T, const void* ep0, const void* ep1,
                     const void* ep2, void* Y, int M, int K, int N, int epilogue, void* stream);
+/* the same with the stream-K workspace of b200q_gemm_ws (and B200Q_FLAG_PDL / B200Q_FLAG_GEMM_[NO_]STREAMK) */
+B200Q_API int b200q_nt_matmul_ws(const void* X, const void* T, const void* ep0, const void* ep1,
+                       const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags,
+                       void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -96,6 +96,7 @@ PROTOTYPES = {
                                  c_void_p]),
     "b200q_gemm_ws": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
     "b200q_nt_matmul": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
+    "b200q_nt_matmul_ws": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),
 }
 
 _lib = None

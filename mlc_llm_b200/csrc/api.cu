@@ -65,7 +65,8 @@ int gemm_launch(const void* packed, const void* scale, const void* X, const void
                 const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue, unsigned flags,
                 cudaStream_t stream, void* workspace, size_t workspace_bytes);
 int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,
-                     int M, int K, int N, int epilogue, cudaStream_t stream);
+                     int M, int K, int N, int epilogue, cudaStream_t stream, unsigned flags, void* workspace,
+                     size_t workspace_bytes);
 
 static bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
@@ -425,13 +426,22 @@ int b200q_gemm_ws(const void* packed, const void* scale, const void* zmin, const
 
 int b200q_nt_matmul(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,
                     int M, int K, int N, int epilogue, void* stream) {
+  return b200q_nt_matmul_ws(X, T, ep0, ep1, ep2, Y, M, K, N, epilogue, 0u, nullptr, 0, stream);
+}
+
+int b200q_nt_matmul_ws(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y,
+                       int M, int K, int N, int epilogue, unsigned flags, void* workspace, size_t workspace_bytes,
+                       void* stream) {
+  if (workspace && !aligned(workspace, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_nt_matmul_ws: workspace must be 16-byte aligned");
+  if (!workspace) workspace_bytes = 0;
   if (!X || !T || !Y) return set_error(B200Q_ERR_NULL, "b200q_nt_matmul: NULL pointer");
   if (M < 0 || K <= 0 || N <= 0 || N % 8 != 0 || K % 8 != 0)
     return set_error(B200Q_ERR_BAD_SHAPE, "b200q_nt_matmul: M=%d K=%d N=%d", M, K, N);
   if (M == 0) return B200Q_OK;
   if (!aligned(X, 16) || !aligned(T, 16) || !aligned(Y, 16))
     return set_error(B200Q_ERR_BAD_ALIGN, "b200q_nt_matmul: pointers must be 16-byte aligned");
-  return nt_matmul_launch(X, T, ep0, ep1, ep2, Y, M, K, N, epilogue, reinterpret_cast<cudaStream_t>(stream));
+  return nt_matmul_launch(X, T, ep0, ep1, ep2, Y, M, K, N, epilogue, reinterpret_cast<cudaStream_t>(stream), flags, workspace,
+                          workspace_bytes);
 }
 
 }  // extern "C"

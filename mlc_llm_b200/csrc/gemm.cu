@@ -620,7 +620,10 @@ struct TileSched {
 };
 constexpr int kWsFlagBytes = 16384;  // flags of up to 512 pairs
 
-template <int MODE, int BN>
+#ifndef B200Q_GEMM_BSTAGES
+#define B200Q_GEMM_BSTAGES 6
+#endif
+template <int MODE, int BN, bool kGelu = false>
 struct Pair {
   using B = BCfg<MODE>;
   static constexpr bool kDenseB = (MODE == kDense);
@@ -639,7 +642,8 @@ struct Pair {
   static constexpr int kRows = kDenseB ? 8 : B::kRows;  // packed word rows per stage: 8 / 8 / 16
   static constexpr int kItems = kRows / 8;              // passes per stage: 1 (2 for int8)
   static constexpr int kBStage = kHalfN * kBK * 2;      // 16 KB (20 KB int3) / half of it for BN 128
-  static constexpr int kBStages = (BN == 256) ? 6 : 8;  // a multiple of kDqGroups
+  // a multiple of kDqGroups; the GELU-table instantiation gives 34 KB of the ring to the table
+  static constexpr int kBStages = (BN == 256) ? (kGelu ? 6 : B200Q_GEMM_BSTAGES) : 8;
   static constexpr int kThreads = (kFirstDqWarp + (kDenseB ? 0 : kDqWarpsAll)) * 32;
   static constexpr int kAOff = 0;
   static constexpr int kBOff = kAStages * kAStageBytes;
@@ -653,8 +657,8 @@ struct Pair {
 };
 
 template <int MODE, int BN, bool kGelu = false>
-__global__ void __launch_bounds__(Pair<MODE, BN>::kThreads, 1) gemm_tc2_kernel(const __grid_constant__ GemmParams p) {
-  using C = Pair<MODE, BN>;
+__global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_kernel(const __grid_constant__ GemmParams p) {
+  using C = Pair<MODE, BN, kGelu>;
   using B = BCfg<MODE>;
   constexpr bool kDenseB = C::kDenseB;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -1084,9 +1088,10 @@ int launch_gemm_pair(GemmParams& p, int n_pairs, void* workspace, size_t workspa
   // bias + GELU on a single weight with 256-wide tiles: the instantiation that tabulates erf in shared memory
   const bool gelu = (BN == 256) && p.n_ops == 1 && p.op[0].epilogue == B200Q_EP_BIAS_GELU;
   p.gelu_lut = gelu ? 1 : 0;
-  const size_t smem_max = (size_t)C::kLutOff + kGeluLutBytes + 1024;
-  const size_t smem = gelu ? smem_max : (size_t)C::kBytes + 1024;
-  static_assert(C::kLutOff + kGeluLutBytes + 1024 <= 232448, "pair kernel + GELU table exceed 227 KB of shared memory");
+  using CG = Pair<MODE, BN, true>;
+  const size_t smem = gelu ? (size_t)CG::kLutOff + kGeluLutBytes + 1024 : (size_t)C::kBytes + 1024;
+  static_assert(CG::kLutOff + kGeluLutBytes + 1024 <= 232448, "pair kernel + GELU table exceed 227 KB of shared memory");
+  static_assert(C::kBytes + 1024 <= 232448, "pair kernel exceeds 227 KB of shared memory");
   using KernT = void (*)(GemmParams);
   KernT kern = gemm_tc2_kernel<MODE, BN, false>;
   if constexpr (BN == 256) {
@@ -1284,7 +1289,8 @@ int gemm_multi_launch(const b200q_gemm_op* ops, int n_ops, const void* X, int M,
 }
 
 int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* ep1, const void* ep2, void* Y, int M,
-                     int K, int N, int epilogue, cudaStream_t stream) {
+                     int K, int N, int epilogue, cudaStream_t stream, unsigned flags, void* workspace,
+                     size_t workspace_bytes) {
   if (epilogue < 0 || epilogue >= B200Q_NUM_EP) return set_error(B200Q_ERR_UNSUPPORTED, "b200q_nt_matmul: epilogue %d", epilogue);
   if (int e = check_epilogue_operands(epilogue, ep0, ep1, ep2, "b200q_nt_matmul")) return e;
   GemmParams p{};
@@ -1294,10 +1300,11 @@ int nt_matmul_launch(const void* X, const void* T, const void* ep0, const void* 
   p.Y = Y;
   p.M = M; p.K = K; p.N = N;
   p.epilogue = epilogue;
+  p.flags = flags & (B200Q_FLAG_PDL | B200Q_FLAG_GEMM_STREAMK | B200Q_FLAG_GEMM_NO_STREAMK);
   if (int e = make_tmap_2d(&p.tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, X, K, M, kAK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
   const int bn = pick_pair_bn(M, N, device_sm_count() / 2);  // the pair kernel loads BN / 2 rows of T per CTA
   if (int e = make_tmap_2d(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, T, K, N, kAK, bn ? bn / 2 : kBN, CU_TENSOR_MAP_SWIZZLE_128B)) return e;
-  return launch_gemm<kDense>(p, stream);
+  return launch_gemm<kDense>(p, stream, workspace, workspace_bytes);
 }
 
 }  // namespace b200q

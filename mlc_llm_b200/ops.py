@@ -390,8 +390,8 @@ def gemm_multi(weights, X, spec, epilogues=None, ep0s=None, outs=None, ws=None, 
     return res
 
 
-def nt_matmul(X, T, epilogue="none", ep0=None, ep1=None, ep2=None, out=None):
-    """NT_matmul: Y[m, n] = sum_k X[m, k] * T[n, k] (+ epilogue), f16, tcgen05."""
+def nt_matmul(X, T, epilogue="none", ep0=None, ep1=None, ep2=None, out=None, ws=None, streamk=True, pdl=False):
+    """NT_matmul: Y[m, n] = sum_k X[m, k] * T[n, k] (+ epilogue), f16, tcgen05 (ws / streamk / pdl as in gemm)."""
     ep = _ep_id(epilogue)
     _need_cuda(X, T, ep0, ep1, ep2, out)
     K = X.shape[-1]
@@ -403,8 +403,14 @@ def nt_matmul(X, T, epilogue="none", ep0=None, ep1=None, ep2=None, out=None):
     if out is None:
         out = torch.empty(tuple(X.shape[:-1]) + (N,), dtype=odt, device=X.device)
     L = _lib.lib()
-    _lib.check(L.b200q_nt_matmul(X.data_ptr(), T.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2), out.data_ptr(),
-                                 M, K, N, ep, _stream()))
+    flags = (FLAG_PDL if pdl else 0) | (FLAG_GEMM_STREAMK if streamk == "force" else (0 if streamk else FLAG_GEMM_NO_STREAMK))
+    if ws is False:
+        wp, wb = None, 0
+    else:
+        w_ = gemm_workspace(X.device) if ws is None else ws
+        wp, wb = w_.data_ptr(), w_.numel() * w_.element_size()
+    _lib.check(L.b200q_nt_matmul_ws(X.data_ptr(), T.data_ptr(), _ptr(ep0), _ptr(ep1), _ptr(ep2), out.data_ptr(),
+                                    M, K, N, ep, flags, wp, wb, _stream()))
     return out
 
 

@@ -297,3 +297,20 @@ def test_gemm_gelu_table_equals_erff(name):
     assert ulp.max() <= 1
     t = (y0.astype(np.float32) + bias) * 0.7071
     assert (np.abs(t) >= 4).any() and (np.abs(t) < 1e-2).any()
+
+
+@pytest.mark.parametrize("M,K,N", [(2048, 2560, 2560), (300, 640, 520)])
+def test_nt_matmul_streamk(M, K, N):
+    """dense NT_matmul through the same pair kernel with the stream-K workspace: deterministic, inside the bound"""
+    rng = np.random.default_rng(M + N)
+    X = rng.standard_normal((M, K)).astype(np.float16)
+    T = (rng.standard_normal((N, K)) * 0.02).astype(np.float16)
+    xd, td = dev(X), dev(T)
+    whole = host(ops.nt_matmul(xd, td, streamk=False))
+    assert beq(whole, host(ops.nt_matmul(xd, td, ws=False)))
+    a = host(ops.nt_matmul(xd, td, streamk="force"))
+    assert beq(a, host(ops.nt_matmul(xd, td, streamk="force")))
+    rows = rng.choice(M, 32, replace=False)
+    y64, ab = co.nt_matmul_f64_f16(X[rows], T)
+    assert (np.abs(a[rows].astype(np.float64) - y64) <= qo.tolerance(y64, ab, False)).all()
+    assert (np.abs(whole[rows].astype(np.float64) - y64) <= qo.tolerance(y64, ab, False)).all()
