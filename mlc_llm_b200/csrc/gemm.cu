@@ -46,6 +46,10 @@ constexpr int kBN = 256;                 // tile columns (UMMA N)
 constexpr int kAK = 64;                  // k per A stage (one 128-byte swizzle row of f16)
 constexpr int kAStageBytes = kBM * kAK * 2;  // 16 KB
 constexpr int kAStages = 4;
+#ifndef B200Q_GEMM_ASTAGES
+#define B200Q_GEMM_ASTAGES 4
+#endif
+constexpr int kAStagesP = B200Q_GEMM_ASTAGES;  // X stages of the pair kernel
 constexpr int kNAtoms = kBN / 64;        // MN-major swizzle atoms along N per B stage
 constexpr int kKAtomBytes = kNAtoms * 1024;  // one 8-k slab of a B stage: [n atom][8 k rows][128 B]
 constexpr int kDqWarps = 8;
@@ -643,12 +647,12 @@ struct Pair {
   static constexpr int kItems = kRows / 8;              // passes per stage: 1 (2 for int8)
   static constexpr int kBStage = kHalfN * kBK * 2;      // 16 KB (20 KB int3) / half of it for BN 128
   // a multiple of kDqGroups; the GELU-table instantiation gives 34 KB of the ring to the table
-  static constexpr int kBStages = (BN == 256) ? (kGelu ? 6 : B200Q_GEMM_BSTAGES) : 8;
+  static constexpr int kBStages = (BN == 256) ? (kGelu ? (kAStagesP > 4 ? 4 : 6) : B200Q_GEMM_BSTAGES) : 8;
   static constexpr int kThreads = (kFirstDqWarp + (kDenseB ? 0 : kDqWarpsAll)) * 32;
   static constexpr int kAOff = 0;
-  static constexpr int kBOff = kAStages * kAStageBytes;
+  static constexpr int kBOff = kAStagesP * kAStageBytes;
   static constexpr int kBarOff = kBOff + kBStages * kBStage;
-  static constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 4;
+  static constexpr int kNumBars = 2 * kAStagesP + 2 * kBStages + 4;
   static constexpr int kBytes = kBarOff + kNumBars * 8 + 16;
   static constexpr int kLutOff = (kBytes + 15) / 16 * 16;  // GELU table (only allocated for launches with a GELU epilogue)
   static constexpr int kTmemCols = 2 * BN;              // two accumulators: 512 or 256 columns
@@ -666,8 +670,8 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
   unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t a_ring = base + C::kAOff, b_ring = base + C::kBOff;
   const uint32_t bars = base + C::kBarOff;
-  const uint32_t a_full = bars, a_empty = a_full + 8 * kAStages;
-  const uint32_t b_full = a_empty + 8 * kAStages, b_empty = b_full + 8 * C::kBStages;
+  const uint32_t a_full = bars, a_empty = a_full + 8 * kAStagesP;
+  const uint32_t b_full = a_empty + 8 * kAStagesP, b_empty = b_full + 8 * C::kBStages;
   const uint32_t t_full = b_empty + 8 * C::kBStages, t_empty = t_full + 16;
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(base_ptr + C::kBarOff + C::kNumBars * 8);
 
@@ -689,7 +693,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tm_a);
     if constexpr (kDenseB) prefetch_tmap(&p.tm_b);
-    for (int s = 0; s < kAStages; ++s) {
+    for (int s = 0; s < kAStagesP; ++s) {
       mbar_init(a_full + 8 * s, 1);   // the leader's expect_tx arrive; both CTAs' TMA bytes
       mbar_init(a_empty + 8 * s, 1);  // multicast commit
     }
@@ -728,7 +732,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
           if (rank == 0) mbar_expect_tx(a_full + 8 * sa, 2 * kAStageBytes);
           tma_load_2d_pair(a_ring + sa * kAStageBytes, &p.tm_a, i * kAK, m0, a_full + 8 * sa);
         }
-        if (++sa == kAStages) { sa = 0; pa ^= 1; }
+        if (++sa == kAStagesP) { sa = 0; pa ^= 1; }
         if constexpr (kDenseB) {
           mbar_wait(b_empty + 8 * sb, pb ^ 1);
           if (elect_one()) {
@@ -773,7 +777,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
             if (rel_a) umma_commit_pair(a_empty + 8 * sa);
             if (rel_b) umma_commit_pair(b_empty + 8 * sb);
             if (last) umma_commit_pair(t_full + 8 * acc);
-            if (rel_a) { ka = 0; if (++sa == kAStages) { sa = 0; pa ^= 1; } } else { ++ka; }
+            if (rel_a) { ka = 0; if (++sa == kAStagesP) { sa = 0; pa ^= 1; } } else { ++ka; }
             if (rel_b) { kb = 0; if (++sb == C::kBStages) { sb = 0; pb ^= 1; } } else { ++kb; }
           }
         }
