@@ -192,7 +192,7 @@ B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* 
  * replays give identical bits for a given SM count.
  * Launch: the tcgen05 programs use programmatic dependent launch (B200Q_PROG_PDL): consecutive program launches on
  * a stream overlap their set-up with the predecessor's tail; kernels of other kinds before / after are ordered as
- * usual.
+ * usual.  As with B200Q_FLAG_PDL, no kernel in flight may WRITE the packed words or scales a program reads.
  *
  *   1. b200q_gemv_program_build fills a HOST blob of b200q_gemv_program_bytes(n_steps) bytes
  *      (tensor-map descriptors + step table; needs a CUDA context but launches nothing);
