@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 107 /* major*100 + minor */
+#define B200Q_VERSION 108 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -348,6 +348,12 @@ typedef struct {
 } b200q_gemm_op;
 B200Q_API int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt,
                      unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Host-side evaluation of the CTA-pair kernel's work distribution (no GPU needed; for tests): writes the segments of
+ * `pair` in processing order as 5 ints each (tile, first 16-k step, end step, kind 0 whole / 1 partial writer /
+ * 2 finisher, end of the finisher's contributor pairs) and returns the number of segments (-1: bad arguments). */
+B200Q_API int b200q_debug_gemm_schedule(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair,
+                              int* out, int max_seg);
 
 /* Dense NT GEMM on an already dequantized weight  T dtype[N, K]  (replaces NT_matmul*,
  * transform/transpose_matmul.py:34-101, dispatch/llama/main.py:3884-3981). f16 only. */

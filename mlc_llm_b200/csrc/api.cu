@@ -57,6 +57,7 @@ int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, co
                      const void* ep2, void* Y, int M, int K, int N, int epilogue, unsigned flags, cudaStream_t stream,
                      void* workspace, size_t workspace_bytes);
 size_t gemm_workspace_bytes();
+int gemm_schedule_debug(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair, int* out, int max_seg);
 int gemm_multi_launch(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,
                       cudaStream_t stream, void* workspace, size_t workspace_bytes);
 int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
@@ -377,6 +378,11 @@ int b200q_gemm_asym(const void* packed, const void* scale, const void* zmin, con
 }
 
 size_t b200q_gemm_workspace_bytes(void) { return gemm_workspace_bytes(); }
+
+int b200q_debug_gemm_schedule(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair, int* out, int max_seg) {
+  if (!out || n_tiles < 1 || n_ksteps < 1 || chunk < 1 || n_pairs < 1 || pair < 0 || pair >= n_pairs || max_seg < 0) return -1;
+  return gemm_schedule_debug(streamk, n_tiles, n_ksteps, chunk, n_pairs, pair, out, max_seg);
+}
 
 int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,
                      void* workspace, size_t workspace_bytes, void* stream) {

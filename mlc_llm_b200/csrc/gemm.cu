@@ -577,7 +577,7 @@ struct TileSched {
   long long W;
   int n_seg, first_tile, a_off, b_off;
   bool has_tail, has_head;
-  __device__ void init(int streamk_, int pair_, int n_pairs_, int n_tiles, int n_ksteps_, int chunk_) {
+  __host__ __device__ void init(int streamk_, int pair_, int n_pairs_, int n_tiles, int n_ksteps_, int chunk_) {
     streamk = streamk_; pair = pair_; n_pairs = n_pairs_; n_ksteps = n_ksteps_; chunk = chunk_;
     C = (n_ksteps + chunk - 1) / chunk;
     W = (long long)n_tiles * C;
@@ -597,9 +597,9 @@ struct TileSched {
     has_tail = a_off > 0;
     has_head = b_off < C && (n_seg > 1 || !has_tail);
   }
-  __device__ long long range_begin(int q) const { return W * q / n_pairs; }
+  __host__ __device__ long long range_begin(int q) const { return W * q / n_pairs; }
   // i-th segment in PROCESSING order: the tail, the head, then the whole tiles
-  __device__ Seg get(int i) const {
+  __host__ __device__ Seg get(int i) const {
     Seg sg;
     if (!streamk) {
       sg.tile = pair + i * n_pairs; sg.ks0 = 0; sg.ks1 = n_ksteps; sg.kind = 0;
@@ -611,12 +611,12 @@ struct TileSched {
     const int c0 = (j == 0) ? a_off : 0, c1 = (j == n_seg - 1) ? b_off : C;
     sg.tile = first_tile + j;
     sg.ks0 = c0 * chunk;
-    sg.ks1 = min(c1 * chunk, n_ksteps);
+    sg.ks1 = (c1 * chunk < n_ksteps) ? c1 * chunk : n_ksteps;
     sg.kind = (c0 > 0) ? 1 : (c1 < C ? 2 : 0);
     return sg;
   }
   // pairs behind this one that hold a partial of `tile` (the finisher's contributors): (pair, end)
-  __device__ int contributors_end(int tile) const {
+  __host__ __device__ int contributors_end(int tile) const {
     int q = pair + 1;
     while (q < n_pairs && range_begin(q) < (long long)(tile + 1) * C) ++q;
     return q;
@@ -1196,6 +1196,20 @@ int check_epilogue_operands(int epilogue, const void* ep0, const void* ep1, cons
 }
 
 }  // namespace
+
+// The pair kernel's work distribution, evaluated on the host (tests/test_cabi_cpu.py checks its invariants without a
+// GPU): segments of `pair` in PROCESSING order as (tile, ks0, ks1, kind), plus the finisher's contributor range end.
+int gemm_schedule_debug(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair, int* out, int max_seg) {
+  TileSched sc;
+  sc.init(streamk, pair, n_pairs, n_tiles, n_ksteps, chunk);
+  const int n = sc.n_seg < max_seg ? sc.n_seg : max_seg;
+  for (int i = 0; i < n; ++i) {
+    const Seg sg = sc.get(i);
+    out[5 * i + 0] = sg.tile; out[5 * i + 1] = sg.ks0; out[5 * i + 2] = sg.ks1; out[5 * i + 3] = sg.kind;
+    out[5 * i + 4] = (sg.kind == 2) ? sc.contributors_end(sg.tile) : pair + 1;
+  }
+  return sc.n_seg;
+}
 
 size_t gemm_workspace_bytes() {  // flags + one 256 x 256 f32 partial tile per CTA pair
   return (size_t)kWsFlagBytes + (size_t)(device_sm_count() / 2) * 2 * kBM * 256 * sizeof(float);
