@@ -193,6 +193,11 @@ B200Q_API int b200q_gemv_multi(const b200q_gemv_op* ops, int n_ops, const void* 
  * Launch: the tcgen05 programs use programmatic dependent launch (B200Q_PROG_PDL): consecutive program launches on
  * a stream overlap their set-up with the predecessor's tail; kernels of other kinds before / after are ordered as
  * usual.  As with B200Q_FLAG_PDL, no kernel in flight may WRITE the packed words or scales a program reads.
+ * These launches do not carry the cooperative attribute (it serialises consecutive launches: 689 vs 803 tok/s
+ * for a program cut into 97 launches), so two programs launched CONCURRENTLY on different streams of one device
+ * could each hold part of the SMs and wait for the rest: keep the program launches of a device on one stream, or
+ * set B200Q_PROG_PDL=0 (cooperative launches: the driver then never co-schedules two of them).  The watchdog
+ * (b200q_gemv_program_set_watchdog) turns such a wait into an error instead of a hang.
  *
  *   1. b200q_gemv_program_build fills a HOST blob of b200q_gemv_program_bytes(n_steps) bytes
  *      (tensor-map descriptors + step table; needs a CUDA context but launches nothing);
