@@ -65,6 +65,12 @@ constexpr int kBSlots = 2 * kABufs;          // B operand slots: two per (slice,
 #ifndef B200Q_TC_NACC
 #define B200Q_TC_NACC 8
 #endif
+#ifndef B200Q_TC_PBATCH
+#define B200Q_TC_PBATCH 5
+#endif
+// partial-sum slots of a K-split panel polled together by its finisher.  A panel of the 7B shapes spans 5-6 CTAs
+// (4-5 foreign slots).  Measured: 4 per batch 1114, 5: 1123, 6: 1114, 8: 1104 tok/s
+constexpr int kPBatch = B200Q_TC_PBATCH;
 constexpr int kNAcc = B200Q_TC_NACC;         // accumulators in flight (one per block, 16 columns each): 8 or 16
 // ring of per-block group corrections: the activation warps run up to 8 blocks ahead of the MMAs, the MMAs up to
 // kNAcc blocks ahead of the epilogue warps
@@ -761,14 +767,14 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
             finalize = false;
           } else {
             // the other contributors finish their last block of the panel about now: all their slots are polled
-            // at once (one L2 round trip when the sums are there), four at a time
-            for (int o0 = 1; o0 < n_contrib; o0 += 4) {
-              uint2 pv[4];
+            // at once (one L2 round trip when the sums are there), kPBatch at a time
+            for (int o0 = 1; o0 < n_contrib; o0 += kPBatch) {
+              uint2 pv[kPBatch];
 #pragma unroll
-              for (int o = 0; o < 4; ++o)
+              for (int o = 0; o < kPBatch; ++o)
                 if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
 #pragma unroll
-              for (int o = 0; o < 4; ++o)
+              for (int o = 0; o < kPBatch; ++o)
                 if (o0 + o < n_contrib) {  // added in block order
                   if (pv[o].y != tag) {
                     WdSpin sp;
