@@ -366,7 +366,7 @@ def prefill_record(args, torch, dev, clocks_fn):
         "metric": "dolly_v2_3b_q3f16_0_prefill2048_linear_tflops", "value": tf, "unit": "TFLOP/s", "ms_per_pass": ms,
         "config": {"workload": f"{model} {fmt} prefill, M={M}: 6 quantized Linears x {st.n_layers} layers with fused epilogues "
                                "(bias, bias+GELU, bias+2 residual adds); attention / norms excluded", "flop": flops,
-                   "l2": "192 Linears (q|k|v of a layer in one launch: 128 launches) over 1.1 GB of distinct packed weights per pass"},
+                   "l2": "192 Linears (q|k|v|h_to_4h of a layer in one launch: 96 launches) over 1.1 GB of distinct packed weights per pass"},
         "roofline": {"bound": "tensor", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
                      "frac_of_burst": tf / burst, "kernel": "b200q::gemm_tc2_kernel<q3f16_0, 256> (CTA pair, tcgen05.mma.cta_group::2 M = 256, dequant in the B-operand warps, stream-K schedule when whole tiles fill the pairs badly)",
                      "flop_per_launch": flops / max(1, launches), "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (burst beside it)"},

@@ -334,7 +334,8 @@ B200Q_API int b200q_gemm_ws(const void* packed, const void* scale, const void* z
                   const void* ep1, const void* ep2, void* Y, int M, int K, int N, int fmt, int epilogue,
                   unsigned flags, void* workspace, size_t workspace_bytes, void* stream);
 
-/* Up to three weights that read the SAME X in one launch (q | k | v: the reference launches them back to back on the
+/* Up to four weights that read the SAME X in one launch (a fourth one: h_to_4h of a GPT-NeoX layer, which reads the
+ * layer input like q | k | v - one launch when it carries the bias + GELU epilogue and M > 128, two otherwise) (q | k | v: the reference launches them back to back on the
  * same x, relax_model/llama.py:233-236; gpt_neox.py query/key/value).  Tensors stay the reference's separate
  * per-Linear arrays, every weight has its own epilogue and output.  The column tiles of all weights form ONE tile
  * space (and one stream-K split): three 2560-wide NeoX projections cost 3.24 rounds of tiles instead of 3 x 2.

@@ -391,7 +391,7 @@ int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* X, int M, 
   if (fmt_is_variant(fmt) || fmt_is_f32(fmt) || (asym && fmt != B200Q_Q4F16_ASYM))
     return set_error(B200Q_ERR_UNSUPPORTED, "b200q_gemm_multi: fmt %d has no prefill GEMM", fmt);
   if (!ops || !X) return set_error(B200Q_ERR_NULL, "b200q_gemm_multi: NULL ops / X");
-  if (n_ops < 1 || n_ops > 3) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: n_ops=%d not in [1,3]", n_ops);
+  if (n_ops < 1 || n_ops > 4) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: n_ops=%d not in [1,4]", n_ops);
   if (M < 0 || K <= 0) return set_error(B200Q_ERR_BAD_SHAPE, "b200q_gemm_multi: M=%d K=%d", M, K);
   if (M == 0) return B200Q_OK;
   if (!aligned(X, 16)) return set_error(B200Q_ERR_BAD_ALIGN, "b200q_gemm_multi: X must be 16-byte aligned");

@@ -87,7 +87,7 @@ struct GemmOp {
   int N;
   int epilogue;
 };
-constexpr int kMaxGemmOps = 3;
+constexpr int kMaxGemmOps = 4;  // (the fourth only in the GELU-table instantiation: q | k | v | h_to_4h of a NeoX layer)
 
 struct GemmParams {
   CUtensorMap tm_a;  // X f16 [M, K], box 128 x 64, 128B swizzle
@@ -683,7 +683,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
   const int tiles_n = p.nt_begin[p.n_ops];  // over all weights of the launch
   const int n_tiles = tiles_m * tiles_n;
   // column tile -> (weight, first column inside it)
-  auto op_of = [&](int tn) { return (tn >= p.nt_begin[1] ? 1 : 0) + (tn >= p.nt_begin[2] ? 1 : 0); };
+  auto op_of = [&](int tn) { return (tn >= p.nt_begin[1] ? 1 : 0) + (tn >= p.nt_begin[2] ? 1 : 0) + (tn >= p.nt_begin[3] ? 1 : 0); };
   // (the weights are kernel parameters: they are only ever indexed with constants, so every field stays a
   // constant-bank operand - a run-time index made ptxas copy the table to local memory, 2x slower kernels)
   const int n_ksteps = (p.K + 15) >> 4;
@@ -821,7 +821,7 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
       const int tile = sg.tile;
       const int acc = it & 1;
       const int tn = tile / tiles_m, oi = op_of(tn);
-      const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tn - (oi == 0 ? 0 : (oi == 1 ? p.nt_begin[1] : p.nt_begin[2]))) * BN;
+      const int m0 = (tile % tiles_m) * 256 + (int)rank * kBM, n0 = (tn - (oi == 0 ? 0 : (oi == 1 ? p.nt_begin[1] : (oi == 2 ? p.nt_begin[2] : p.nt_begin[3])))) * BN;
       const int m = m0 + row_local;
       const uint32_t t_acc = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
       if (sg.kind == 1) {
@@ -890,8 +890,12 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
             }
           }
           if (m < p.M) {  // (weights indexed with constants only, see pick_op)
-            if constexpr (kGelu) {  // (single-weight launches only)
-              if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c, gelu_lut);
+            if constexpr (kGelu) {  // the LAST weight of the launch (of one, or of four) has the bias + GELU epilogue
+              if (p.n_ops == 1) { if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c, gelu_lut); }
+              else if (oi == 3) { if (n0 + c < p.op[3].N) epilogue_row(p.op[3], v, m, n0 + c, gelu_lut); }
+              else if (oi == 0) { if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c); }
+              else if (oi == 1) { if (n0 + c < p.op[1].N) epilogue_row(p.op[1], v, m, n0 + c); }
+              else { if (n0 + c < p.op[2].N) epilogue_row(p.op[2], v, m, n0 + c); }
             } else {
               if (oi == 0) { if (n0 + c < p.op[0].N) epilogue_row(p.op[0], v, m, n0 + c); }
               else if (oi == 1) { if (n0 + c < p.op[1].N) epilogue_row(p.op[1], v, m, n0 + c); }
@@ -953,7 +957,8 @@ __global__ void __launch_bounds__(Pair<MODE, BN, kGelu>::kThreads, 1) gemm_tc2_k
         const int half0 = (int)rank * C::kHalfN;
         if (oi == 0) load_stage_op(p.op[0], tn * BN + half0, i);
         else if (oi == 1) load_stage_op(p.op[1], (tn - p.nt_begin[1]) * BN + half0, i);
-        else load_stage_op(p.op[2], (tn - p.nt_begin[2]) * BN + half0, i);
+        else if (oi == 2) load_stage_op(p.op[2], (tn - p.nt_begin[2]) * BN + half0, i);
+        else load_stage_op(p.op[3], (tn - p.nt_begin[3]) * BN + half0, i);
       };
       // c = running number of B stages of this CTA over all its segments; this group takes those with c % groups == grp
       long long c0 = 0;  // stages before the current segment
@@ -1090,7 +1095,8 @@ int launch_gemm_pair(GemmParams& p, int n_pairs, void* workspace, size_t workspa
     p.debug = dbg;  // experiments: 4 = partial tiles are not stored, 8 = not loaded (results wrong, protocol intact)
   }
   // bias + GELU on a single weight with 256-wide tiles: the instantiation that tabulates erf in shared memory
-  const bool gelu = (BN == 256) && p.n_ops == 1 && p.op[0].epilogue == B200Q_EP_BIAS_GELU;
+  const bool gelu = (BN == 256) && (p.n_ops == 1 || p.n_ops == 4) && p.op[p.n_ops - 1].epilogue == B200Q_EP_BIAS_GELU;
+  if (p.n_ops == 4 && !gelu) return set_error(B200Q_ERR_UNSUPPORTED, "gemm pair: four weights only as q | k | v | (bias + GELU) on 256-wide tiles");
   p.gelu_lut = gelu ? 1 : 0;
   using CG = Pair<MODE, BN, true>;
   const size_t smem = gelu ? (size_t)CG::kLutOff + kGeluLutBytes + 1024 : (size_t)C::kBytes + 1024;
@@ -1267,6 +1273,11 @@ int gemm_multi_launch(const b200q_gemm_op* ops, int n_ops, const void* X, int M,
   const bool asym = fmt == B200Q_Q4F16_ASYM;
   const int n_pairs = device_sm_count() / 2;
   const int bn = pick_pair_bn(M, ops[0].N, n_pairs, flags);
+  if (n_ops == 4 && !(bn == 256 && ops[3].epilogue == B200Q_EP_BIAS_GELU)) {
+    // four weights in one launch only as q | k | v | (bias + GELU) on 256-wide tiles (the GELU-table instantiation)
+    if (int e = gemm_multi_launch(ops, 3, X, M, K, fmt, flags, stream, workspace, workspace_bytes)) return e;
+    return gemm_multi_launch(ops + 3, 1, X, M, K, fmt, flags, stream, workspace, workspace_bytes);
+  }
   if (n_ops == 1 || bn == 0) {  // the single-CTA kernel takes one weight per launch
     for (int i = 0; i < n_ops; ++i) {
       const b200q_gemm_op& o = ops[i];

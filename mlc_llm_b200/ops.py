@@ -351,7 +351,8 @@ def gemm(packed, scale, X, spec, epilogue="none", ep0=None, ep1=None, ep2=None, 
 
 
 def gemm_multi(weights, X, spec, epilogues=None, ep0s=None, outs=None, ws=None, streamk=True, tile=None, pdl=False):
-    """b200q_gemm_multi: up to three weights that read the same X (q | k | v) in ONE launch of the CTA-pair kernel.
+    """b200q_gemm_multi: up to four weights that read the same X (q | k | v [| h_to_4h with bias + GELU]) in ONE launch
+    of the CTA-pair kernel.
     weights: [(packed, scale) | (packed, scale, zmin), ...]; epilogues / ep0s: per weight ("none" | "bias" | ..).
     Returns the outputs [dtype[..., M, N_i]]."""
     spec = _spec(spec)

@@ -109,8 +109,16 @@ class PrefillStack:
                 self._row(w["down"], self.a, out, "add", self.x1)
             else:
                 b = st.biases[li]
-                self._qkv(w, x, "bias", b)
-                self._gemm(w["h_to_4h"], x, "bias_gelu", self.a, b["h_to_4h"])
+                if self.fuse_qkv and self.M > 128:
+                    # q | k | v | h_to_4h all read the layer input (parallel residual): ONE launch, four outputs
+                    names = ("q", "k", "v", "h_to_4h")
+                    ops.gemm_multi([(w[n].packed, w[n].scale) for n in names], x, self.st.spec, ["bias"] * 3 + ["bias_gelu"],
+                                   [b[n] for n in names], outs=[self.q, self.k, self.v, self.a], pdl=self.pdl)
+                    self.gemms_per_pass += 4
+                    self.launches_per_pass += 1
+                else:
+                    self._qkv(w, x, "bias", b)
+                    self._gemm(w["h_to_4h"], x, "bias_gelu", self.a, b["h_to_4h"])
                 self._row(w["4h_to_h"], self.a, self.m_out, "bias", b["4h_to_h"])
                 self._row(w["dense"], self.q, out, "bias_add2", b["dense"], self.m_out, x)
             x = out

@@ -314,3 +314,32 @@ def test_nt_matmul_streamk(M, K, N):
     y64, ab = co.nt_matmul_f64_f16(X[rows], T)
     assert (np.abs(a[rows].astype(np.float64) - y64) <= qo.tolerance(y64, ab, False)).all()
     assert (np.abs(whole[rows].astype(np.float64) - y64) <= qo.tolerance(y64, ab, False)).all()
+
+
+def test_gemm_multi_four_weights_with_gelu():
+    """q | k | v | h_to_4h of a GPT-NeoX layer in one launch (the GELU-table instantiation with four weights): each
+    output equals the single launch of its weight under the whole-tile schedule; stream-K stays inside the bound."""
+    name = "q3f16_0"
+    fmt = qo.FORMATS[name]
+    M, K, Ns = 520, 640, (264, 264, 264, 1032)
+    rng = np.random.default_rng(3)
+    X = (rng.standard_normal((M, K)) * 0.5).astype(np.float16)
+    xd = dev(X)
+    ws, hw, bs = [], [], []
+    for i, N in enumerate(Ns):
+        packed, scale = rand_weight(fmt, K, N, seed=40 + i)
+        hw.append((packed, scale)); ws.append((dev(packed), dev(scale)))
+        bs.append(dev((rng.standard_normal(N) * 0.3).astype(np.float16)))
+    eps = ["bias", "bias", "bias", "bias_gelu"]
+    single = [host(ops.gemm(w[0], w[1], xd, name, e, b, ws=False)) for w, e, b in zip(ws, eps, bs)]
+    multi = [host(y) for y in ops.gemm_multi(ws, xd, name, eps, bs, streamk=False)]
+    for a, b in zip(single, multi):
+        assert beq(a, b)
+    sk = [host(y) for y in ops.gemm_multi(ws, xd, name, eps, bs, streamk="force")]
+    for a, b in zip(single, sk):
+        d = np.abs(a.astype(np.float64) - b.astype(np.float64))
+        assert (d <= 2.0 ** -8 * np.abs(a.astype(np.float64)) + 2.0 ** -8).all()
+    # four weights without a GELU tail: two launches behind the same call, same results
+    multi2 = [host(y) for y in ops.gemm_multi(ws, xd, name, ["bias"] * 4, bs, streamk=False)]
+    for (packed, scale), y, b in zip(hw, multi2, bs):
+        assert beq(y, host(ops.gemm(dev(packed), dev(scale), xd, name, "bias", b, ws=False)))
