@@ -768,13 +768,14 @@ gemv_program_tc_kernel(const ProgStep* __restrict__ prog, int n_steps, unsigned*
           } else {
             // the other contributors finish their last block of the panel about now: all their slots are polled
             // at once (one L2 round trip when the sums are there), kPBatch at a time
-            for (int o0 = 1; o0 < n_contrib; o0 += kPBatch) {
-              uint2 pv[kPBatch];
+            constexpr int kPB = kTp ? 4 : kPBatch;  // (the tensor-parallel instantiation keeps the batch it was measured with)
+            for (int o0 = 1; o0 < n_contrib; o0 += kPB) {
+              uint2 pv[kPB];
 #pragma unroll
-              for (int o = 0; o < kPBatch; ++o)
+              for (int o = 0; o < kPB; ++o)
                 if (o0 + o < n_contrib) pv[o] = ld_vol_v2(slot0 + (size_t)(o0 + o) * kPanelCols + ht);
 #pragma unroll
-              for (int o = 0; o < kPBatch; ++o)
+              for (int o = 0; o < kPB; ++o)
                 if (o0 + o < n_contrib) {  // added in block order
                   if (pv[o].y != tag) {
                     WdSpin sp;
