@@ -89,6 +89,49 @@ def test_argument_validation_codes():
     assert L.b200q_gemm_asym(a, a, None, a, None, None, None, c, 16, 4096, 4096, 5, 0, 0, st) == -3  # f32 prefill
 
 
+def test_round2_entry_points_validate_before_launching():
+    """b200q_gemm_ws / b200q_gemm_multi / b200q_nt_matmul_ws / b200q_gemv_static: every refusal below happens before
+    any CUDA call, so it can be checked without a GPU."""
+    import ctypes
+
+    L = _lib.lib()
+    a, b, c, d = 0x100000, 0x4000000, 0x8000000, 0xC000000
+    st = None
+    # stream-K workspace: alignment; formats without a prefill GEMM
+    assert L.b200q_gemm_ws(a, a, None, a, None, None, None, b, 256, 4096, 4096, 0, 0, 0, c + 8, 1 << 20, st) == -2
+    assert L.b200q_gemm_ws(a, a, None, a, None, None, None, b, 256, 4096, 4096, 2, 0, 0, None, 0, st) == -3   # q4f32_0
+    assert L.b200q_gemm_ws(a, a, None, a, None, None, None, b, 256, 4096, 4096, 6, 0, 0, None, 0, st) == -3   # uint16 int3
+    assert L.b200q_gemm_ws(a, a, None, a, None, None, None, b, 256, 4096, 4096, 4, 0, 0, None, 0, st) == -5   # asym needs min
+    assert L.b200q_nt_matmul_ws(a, a, None, None, None, b, 256, 4096, 4096, 0, 0, c + 4, 64, st) == -2
+    assert L.b200q_nt_matmul_ws(a, a, None, None, None, b, 256, 4100, 4096, 0, 0, None, 0, st) == -1
+    # several weights in one launch
+    ops4 = (_lib.GemmOp * 5)()
+    for i in range(5):
+        ops4[i] = _lib.GemmOp(a, a, None, None, None, None, b + i * 0x400000, 512, 0)
+    assert L.b200q_gemm_multi(ops4, 5, c, 256, 4096, 0, 0, None, 0, st) == -1 and b"[1,4]" in L.b200q_last_error()
+    assert L.b200q_gemm_multi(ops4, 0, c, 256, 4096, 0, 0, None, 0, st) == -1
+    assert L.b200q_gemm_multi(None, 2, c, 256, 4096, 0, 0, None, 0, st) == -5
+    assert L.b200q_gemm_multi(ops4, 2, c, 0, 4096, 0, 0, None, 0, st) == 0      # M = 0: nothing to do
+    ops4[1].N = 12
+    assert L.b200q_gemm_multi(ops4, 2, c, 256, 4096, 0, 0, None, 0, st) == -1
+    ops4[1].N = 512
+    ops4[1].Y = ops4[0].Y + 1024                                                   # outputs overlap
+    assert L.b200q_gemm_multi(ops4, 2, c, 256, 4096, 0, 0, None, 0, st) == -3 and b"overlap" in L.b200q_last_error()
+    ops4[1].Y = c                                                                  # output aliases X
+    assert L.b200q_gemm_multi(ops4, 2, c, 256, 4096, 0, 0, None, 0, st) == -3 and b"aliases X" in L.b200q_last_error()
+    ops4[1].Y = b + 0x400000
+    ops4[1].epilogue, ops4[1].ep0 = 4, ops4[0].Y                                   # op 1's bias lives in op 0's output
+    assert L.b200q_gemm_multi(ops4, 2, c, 256, 4096, 0, 0, None, 0, st) == -3
+    assert L.b200q_gemm_multi(ops4, 2, c, 256, 4096, 2, 0, None, 0, st) == -3      # f32 format
+    # the allocation-free GEMV: formats without a split-K kernel, bad shapes
+    assert L.b200q_gemv_static(a, a, b, None, c, 40, 8, 6, 0, 0, st) == -3
+    assert L.b200q_gemv_static(a, a, b, None, c, 4096, 12, 0, 0, 0, st) == -1
+    assert L.b200q_gemv_static(a, a, b, None, b, 4096, 4096, 0, 0, 0, st) == -3    # out aliases x
+    # host-side schedule query
+    out = (ctypes.c_int * 20)()
+    assert L.b200q_debug_gemm_schedule(1, 80, 160, 4, 74, 0, out, 4) == 2
+
+
 def test_spec_from_flags():
     assert spec_from_flags("float16", "int4", True, 32).name == "q4f16_0"
     assert spec_from_flags("float16", "int3", True, 32).name == "q3f16_0"
