@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200Q_VERSION 108 /* major*100 + minor */
+#define B200Q_VERSION 109 /* major*100 + minor */
 
 #if defined(__GNUC__)
 #define B200Q_API __attribute__((visibility("default")))
@@ -360,6 +360,16 @@ B200Q_API int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* 
  * 2 finisher, end of the finisher's contributor pairs) and returns the number of segments (-1: bad arguments). */
 B200Q_API int b200q_debug_gemm_schedule(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair,
                               int* out, int max_seg);
+
+/* The same for one step of a decode program (no GPU needed; for tests): a step of n_panels 128-column panels x
+ * row_blocks 16-row blocks is divided evenly over n_ctas CTAs; writes the panel segments of `cta` in processing order
+ * as 6 ints each (panel, first row block, end row block, kind 0 whole panel / 1 writes a partial sum / 2 finishes the
+ * panel, partial-sum slot of the CTA inside the panel, number of contributing CTAs the finisher adds up - 1 otherwise),
+ * *slots_per_panel (may be NULL) = the slots the program builder reserves per panel, and returns the number of segments
+ * (-1: bad arguments).  finisher_first: 1 = the tcgen05 kernel's rule (the owner of the panel's first block finishes it),
+ * 0 = the register-level kernel's (the owner of its last block). */
+B200Q_API int b200q_debug_gemv_schedule(int n_panels, int row_blocks, int n_ctas, int cta, int finisher_first, int* out,
+                              int max_seg, int* slots_per_panel);
 
 /* Dense NT GEMM on an already dequantized weight  T dtype[N, K]  (replaces NT_matmul*,
  * transform/transpose_matmul.py:34-101, dispatch/llama/main.py:3884-3981). f16 only. */

@@ -93,6 +93,7 @@ PROTOTYPES = {
     "b200q_gemm": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_uint, c_void_p]),
     "b200q_gemm_workspace_bytes": (ctypes.c_size_t, []),
     "b200q_debug_gemm_schedule": (c_int, [c_int] * 6 + [c_void_p, c_int]),
+    "b200q_debug_gemv_schedule": (c_int, [c_int] * 5 + [c_void_p, c_int, c_void_p]),
     "b200q_gemm_multi": (c_int, [ctypes.POINTER(GemmOp), c_int, c_void_p, c_int, c_int, c_int, c_uint, c_void_p, ctypes.c_size_t,
                                  c_void_p]),
     "b200q_gemm_ws": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_uint, c_void_p, ctypes.c_size_t, c_void_p]),

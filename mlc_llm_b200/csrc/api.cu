@@ -58,6 +58,7 @@ int gemm_asym_launch(const void* packed, const void* scale, const void* zmin, co
                      void* workspace, size_t workspace_bytes);
 size_t gemm_workspace_bytes();
 int gemm_schedule_debug(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair, int* out, int max_seg);
+int gemv_program_schedule_debug(int n_panels, int RB, int G, int cta, int finisher_first, int* out, int max_seg, int* c_max);
 int gemm_multi_launch(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,
                       cudaStream_t stream, void* workspace, size_t workspace_bytes);
 int encode_launch(const void* W, void* packed, void* scale, int N, int K, int fmt, int transpose,
@@ -382,6 +383,13 @@ size_t b200q_gemm_workspace_bytes(void) { return gemm_workspace_bytes(); }
 int b200q_debug_gemm_schedule(int streamk, int n_tiles, int n_ksteps, int chunk, int n_pairs, int pair, int* out, int max_seg) {
   if (!out || n_tiles < 1 || n_ksteps < 1 || chunk < 1 || n_pairs < 1 || pair < 0 || pair >= n_pairs || max_seg < 0) return -1;
   return gemm_schedule_debug(streamk, n_tiles, n_ksteps, chunk, n_pairs, pair, out, max_seg);
+}
+
+int b200q_debug_gemv_schedule(int n_panels, int row_blocks, int n_ctas, int cta, int finisher_first, int* out, int max_seg,
+                              int* slots_per_panel) {
+  if (!out || n_panels < 1 || row_blocks < 1 || n_ctas < 1 || cta < 0 || cta >= n_ctas || max_seg < 0) return -1;
+  if ((long long)n_panels * row_blocks > 0x3FFFFFFFll) return -1;
+  return gemv_program_schedule_debug(n_panels, row_blocks, n_ctas, cta, finisher_first, out, max_seg, slots_per_panel);
 }
 
 int b200q_gemm_multi(const b200q_gemm_op* ops, int n_ops, const void* X, int M, int K, int fmt, unsigned flags,

@@ -207,8 +207,15 @@ __device__ __forceinline__ int find_op(const ProgStep& st, int panel) {
     if (t < st.n_ops && panel >= st.op[t].panel_begin) oi = t;
   return oi;
 }
-__device__ __forceinline__ int cta_begin(int T, int i, int G) { return (int)((long long)i * T / G); }
-__device__ __forceinline__ int block_owner(int T, int t, int G) { return (int)((((long long)t + 1) * G - 1) / T); }
+// (also evaluated on the host: gemv_program_schedule_debug below, tests/test_gemv_schedule_cpu.py)
+__host__ __device__ __forceinline__ int cta_begin(int T, int i, int G) { return (int)((long long)i * T / G); }
+__host__ __device__ __forceinline__ int block_owner(int T, int t, int G) { return (int)((((long long)t + 1) * G - 1) / T); }
+// partial-sum slots reserved per panel: every CTA holds >= T / G blocks, so the RB blocks of a panel span at most
+// this many CTAs (T < G: one CTA per block, slot = row block)
+inline int partial_slots_per_panel(int T, int RB, int G) {
+  const int per_cta = T / G > 0 ? T / G : 1;
+  return ceil_div(RB, per_cta) + 1;
+}
 
 // A workspace belongs to ONE program: the first launch stamps the program's id into ws_ctrl[3], every later launch
 // checks it (a workspace reused by another program would pick up stale tags silently).
@@ -637,8 +644,7 @@ int build_step(ProgStep& st, const b200q_gemv_step& in, int G, bool use_tc) {
   }
   st.n_panels = panels;
   st.T = panels * st.RB;
-  const int per_cta = st.T / G > 0 ? st.T / G : 1;
-  st.c_max = ceil_div(st.RB, per_cta) + 1;
+  st.c_max = partial_slots_per_panel(st.T, st.RB, G);
   return B200Q_OK;
 }
 
@@ -933,6 +939,34 @@ int gemv_program_run(const void* host_blob, const void* dev_blob, void* workspac
   if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelExC(gemv program)");
   count_launch();
   return B200Q_OK;
+}
+
+// Host-side evaluation of a step's work distribution (b200q_debug_gemv_schedule): the panel segments of one CTA in
+// processing order, with the roles the kernels' epilogue warps derive from cta_begin / block_owner.
+int gemv_program_schedule_debug(int n_panels, int RB, int G, int cta, int finisher_first, int* out, int max_seg, int* c_max) {
+  const int T = n_panels * RB;
+  if (c_max) *c_max = partial_slots_per_panel(T, RB, G);
+  const int t0 = cta_begin(T, cta, G), t1 = cta_begin(T, cta + 1, G);
+  const bool sparse = (T < G);
+  int panel = t0 / RB, rb = t0 - panel * RB, n = 0;
+  for (int t = t0; t < t1;) {
+    const int n_blk = (t1 - t < RB - rb) ? t1 - t : RB - rb;
+    const bool complete = (rb == 0) && (n_blk == RB);
+    const int first = block_owner(T, panel * RB, G), last = block_owner(T, panel * RB + RB - 1, G);
+    // tcgen05 kernel: the owner of the panel's FIRST block finishes it; register-level kernel: the owner of the LAST
+    const bool finisher = complete || (finisher_first ? rb == 0 : rb + n_blk == RB);
+    const int n_contrib = complete ? 1 : (sparse ? RB : last - first + 1);
+    const int slot = complete ? 0 : (sparse ? rb : cta - first);  // the finisher of the tcgen05 kernel keeps its sum (slot 0 unused)
+    if (n < max_seg) {
+      int* o = out + 6 * n;
+      o[0] = panel; o[1] = rb; o[2] = rb + n_blk; o[3] = complete ? 0 : (finisher ? 2 : 1); o[4] = slot; o[5] = finisher ? n_contrib : 1;
+    }
+    ++n;
+    t += n_blk;
+    rb += n_blk;
+    if (rb == RB) { rb = 0; ++panel; }
+  }
+  return n;
 }
 
 }  // namespace b200q

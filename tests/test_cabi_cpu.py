@@ -31,7 +31,7 @@ def test_header_symbols_exported_and_bound():
 
 def test_version_and_layout_helpers_match_oracle():
     L = _lib.lib()
-    assert L.b200q_version() == 108
+    assert L.b200q_version() == 109
     for name, spec in SPECS.items():
         f = qo.ALL_FORMATS[name]
         assert spec.fmt_id == {"q4f16_0": 0, "q3f16_0": 1, "q4f32_0": 2, "q8f16_0": 3, "q4f16_asym": 4, "q4f32_asym": 5,
